@@ -1,0 +1,887 @@
+// libfluid_cuda.so -- the C ABI declared in include/fluid_cuda.h.
+//
+// Host side of the drop-in boundary: a resident context that plays the role of
+// the reference's FluidSystem (FSType::ORIGINAL, one fluid; FluidSystem.cpp:18-128)
+// and the Stam-signature host-pointer entry points layered on top of it.
+// There is no CPU fallback anywhere in this file: every arithmetic step is a
+// kernel launch, and without a CUDA device every entry point fails.
+#include "../../include/fluid_cuda.h"
+
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "grid.cuh"
+#include "kernels_basic.cuh"
+#include "kernels_relax.cuh"
+
+using namespace fluid;
+
+// ---------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------
+static thread_local char t_err[512] = "";
+static thread_local unsigned long long t_launches = 0;
+
+static int fail(int code, const char* fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(t_err, sizeof t_err, fmt, ap);
+	va_end(ap);
+	return code;
+}
+
+#define CU_TRY(expr)                                                                                              \
+	do {                                                                                                      \
+		cudaError_t e__ = (expr);                                                                         \
+		if (e__ != cudaSuccess)                                                                           \
+			return fail(FLUID_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__),      \
+				    __FILE__, __LINE__);                                                          \
+	} while (0)
+
+#define FL_TRY(expr)                                                                                              \
+	do {                                                                                                      \
+		int r__ = (expr);                                                                                 \
+		if (r__ != FLUID_OK) return r__;                                                                  \
+	} while (0)
+
+// every kernel launch goes through this so that gpu_launches is a real count
+#define LAUNCH(kernel, grid, block, smem, stream, ...)                                                            \
+	do {                                                                                                      \
+		kernel<<<grid, block, smem, stream>>>(__VA_ARGS__);                                               \
+		t_launches++;                                                                                     \
+	} while (0)
+
+static inline int cdiv(long long a, long long b) { return (int) ((a + b - 1) / b); }
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+struct fluid_ctx {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	bool timed = false;
+	GridDesc g{};
+	int batch = 1;
+	int gs_iters = 20, gs_order = FLUID_GS_WAVEFRONT, advect_mode = FLUID_ADVECT_MIDPOINT;
+	float visc = 0, diff = 0, vorticity = 0, damp = 0;
+	size_t field_bytes = 0;   // one field, all ensemble members
+	float* f[FLUID_FIELD_COUNT] = {}; // field id -> device array (ids are fixed; steps swap locals)
+	float* vscr[4] = {};      // vorticity scratch, allocated on first use
+	SourceDev* d_src = nullptr;
+	int* d_first = nullptr;
+	int n_src = 0;
+	std::vector<std::vector<SourceDev>> src; // per ensemble member
+	bool src_dirty = false;
+};
+
+static int ctx_bind(fluid_ctx* c)
+{
+	CU_TRY(cudaSetDevice(c->device));
+	return FLUID_OK;
+}
+
+static inline long long n4_of(const fluid_ctx* c) { return c->g.plane * c->batch / 4; }
+
+static inline dim3 rowgroup_grid(const fluid_ctx* c, int rows) { return dim3(cdiv(c->g.pitch / 4, 32), cdiv(rows, 8), c->batch); }
+static inline dim3 cell_grid(const fluid_ctx* c) { return dim3(cdiv(c->g.N, 32), cdiv(c->g.NY, 8), c->batch); }
+static const dim3 kBlk2D(32, 8);
+
+static int flat_blocks(const fluid_ctx* c)
+{
+	long long need = (n4_of(c) + 255) / 256;
+	return (int) std::min<long long>(need, 148LL * 16);
+}
+
+// ---------------------------------------------------------------------------
+// device-level primitives (all asynchronous on c->stream)
+// ---------------------------------------------------------------------------
+static int dev_add_source(fluid_ctx* c, float* x, const float* s, float dt)
+{
+	LAUNCH(k_add_source, flat_blocks(c), 256, 0, c->stream, (float4*) x, (const float4*) s, dt, n4_of(c));
+	return FLUID_OK;
+}
+
+static int dev_add_source2(fluid_ctx* c, float* x, const float* s, float* y, const float* t, float dt)
+{
+	LAUNCH(k_add_source2, flat_blocks(c), 256, 0, c->stream, (float4*) x, (const float4*) s, (float4*) y,
+	       (const float4*) t, dt, n4_of(c));
+	return FLUID_OK;
+}
+
+static int dev_set_bnd(fluid_ctx* c, int b, float* x)
+{
+	const int n = std::max(c->g.N, c->g.NY);
+	LAUNCH(k_set_bnd, dim3(cdiv(n, 256), 1, c->batch), 256, 0, c->stream, c->g, b, x);
+	return FLUID_OK;
+}
+
+static int dev_zero_bnd(fluid_ctx* c, float* x)
+{
+	const int n = std::max(c->g.N, c->g.NY) + 2;
+	LAUNCH(k_zero_bnd, dim3(cdiv(n, 256), 1, c->batch), 256, 0, c->stream, c->g, x);
+	return FLUID_OK;
+}
+
+// LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
+static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
+{
+	const int limit = a > 0 ? c->gs_iters : 1;
+	if (c->gs_order == FLUID_GS_REDBLACK) {
+		for (int k = 0; k < limit; k++) {
+			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 0);
+			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 1);
+		}
+	} else {
+		constexpr int T = 64;
+		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
+		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
+		for (int s = 0; s <= last; s++)
+			LAUNCH(k_gs_wavefront<T>, dim3(ntx, limit, c->batch), T, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx,
+			       nty);
+	}
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+// Blur (FluidSystem.cpp:722-743).  x and x0 are the caller's two buffers; on
+// return the result is in x and the penultimate iterate in x0.
+static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
+{
+	int limit = a > 0 ? c->gs_iters : 1;
+	if (limit % 2 == 0) limit += 1;
+	float *dst = x, *src = x0;
+	FL_TRY(dev_set_bnd(c, b, src));
+	for (int k = 0; k < limit; k++) {
+		if (k > 0) std::swap(dst, src);
+		LAUNCH(k_blur_pass, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, dst, src, a, cc,
+		       k + 1 < limit ? 1 : 0);
+	}
+	FL_TRY(dev_zero_bnd(c, dst));
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+static int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, const float* v, float dt)
+{
+	const float dtN = dt * c->g.N;
+	LAUNCH(k_advect, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode);
+	return FLUID_OK;
+}
+
+static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const float* v0, float dt)
+{
+	const float dtN = dt * c->g.N;
+	LAUNCH(k_advect_velocity, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode);
+	return FLUID_OK;
+}
+
+// Project (FluidSystem.cpp:982-1007).
+static int dev_project(fluid_ctx* c, float* u, float* v, float* p, float* div)
+{
+	LAUNCH(k_divergence, rowgroup_grid(c, c->g.NY + 2), kBlk2D, 0, c->stream, c->g, u, v, div, p);
+	FL_TRY(dev_lin_solve(c, 0, p, div, 1.0f, 4.0f));
+	LAUNCH(k_subtract_gradient, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, u, v, p);
+	return FLUID_OK;
+}
+
+// Diffuse1 (FluidSystem.cpp:810-814): a = dt*diff*N*N left to right in float.
+static inline float diffusion_a(const fluid_ctx* c, float coef, float dt) { return dt * coef * c->g.N * c->g.N; }
+
+// VelStep1 (FluidSystem.cpp:354-376).  The four pointers are locals: the
+// reference's two Swap() calls per FlipFlopArr become local pointer swaps, so
+// the result lands in the arrays passed as u and v.
+static int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt)
+{
+	FL_TRY(dev_add_source2(c, u, u0, v, v0, dt));
+	std::swap(u, u0);
+	const float a = diffusion_a(c, visc, dt);
+	FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
+	std::swap(v, v0);
+	FL_TRY(dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a));
+	FL_TRY(dev_project(c, u, v, u0, v0));
+	std::swap(u, u0);
+	std::swap(v, v0);
+	FL_TRY(dev_advect_velocity(c, u, v, u0, v0, dt));
+	FL_TRY(dev_project(c, u, v, u0, v0));
+	return FLUID_OK;
+}
+
+// DensStep1 (FluidSystem.cpp:289-299), one fluid.
+static int dev_dens_step(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float diff, float dt)
+{
+	FL_TRY(dev_add_source(c, x, x0, dt));
+	std::swap(x, x0);
+	const float a = diffusion_a(c, diff, dt);
+	FL_TRY(dev_blur(c, 0, x, x0, a, 1 + 4 * a));
+	std::swap(x, x0);
+	FL_TRY(dev_advect(c, 0, x, x0, u, v, dt));
+	return FLUID_OK;
+}
+
+static int ensure_vort_scratch(fluid_ctx* c)
+{
+	for (int k = 0; k < 4; k++) {
+		if (!c->vscr[k]) {
+			CU_TRY(cudaMalloc(&c->vscr[k], c->field_bytes));
+			CU_TRY(cudaMemsetAsync(c->vscr[k], 0, c->field_bytes, c->stream));
+		}
+	}
+	return FLUID_OK;
+}
+
+// VortConfinement (FluidSystem.cpp:1124-1175).
+static int dev_vort_confinement(fluid_ctx* c, float* u, float* v, float vorticity)
+{
+	FL_TRY(ensure_vort_scratch(c));
+	LAUNCH(k_vort_curl, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, c->vscr[0], c->vscr[1]);
+	LAUNCH(k_vort_dir, cell_grid(c), kBlk2D, 0, c->stream, c->g, c->vscr[1], c->vscr[2], c->vscr[3]);
+	LAUNCH(k_vort_apply, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, c->vscr[0], c->vscr[2], c->vscr[3], vorticity);
+	return FLUID_OK;
+}
+
+static int dev_damp(fluid_ctx* c, float* vel, float amount, float dt)
+{
+	const float f = powf(1 - amount, dt); // host libm, as the reference (FluidSystem.cpp:1181)
+	LAUNCH(k_scale, flat_blocks(c), 256, 0, c->stream, (float4*) vel, f, n4_of(c));
+	return FLUID_OK;
+}
+
+static int sync_sources(fluid_ctx* c)
+{
+	if (!c->src_dirty) return FLUID_OK;
+	std::vector<SourceDev> flat;
+	std::vector<int> first(c->batch + 1, 0);
+	for (int s = 0; s < c->batch; s++) {
+		first[s] = (int) flat.size();
+		flat.insert(flat.end(), c->src[s].begin(), c->src[s].end());
+	}
+	first[c->batch] = (int) flat.size();
+	if (c->d_src) CU_TRY(cudaFree(c->d_src));
+	c->d_src = nullptr;
+	if (!c->d_first) CU_TRY(cudaMalloc(&c->d_first, sizeof(int) * (c->batch + 1)));
+	if (!flat.empty()) {
+		CU_TRY(cudaMalloc(&c->d_src, sizeof(SourceDev) * flat.size()));
+		CU_TRY(cudaMemcpy(c->d_src, flat.data(), sizeof(SourceDev) * flat.size(), cudaMemcpyHostToDevice));
+	}
+	CU_TRY(cudaMemcpy(c->d_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice));
+	c->n_src = (int) flat.size();
+	c->src_dirty = false;
+	return FLUID_OK;
+}
+
+// FluidSystem::Update (FluidSystem.cpp:101-128) for FSType::ORIGINAL.
+static int dev_update(fluid_ctx* c, float dt)
+{
+	CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));
+	CU_TRY(cudaMemsetAsync(c->f[FLUID_V_PREV], 0, c->field_bytes, c->stream));
+	CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV], 0, c->field_bytes, c->stream));
+	if (c->n_src > 0) {
+		FieldPtrs fp;
+		for (int k = 0; k < 3; k++) {
+			fp.cur[k] = c->f[k];
+			fp.prev[k] = c->f[k + 3];
+		}
+		LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
+	}
+	if (c->vorticity != 0.0f) FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
+	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], c->visc, dt));
+	FL_TRY(dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], c->diff, dt));
+	if (c->damp != 0.0f) {
+		FL_TRY(dev_damp(c, c->f[FLUID_U], c->damp, dt));
+		FL_TRY(dev_damp(c, c->f[FLUID_V], c->damp, dt));
+	}
+	return FLUID_OK;
+}
+
+// ---------------------------------------------------------------------------
+// library-level entry points
+// ---------------------------------------------------------------------------
+extern "C" const char* fluid_last_error(void) { return t_err; }
+
+extern "C" const char* fluid_version(void)
+{
+	return "fluid_cuda 0.1 (sm_100a, -fmad=false -prec-div=true -prec-sqrt=true -ftz=false)";
+}
+
+extern "C" unsigned long long fluid_launch_count(void) { return t_launches; }
+extern "C" void fluid_launch_count_reset(void) { t_launches = 0; }
+
+static thread_local int t_gs_order = FLUID_GS_WAVEFRONT;
+static thread_local int t_gs_iters = 20;
+static thread_local int t_advect_mode = FLUID_ADVECT_MIDPOINT;
+static thread_local int t_scratch_download = 1;
+
+extern "C" int fluid_set_gs_order(int order)
+{
+	if (order != FLUID_GS_WAVEFRONT && order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs order %d", order);
+	t_gs_order = order;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_set_gs_iters(int iters)
+{
+	if (iters < 1) return fail(FLUID_ERR_INVALID, "gs_iters must be >= 1 (got %d)", iters);
+	t_gs_iters = iters;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_set_advect_mode(int mode)
+{
+	if (mode != FLUID_ADVECT_MIDPOINT && mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect mode %d", mode);
+	t_advect_mode = mode;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_set_scratch_download(int on)
+{
+	t_scratch_download = on ? 1 : 0;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_host_alloc(void** p, size_t bytes)
+{
+	if (!p) return fail(FLUID_ERR_INVALID, "null pointer");
+	CU_TRY(cudaHostAlloc(p, bytes, cudaHostAllocDefault));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_host_free(void* p)
+{
+	CU_TRY(cudaFreeHost(p));
+	return FLUID_OK;
+}
+
+extern "C" void fluid_params_default(fluid_params* p)
+{
+	if (!p) return;
+	memset(p, 0, sizeof *p);
+	p->N = 64;
+	p->batch = 1;
+	p->gs_iters = 20;
+	p->gs_order = FLUID_GS_WAVEFRONT;
+	p->advect_mode = FLUID_ADVECT_MIDPOINT;
+	p->device = -1;
+}
+
+extern "C" int fluid_ctx_destroy(fluid_ctx* c)
+{
+	if (!c) return FLUID_OK;
+	cudaSetDevice(c->device);
+	if (c->stream) cudaStreamSynchronize(c->stream);
+	for (auto& p : c->f) if (p) cudaFree(p);
+	for (auto& p : c->vscr) if (p) cudaFree(p);
+	if (c->d_src) cudaFree(c->d_src);
+	if (c->d_first) cudaFree(c->d_first);
+	if (c->ev0) cudaEventDestroy(c->ev0);
+	if (c->ev1) cudaEventDestroy(c->ev1);
+	if (c->stream) cudaStreamDestroy(c->stream);
+	delete c;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
+{
+	if (!p || !out) return fail(FLUID_ERR_INVALID, "null argument");
+	*out = nullptr;
+	if (p->N < 1 || p->N > 32768) return fail(FLUID_ERR_INVALID, "N=%d out of range [1,32768]", p->N);
+	if (p->batch < 1 || p->batch > 65535) return fail(FLUID_ERR_INVALID, "batch=%d out of range [1,65535]", p->batch);
+	if (p->gs_iters < 1) return fail(FLUID_ERR_INVALID, "gs_iters=%d must be >= 1", p->gs_iters);
+	if (p->gs_order != FLUID_GS_WAVEFRONT && p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", p->gs_order);
+	if (p->advect_mode != FLUID_ADVECT_MIDPOINT && p->advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", p->advect_mode);
+	for (int r : p->reserved) if (r != 0) return fail(FLUID_ERR_INVALID, "reserved fields must be 0");
+
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0)
+		return fail(FLUID_ERR_CUDA, "no CUDA device available (%s); this library has no CPU fallback",
+			    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+	int dev = p->device;
+	if (dev < 0) CU_TRY(cudaGetDevice(&dev));
+	if (dev >= ndev) return fail(FLUID_ERR_INVALID, "device %d does not exist (%d devices)", dev, ndev);
+
+	fluid_ctx* c = new (std::nothrow) fluid_ctx();
+	if (!c) return fail(FLUID_ERR_NOMEM, "host allocation failed");
+	c->device = dev;
+	c->batch = p->batch;
+	c->gs_iters = p->gs_iters;
+	c->gs_order = p->gs_order;
+	c->advect_mode = p->advect_mode;
+	c->visc = p->visc;
+	c->diff = p->diff;
+	c->vorticity = p->vorticity;
+	c->damp = p->damp;
+	c->g.N = p->N;
+	c->g.NY = p->N;
+	c->g.pitch = ((XO + p->N + 2 + 31) / 32) * 32;
+	c->g.plane = (long long) c->g.pitch * (c->g.NY + 2);
+	c->field_bytes = (size_t) c->g.plane * c->batch * sizeof(float);
+	c->src.resize(c->batch);
+
+	int rc = FLUID_OK;
+	do {
+		if (cudaSetDevice(dev) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaSetDevice(%d) failed", dev); break; }
+		if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+		if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaEventCreate failed"); break; }
+		for (int k = 0; k < FLUID_FIELD_COUNT && rc == FLUID_OK; k++) {
+			e = cudaMalloc(&c->f[k], c->field_bytes);
+			if (e != cudaSuccess) {
+				rc = fail(FLUID_ERR_NOMEM, "cudaMalloc of %zu bytes failed: %s", c->field_bytes, cudaGetErrorString(e));
+				cudaGetLastError();
+				break;
+			}
+			e = cudaMemsetAsync(c->f[k], 0, c->field_bytes, c->stream);
+			if (e != cudaSuccess) rc = fail(FLUID_ERR_CUDA, "cudaMemset failed: %s", cudaGetErrorString(e));
+		}
+		if (rc != FLUID_OK) break;
+		c->src_dirty = true;
+		rc = sync_sources(c);
+		if (rc != FLUID_OK) break;
+		if (cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "stream sync failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+	} while (0);
+	if (rc != FLUID_OK) {
+		char keep[sizeof t_err];
+		memcpy(keep, t_err, sizeof keep);
+		fluid_ctx_destroy(c);
+		memcpy(t_err, keep, sizeof keep);
+		return rc;
+	}
+	*out = c;
+	return FLUID_OK;
+}
+
+#define CHECK_CTX(c)                                                                                              \
+	do {                                                                                                      \
+		if (!(c)) return fail(FLUID_ERR_INVALID, "null context");                                         \
+		FL_TRY(ctx_bind(c));                                                                              \
+	} while (0)
+
+static int check_field(int f) { return (f >= 0 && f < FLUID_FIELD_COUNT) ? FLUID_OK : fail(FLUID_ERR_INVALID, "field id %d out of range", f); }
+
+static int check_distinct(std::initializer_list<int> ids)
+{
+	std::vector<int> v(ids);
+	for (size_t a = 0; a < v.size(); a++) {
+		FL_TRY(check_field(v[a]));
+		for (size_t b = a + 1; b < v.size(); b++)
+			if (v[a] == v[b]) return fail(FLUID_ERR_INVALID, "field %d passed twice where distinct arrays are required", v[a]);
+	}
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_clear(fluid_ctx* c)
+{
+	CHECK_CTX(c);
+	for (auto& p : c->f) CU_TRY(cudaMemsetAsync(p, 0, c->field_bytes, c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_upload(fluid_ctx* c, int field, int sim, const float* host)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(field));
+	if (!host) return fail(FLUID_ERR_INVALID, "null host pointer");
+	if (sim < 0 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range [0,%d)", sim, c->batch);
+	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
+	CU_TRY(cudaMemcpy2DAsync(c->f[field] + (long long) sim * c->g.plane + XO, (size_t) c->g.pitch * sizeof(float), host, w, w,
+				 c->g.NY + 2, cudaMemcpyHostToDevice, c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_download(fluid_ctx* c, int field, int sim, float* host)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(field));
+	if (!host) return fail(FLUID_ERR_INVALID, "null host pointer");
+	if (sim < 0 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range [0,%d)", sim, c->batch);
+	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
+	CU_TRY(cudaMemcpy2DAsync(host, w, c->f[field] + (long long) sim * c->g.plane + XO, (size_t) c->g.pitch * sizeof(float), w,
+				 c->g.NY + 2, cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_sources(fluid_ctx* c, int sim, int n, const fluid_source* src)
+{
+	CHECK_CTX(c);
+	if (n < 0 || (n > 0 && !src)) return fail(FLUID_ERR_INVALID, "bad source list");
+	if (sim < -1 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range", sim);
+	std::vector<SourceDev> v;
+	for (int k = 0; k < n; k++) {
+		const fluid_source& s = src[k];
+		if (s.field < FLUID_U || s.field > FLUID_DENS) return fail(FLUID_ERR_INVALID, "source %d: field %d is not U, V or DENS", k, s.field);
+		if (s.i < 0 || s.i > c->g.N + 1 || s.j < 0 || s.j > c->g.NY + 1) return fail(FLUID_ERR_INVALID, "source %d: cell (%d,%d) outside the grid", k, s.i, s.j);
+		if (s.mode < FLUID_SRC_PREV_SET || s.mode > FLUID_SRC_CURR_SET) return fail(FLUID_ERR_INVALID, "source %d: unknown mode %d", k, s.mode);
+		v.push_back({ s.field, s.i, s.j, s.mode, s.value });
+	}
+	if (sim < 0) for (auto& e : c->src) e = v;
+	else c->src[sim] = v;
+	c->src_dirty = true;
+	CU_TRY(cudaStreamSynchronize(c->stream)); // the old list may still be in use
+	return sync_sources(c);
+}
+
+extern "C" int fluid_ctx_set_modes(fluid_ctx* c, int gs_order, int gs_iters, int advect_mode)
+{
+	CHECK_CTX(c);
+	if (gs_order != FLUID_GS_WAVEFRONT && gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", gs_order);
+	if (gs_iters < 1) return fail(FLUID_ERR_INVALID, "gs_iters=%d must be >= 1", gs_iters);
+	if (advect_mode != FLUID_ADVECT_MIDPOINT && advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", advect_mode);
+	c->gs_order = gs_order;
+	c->gs_iters = gs_iters;
+	c->advect_mode = advect_mode;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_coeffs(fluid_ctx* c, float visc, float diff, float vorticity, float damp)
+{
+	CHECK_CTX(c);
+	c->visc = visc;
+	c->diff = diff;
+	c->vorticity = vorticity;
+	c->damp = damp;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_vel_step(fluid_ctx* c, float dt)
+{
+	CHECK_CTX(c);
+	return dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], c->visc, dt);
+}
+
+extern "C" int fluid_ctx_dens_step(fluid_ctx* c, float dt)
+{
+	CHECK_CTX(c);
+	return dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], c->diff, dt);
+}
+
+extern "C" int fluid_ctx_step(fluid_ctx* c, float dt, int nsteps)
+{
+	CHECK_CTX(c);
+	if (nsteps < 0) return fail(FLUID_ERR_INVALID, "nsteps=%d must be >= 0", nsteps);
+	CU_TRY(cudaEventRecord(c->ev0, c->stream));
+	for (int s = 0; s < nsteps; s++) FL_TRY(dev_update(c, dt));
+	CU_TRY(cudaEventRecord(c->ev1, c->stream));
+	c->timed = true;
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_sync(fluid_ctx* c)
+{
+	CHECK_CTX(c);
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_last_step_ms(fluid_ctx* c, float* ms)
+{
+	CHECK_CTX(c);
+	if (!ms) return fail(FLUID_ERR_INVALID, "null pointer");
+	if (!c->timed) return fail(FLUID_ERR_INVALID, "no fluid_ctx_step call to time yet");
+	CU_TRY(cudaEventSynchronize(c->ev1));
+	CU_TRY(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_add_source(fluid_ctx* c, int x, int s, float dt)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_distinct({ x, s }));
+	return dev_add_source(c, c->f[x], c->f[s], dt);
+}
+
+extern "C" int fluid_ctx_set_bnd(fluid_ctx* c, int b, int x)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(x));
+	return dev_set_bnd(c, b, c->f[x]);
+}
+
+extern "C" int fluid_ctx_lin_solve(fluid_ctx* c, int b, int x, int x0, float a, float cc)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_distinct({ x, x0 }));
+	return dev_lin_solve(c, b, c->f[x], c->f[x0], a, cc);
+}
+
+extern "C" int fluid_ctx_blur(fluid_ctx* c, int b, int x, int x0, float a, float cc)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_distinct({ x, x0 }));
+	return dev_blur(c, b, c->f[x], c->f[x0], a, cc);
+}
+
+extern "C" int fluid_ctx_advect(fluid_ctx* c, int b, int d, int d0, int u, int v, float dt)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(d0));
+	FL_TRY(check_distinct({ d, u, v }));
+	if (d == d0) return fail(FLUID_ERR_INVALID, "advect: d and d0 must be different arrays");
+	return dev_advect(c, b, c->f[d], c->f[d0], c->f[u], c->f[v], dt);
+}
+
+extern "C" int fluid_ctx_advect_velocity(fluid_ctx* c, int u, int v, int u0, int v0, float dt)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_distinct({ u, v, u0, v0 }));
+	return dev_advect_velocity(c, c->f[u], c->f[v], c->f[u0], c->f[v0], dt);
+}
+
+extern "C" int fluid_ctx_project(fluid_ctx* c, int u, int v, int p, int div)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_distinct({ u, v, p, div }));
+	return dev_project(c, c->f[u], c->f[v], c->f[p], c->f[div]);
+}
+
+extern "C" int fluid_ctx_time_kernel(fluid_ctx* c, int which, int reps, float* ms)
+{
+	CHECK_CTX(c);
+	if (!ms || reps < 1) return fail(FLUID_ERR_INVALID, "bad arguments");
+	const float a = diffusion_a(c, c->visc > 0 ? c->visc : 1e-4f, 0.1f);
+	float *U = c->f[FLUID_U], *V = c->f[FLUID_V], *D = c->f[FLUID_DENS];
+	float *U0 = c->f[FLUID_U_PREV], *V0 = c->f[FLUID_V_PREV], *D0 = c->f[FLUID_DENS_PREV];
+	CU_TRY(cudaEventRecord(c->ev0, c->stream));
+	for (int r = 0; r < reps; r++) {
+		switch (which) {
+		case FLUID_K_LIN_SOLVE: FL_TRY(dev_lin_solve(c, 1, U0, U, a, 1 + 4 * a)); break;
+		case FLUID_K_BLUR: FL_TRY(dev_blur(c, 0, D0, D, a, 1 + 4 * a)); break;
+		case FLUID_K_ADVECT: FL_TRY(dev_advect(c, 0, D0, D, U, V, 0.1f)); break;
+		case FLUID_K_ADVECT_VEL: FL_TRY(dev_advect_velocity(c, U0, V0, U, V, 0.1f)); break;
+		case FLUID_K_PROJECT: FL_TRY(dev_project(c, U, V, U0, V0)); break;
+		case FLUID_K_ADD_SOURCE: FL_TRY(dev_add_source(c, D0, D, 0.1f)); break;
+		default: return fail(FLUID_ERR_INVALID, "unknown kernel id %d", which);
+		}
+	}
+	CU_TRY(cudaEventRecord(c->ev1, c->stream));
+	CU_TRY(cudaEventSynchronize(c->ev1));
+	float t = 0;
+	CU_TRY(cudaEventElapsedTime(&t, c->ev0, c->ev1));
+	*ms = t / reps;
+	return FLUID_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Stam-signature host-pointer entry points.  One cached context per host
+// thread (re-created when N changes); arrays are copied in, the primitive runs
+// on the GPU, and every array the reference writes is copied back.
+// ---------------------------------------------------------------------------
+struct HostCtxCache {
+	fluid_ctx* c = nullptr;
+	~HostCtxCache() { /* process teardown: the CUDA runtime may already be gone, do not touch it */ }
+};
+static thread_local HostCtxCache t_cache;
+
+static int host_ctx(int N, fluid_ctx** out)
+{
+	if (N < 1) return fail(FLUID_ERR_INVALID, "N=%d must be >= 1", N);
+	if (t_cache.c && t_cache.c->g.N != N) {
+		fluid_ctx_destroy(t_cache.c);
+		t_cache.c = nullptr;
+	}
+	if (!t_cache.c) {
+		fluid_params p;
+		fluid_params_default(&p);
+		p.N = N;
+		FL_TRY(fluid_ctx_create(&p, &t_cache.c));
+	}
+	fluid_ctx* c = t_cache.c;
+	FL_TRY(ctx_bind(c));
+	c->gs_order = t_gs_order;
+	c->gs_iters = t_gs_iters;
+	c->advect_mode = t_advect_mode;
+	*out = c;
+	return FLUID_OK;
+}
+
+static int up(fluid_ctx* c, int field, const float* h) { return fluid_ctx_upload(c, field, 0, h); }
+
+static int down_async(fluid_ctx* c, int field, float* h)
+{
+	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
+	CU_TRY(cudaMemcpy2DAsync(h, w, c->f[field] + XO, (size_t) c->g.pitch * sizeof(float), w, c->g.NY + 2,
+				 cudaMemcpyDeviceToHost, c->stream));
+	return FLUID_OK;
+}
+
+static int finish(fluid_ctx* c)
+{
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+#define NEED(p)                                                                                                   \
+	do {                                                                                                      \
+		if (!(p)) return fail(FLUID_ERR_INVALID, "null array argument '%s'", #p);                         \
+	} while (0)
+
+extern "C" int fluid_add_source(int N, float* x, const float* s, float dt)
+{
+	NEED(x); NEED(s);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, x));
+	FL_TRY(up(c, 1, s));
+	FL_TRY(dev_add_source(c, c->f[0], c->f[1], dt));
+	FL_TRY(down_async(c, 0, x));
+	return finish(c);
+}
+
+extern "C" int fluid_set_bnd(int N, int b, float* x)
+{
+	NEED(x);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, x));
+	FL_TRY(dev_set_bnd(c, b, c->f[0]));
+	FL_TRY(down_async(c, 0, x));
+	return finish(c);
+}
+
+extern "C" int fluid_lin_solve(int N, int b, float* x, const float* x0, float a, float cc)
+{
+	NEED(x); NEED(x0);
+	if (x == x0) return fail(FLUID_ERR_INVALID, "lin_solve: x and x0 must not alias");
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, x));
+	FL_TRY(up(c, 1, x0));
+	FL_TRY(dev_lin_solve(c, b, c->f[0], c->f[1], a, cc));
+	FL_TRY(down_async(c, 0, x));
+	return finish(c);
+}
+
+extern "C" int fluid_diffuse(int N, int b, float* x, const float* x0, float diff, float dt)
+{
+	NEED(x); NEED(x0);
+	if (x == x0) return fail(FLUID_ERR_INVALID, "diffuse: x and x0 must not alias");
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, x));
+	FL_TRY(up(c, 1, x0));
+	const float a = diffusion_a(c, diff, dt);
+	FL_TRY(dev_lin_solve(c, b, c->f[0], c->f[1], a, 1 + 4 * a));
+	FL_TRY(down_async(c, 0, x));
+	return finish(c);
+}
+
+extern "C" int fluid_diffuse_blur(int N, int b, float* x, float* x0, float diff, float dt)
+{
+	NEED(x); NEED(x0);
+	if (x == x0) return fail(FLUID_ERR_INVALID, "diffuse_blur: x and x0 must not alias");
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, x));
+	FL_TRY(up(c, 1, x0));
+	const float a = diffusion_a(c, diff, dt);
+	FL_TRY(dev_blur(c, b, c->f[0], c->f[1], a, 1 + 4 * a));
+	FL_TRY(down_async(c, 0, x));
+	if (t_scratch_download) FL_TRY(down_async(c, 1, x0));
+	return finish(c);
+}
+
+extern "C" int fluid_advect(int N, int b, float* d, const float* d0, const float* u, const float* v, float dt)
+{
+	NEED(d); NEED(d0); NEED(u); NEED(v);
+	if (d == d0 || d == u || d == v) return fail(FLUID_ERR_INVALID, "advect: the output d must not alias an input");
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	// d0 may alias u or v (VelStep1 does exactly that, FluidSystem.cpp:372-373)
+	FL_TRY(up(c, 0, d));
+	FL_TRY(up(c, 2, u));
+	FL_TRY(up(c, 3, v));
+	int f0 = 1;
+	if (d0 == u) f0 = 2;
+	else if (d0 == v) f0 = 3;
+	else FL_TRY(up(c, 1, d0));
+	FL_TRY(dev_advect(c, b, c->f[0], c->f[f0], c->f[2], c->f[3], dt));
+	FL_TRY(down_async(c, 0, d));
+	return finish(c);
+}
+
+extern "C" int fluid_project(int N, float* u, float* v, float* p, float* div)
+{
+	NEED(u); NEED(v); NEED(p); NEED(div);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, u));
+	FL_TRY(up(c, 1, v));
+	FL_TRY(up(c, 3, div)); // div's border cells survive the call (FluidSystem.cpp:986-990 write the interior only)
+	FL_TRY(dev_project(c, c->f[0], c->f[1], c->f[2], c->f[3]));
+	FL_TRY(down_async(c, 0, u));
+	FL_TRY(down_async(c, 1, v));
+	if (t_scratch_download) {
+		FL_TRY(down_async(c, 2, p));
+		FL_TRY(down_async(c, 3, div));
+	}
+	return finish(c);
+}
+
+extern "C" int fluid_vel_step(int N, float* u, float* v, float* u0, float* v0, float visc, float dt)
+{
+	NEED(u); NEED(v); NEED(u0); NEED(v0);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, FLUID_U, u));
+	FL_TRY(up(c, FLUID_V, v));
+	FL_TRY(up(c, FLUID_U_PREV, u0));
+	FL_TRY(up(c, FLUID_V_PREV, v0));
+	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc, dt));
+	FL_TRY(down_async(c, FLUID_U, u));
+	FL_TRY(down_async(c, FLUID_V, v));
+	if (t_scratch_download) {
+		FL_TRY(down_async(c, FLUID_U_PREV, u0));
+		FL_TRY(down_async(c, FLUID_V_PREV, v0));
+	}
+	return finish(c);
+}
+
+extern "C" int fluid_dens_step(int N, float* x, float* x0, const float* u, const float* v, float diff, float dt)
+{
+	NEED(x); NEED(x0); NEED(u); NEED(v);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, FLUID_DENS, x));
+	FL_TRY(up(c, FLUID_DENS_PREV, x0));
+	FL_TRY(up(c, FLUID_U, u));
+	FL_TRY(up(c, FLUID_V, v));
+	FL_TRY(dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], diff, dt));
+	FL_TRY(down_async(c, FLUID_DENS, x));
+	if (t_scratch_download) FL_TRY(down_async(c, FLUID_DENS_PREV, x0));
+	return finish(c);
+}
+
+extern "C" int fluid_vort_confinement(int N, float* u, float* v, float vorticity)
+{
+	NEED(u); NEED(v);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, u));
+	FL_TRY(up(c, 1, v));
+	FL_TRY(dev_vort_confinement(c, c->f[0], c->f[1], vorticity));
+	FL_TRY(down_async(c, 0, u));
+	FL_TRY(down_async(c, 1, v));
+	return finish(c);
+}
+
+extern "C" int fluid_damp(int N, float* vel, float amount, float dt)
+{
+	NEED(vel);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(up(c, 0, vel));
+	FL_TRY(dev_damp(c, c->f[0], amount, dt));
+	FL_TRY(down_async(c, 0, vel));
+	return finish(c);
+}

@@ -1,0 +1,412 @@
+// Streaming / gather kernels of the Stable-Fluids step: add_source, set_bnd,
+// divergence, gradient subtraction, advect, forcing, vorticity, damp.
+// blockIdx.z always selects the ensemble member.
+#pragma once
+#include "grid.cuh"
+
+namespace fluid {
+
+// ---------------------------------------------------------------------------
+// AddArrDt (FluidSystem.cpp:449-453): x += dt*s on every stored float (border
+// included; pad columns are don't-care).  12 B per cell, pure streaming.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_add_source(float4* __restrict__ x, const float4* __restrict__ s, float dt,
+						     long long n4)
+{
+	long long k = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+	const long long stride = (long long) gridDim.x * blockDim.x;
+	for (; k < n4; k += stride) {
+		float4 a = x[k];
+		const float4 b = __ldg(&s[k]);
+		a.x += dt * b.x;
+		a.y += dt * b.y;
+		a.z += dt * b.z;
+		a.w += dt * b.w;
+		x[k] = a;
+	}
+}
+
+// Two fields in one launch (VelStep1's two AddArrDt calls, FluidSystem.cpp:356-357).
+__global__ void __launch_bounds__(256) k_add_source2(float4* __restrict__ x, const float4* __restrict__ s,
+						      float4* __restrict__ y, const float4* __restrict__ t, float dt,
+						      long long n4)
+{
+	long long k = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+	const long long stride = (long long) gridDim.x * blockDim.x;
+	for (; k < n4; k += stride) {
+		float4 a = x[k];
+		const float4 b = __ldg(&s[k]);
+		float4 c = y[k];
+		const float4 d = __ldg(&t[k]);
+		a.x += dt * b.x; a.y += dt * b.y; a.z += dt * b.z; a.w += dt * b.w;
+		c.x += dt * d.x; c.y += dt * d.y; c.z += dt * d.z; c.w += dt * d.w;
+		x[k] = a;
+		y[k] = c;
+	}
+}
+
+// vel *= factor on every stored float (Damp, FluidSystem.cpp:1177-1183; the
+// powf factor is loop invariant and comes from the host's libm).
+__global__ void __launch_bounds__(256) k_scale(float4* __restrict__ x, float f, long long n4)
+{
+	long long k = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+	const long long stride = (long long) gridDim.x * blockDim.x;
+	for (; k < n4; k += stride) {
+		float4 a = x[k];
+		a.x *= f; a.y *= f; a.z *= f; a.w *= f;
+		x[k] = a;
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Stand-alone SetBorder / ZeroBorder (FluidSystem.cpp:465-500, 455-463).  The
+// fast paths fuse this into the producing kernel (mirror_border); it remains
+// for the ABI (fluid_set_bnd) and for the first Blur pass.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_set_bnd(GridDesc g, int b, float* __restrict__ xb)
+{
+	float* x = xb + (long long) blockIdx.z * g.plane;
+	const int k = blockIdx.x * blockDim.x + threadIdx.x + 1;
+	const bool sides = (b >= 0 && b <= 2);
+	if (sides) {
+		if (k <= g.NY) {
+			const float l = x[cell(g, 1, k)], r = x[cell(g, g.N, k)];
+			x[cell(g, 0, k)] = (b == 1) ? -l : l;
+			x[cell(g, g.N + 1, k)] = (b == 1) ? -r : r;
+		}
+		if (k <= g.N) {
+			const float lo = x[cell(g, k, 1)], hi = x[cell(g, k, g.NY)];
+			x[cell(g, k, 0)] = (b == 2) ? -lo : lo;
+			x[cell(g, k, g.NY + 1)] = (b == 2) ? -hi : hi;
+		}
+	}
+	if (k == 1) {
+		// corners from the values the side pass writes (recomputed here from
+		// their interior sources so no inter-thread ordering is needed)
+		const int N = g.N, M = g.NY;
+		float b10, b01, b1M1, b0M, bN0, bN11, bNM1, bN1M;
+		if (sides) {
+			const float c11 = x[cell(g, 1, 1)], c1M = x[cell(g, 1, M)], cN1 = x[cell(g, N, 1)], cNM = x[cell(g, N, M)];
+			b10 = (b == 2) ? -c11 : c11;   b01 = (b == 1) ? -c11 : c11;
+			b1M1 = (b == 2) ? -c1M : c1M;  b0M = (b == 1) ? -c1M : c1M;
+			bN0 = (b == 2) ? -cN1 : cN1;   bN11 = (b == 1) ? -cN1 : cN1;
+			bNM1 = (b == 2) ? -cNM : cNM;  bN1M = (b == 1) ? -cNM : cNM;
+		} else {
+			b10 = x[cell(g, 1, 0)];      b01 = x[cell(g, 0, 1)];
+			b1M1 = x[cell(g, 1, M + 1)]; b0M = x[cell(g, 0, M)];
+			bN0 = x[cell(g, N, 0)];      bN11 = x[cell(g, N + 1, 1)];
+			bNM1 = x[cell(g, N, M + 1)]; bN1M = x[cell(g, N + 1, M)];
+		}
+		x[cell(g, 0, 0)] = 0.5f * (b10 + b01);
+		x[cell(g, 0, M + 1)] = 0.5f * (b1M1 + b0M);
+		x[cell(g, N + 1, 0)] = 0.5f * (bN0 + bN11);
+		x[cell(g, N + 1, M + 1)] = 0.5f * (bNM1 + bN1M);
+	}
+}
+
+__global__ void __launch_bounds__(256) k_zero_bnd(GridDesc g, float* __restrict__ xb)
+{
+	float* x = xb + (long long) blockIdx.z * g.plane;
+	const int k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k <= g.N + 1) {
+		x[cell(g, k, 0)] = 0.0f;
+		x[cell(g, k, g.NY + 1)] = 0.0f;
+	}
+	if (k <= g.NY + 1) {
+		x[cell(g, 0, k)] = 0.0f;
+		x[cell(g, g.N + 1, k)] = 0.0f;
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Project part 1 (FluidSystem.cpp:986-994): div = -0.5f*(uE-uW+vN-vS)/N on the
+// interior (div's border is left untouched, as in the reference) fused with
+// the whole-array p = 0.  One thread = one float4 group of one row.
+// Algorithmic bytes: u,v read, div,p written = 16 B per cell.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_divergence(GridDesc g, const float* __restrict__ ub,
+						     const float* __restrict__ vb, float* __restrict__ divb,
+						     float* __restrict__ pb)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const float* u = ub + off;
+	const float* v = vb + off;
+	float* dv = divb + off;
+	float* p = pb + off;
+	const int q = blockIdx.x * blockDim.x + threadIdx.x; // float4 group in the row
+	const int j = blockIdx.y * blockDim.y + threadIdx.y; // row 0..NY+1
+	if (q * 4 >= g.pitch || j > g.NY + 1) return;
+	const long long base = (long long) j * g.pitch + q * 4;
+	*reinterpret_cast<float4*>(p + base) = make_float4(0.f, 0.f, 0.f, 0.f);
+	const int i0 = q * 4 - XO; // interior index of lane 0
+	if (j < 1 || j > g.NY || i0 + 3 < 1 || i0 > g.N) return;
+	const float4 vn = __ldg(reinterpret_cast<const float4*>(v + base + g.pitch));
+	const float4 vs = __ldg(reinterpret_cast<const float4*>(v + base - g.pitch));
+	const float4 uc = __ldg(reinterpret_cast<const float4*>(u + base));
+	const float uw = __ldg(u + base - 1), ue = __ldg(u + base + 4);
+	const float fN = (float) g.N;
+	float4 r;
+	r.x = -0.5f * (uc.y - uw + vn.x - vs.x) / fN;
+	r.y = -0.5f * (uc.z - uc.x + vn.y - vs.y) / fN;
+	r.z = -0.5f * (uc.w - uc.y + vn.z - vs.z) / fN;
+	r.w = -0.5f * (ue - uc.z + vn.w - vs.w) / fN;
+	if (i0 >= 1 && i0 + 3 <= g.N) {
+		*reinterpret_cast<float4*>(dv + base) = r;
+	} else {
+		if (i0 >= 1 && i0 <= g.N) dv[base] = r.x;
+		if (i0 + 1 >= 1 && i0 + 1 <= g.N) dv[base + 1] = r.y;
+		if (i0 + 2 >= 1 && i0 + 2 <= g.N) dv[base + 2] = r.z;
+		if (i0 + 3 >= 1 && i0 + 3 <= g.N) dv[base + 3] = r.w;
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Project part 3 (FluidSystem.cpp:998-1006): u -= 0.5f*N*(pE-pW),
+// v -= 0.5f*N*(pN-pS), with SetBorder(1,u) and SetBorder(2,v) fused.
+// Algorithmic bytes: p read, u,v read+write = 20 B per cell.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_subtract_gradient(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
+							    const float* __restrict__ pb)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	float* u = ub + off;
+	float* v = vb + off;
+	const float* p = pb + off;
+	const int q = blockIdx.x * blockDim.x + threadIdx.x;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1; // row 1..NY
+	const int i0 = q * 4 - XO;
+	if (q * 4 >= g.pitch || j > g.NY || i0 + 3 < 1 || i0 > g.N) return;
+	const long long base = (long long) j * g.pitch + q * 4;
+	const float4 pc = __ldg(reinterpret_cast<const float4*>(p + base));
+	const float4 pn = __ldg(reinterpret_cast<const float4*>(p + base + g.pitch));
+	const float4 ps = __ldg(reinterpret_cast<const float4*>(p + base - g.pitch));
+	const float pw = __ldg(p + base - 1), pe = __ldg(p + base + 4);
+	float4 uc = *reinterpret_cast<const float4*>(u + base);
+	float4 vc = *reinterpret_cast<const float4*>(v + base);
+	const float h = 0.5f * (float) g.N;
+	uc.x -= h * (pc.y - pw);   vc.x -= h * (pn.x - ps.x);
+	uc.y -= h * (pc.z - pc.x); vc.y -= h * (pn.y - ps.y);
+	uc.z -= h * (pc.w - pc.y); vc.z -= h * (pn.z - ps.z);
+	uc.w -= h * (pe - pc.z);   vc.w -= h * (pn.w - ps.w);
+	const float un[4] = { uc.x, uc.y, uc.z, uc.w }, vn[4] = { vc.x, vc.y, vc.z, vc.w };
+	const bool full = (i0 >= 1 && i0 + 3 <= g.N);
+	if (full) {
+		*reinterpret_cast<float4*>(u + base) = uc;
+		*reinterpret_cast<float4*>(v + base) = vc;
+	}
+#pragma unroll
+	for (int l = 0; l < 4; l++) {
+		const int i = i0 + l;
+		if (i < 1 || i > g.N) continue;
+		if (!full) {
+			u[base + l] = un[l];
+			v[base + l] = vn[l];
+		}
+		mirror_border(g, u, 1, i, j, un[l]);
+		mirror_border(g, v, 2, i, j, vn[l]);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// BilinearCoeffs::calc + Eval (FluidCode.h:91-112), generalised to NY rows.
+// ---------------------------------------------------------------------------
+struct Bilin {
+	long long o00; // offset of (i0,j0); (i1,j0)=+1, (i0,j1)=+pitch
+	float s0, s1, t0, t1;
+};
+
+__device__ __forceinline__ Bilin bilin_calc(const GridDesc& g, float px, float py)
+{
+	Bilin r;
+	if (px < 0.5f) px = 0.5f;
+	if (px > g.N + 0.5f) px = g.N + 0.5f;
+	int i0 = (int) px;
+	if (py < 0.5f) py = 0.5f;
+	if (py > g.NY + 0.5f) py = g.NY + 0.5f;
+	int j0 = (int) py;
+	// a NaN coordinate makes the reference index out of bounds (undefined); keep the access in range
+	i0 = min(max(i0, 0), g.N);
+	j0 = min(max(j0, 0), g.NY);
+	r.s1 = px - i0;
+	r.s0 = 1 - r.s1;
+	r.t1 = py - j0;
+	r.t0 = 1 - r.t1;
+	r.o00 = cell(g, i0, j0);
+	return r;
+}
+
+__device__ __forceinline__ float bilin_eval(const Bilin& c, const float* __restrict__ f, int pitch)
+{
+	const float d00 = __ldg(f + c.o00), d10 = __ldg(f + c.o00 + 1);
+	const float d01 = __ldg(f + c.o00 + pitch), d11 = __ldg(f + c.o00 + pitch + 1);
+	return c.s0 * (c.t0 * d00 + c.t1 * d01) + c.s1 * (c.t0 * d10 + c.t1 * d11);
+}
+
+// Backtraced sample position of cell (i,j): MidpointBackward (FluidSystem.h:185-206)
+// or EulerBack (FluidSystem.h:208-219).
+__device__ __forceinline__ void backtrace(const GridDesc& g, const float* __restrict__ u, const float* __restrict__ v,
+					  int i, int j, float dtN, int mode, float& px, float& py)
+{
+	const long long id = cell(g, i, j);
+	const float uc = __ldg(u + id), vc = __ldg(v + id);
+	if (mode == 1) {
+		px = i - dtN * uc;
+		py = j - dtN * vc;
+	} else {
+		const float dirx = -dtN * uc;
+		const float diry = -dtN * vc;
+		const float mx = i + 0.5f * dirx;
+		const float my = j + 0.5f * diry;
+		const Bilin m = bilin_calc(g, mx, my);
+		const float vx = bilin_eval(m, u, g.pitch);
+		const float vy = bilin_eval(m, v, g.pitch);
+		px = i - dtN * vx;
+		py = j - dtN * vy;
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Advect1 (FluidSystem.cpp:850-862) for one scalar field, SetBorder fused.
+// Gather kernel: u,v,d0 read, d written = 16 B per cell algorithmic.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __restrict__ db, const float* __restrict__ d0b,
+						 const float* __restrict__ ub, const float* __restrict__ vb, float dtN,
+						 int mode)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+	if (i > g.N || j > g.NY) return;
+	float px, py;
+	backtrace(g, ub + off, vb + off, i, j, dtN, mode, px, py);
+	const Bilin c = bilin_calc(g, px, py);
+	const float val = bilin_eval(c, d0b + off, g.pitch);
+	float* d = db + off;
+	d[cell(g, i, j)] = val;
+	mirror_border(g, d, b, i, j, val);
+}
+
+// VelStep1's self-advection (FluidSystem.cpp:372-373): Advect1(1,u,u0,u0,v0) and
+// Advect1(2,v,v0,u0,v0) share the backtrace, so both components are produced
+// by one pass over (u0,v0): 16 B per cell instead of 2 x 12 B.
+__global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
+							  const float* __restrict__ u0b, const float* __restrict__ v0b,
+							  float dtN, int mode)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+	if (i > g.N || j > g.NY) return;
+	const float* u0 = u0b + off;
+	const float* v0 = v0b + off;
+	float px, py;
+	backtrace(g, u0, v0, i, j, dtN, mode, px, py);
+	const Bilin c = bilin_calc(g, px, py);
+	const float un = bilin_eval(c, u0, g.pitch);
+	const float vn = bilin_eval(c, v0, g.pitch);
+	float* u = ub + off;
+	float* v = vb + off;
+	const long long id = cell(g, i, j);
+	u[id] = un;
+	v[id] = vn;
+	mirror_border(g, u, 1, i, j, un);
+	mirror_border(g, v, 2, i, j, vn);
+}
+
+// ---------------------------------------------------------------------------
+// Forcing: what the reference's updaters do between Update's zero fill and
+// VelStep (FluidSystem.cpp:104-118, FluidUpdaters.cpp:45-67).  Entries of one
+// ensemble member are applied in list order by one thread (as the CPU loop
+// does), members in parallel.
+// ---------------------------------------------------------------------------
+struct SourceDev {
+	int field, i, j, mode;
+	float value;
+};
+
+struct FieldPtrs {
+	float* cur[3];
+	float* prev[3];
+};
+
+__global__ void k_apply_sources(GridDesc g, FieldPtrs f, const SourceDev* __restrict__ src,
+				const int* __restrict__ first, int batch)
+{
+	const int sim = blockIdx.x * blockDim.x + threadIdx.x;
+	if (sim >= batch) return;
+	const long long off = (long long) sim * g.plane;
+	for (int k = first[sim]; k < first[sim + 1]; k++) {
+		const SourceDev e = src[k];
+		const long long id = off + cell(g, e.i, e.j);
+		if (e.mode == 0) f.prev[e.field][id] = e.value;
+		else if (e.mode == 1) f.cur[e.field][id] += e.value;
+		else f.cur[e.field][id] = e.value;
+	}
+}
+
+// ---------------------------------------------------------------------------
+// VortConfinement (FluidSystem.cpp:1124-1175) in three order-independent
+// phases; SetBorder(0) of the intermediate fields fused via mirror_border.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_vort_curl(GridDesc g, const float* __restrict__ ub, const float* __restrict__ vb,
+						    float* __restrict__ wb, float* __restrict__ awb)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+	if (i > g.N || j > g.NY) return;
+	const float* u = ub + off;
+	const float* v = vb + off;
+	const long long id = cell(g, i, j);
+	const float w = 0.5f * (__ldg(v + id + 1) - __ldg(v + id - 1) - __ldg(u + id + g.pitch) + __ldg(u + id - g.pitch));
+	const float aw = (w >= 0.0f) ? w : -w;
+	(wb + off)[id] = w;
+	(awb + off)[id] = aw;
+	mirror_border(g, wb + off, 0, i, j, w);
+	mirror_border(g, awb + off, 0, i, j, aw);
+}
+
+__global__ void __launch_bounds__(256) k_vort_dir(GridDesc g, const float* __restrict__ awb, float* __restrict__ fxb,
+						   float* __restrict__ fyb)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+	if (i > g.N || j > g.NY) return;
+	const float* aw = awb + off;
+	const long long id = cell(g, i, j);
+	const float gx = 0.5f * (__ldg(aw + id + 1) - __ldg(aw + id - 1));
+	const float gy = 0.5f * (__ldg(aw + id + g.pitch) - __ldg(aw + id - g.pitch));
+	const float len = sqrtf(gx * gx + gy * gy);
+	float fx = 0.0f, fy = 0.0f;
+	if (!(len < 0.01f)) {
+		fx = gx / len;
+		fy = gy / len;
+	}
+	(fxb + off)[id] = fx;
+	(fyb + off)[id] = fy;
+	mirror_border(g, fxb + off, 0, i, j, fx);
+	mirror_border(g, fyb + off, 0, i, j, fy);
+}
+
+__global__ void __launch_bounds__(256) k_vort_apply(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
+						     const float* __restrict__ wb, const float* __restrict__ fxb,
+						     const float* __restrict__ fyb, float vorticity)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+	if (i > g.N || j > g.NY) return;
+	const long long id = cell(g, i, j);
+	const float w = __ldg(wb + off + id);
+	float* u = ub + off;
+	float* v = vb + off;
+	const float un = u[id] + vorticity * (__ldg(fyb + off + id) * w);
+	const float vn = v[id] + vorticity * (-__ldg(fxb + off + id) * w);
+	u[id] = un;
+	v[id] = vn;
+	mirror_border(g, u, 0, i, j, un);
+	mirror_border(g, v, 0, i, j, vn);
+}
+
+} // namespace fluid

@@ -1,0 +1,234 @@
+"""ctypes view of libfluid_cuda.so (include/fluid_cuda.h) for the tests and bench.py.
+
+The product is the C-ABI shared library; host applications are C (see
+host/fluid_host_demo.c and INTEGRATION.md).  This module adds no arithmetic and
+no fallback: if the library is missing, or there is no CUDA device, calls fail
+loudly (``FluidError``).
+
+``FluidSystem`` mirrors the names of the reference class it stands in for
+(FluidSystem.h:20-69: Setup / Update / GetVelX / GetVelY / GetDensities / Clear)
+so that parity tests read like reference code.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfluid_cuda.so")
+
+GS_WAVEFRONT, GS_REDBLACK = 0, 1
+ADVECT_MIDPOINT, ADVECT_EULER = 0, 1
+U, V, DENS, U_PREV, V_PREV, DENS_PREV = range(6)
+SRC_PREV_SET, SRC_CURR_ADD, SRC_CURR_SET = 0, 1, 2
+K_LIN_SOLVE, K_BLUR, K_ADVECT, K_ADVECT_VEL, K_PROJECT, K_ADD_SOURCE = range(6)
+
+# every symbol include/fluid_cuda.h declares (tests check the .so exports them all)
+EXPORTS = [
+    "fluid_last_error", "fluid_version", "fluid_launch_count", "fluid_launch_count_reset",
+    "fluid_set_gs_order", "fluid_set_gs_iters", "fluid_set_advect_mode", "fluid_set_scratch_download",
+    "fluid_host_alloc", "fluid_host_free",
+    "fluid_add_source", "fluid_set_bnd", "fluid_lin_solve", "fluid_diffuse", "fluid_diffuse_blur", "fluid_advect",
+    "fluid_project", "fluid_vel_step", "fluid_dens_step", "fluid_vort_confinement", "fluid_damp",
+    "fluid_params_default", "fluid_ctx_create", "fluid_ctx_destroy", "fluid_ctx_clear", "fluid_ctx_upload",
+    "fluid_ctx_download", "fluid_ctx_set_sources", "fluid_ctx_vel_step", "fluid_ctx_dens_step", "fluid_ctx_step",
+    "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
+    "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
+    "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
+]
+
+
+class FluidError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("fluid_cuda error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Params(ctypes.Structure):
+    _fields_ = [("N", ctypes.c_int), ("batch", ctypes.c_int), ("gs_iters", ctypes.c_int), ("gs_order", ctypes.c_int),
+                ("advect_mode", ctypes.c_int), ("device", ctypes.c_int), ("visc", ctypes.c_float),
+                ("diff", ctypes.c_float), ("vorticity", ctypes.c_float), ("damp", ctypes.c_float),
+                ("reserved", ctypes.c_int * 6)]
+
+
+class Source(ctypes.Structure):
+    _fields_ = [("field", ctypes.c_int), ("i", ctypes.c_int), ("j", ctypes.c_int), ("mode", ctypes.c_int),
+                ("value", ctypes.c_float)]
+
+
+_f32 = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+_ci, _cf, _vp = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+
+_lib = None
+
+
+def lib():
+    """Load libfluid_cuda.so once; raise if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FluidError(-1, "%s not built (run `python -c 'import __graft_entry__ as g; g.build()'` or "
+                             "`make -C fluid-simulation_b200`)" % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    L.fluid_last_error.restype = ctypes.c_char_p
+    L.fluid_version.restype = ctypes.c_char_p
+    L.fluid_launch_count.restype = ctypes.c_ulonglong
+    L.fluid_launch_count_reset.restype = None
+    L.fluid_host_alloc.argtypes = [ctypes.POINTER(_vp), ctypes.c_size_t]
+    L.fluid_host_free.argtypes = [_vp]
+    L.fluid_add_source.argtypes = [_ci, _f32, _f32, _cf]
+    L.fluid_set_bnd.argtypes = [_ci, _ci, _f32]
+    L.fluid_lin_solve.argtypes = [_ci, _ci, _f32, _f32, _cf, _cf]
+    L.fluid_diffuse.argtypes = [_ci, _ci, _f32, _f32, _cf, _cf]
+    L.fluid_diffuse_blur.argtypes = [_ci, _ci, _f32, _f32, _cf, _cf]
+    L.fluid_advect.argtypes = [_ci, _ci, _f32, _f32, _f32, _f32, _cf]
+    L.fluid_project.argtypes = [_ci, _f32, _f32, _f32, _f32]
+    L.fluid_vel_step.argtypes = [_ci, _f32, _f32, _f32, _f32, _cf, _cf]
+    L.fluid_dens_step.argtypes = [_ci, _f32, _f32, _f32, _f32, _cf, _cf]
+    L.fluid_vort_confinement.argtypes = [_ci, _f32, _f32, _cf]
+    L.fluid_damp.argtypes = [_ci, _f32, _cf, _cf]
+    L.fluid_params_default.argtypes = [ctypes.POINTER(Params)]
+    L.fluid_params_default.restype = None
+    L.fluid_ctx_create.argtypes = [ctypes.POINTER(Params), ctypes.POINTER(_vp)]
+    L.fluid_ctx_destroy.argtypes = [_vp]
+    L.fluid_ctx_clear.argtypes = [_vp]
+    L.fluid_ctx_upload.argtypes = [_vp, _ci, _ci, _f32]
+    L.fluid_ctx_download.argtypes = [_vp, _ci, _ci, _f32]
+    L.fluid_ctx_set_sources.argtypes = [_vp, _ci, _ci, _vp]
+    L.fluid_ctx_vel_step.argtypes = [_vp, _cf]
+    L.fluid_ctx_dens_step.argtypes = [_vp, _cf]
+    L.fluid_ctx_step.argtypes = [_vp, _cf, _ci]
+    L.fluid_ctx_sync.argtypes = [_vp]
+    L.fluid_ctx_last_step_ms.argtypes = [_vp, ctypes.POINTER(_cf)]
+    L.fluid_ctx_set_modes.argtypes = [_vp, _ci, _ci, _ci]
+    L.fluid_ctx_set_coeffs.argtypes = [_vp, _cf, _cf, _cf, _cf]
+    L.fluid_ctx_add_source.argtypes = [_vp, _ci, _ci, _cf]
+    L.fluid_ctx_set_bnd.argtypes = [_vp, _ci, _ci]
+    L.fluid_ctx_lin_solve.argtypes = [_vp, _ci, _ci, _ci, _cf, _cf]
+    L.fluid_ctx_blur.argtypes = [_vp, _ci, _ci, _ci, _cf, _cf]
+    L.fluid_ctx_advect.argtypes = [_vp, _ci, _ci, _ci, _ci, _ci, _cf]
+    L.fluid_ctx_advect_velocity.argtypes = [_vp, _ci, _ci, _ci, _ci, _cf]
+    L.fluid_ctx_project.argtypes = [_vp, _ci, _ci, _ci, _ci]
+    L.fluid_ctx_time_kernel.argtypes = [_vp, _ci, _ci, ctypes.POINTER(_cf)]
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise FluidError(rc, lib().fluid_last_error().decode())
+
+
+def set_modes(gs_order=GS_WAVEFRONT, gs_iters=20, advect_mode=ADVECT_MIDPOINT, scratch_download=True):
+    """Modes of the Stam-signature host-pointer calls (thread-local in the library)."""
+    L = lib()
+    check(L.fluid_set_gs_order(gs_order))
+    check(L.fluid_set_gs_iters(gs_iters))
+    check(L.fluid_set_advect_mode(advect_mode))
+    check(L.fluid_set_scratch_download(1 if scratch_download else 0))
+
+
+# Stam-signature primitives on host numpy arrays (flat float32, (N+2)^2, in place)
+def add_source(N, x, s, dt): check(lib().fluid_add_source(N, x, s, dt))
+def set_bnd(N, b, x): check(lib().fluid_set_bnd(N, b, x))
+def lin_solve(N, b, x, x0, a, c): check(lib().fluid_lin_solve(N, b, x, x0, a, c))
+def diffuse(N, b, x, x0, diff, dt): check(lib().fluid_diffuse(N, b, x, x0, diff, dt))
+def diffuse_blur(N, b, x, x0, diff, dt): check(lib().fluid_diffuse_blur(N, b, x, x0, diff, dt))
+def advect(N, b, d, d0, u, v, dt): check(lib().fluid_advect(N, b, d, d0, u, v, dt))
+def project(N, u, v, p, div): check(lib().fluid_project(N, u, v, p, div))
+def vel_step(N, u, v, u0, v0, visc, dt): check(lib().fluid_vel_step(N, u, v, u0, v0, visc, dt))
+def dens_step(N, x, x0, u, v, diff, dt): check(lib().fluid_dens_step(N, x, x0, u, v, diff, dt))
+def vort_confinement(N, u, v, vorticity): check(lib().fluid_vort_confinement(N, u, v, vorticity))
+def damp(N, vel, amount, dt): check(lib().fluid_damp(N, vel, amount, dt))
+
+
+def pinned_empty(n_floats):
+    """float32 numpy array backed by pinned host memory from fluid_host_alloc."""
+    p = _vp()
+    check(lib().fluid_host_alloc(ctypes.byref(p), n_floats * 4))
+    arr = np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_float)), (n_floats,))
+    return arr, p
+
+
+class FluidSystem:
+    """Resident GPU context with the reference class's method names
+    (FluidSystem.h:20-69; FSType::ORIGINAL, one fluid)."""
+
+    def __init__(self):
+        self.h = None
+        self.N = 0
+        self.batch = 1
+
+    def Setup(self, N, visc=0.0, diff=0.0, vorticity=0.0, damp=0.0, gs_order=GS_WAVEFRONT, gs_iters=20,
+              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1):
+        self.close()
+        p = Params()
+        lib().fluid_params_default(ctypes.byref(p))
+        p.N, p.batch, p.gs_iters, p.gs_order, p.advect_mode, p.device = N, batch, gs_iters, gs_order, advect_mode, device
+        p.visc, p.diff, p.vorticity, p.damp = visc, diff, vorticity, damp
+        h = _vp()
+        check(lib().fluid_ctx_create(ctypes.byref(p), ctypes.byref(h)))
+        self.h, self.N, self.batch = h, N, batch
+        return self
+
+    def close(self):
+        if self.h:
+            lib().fluid_ctx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def Clear(self): check(lib().fluid_ctx_clear(self.h))
+
+    def SetSources(self, sources, sim=-1):
+        """sources: iterable of (field, i, j, mode, value)."""
+        sources = list(sources)
+        arr = (Source * max(1, len(sources)))(*[Source(*s) for s in sources])
+        check(lib().fluid_ctx_set_sources(self.h, sim, len(sources), ctypes.cast(arr, _vp)))
+
+    def Update(self, dt, nsteps=1):
+        check(lib().fluid_ctx_step(self.h, dt, nsteps))
+
+    def Sync(self): check(lib().fluid_ctx_sync(self.h))
+
+    def LastStepMs(self):
+        ms = _cf()
+        check(lib().fluid_ctx_last_step_ms(self.h, ctypes.byref(ms)))
+        return ms.value
+
+    def VelStep(self, dt): check(lib().fluid_ctx_vel_step(self.h, dt))
+    def DensStep(self, dt): check(lib().fluid_ctx_dens_step(self.h, dt))
+
+    def SetModes(self, gs_order, gs_iters=20, advect_mode=ADVECT_MIDPOINT):
+        check(lib().fluid_ctx_set_modes(self.h, gs_order, gs_iters, advect_mode))
+
+    def SetCoeffs(self, visc, diff, vorticity=0.0, damp=0.0):
+        check(lib().fluid_ctx_set_coeffs(self.h, visc, diff, vorticity, damp))
+
+    def upload(self, field, host, sim=0):
+        check(lib().fluid_ctx_upload(self.h, field, sim, np.ascontiguousarray(host, np.float32).ravel()))
+
+    def download(self, field, sim=0, out=None):
+        if out is None:
+            out = np.empty((self.N + 2) ** 2, np.float32)
+        check(lib().fluid_ctx_download(self.h, field, sim, out))
+        return out
+
+    def GetVelX(self, sim=0): return self.download(U, sim)
+    def GetVelY(self, sim=0): return self.download(V, sim)
+    def GetDensities(self, sim=0): return self.download(DENS, sim)
+
+    # single primitives on resident fields
+    def add_source(self, x, s, dt): check(lib().fluid_ctx_add_source(self.h, x, s, dt))
+    def set_bnd(self, b, x): check(lib().fluid_ctx_set_bnd(self.h, b, x))
+    def lin_solve(self, b, x, x0, a, c): check(lib().fluid_ctx_lin_solve(self.h, b, x, x0, a, c))
+    def blur(self, b, x, x0, a, c): check(lib().fluid_ctx_blur(self.h, b, x, x0, a, c))
+    def advect(self, b, d, d0, u, v, dt): check(lib().fluid_ctx_advect(self.h, b, d, d0, u, v, dt))
+    def advect_velocity(self, u, v, u0, v0, dt): check(lib().fluid_ctx_advect_velocity(self.h, u, v, u0, v0, dt))
+    def project(self, u, v, p, div): check(lib().fluid_ctx_project(self.h, u, v, p, div))
+
+    def time_kernel(self, which, reps=5):
+        ms = _cf()
+        check(lib().fluid_ctx_time_kernel(self.h, which, reps, ctypes.byref(ms)))
+        return ms.value

@@ -1,0 +1,207 @@
+/*
+ * fluid_cuda.h -- C ABI of libfluid_cuda.so: the Stam "Stable Fluids" step of
+ * surajiyer/Fluid-Simulation (FSType::ORIGINAL pipeline) as hand-written
+ * sm_100a CUDA kernels.  Pure C, plain pointers and sizes, no C++/torch types.
+ *
+ * Reference citations are file:line into /root/reference/FluidSim/src/.
+ *
+ * Grids.  A host field is a dense (N+2)*(N+2) float array, cell (i,j) at
+ * i + (N+2)*j with i contiguous (FluidSystem::ID, FluidSystem.h:63-65); i,j in
+ * 1..N are interior cells, 0 and N+1 the border.  Device storage is private
+ * (row-pitched) and only crosses this boundary by copy.
+ *
+ * Numerics.  The library is compiled with -fmad=false -prec-div=true
+ * -prec-sqrt=true -ftz=false and evaluates every expression with the
+ * reference's association, so with FLUID_GS_WAVEFRONT every entry point is
+ * bit-identical to the reference CPU solver; FLUID_GS_REDBLACK changes only
+ * the relaxation order (and is bit-identical to a CPU red-black statement).
+ *
+ * Errors.  Every function returns 0 (FLUID_OK) or a fluid_status code and
+ * never aborts; fluid_last_error() gives a thread-local message.  There is no
+ * CPU fallback: without a usable CUDA device every call fails with
+ * FLUID_ERR_CUDA.  (The reference has no error handling at all: every
+ * primitive is void, FluidSystem.h:71-140.)
+ *
+ * Threading.  One context = one host thread at a time.  The host-pointer
+ * entry points share one internal context per thread.
+ */
+#ifndef FLUID_CUDA_H
+#define FLUID_CUDA_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum fluid_status {
+	FLUID_OK = 0,
+	FLUID_ERR_INVALID = 1,     /* bad argument */
+	FLUID_ERR_CUDA = 2,        /* CUDA runtime/driver error, or no device */
+	FLUID_ERR_NOMEM = 3,       /* device or host allocation failed */
+	FLUID_ERR_UNSUPPORTED = 4  /* valid request this build cannot serve */
+} fluid_status;
+
+/* Relaxation order for lin_solve / diffuse / project. */
+typedef enum fluid_gs_order {
+	FLUID_GS_WAVEFRONT = 0, /* reference order (lexicographic, in place), bitwise == CPU */
+	FLUID_GS_REDBLACK = 1   /* fast path: red (i+j even), black, set_bnd per sweep */
+} fluid_gs_order;
+
+/* Backtrace used by advect. */
+typedef enum fluid_advect_mode {
+	FLUID_ADVECT_MIDPOINT = 0, /* MidpointBackward, FluidSystem.h:185-206 (what Advect1 calls) */
+	FLUID_ADVECT_EULER = 1     /* EulerBack, FluidSystem.h:208-219 (Stam's original, uncalled) */
+} fluid_advect_mode;
+
+/* Field ids of a context: the Curr/Prev halves of the reference's FlipFlopArr
+ * members vX, vY, densList[0] (FluidSystem.h:157-160, FluidCode.h:15-44). */
+typedef enum fluid_field {
+	FLUID_U = 0, FLUID_V = 1, FLUID_DENS = 2,
+	FLUID_U_PREV = 3, FLUID_V_PREV = 4, FLUID_DENS_PREV = 5,
+	FLUID_FIELD_COUNT = 6
+} fluid_field;
+
+/* How a forcing entry is applied each step (between the zero fill of the Prev
+ * arrays and the velocity step, i.e. where FluidSystem::Update calls its
+ * updaters, FluidSystem.cpp:104-118). */
+typedef enum fluid_source_mode {
+	FLUID_SRC_PREV_SET = 0, /* Prev[i,j]  = value  (Stam-style source, scaled by dt in add_source) */
+	FLUID_SRC_CURR_ADD = 1, /* Curr[i,j] += value  (AddFluid density, FluidSystem.cpp:250-257) */
+	FLUID_SRC_CURR_SET = 2  /* Curr[i,j]  = value  (SetVelocity, FluidSystem.cpp:135-140) */
+} fluid_source_mode;
+
+typedef struct fluid_source {
+	int field; /* FLUID_U, FLUID_V or FLUID_DENS */
+	int i, j;  /* cell, 0..N+1 */
+	int mode;  /* fluid_source_mode */
+	float value;
+} fluid_source;
+
+/* What FluidSystem::Setup fixes (FluidSystem.cpp:18-67) plus the knobs the
+ * reference hard-codes.  Zero-initialise, then fluid_params_default(). */
+typedef struct fluid_params {
+	int N;            /* interior cells per side */
+	int batch;        /* independent simulations advanced together (ensemble), >= 1 */
+	int gs_iters;     /* FluidSystem::steps, 20 (FluidSystem.cpp:24) */
+	int gs_order;     /* fluid_gs_order */
+	int advect_mode;  /* fluid_advect_mode */
+	int device;       /* CUDA device ordinal; -1 = current device */
+	float visc;       /* visc_avg (FluidSystem.cpp:26-30) */
+	float diff;       /* FluidProps::Diff of the one fluid */
+	float vorticity;  /* 0 = confinement off (useVort=false) */
+	float damp;       /* 0 = no damping (reference default 0.1, FluidSystem.h:150) */
+	int reserved[6];  /* must be 0 */
+} fluid_params;
+
+typedef struct fluid_ctx fluid_ctx;
+
+/* ---- library ----------------------------------------------------------- */
+
+/* Thread-local description of the last failure ("" if none). */
+const char *fluid_last_error(void);
+/* "major.minor sm_100a ..." build string. */
+const char *fluid_version(void);
+/* Number of this library's kernels launched by the calling thread since the
+ * last reset (bench.py reports it as gpu_launches). */
+unsigned long long fluid_launch_count(void);
+void fluid_launch_count_reset(void);
+
+/* Modes used by the Stam-signature host-pointer entry points below (their
+ * argument lists have no room for them).  Defaults: FLUID_GS_WAVEFRONT, 20,
+ * FLUID_ADVECT_MIDPOINT -- the reference's behaviour.  Thread-local. */
+int fluid_set_gs_order(int order);
+int fluid_set_gs_iters(int iters);
+int fluid_set_advect_mode(int mode);
+/* When 0, vel_step/dens_step/project/diffuse_blur do not copy the arrays the
+ * reference only clobbers as scratch (u0,v0,x0,p,div) back to the host.
+ * Default 1 = every array the reference writes is written. */
+int fluid_set_scratch_download(int on);
+
+/* Pinned host memory for callers that want full-speed transfers. */
+int fluid_host_alloc(void **p, size_t bytes);
+int fluid_host_free(void *p);
+
+/* ---- host-pointer entry points: the reference's primitives ------------- *
+ * Synchronous; arrays are dense (N+2)^2 host floats; copy in, run on the    *
+ * GPU, copy out; nothing is retained.  `list` (std::vector<float>&,         *
+ * FluidCode.h:4) becomes float*; raw-pointer twins of two of them already   *
+ * exist in the reference (main.cpp:24,43).                                  */
+
+/* AddArrDt, FluidSystem.cpp:449-453: x += dt*s on all (N+2)^2 cells. */
+int fluid_add_source(int N, float *x, const float *s, float dt);
+/* SetBorder, FluidSystem.cpp:465-500. */
+int fluid_set_bnd(int N, int b, float *x);
+/* LinearSolve1, FluidSystem.cpp:534-548: a>0 ? gs_iters : 1 sweeps, SetBorder each. */
+int fluid_lin_solve(int N, int b, float *x, const float *x0, float a, float c);
+/* Diffuse1, FluidSystem.cpp:810-814. */
+int fluid_diffuse(int N, int b, float *x, const float *x0, float diff, float dt);
+/* Diffuse_blur -> Blur, FluidSystem.cpp:833-837, 722-743: result in x, the
+ * penultimate iterate in x0 (x0 is clobbered, as in the reference). */
+int fluid_diffuse_blur(int N, int b, float *x, float *x0, float diff, float dt);
+/* Advect1, FluidSystem.cpp:850-862; d0 may alias u or v. */
+int fluid_advect(int N, int b, float *d, const float *d0, const float *u, const float *v, float dt);
+/* Project, FluidSystem.cpp:982-1007; p and div are scratch outputs. */
+int fluid_project(int N, float *u, float *v, float *p, float *div);
+/* VelStep1, FluidSystem.cpp:354-376; u0,v0 = sources in, scratch out. */
+int fluid_vel_step(int N, float *u, float *v, float *u0, float *v0, float visc, float dt);
+/* DensStep1 (one fluid), FluidSystem.cpp:289-299; x0 = source in, scratch out. */
+int fluid_dens_step(int N, float *x, float *x0, const float *u, const float *v, float diff, float dt);
+/* VortConfinement, FluidSystem.cpp:1124-1175. */
+int fluid_vort_confinement(int N, float *u, float *v, float vorticity);
+/* Damp, FluidSystem.cpp:1177-1183: vel *= powf(1-amount, dt), factor computed on the host. */
+int fluid_damp(int N, float *vel, float amount, float dt);
+
+/* ---- resident context: the timed path ---------------------------------- *
+ * Plays the role of a FluidSystem set up with FSType::ORIGINAL and one      *
+ * fluid (FluidSystem.cpp:18-99): owns the six fields on the device.         */
+
+void fluid_params_default(fluid_params *p);
+int fluid_ctx_create(const fluid_params *p, fluid_ctx **out);
+int fluid_ctx_destroy(fluid_ctx *ctx);
+/* FluidSystem::Clear, FluidSystem.cpp:163-170. */
+int fluid_ctx_clear(fluid_ctx *ctx);
+/* Dense host array <-> device field; `sim` selects the ensemble member. */
+int fluid_ctx_upload(fluid_ctx *ctx, int field, int sim, const float *host);
+int fluid_ctx_download(fluid_ctx *ctx, int field, int sim, float *host);
+/* Forcing applied at the start of every step; n entries for ensemble member
+ * `sim` (sim = -1: the same list for every member). */
+int fluid_ctx_set_sources(fluid_ctx *ctx, int sim, int n, const fluid_source *src);
+/* pVelStep / pDensStep, FluidSystem.cpp:120,124 (no zero fill, no sources). */
+int fluid_ctx_vel_step(fluid_ctx *ctx, float dt);
+int fluid_ctx_dens_step(fluid_ctx *ctx, float dt);
+/* FluidSystem::Update, FluidSystem.cpp:101-128, nsteps times: zero the Prev
+ * fields, apply sources, [vorticity], vel step, dens step, [damp].  Asynchronous. */
+int fluid_ctx_step(fluid_ctx *ctx, float dt, int nsteps);
+/* Block until everything queued on the context has finished. */
+int fluid_ctx_sync(fluid_ctx *ctx);
+/* Device time of the work queued by the last fluid_ctx_step call, in ms
+ * (CUDA events on the context's stream; waits for completion). */
+int fluid_ctx_last_step_ms(fluid_ctx *ctx, float *ms);
+/* Change modes / coefficients of a live context (steps, visc... are public
+ * members of FluidSystem, FluidSystem.h:142-152). */
+int fluid_ctx_set_modes(fluid_ctx *ctx, int gs_order, int gs_iters, int advect_mode);
+int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity, float damp);
+
+/* Single primitives on resident fields (x, x0 ... are fluid_field ids; every
+ * ensemble member is processed).  Used by the parity tests and by bench.py's
+ * per-kernel roofline measurement. */
+int fluid_ctx_add_source(fluid_ctx *ctx, int x, int s, float dt);
+int fluid_ctx_set_bnd(fluid_ctx *ctx, int b, int x);
+int fluid_ctx_lin_solve(fluid_ctx *ctx, int b, int x, int x0, float a, float c);
+int fluid_ctx_blur(fluid_ctx *ctx, int b, int x, int x0, float a, float c);
+int fluid_ctx_advect(fluid_ctx *ctx, int b, int d, int d0, int u, int v, float dt);
+int fluid_ctx_advect_velocity(fluid_ctx *ctx, int u, int v, int u0, int v0, float dt);
+int fluid_ctx_project(fluid_ctx *ctx, int u, int v, int p, int div);
+/* Time `reps` back-to-back repetitions of one primitive with CUDA events on
+ * the context's stream; *ms = mean per repetition.  which: see fluid_kernel_id. */
+typedef enum fluid_kernel_id {
+	FLUID_K_LIN_SOLVE = 0, FLUID_K_BLUR = 1, FLUID_K_ADVECT = 2, FLUID_K_ADVECT_VEL = 3,
+	FLUID_K_PROJECT = 4, FLUID_K_ADD_SOURCE = 5
+} fluid_kernel_id;
+int fluid_ctx_time_kernel(fluid_ctx *ctx, int which, int reps, float *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLUID_CUDA_H */

@@ -1,0 +1,345 @@
+"""GPU suite: every entry point of libfluid_cuda.so, called through the C ABI,
+against the oracle (oracle/stam_oracle.c) and the committed golden vectors.
+
+Bar: BIT-EXACT (the float bit patterns are compared as integers) for
+  * the wavefront order vs the reference order            (north_star: bitwise)
+  * the red-black kernels vs the CPU red-black statement  (same arithmetic, same order)
+and a relative-L2 tolerance of 1e-4 (north_star) for red-black vs the reference
+run to convergence.  Nothing here reads /root/reference.
+"""
+import numpy as np
+import pytest
+
+from conftest import assert_bits, rand_field
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [1, 2, 3, 7, 16, 63, 64, 65, 130, 200]
+
+
+@pytest.fixture(autouse=True)
+def _default_modes(fl):
+    fl.set_modes()
+    yield
+    fl.set_modes()
+
+
+def test_device_is_b200_class(fl):
+    import torch
+    assert torch.cuda.is_available(), "GPU suite needs a CUDA device"
+    assert b"sm_100a" in fl.lib().fluid_version()
+    cc = torch.cuda.get_device_capability(0)
+    assert cc[0] == 10, "built for sm_100a only, found compute capability %r" % (cc,)
+
+
+@pytest.mark.parametrize("N", SIZES)
+def test_add_source_and_set_bnd(fl, oracle, N):
+    rng = np.random.default_rng(N)
+    x, s = rand_field(rng, N), rand_field(rng, N)
+    y = x.copy()
+    fl.add_source(N, x, s, 0.1)
+    oracle.add_source(N, y, s, 0.1)
+    assert_bits(x, y, "add_source")
+    for b in (0, 1, 2, 3, -1):
+        x = rand_field(rng, N)
+        y = x.copy()
+        fl.set_bnd(N, b, x)
+        oracle.set_bnd(N, b, y)
+        assert_bits(x, y, "set_bnd b=%d" % b)
+
+
+@pytest.mark.parametrize("order", [0, 1])
+@pytest.mark.parametrize("N", SIZES)
+def test_lin_solve(fl, oracle, N, order):
+    rng = np.random.default_rng(100 + N)
+    fl.set_modes(gs_order=order)
+    for b in (0, 1, 2, 3):
+        for a in (0.0, 1.0, 0.1 * 1e-4 * N * N):
+            a = np.float32(a)
+            c = np.float32(4.0) if a == 1 else 1 + 4 * a
+            x, x0 = rand_field(rng, N), rand_field(rng, N)
+            y = x.copy()
+            fl.lin_solve(N, b, x, x0, a, c)
+            oracle.lin_solve(N, b, y, x0, a, c, 20, order)
+            assert_bits(x, y, "lin_solve N=%d b=%d a=%g order=%d" % (N, b, a, order))
+
+
+@pytest.mark.parametrize("iters", [1, 2, 5, 33])
+def test_lin_solve_iteration_counts(fl, oracle, iters):
+    N = 70
+    rng = np.random.default_rng(iters)
+    for order in (0, 1):
+        fl.set_modes(gs_order=order, gs_iters=iters)
+        x, x0 = rand_field(rng, N), rand_field(rng, N)
+        y = x.copy()
+        fl.lin_solve(N, 1, x, x0, 0.5, 3.0)
+        oracle.lin_solve(N, 1, y, x0, 0.5, 3.0, iters, order)
+        assert_bits(x, y, "iters=%d order=%d" % (iters, order))
+
+
+@pytest.mark.parametrize("N", SIZES)
+def test_diffuse_and_blur(fl, oracle, N):
+    rng = np.random.default_rng(200 + N)
+    for b in (0, 1, 2, 3):
+        for diff in (0.0, 1e-4, 1e-2):
+            x, x0 = rand_field(rng, N), rand_field(rng, N)
+            y = x.copy()
+            fl.diffuse(N, b, x, x0, diff, 0.1)
+            oracle.diffuse(N, b, y, x0, diff, 0.1)
+            assert_bits(x, y, "diffuse")
+            x, x0 = rand_field(rng, N), rand_field(rng, N)
+            y, y0 = x.copy(), x0.copy()
+            fl.diffuse_blur(N, b, x, x0, diff, 0.1)
+            oracle.diffuse_blur(N, b, y, y0, diff, 0.1)
+            assert_bits(x, y, "blur result N=%d b=%d diff=%g" % (N, b, diff))
+            assert_bits(x0, y0, "blur scratch (penultimate iterate)")
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("N", SIZES)
+def test_advect(fl, oracle, N, mode):
+    rng = np.random.default_rng(300 + N)
+    fl.set_modes(advect_mode=mode)
+    for b in (0, 1, 2):
+        for scale in (0.05, 1.0, 40.0):  # 40: backtraces leave the domain, exercising the clamp
+            d, d0 = rand_field(rng, N), rand_field(rng, N)
+            u, v = rand_field(rng, N, scale), rand_field(rng, N, scale)
+            e = d.copy()
+            fl.advect(N, b, d, d0, u, v, 0.1)
+            oracle.advect(N, b, e, d0, u, v, 0.1, mode)
+            assert_bits(d, e, "advect N=%d b=%d scale=%g mode=%d" % (N, b, scale, mode))
+    # d0 aliasing u (what VelStep1 does, FluidSystem.cpp:372)
+    d, u, v = rand_field(rng, N), rand_field(rng, N), rand_field(rng, N)
+    e = d.copy()
+    fl.advect(N, 1, d, u, u, v, 0.1)
+    oracle.advect(N, 1, e, u, u, v, 0.1, mode)
+    assert_bits(d, e, "advect with d0 aliasing u")
+
+
+@pytest.mark.parametrize("order", [0, 1])
+@pytest.mark.parametrize("N", SIZES)
+def test_project(fl, oracle, N, order):
+    rng = np.random.default_rng(400 + N)
+    fl.set_modes(gs_order=order)
+    a = [rand_field(rng, N) for _ in range(4)]
+    b = [z.copy() for z in a]
+    fl.project(N, *a)
+    oracle.project(N, *b, 20, order)
+    for name, p, q in zip(("u", "v", "p", "div"), a, b):
+        assert_bits(p, q, "project %s N=%d order=%d" % (name, N, order))
+
+
+@pytest.mark.parametrize("order", [0, 1])
+@pytest.mark.parametrize("N", [2, 16, 65, 200, 513])
+def test_vel_and_dens_step(fl, oracle, N, order):
+    rng = np.random.default_rng(500 + N)
+    fl.set_modes(gs_order=order)
+    f = [rand_field(rng, N) for _ in range(6)]  # u v d u0 v0 d0
+    g = [z.copy() for z in f]
+    fl.vel_step(N, f[0], f[1], f[3], f[4], 1e-4, 0.1)
+    fl.dens_step(N, f[2], f[5], f[0], f[1], 1e-4, 0.1)
+    oracle.vel_step(N, g[0], g[1], g[3], g[4], 1e-4, 0.1, 20, order)
+    oracle.dens_step(N, g[2], g[5], g[0], g[1], 1e-4, 0.1)
+    for name, p, q in zip("u v dens u0(scratch) v0(scratch) dens0(scratch)".split(), f, g):
+        assert_bits(p, q, "%s N=%d order=%d" % (name, N, order))
+
+
+def test_golden_primitive_fields(fl, golden_fields):
+    """The committed fixtures made by the unmodified reference (tests/golden/make_golden.py)."""
+    G = golden_fields
+    for N in (12, 16):
+        t = "N%d_" % N
+        for b in (0, 1, 2):
+            for tag, a in (("a0", 0.0), ("a1", 1.0), ("ad", 0.1 * 1e-4 * N * N)):
+                c = 4.0 if tag == "a1" else 1 + 4 * a
+                x = G[t + "lin_solve_b%d_%s_in_x" % (b, tag)].copy()
+                fl.lin_solve(N, b, x, G[t + "lin_solve_b%d_%s_in_x0" % (b, tag)].copy(), np.float32(a), np.float32(c))
+                assert_bits(x, G[t + "lin_solve_b%d_%s_out" % (b, tag)], "golden lin_solve")
+            for tag, diff in (("d0", 0.0), ("d1", 1e-3)):
+                x, x0 = G[t + "blur_b%d_%s_in_x" % (b, tag)].copy(), G[t + "blur_b%d_%s_in_x0" % (b, tag)].copy()
+                fl.diffuse_blur(N, b, x, x0, diff, 0.1)
+                assert_bits(x, G[t + "blur_b%d_%s_out_x" % (b, tag)], "golden blur")
+                assert_bits(x0, G[t + "blur_b%d_%s_out_x0" % (b, tag)], "golden blur x0")
+            for tag in ("slow", "fast"):
+                k = t + "advect_b%d_%s_" % (b, tag)
+                for mode, name in ((0, "midpoint"), (1, "euler")):
+                    fl.set_modes(advect_mode=mode)
+                    d = G[k + "in_d"].copy()
+                    fl.advect(N, b, d, G[k + "in_d0"].copy(), G[k + "in_u"].copy(), G[k + "in_v"].copy(), 0.1)
+                    assert_bits(d, G[k + "out_" + name], "golden advect " + name)
+                fl.set_modes()
+        a = [G[t + "project_in_" + k].copy() for k in ("u", "v", "p", "div")]
+        fl.project(N, *a)
+        for k, arr in zip(("u", "v", "p", "div"), a):
+            assert_bits(arr, G[t + "project_out_" + k], "golden project " + k)
+        f = [G[t + "step_in_%d" % w].copy() for w in range(6)]
+        fl.vel_step(N, f[0], f[1], f[3], f[4], 1e-3, 0.1)
+        fl.dens_step(N, f[2], f[5], f[0], f[1], 1e-3, 0.1)
+        for w in range(6):
+            assert_bits(f[w], G[t + "step_out_%d" % w], "golden vel+dens step field %d" % w)
+
+
+def _sources(name, N):
+    import oracle_py as op
+    return op.stam_sources(N) if name == "stam" else op.blower_sources(N)
+
+
+def test_golden_frames_wavefront_bitwise(fl, golden_hashes):
+    """Whole frames (FluidSystem::Update) on the resident context vs the hashes of
+    the unmodified reference: N=64 x 100 and x 1000 steps (BASELINE config 1),
+    vorticity+damp, the Blower forcing, and the first step of config 2 (N=1024)."""
+    import oracle_py as op
+    for fr in golden_hashes:
+        fs = fl.FluidSystem().Setup(fr["N"], fr["visc"], fr["diff"], fr["vorticity"], fr["damp"])
+        fs.SetSources(_sources(fr["source"], fr["N"]))
+        fs.Update(fr["dt"], fr["steps"])
+        got = (op.fnv1a64(fs.GetDensities()), op.fnv1a64(fs.GetVelX()), op.fnv1a64(fs.GetVelY()))
+        assert got == (fr["dens"], fr["u"], fr["v"]), fr
+        fs.close()
+
+
+def test_config2_n1024_100_steps_wavefront_bitwise(fl, oracle):
+    """BASELINE config 2: N=1024, diff=visc=1e-4; the oracle needs ~1.3 s per step,
+    so the bitwise check covers the first 3 steps; red-black is compared on the same run."""
+    import oracle_py as op
+    N, steps = 1024, 3
+    src = op.stam_sources(N)
+    f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+    oracle.update(N, f, src, 1e-4, 1e-4, 0.1, steps)
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4)
+    fs.SetSources(src)
+    fs.Update(0.1, steps)
+    assert_bits(fs.GetVelX(), f["u"], "u")
+    assert_bits(fs.GetVelY(), f["v"], "v")
+    assert_bits(fs.GetDensities(), f["d"], "dens")
+    fs.close()
+    # red-black on the same problem: bit-exact against the CPU red-black statement
+    g = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+    oracle.update(N, g, src, 1e-4, 1e-4, 0.1, steps, order=op.GS_RB)
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK)
+    fs.SetSources(src)
+    fs.Update(0.1, steps)
+    assert_bits(fs.GetVelX(), g["u"], "rb u")
+    assert_bits(fs.GetDensities(), g["d"], "rb dens")
+    fs.close()
+
+
+def test_redblack_tolerance_vs_reference_order_converged(fl, oracle):
+    """north_star: red-black within 1e-4 relative of the reference run to convergence.
+    The Poisson solve needs O(N^2) sweeps, so this is evaluated at N=64 with 4000
+    sweeps on both sides (SURVEY.md 7 hard part 2), after 1 and after 10 steps."""
+    import oracle_py as op
+    N, iters = 64, 4000
+    src = op.stam_sources(N)
+    for steps in (1, 10):
+        f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+        oracle.update(N, f, src, 1e-4, 1e-4, 0.1, steps, iters=iters, order=op.GS_LEX)
+        fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, gs_iters=iters)
+        fs.SetSources(src)
+        fs.Update(0.1, steps)
+        for name, got in (("u", fs.GetVelX()), ("v", fs.GetVelY()), ("d", fs.GetDensities())):
+            want = f[name].astype(np.float64)
+            rel = np.linalg.norm(got - want) / np.linalg.norm(want)
+            assert rel <= 1e-4, (name, steps, rel)
+        fs.close()
+
+
+def test_ensemble_members_are_independent(fl, oracle):
+    """Batched ensemble (BASELINE config 5, scaled down): each member equals the
+    single simulation with the same source position, bit for bit."""
+    import oracle_py as op
+    N, B, steps = 48, 5, 4
+    for order in (0, 1):
+        fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=order, batch=B)
+        srcs = []
+        for b in range(B):
+            cx, cy = 1 + (37 * b) % N, 1 + (101 * b) % N
+            srcs.append([(2, cx, cy, 0, 100.0), (0, cx, cy, 0, 5.0), (1, cx, cy, 0, 5.0)])
+            fs.SetSources(srcs[-1], sim=b)
+        fs.Update(0.1, steps)
+        for b in range(B):
+            f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+            oracle.update(N, f, srcs[b], 1e-4, 1e-4, 0.1, steps, order=order)
+            assert_bits(fs.GetVelX(b), f["u"], "member %d u" % b)
+            assert_bits(fs.GetDensities(b), f["d"], "member %d dens" % b)
+        fs.close()
+
+
+def test_vorticity_and_damp(fl, oracle):
+    N = 45
+    rng = np.random.default_rng(9)
+    u, v = rand_field(rng, N), rand_field(rng, N)
+    a, b = u.copy(), v.copy()
+    fl.vort_confinement(N, u, v, 0.55)
+    oracle.vort_confinement(N, a, b, 0.55)
+    assert_bits(u, a, "vorticity u")
+    assert_bits(v, b, "vorticity v")
+    fl.damp(N, u, 0.1, 0.1)
+    oracle.damp(N, a, 0.1, 0.1)
+    assert_bits(u, a, "damp")
+
+
+def test_full_size_primitives_n8192(fl, oracle):
+    """BASELINE config 3 size.  The oracle runs single primitives at N=8192 in
+    seconds when the sweep count is small, so these are still bit-exact checks."""
+    N = 8192
+    rng = np.random.default_rng(8192)
+    n = (N + 2) ** 2
+    x0 = rng.uniform(-1, 1, n).astype(np.float32)
+    a = np.float32(0.1 * 1e-4 * N * N)
+    for order in (0, 1):
+        fl.set_modes(gs_order=order, gs_iters=2)
+        x = np.zeros(n, np.float32)
+        y = x.copy()
+        fl.lin_solve(N, 1, x, x0, a, 1 + 4 * a)
+        oracle.lin_solve(N, 1, y, x0, a, 1 + 4 * a, 2, order)
+        assert_bits(x, y, "N=8192 lin_solve order=%d" % order)
+    fl.set_modes()
+    u = rng.uniform(-1, 1, n).astype(np.float32)
+    v = rng.uniform(-1, 1, n).astype(np.float32)
+    d = np.zeros(n, np.float32)
+    e = d.copy()
+    fl.advect(N, 0, d, x0, u, v, 0.1)
+    oracle.advect(N, 0, e, x0, u, v, 0.1)
+    assert_bits(d, e, "N=8192 advect")
+    # size-independent properties: set_bnd is idempotent; add_source is exact for dt = 0
+    z = d.copy()
+    fl.set_bnd(N, 1, z)
+    z2 = z.copy()
+    fl.set_bnd(N, 1, z2)
+    assert_bits(z, z2, "set_bnd idempotent")
+
+
+def test_full_step_n2048_bitwise(fl, oracle):
+    import oracle_py as op
+    N = 2048
+    src = op.stam_sources(N)
+    f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+    oracle.update(N, f, src, 1e-4, 1e-4, 0.1, 1)
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4)
+    fs.SetSources(src)
+    fs.Update(0.1, 1)
+    assert_bits(fs.GetVelX(), f["u"], "u")
+    assert_bits(fs.GetDensities(), f["d"], "dens")
+    fs.close()
+
+
+def test_mass_is_reported_like_the_reference(fl, golden_hashes, oracle):
+    fr = golden_hashes[0]
+    fs = fl.FluidSystem().Setup(fr["N"], fr["visc"], fr["diff"])
+    fs.SetSources(_sources(fr["source"], fr["N"]))
+    fs.Update(fr["dt"], fr["steps"])
+    assert oracle.total_inner_mass(fr["N"], fs.GetDensities()) == fr["mass"]
+    fs.close()
+
+
+def test_errors_are_status_codes(fl):
+    L = fl.lib()
+    x = np.zeros(16, np.float32)
+    assert L.fluid_lin_solve(2, 0, x, x, 1.0, 4.0) == 1  # aliasing rejected
+    fs = fl.FluidSystem().Setup(8)
+    assert L.fluid_ctx_lin_solve(fs.h, 0, 0, 0, 1.0, 4.0) == 1
+    assert L.fluid_ctx_upload(fs.h, 9, 0, x) == 1
+    with pytest.raises(fl.FluidError):
+        fs.SetSources([(0, 99, 1, 0, 1.0)])
+    fs.close()

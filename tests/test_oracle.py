@@ -1,0 +1,168 @@
+"""CPU suite, part 1: the oracle (oracle/stam_oracle.c) against the golden
+vectors generated from the unmodified reference, and against the live reference
+build when it is present.  Bit-exact everywhere (integer compare of the float
+bit patterns)."""
+import numpy as np
+import pytest
+
+from conftest import assert_bits, rand_field
+
+
+def _sources(name, N):
+    import oracle_py as op
+    return op.stam_sources(N) if name == "stam" else op.blower_sources(N)
+
+
+def test_oracle_frames_match_golden_hashes(oracle, golden_hashes):
+    import oracle_py as op
+    for fr in golden_hashes:
+        if fr["N"] * fr["N"] * fr["steps"] > 64 * 64 * 1000 + 1:
+            continue  # N=1024 (1.3 s) is covered in the GPU suite's oracle leg; keep the CPU suite short
+        N = fr["N"]
+        f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+        oracle.update(N, f, _sources(fr["source"], N), fr["visc"], fr["diff"], fr["dt"], fr["steps"],
+                      vorticity=fr["vorticity"], damp=fr["damp"])
+        got = (op.fnv1a64(f["d"]), op.fnv1a64(f["u"]), op.fnv1a64(f["v"]))
+        assert got == (fr["dens"], fr["u"], fr["v"]), fr
+        assert oracle.total_inner_mass(N, f["d"]) == fr["mass"]
+
+
+def test_oracle_primitives_match_golden_fields(oracle, golden_fields):
+    import oracle_py as op
+    G = golden_fields
+    for N in (12, 16):
+        t = "N%d_" % N
+        x = G[t + "add_source_in_x"].copy()
+        oracle.add_source(N, x, G[t + "add_source_in_s"], 0.1)
+        assert_bits(x, G[t + "add_source_out"], "add_source")
+        for b in (0, 1, 2, 3):
+            x = G[t + "set_bnd_b%d_in" % b].copy()
+            oracle.set_bnd(N, b, x)
+            assert_bits(x, G[t + "set_bnd_b%d_out" % b], "set_bnd b=%d" % b)
+        for b in (0, 1, 2):
+            for tag, a in (("a0", 0.0), ("a1", 1.0), ("ad", 0.1 * 1e-4 * N * N)):
+                c = 4.0 if tag == "a1" else 1 + 4 * a
+                x = G[t + "lin_solve_b%d_%s_in_x" % (b, tag)].copy()
+                oracle.lin_solve(N, b, x, G[t + "lin_solve_b%d_%s_in_x0" % (b, tag)], np.float32(a), np.float32(c), 20)
+                assert_bits(x, G[t + "lin_solve_b%d_%s_out" % (b, tag)], "lin_solve")
+            for tag, diff in (("d0", 0.0), ("d1", 1e-3)):
+                x, x0 = G[t + "blur_b%d_%s_in_x" % (b, tag)].copy(), G[t + "blur_b%d_%s_in_x0" % (b, tag)].copy()
+                oracle.diffuse_blur(N, b, x, x0, diff, 0.1, 20)
+                assert_bits(x, G[t + "blur_b%d_%s_out_x" % (b, tag)], "blur x")
+                assert_bits(x0, G[t + "blur_b%d_%s_out_x0" % (b, tag)], "blur x0")
+            for tag in ("slow", "fast"):
+                k = t + "advect_b%d_%s_" % (b, tag)
+                for mode, name in ((op.ADV_MIDPOINT, "midpoint"), (op.ADV_EULER, "euler")):
+                    d = G[k + "in_d"].copy()
+                    oracle.advect(N, b, d, G[k + "in_d0"], G[k + "in_u"], G[k + "in_v"], 0.1, mode)
+                    assert_bits(d, G[k + "out_" + name], "advect " + name)
+        a = [G[t + "project_in_" + k].copy() for k in ("u", "v", "p", "div")]
+        oracle.project(N, *a, 20)
+        for k, arr in zip(("u", "v", "p", "div"), a):
+            assert_bits(arr, G[t + "project_out_" + k], "project " + k)
+        f = [G[t + "step_in_%d" % w].copy() for w in range(6)]
+        oracle.vel_step(N, f[0], f[1], f[3], f[4], 1e-3, 0.1)
+        oracle.dens_step(N, f[2], f[5], f[0], f[1], 1e-3, 0.1)
+        for w in range(6):
+            assert_bits(f[w], G[t + "step_out_%d" % w], "vel+dens step field %d" % w)
+
+
+def test_oracle_matches_live_reference(oracle, ref):
+    """Fresh random inputs against the unmodified reference, odd sizes included."""
+    import oracle_py as op
+    rng = np.random.default_rng(7)
+    for N in (1, 2, 3, 31, 50):
+        for b in (0, 1, 2):
+            a = np.float32(0.37)
+            x, x0 = rand_field(rng, N), rand_field(rng, N)
+            y = x.copy()
+            oracle.lin_solve(N, b, x, x0, a, 1 + 4 * a, 20)
+            ref.L.ref_lin_solve(N, b, y, x0, a, 1 + 4 * a, 20)
+            assert_bits(x, y, "lin_solve N=%d" % N)
+            d, d0, u, v = (rand_field(rng, N), rand_field(rng, N), rand_field(rng, N, 3.0), rand_field(rng, N, 3.0))
+            e = d.copy()
+            oracle.advect(N, b, d, d0, u, v, 0.1, op.ADV_MIDPOINT)
+            ref.L.ref_advect(N, b, e, d0, u, v, 0.1)
+            assert_bits(d, e, "advect N=%d" % N)
+    N = 40
+    sim = ref.sim(N, 2e-4, 3e-4, 0.3, 20, 0.05)
+    src = op.stam_sources(N) + op.blower_sources(N)
+    sim.set_sources(src)
+    sim.update(0.05, 7)
+    f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+    oracle.update(N, f, src, 2e-4, 3e-4, 0.05, 7, vorticity=0.3, damp=0.05)
+    for name, w in (("u", 0), ("v", 1), ("d", 2), ("u0", 3), ("v0", 4), ("d0", 5)):
+        assert_bits(f[name], sim.field(w), "update " + name)
+    sim.close()
+
+
+def test_set_bnd_sign_table(oracle):
+    """SetBorder sign table and corners (FluidSystem.cpp:465-500)."""
+    N = 5
+    rng = np.random.default_rng(3)
+    for b in (0, 1, 2):
+        x = rand_field(rng, N)
+        oracle.set_bnd(N, b, x)
+        g = x.reshape(N + 2, N + 2)  # g[j, i]
+        sx, sy = (-1 if b == 1 else 1), (-1 if b == 2 else 1)
+        assert np.array_equal(g[1:-1, 0], sx * g[1:-1, 1]) and np.array_equal(g[1:-1, -1], sx * g[1:-1, -2])
+        assert np.array_equal(g[0, 1:-1], sy * g[1, 1:-1]) and np.array_equal(g[-1, 1:-1], sy * g[-2, 1:-1])
+        assert g[0, 0] == np.float32(0.5) * (g[0, 1] + g[1, 0])
+        assert g[-1, -1] == np.float32(0.5) * (g[-1, -2] + g[-2, -1])
+
+
+def test_iteration_count_logic(oracle):
+    """a == 0 means one sweep (FluidSystem.cpp:538); Blur makes the count odd (:726-727)."""
+    N = 8
+    rng = np.random.default_rng(5)
+    x0 = rand_field(rng, N)
+    x1, x20 = rand_field(rng, N), None
+    x20 = x1.copy()
+    oracle.lin_solve(N, 0, x1, x0, 0.0, 1.0, 1)
+    oracle.lin_solve(N, 0, x20, x0, 0.0, 1.0, 20)
+    assert_bits(x1, x20, "a=0 ignores iters")
+    # blur with iters=20 equals blur with iters=21 (20 is made odd), differs from 19
+    a, b_, c_ = rand_field(rng, N), None, None
+    s = rand_field(rng, N)
+    r20, r21, r19 = a.copy(), a.copy(), a.copy()
+    oracle.diffuse_blur(N, 0, r20, s.copy(), 1e-2, 0.1, 20)
+    oracle.diffuse_blur(N, 0, r21, s.copy(), 1e-2, 0.1, 21)
+    oracle.diffuse_blur(N, 0, r19, s.copy(), 1e-2, 0.1, 19)
+    assert_bits(r20, r21, "blur 20 -> 21 passes")
+    assert r19.tobytes() != r21.tobytes()
+    assert not r20.reshape(N + 2, N + 2)[0].any() and not r20.reshape(N + 2, N + 2)[:, 0].any()  # ZeroBorder
+
+
+def test_redblack_converges_to_lexicographic(oracle):
+    """The fast path's ordering solves the same system: run to convergence the two
+    orders agree to <= 1e-4 relative L2 (north_star tolerance; SURVEY 7 hard part 2)."""
+    import oracle_py as op
+    N = 32
+    rng = np.random.default_rng(11)
+    x0 = rand_field(rng, N)
+    a = np.float32(0.1 * 1e-4 * N * N)
+    lex, rb = np.zeros_like(x0), np.zeros_like(x0)
+    oracle.lin_solve(N, 1, lex, x0, a, 1 + 4 * a, 400, op.GS_LEX)
+    oracle.lin_solve(N, 1, rb, x0, a, 1 + 4 * a, 400, op.GS_RB)
+    rel = np.linalg.norm(lex.astype(np.float64) - rb) / np.linalg.norm(lex.astype(np.float64))
+    assert rel <= 1e-4, rel
+
+
+def test_projection_reduces_divergence(oracle):
+    N = 32
+    # smooth field: the collocated central-difference projection cannot remove grid-scale noise
+    jj, ii = np.meshgrid(np.arange(N + 2), np.arange(N + 2), indexing="ij")
+    u = (np.sin(2 * np.pi * ii / N) * np.cos(np.pi * jj / N)).astype(np.float32).ravel()
+    v = (np.cos(np.pi * ii / N) * np.sin(3 * np.pi * jj / N)).astype(np.float32).ravel()
+    oracle.set_bnd(N, 1, u)
+    oracle.set_bnd(N, 2, v)
+
+    def div_norm(u, v):
+        U, V = u.reshape(N + 2, N + 2).astype(np.float64), v.reshape(N + 2, N + 2).astype(np.float64)
+        d = (U[1:-1, 2:] - U[1:-1, :-2]) + (V[2:, 1:-1] - V[:-2, 1:-1])
+        return np.linalg.norm(d)
+
+    before = div_norm(u, v)
+    p, dv = np.zeros_like(u), np.zeros_like(u)
+    oracle.project(N, u, v, p, dv, 200)
+    assert div_norm(u, v) < 0.2 * before
