@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""Headline benchmark: grid cell-updates/s per vel_step+dens_step (20 GS
+iterations) with the HBM roofline of the dominant kernel, on N GPUs of one node.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU solver
+
+One "step" = one FluidSystem::Update-equivalent (zero the source arrays, apply
+the synthetic forcing S1, vel_step, dens_step) over the whole grid; a
+cell-update = one interior cell advanced through one such step.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "fluid-simulation_b200"))
+
+METRIC = "grid cell-updates/s per vel_step+dens_step (20 GS iters); HBM GB/s vs roofline"
+UNIT = "cell-updates/s"
+DT, VISC, DIFF, ITERS = 0.1, 1e-4, 1e-4, 20
+
+# Algorithmic bytes per cell: fp32, every array read/written once per pass.
+B_GS_SWEEP = 12          # x0 R, x R, x W (a red-black sweep = both colours)
+B_CELL_UPDATE = 1276     # whole vel_step + dens_step with visc,diff > 0 and 20 iterations
+GS_SWEEPS_PER_STEP = 80  # 2 diffusions + 2 projections, 20 sweeps each
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=8192, help="interior cells per side per GPU (BASELINE config 3: 8192)")
+    ap.add_argument("--order", default="redblack", choices=["redblack", "wavefront"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_setup(n_gpus):
+    """One process per GPU under torchrun; returns (rank, world, local_rank, dist or None)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        return rank, world, local, dist
+    return rank, world, local, None
+
+
+def barrier_sync(dist, local):
+    import torch
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(local)
+
+
+def max_over_ranks(dist, local, value):
+    if dist is None:
+        return value
+    import torch
+    t = torch.tensor([value], dtype=torch.float64, device="cuda:%d" % local)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def cpu_baseline_single(sample_n=2048, sample_steps=2):
+    """The reference's own solver (oracle/_ref, unmodified FluidSystem.cpp) -- or the
+    oracle port when that build is absent -- on ONE host core (the reference is
+    single-threaded), on a bounded sample of the workload."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import oracle_py as op
+    src = op.stam_sources(sample_n)
+    if os.path.exists(op.REF_SO):
+        sim = op.Ref().sim(sample_n, VISC, DIFF, 0.0, ITERS, 0.0)
+        sim.set_sources(src)
+        sim.update(DT, 1)  # warm-up (page faults)
+        t0 = time.perf_counter()
+        sim.update(DT, sample_steps)
+        dt = time.perf_counter() - t0
+        sim.close()
+        kind = "reference"
+    else:
+        op.build()
+        orc = op.Oracle()
+        f = {k: np.zeros((sample_n + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+        orc.update(sample_n, f, src, VISC, DIFF, DT, 1)
+        t0 = time.perf_counter()
+        orc.update(sample_n, f, src, VISC, DIFF, DT, sample_steps)
+        dt = time.perf_counter() - t0
+        kind = "port"
+    return {"value": sample_n * sample_n * sample_steps / dt, "unit": UNIT, "cores": 1, "kind": kind,
+            "sample": "N=%d grid, %d steps after 1 warm-up step, same dt/visc/diff/forcing as the GPU run "
+                      "(%.1f s of CPU work; the reference solver is single-threaded)" % (sample_n, sample_steps, dt)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU solver on all host cores.  The solver
+    itself is single-threaded (no threads, SIMD or BLAS anywhere in FluidSystem.cpp),
+    so "all the host threads it can use" = one independent simulation per core,
+    each step a bounded N=1024 sample of the workload per core."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import oracle_py as op
+    sample_n = 1024
+    cores = max(1, len(os.sched_getaffinity(0)))
+    src = op.stam_sources(sample_n)
+    have_ref = os.path.exists(op.REF_SO)
+    if have_ref:
+        R = op.Ref()
+        sims = [R.sim(sample_n, VISC, DIFF, 0.0, ITERS, 0.0) for _ in range(cores)]
+        for s in sims:
+            s.set_sources(src)
+        step_fns = [lambda s=s: s.update(DT, 1) for s in sims]
+    else:
+        op.build()
+        orc = op.Oracle()
+        fields = [{k: np.zeros((sample_n + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()} for _ in range(cores)]
+        step_fns = [lambda f=f: orc.update(sample_n, f, src, VISC, DIFF, DT, 1) for f in fields]
+
+    def one_step():
+        # ctypes releases the GIL during the foreign call, so these run in parallel
+        th = [threading.Thread(target=fn) for fn in step_fns]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+
+    for _ in range(args.warmup):
+        one_step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_step()
+    dt = time.perf_counter() - t0
+    value = cores * sample_n * sample_n * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "N=%d single-GPU throughput run (BASELINE config 3): dt=0.1 visc=diff=1e-4, 20 GS iterations, "
+                               "source S1; CPU arm: bounded sample, one N=%d simulation per host core per step" % (args.n, sample_n),
+                   "N": args.n, "sample_N": sample_n},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if have_ref else "port",
+                         "sample": "%d independent N=%d simulations (one per core), %d steps" % (cores, sample_n, args.steps)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import fluid_b200 as fl
+
+    rank, world, local, dist = dist_setup(args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this framework has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    fl.check(fl.lib().fluid_set_device(local))
+    N = args.n
+    order = fl.GS_REDBLACK if args.order == "redblack" else fl.GS_WAVEFRONT
+    L = fl.lib()
+
+    fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local)
+    c = N // 2
+    fs.SetSources([(fl.DENS, c, c, fl.SRC_PREV_SET, 100.0), (fl.U, c, c, fl.SRC_PREV_SET, 5.0),
+                   (fl.V, c, c, fl.SRC_PREV_SET, 5.0)])
+    # spin-up + warm-up (untimed)
+    fs.Update(DT, max(args.warmup, 3))
+    fs.Sync()
+
+    sampler = ClockSampler(local)
+    fs.SetProfiling(True)
+    fs.Profile(reset=True)
+    barrier_sync(dist, local)
+    sampler.start()
+    L.fluid_launch_count_reset()
+    t0 = time.perf_counter()
+    fs.Update(DT, args.steps)           # K steps, asynchronous on the context's stream
+    fs.Sync()
+    barrier_sync(dist, local)
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    dev_ms = fs.LastStepMs()            # CUDA events on the launching stream, around exactly the K steps
+    launches = int(L.fluid_launch_count())
+    clocks = sampler.stop()
+    prof = fs.Profile(reset=True)
+    fs.SetProfiling(False)
+    ms = max_over_ranks(dist, local, dev_ms)
+    wall_ms = max_over_ranks(dist, local, wall_ms)
+    cells = float(N) * N * world
+    value = cells * args.steps / (ms * 1e-3)
+
+    # roofline of the dominant kernel class (Gauss-Seidel sweeps), measured inside the timed region
+    peak, peak_src = peaks()
+    gs_ms, gs_launches = prof["lin_solve"]
+    gs_bytes = B_GS_SWEEP * float(N) * N * GS_SWEEPS_PER_STEP * args.steps
+    achieved = gs_bytes / (gs_ms * 1e-3) / 1e9 if gs_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get("traffic_bytes_per_launch")
+    step_gbs = B_CELL_UPDATE * float(N) * N * args.steps / (ms * 1e-3) / 1e9
+    roofline = {
+        "bound": "hbm", "kernel": "Gauss-Seidel relaxation (%s), %d launches in the timed region" % (args.order, gs_launches),
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+        "traffic": traffic,
+        "algorithmic_bytes_per_launch": gs_bytes / max(1, gs_launches),
+        "ms_per_launch": gs_ms / max(1, gs_launches),
+        "share_of_step": gs_ms / max(1e-9, sum(v[0] for v in prof.values())),
+        "whole_step": {"achieved": step_gbs, "frac": step_gbs / peak, "bytes_per_cell_update": B_CELL_UPDATE},
+        "classes_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
+    }
+
+    e2e = None
+    if not args.no_e2e:
+        e2e = measure_e2e(fl, np, N, order, max(1, min(args.steps, 5)), dist, local, world)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_single()
+    fs.close()
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "N=%d single-GPU throughput run (BASELINE config 3): dt=0.1 visc=diff=1e-4, 20 GS iterations, "
+                                   "%s relaxation, source S1 (dens 100, u=v=5 at the centre cell each step)" % (N, args.order),
+                       "N": N, "gs_order": args.order, "gs_iters": ITERS, "advect": "midpoint",
+                       "l2": "inputs larger than L2 (six %.0f MB fields vs 126 MB L2), no explicit flush" % (4e-6 * (N + 2) ** 2),
+                       "parallelism": "1 GPU" if world == 1 else "%d independent N=%d simulations, one per GPU, no exchange" % (world, N)},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "wall_ms_per_step": wall_ms / args.steps,
+            "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def measure_e2e(fl, np, N, order, steps, dist, local, world):
+    """Same metric through the reference-facing host-pointer calls (fluid_vel_step +
+    fluid_dens_step, Stam signatures) with HOST buffers: every step uploads its
+    inputs from pinned memory and downloads u, v, dens; copies are inside the timing."""
+    import torch
+    n = (N + 2) ** 2
+    bufs = {}
+    for k in ("u", "v", "d", "u0", "v0", "d0"):
+        bufs[k], _ = fl.pinned_empty(n)
+        bufs[k][:] = 0
+    fl.set_modes(gs_order=order, gs_iters=ITERS, scratch_download=False)
+    c = N // 2
+    idx = c + (N + 2) * c
+
+    def one():
+        for k in ("u0", "v0", "d0"):
+            bufs[k][:] = 0          # FluidSystem::Update's zero fill + forcing, done by the host as in the reference
+        bufs["d0"][idx], bufs["u0"][idx], bufs["v0"][idx] = 100.0, 5.0, 5.0
+        fl.vel_step(N, bufs["u"], bufs["v"], bufs["u0"], bufs["v0"], VISC, DT)
+        fl.dens_step(N, bufs["d"], bufs["d0"], bufs["u"], bufs["v"], DIFF, DT)
+
+    one()  # warm-up: creates the library's cached context
+    barrier_sync(dist, local)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    torch.cuda.synchronize(local)
+    dt = time.perf_counter() - t0
+    dt = max_over_ranks(dist, local, dt)
+    fl.set_modes()
+    return {"value": float(N) * N * world * steps / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * n * 4 * world,
+            "d2h_bytes_per_step": 3 * n * 4 * world, "steps": steps,
+            "api": "fluid_vel_step + fluid_dens_step (host pointers, pinned), scratch download off"}
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

@@ -81,6 +81,38 @@ struct fluid_ctx {
 	int n_src = 0;
 	std::vector<std::vector<SourceDev>> src; // per ensemble member
 	bool src_dirty = false;
+	// optional per-kernel-class device timing (CUDA event pairs on c->stream)
+	bool prof_on = false;
+	struct ProfSeg { cudaEvent_t a, b; int cls; unsigned long long launches; };
+	std::vector<ProfSeg> prof_segs;
+	std::vector<cudaEvent_t> prof_pool;
+};
+
+// RAII segment: brackets the launches of one primitive with two events when
+// profiling is on; costs nothing otherwise.
+struct ProfScope {
+	fluid_ctx* c;
+	int idx = -1;
+	unsigned long long l0 = 0;
+	ProfScope(fluid_ctx* ctx, int cls) : c(ctx)
+	{
+		if (!c->prof_on) return;
+		cudaEvent_t ev[2];
+		for (auto& e : ev) {
+			if (!c->prof_pool.empty()) { e = c->prof_pool.back(); c->prof_pool.pop_back(); }
+			else if (cudaEventCreate(&e) != cudaSuccess) return;
+		}
+		cudaEventRecord(ev[0], c->stream);
+		l0 = t_launches;
+		c->prof_segs.push_back({ ev[0], ev[1], cls, 0 });
+		idx = (int) c->prof_segs.size() - 1;
+	}
+	~ProfScope()
+	{
+		if (idx < 0) return;
+		cudaEventRecord(c->prof_segs[idx].b, c->stream);
+		c->prof_segs[idx].launches = t_launches - l0;
+	}
 };
 
 static int ctx_bind(fluid_ctx* c)
@@ -106,12 +138,14 @@ static int flat_blocks(const fluid_ctx* c)
 // ---------------------------------------------------------------------------
 static int dev_add_source(fluid_ctx* c, float* x, const float* s, float dt)
 {
+	ProfScope ps(c, FLUID_PROF_ADD_SOURCE);
 	LAUNCH(k_add_source, flat_blocks(c), 256, 0, c->stream, (float4*) x, (const float4*) s, dt, n4_of(c));
 	return FLUID_OK;
 }
 
 static int dev_add_source2(fluid_ctx* c, float* x, const float* s, float* y, const float* t, float dt)
 {
+	ProfScope ps(c, FLUID_PROF_ADD_SOURCE);
 	LAUNCH(k_add_source2, flat_blocks(c), 256, 0, c->stream, (float4*) x, (const float4*) s, (float4*) y,
 	       (const float4*) t, dt, n4_of(c));
 	return FLUID_OK;
@@ -134,6 +168,7 @@ static int dev_zero_bnd(fluid_ctx* c, float* x)
 // LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
 static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
 {
+	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
 	const int limit = a > 0 ? c->gs_iters : 1;
 	if (c->gs_order == FLUID_GS_REDBLACK) {
 		for (int k = 0; k < limit; k++) {
@@ -156,6 +191,7 @@ static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 // return the result is in x and the penultimate iterate in x0.
 static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 {
+	ProfScope ps(c, FLUID_PROF_BLUR);
 	int limit = a > 0 ? c->gs_iters : 1;
 	if (limit % 2 == 0) limit += 1;
 	float *dst = x, *src = x0;
@@ -172,6 +208,7 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 
 static int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, const float* v, float dt)
 {
+	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
 	LAUNCH(k_advect, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode);
 	return FLUID_OK;
@@ -179,6 +216,7 @@ static int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const floa
 
 static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const float* v0, float dt)
 {
+	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
 	LAUNCH(k_advect_velocity, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode);
 	return FLUID_OK;
@@ -187,9 +225,15 @@ static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0
 // Project (FluidSystem.cpp:982-1007).
 static int dev_project(fluid_ctx* c, float* u, float* v, float* p, float* div)
 {
-	LAUNCH(k_divergence, rowgroup_grid(c, c->g.NY + 2), kBlk2D, 0, c->stream, c->g, u, v, div, p);
+	{
+		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
+		LAUNCH(k_divergence, rowgroup_grid(c, c->g.NY + 2), kBlk2D, 0, c->stream, c->g, u, v, div, p);
+	}
 	FL_TRY(dev_lin_solve(c, 0, p, div, 1.0f, 4.0f));
-	LAUNCH(k_subtract_gradient, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, u, v, p);
+	{
+		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
+		LAUNCH(k_subtract_gradient, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, u, v, p);
+	}
 	return FLUID_OK;
 }
 
@@ -242,6 +286,7 @@ static int ensure_vort_scratch(fluid_ctx* c)
 static int dev_vort_confinement(fluid_ctx* c, float* u, float* v, float vorticity)
 {
 	FL_TRY(ensure_vort_scratch(c));
+	ProfScope ps(c, FLUID_PROF_OTHER);
 	LAUNCH(k_vort_curl, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, c->vscr[0], c->vscr[1]);
 	LAUNCH(k_vort_dir, cell_grid(c), kBlk2D, 0, c->stream, c->g, c->vscr[1], c->vscr[2], c->vscr[3]);
 	LAUNCH(k_vort_apply, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, c->vscr[0], c->vscr[2], c->vscr[3], vorticity);
@@ -251,6 +296,7 @@ static int dev_vort_confinement(fluid_ctx* c, float* u, float* v, float vorticit
 static int dev_damp(fluid_ctx* c, float* vel, float amount, float dt)
 {
 	const float f = powf(1 - amount, dt); // host libm, as the reference (FluidSystem.cpp:1181)
+	ProfScope ps(c, FLUID_PROF_OTHER);
 	LAUNCH(k_scale, flat_blocks(c), 256, 0, c->stream, (float4*) vel, f, n4_of(c));
 	return FLUID_OK;
 }
@@ -281,16 +327,19 @@ static int sync_sources(fluid_ctx* c)
 // FluidSystem::Update (FluidSystem.cpp:101-128) for FSType::ORIGINAL.
 static int dev_update(fluid_ctx* c, float dt)
 {
-	CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));
-	CU_TRY(cudaMemsetAsync(c->f[FLUID_V_PREV], 0, c->field_bytes, c->stream));
-	CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV], 0, c->field_bytes, c->stream));
-	if (c->n_src > 0) {
-		FieldPtrs fp;
-		for (int k = 0; k < 3; k++) {
-			fp.cur[k] = c->f[k];
-			fp.prev[k] = c->f[k + 3];
+	{
+		ProfScope ps(c, FLUID_PROF_OTHER);
+		CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));
+		CU_TRY(cudaMemsetAsync(c->f[FLUID_V_PREV], 0, c->field_bytes, c->stream));
+		CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV], 0, c->field_bytes, c->stream));
+		if (c->n_src > 0) {
+			FieldPtrs fp;
+			for (int k = 0; k < 3; k++) {
+				fp.cur[k] = c->f[k];
+				fp.prev[k] = c->f[k + 3];
+			}
+			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 		}
-		LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 	}
 	if (c->vorticity != 0.0f) FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
 	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], c->visc, dt));
@@ -314,6 +363,14 @@ extern "C" const char* fluid_version(void)
 
 extern "C" unsigned long long fluid_launch_count(void) { return t_launches; }
 extern "C" void fluid_launch_count_reset(void) { t_launches = 0; }
+
+extern "C" int fluid_ctx_destroy(fluid_ctx* c);
+
+struct HostCtxCache {
+	fluid_ctx* c = nullptr;
+	~HostCtxCache() { /* process teardown: the CUDA runtime may already be gone, do not touch it */ }
+};
+static thread_local HostCtxCache t_cache;
 
 static thread_local int t_gs_order = FLUID_GS_WAVEFRONT;
 static thread_local int t_gs_iters = 20;
@@ -344,6 +401,23 @@ extern "C" int fluid_set_advect_mode(int mode)
 extern "C" int fluid_set_scratch_download(int on)
 {
 	t_scratch_download = on ? 1 : 0;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_set_device(int device)
+{
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0)
+		return fail(FLUID_ERR_CUDA, "no CUDA device available (%s); this library has no CPU fallback",
+			    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+	if (device < 0 || device >= ndev) return fail(FLUID_ERR_INVALID, "device %d does not exist (%d devices)", device, ndev);
+	CU_TRY(cudaSetDevice(device));
+	if (t_cache.c && t_cache.c->device != device) {
+		fluid_ctx_destroy(t_cache.c);
+		t_cache.c = nullptr;
+		CU_TRY(cudaSetDevice(device));
+	}
 	return FLUID_OK;
 }
 
@@ -381,6 +455,8 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& p : c->vscr) if (p) cudaFree(p);
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_first) cudaFree(c->d_first);
+	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
+	for (auto& e : c->prof_pool) cudaEventDestroy(e);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);
 	if (c->stream) cudaStreamDestroy(c->stream);
@@ -593,6 +669,32 @@ extern "C" int fluid_ctx_last_step_ms(fluid_ctx* c, float* ms)
 	return FLUID_OK;
 }
 
+extern "C" int fluid_ctx_set_profiling(fluid_ctx* c, int on)
+{
+	CHECK_CTX(c);
+	c->prof_on = on != 0;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_profile(fluid_ctx* c, float* ms, unsigned long long* launches, int reset)
+{
+	CHECK_CTX(c);
+	if (!ms || !launches) return fail(FLUID_ERR_INVALID, "null pointer");
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	for (int k = 0; k < FLUID_PROF_COUNT; k++) { ms[k] = 0; launches[k] = 0; }
+	for (auto& sg : c->prof_segs) {
+		float t = 0;
+		CU_TRY(cudaEventElapsedTime(&t, sg.a, sg.b));
+		ms[sg.cls] += t;
+		launches[sg.cls] += sg.launches;
+	}
+	if (reset) {
+		for (auto& sg : c->prof_segs) { c->prof_pool.push_back(sg.a); c->prof_pool.push_back(sg.b); }
+		c->prof_segs.clear();
+	}
+	return FLUID_OK;
+}
+
 extern "C" int fluid_ctx_add_source(fluid_ctx* c, int x, int s, float dt)
 {
 	CHECK_CTX(c);
@@ -676,12 +778,6 @@ extern "C" int fluid_ctx_time_kernel(fluid_ctx* c, int which, int reps, float* m
 // thread (re-created when N changes); arrays are copied in, the primitive runs
 // on the GPU, and every array the reference writes is copied back.
 // ---------------------------------------------------------------------------
-struct HostCtxCache {
-	fluid_ctx* c = nullptr;
-	~HostCtxCache() { /* process teardown: the CUDA runtime may already be gone, do not touch it */ }
-};
-static thread_local HostCtxCache t_cache;
-
 static int host_ctx(int N, fluid_ctx** out)
 {
 	if (N < 1) return fail(FLUID_ERR_INVALID, "N=%d must be >= 1", N);

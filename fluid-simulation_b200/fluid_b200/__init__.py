@@ -27,12 +27,13 @@ K_LIN_SOLVE, K_BLUR, K_ADVECT, K_ADVECT_VEL, K_PROJECT, K_ADD_SOURCE = range(6)
 EXPORTS = [
     "fluid_last_error", "fluid_version", "fluid_launch_count", "fluid_launch_count_reset",
     "fluid_set_gs_order", "fluid_set_gs_iters", "fluid_set_advect_mode", "fluid_set_scratch_download",
-    "fluid_host_alloc", "fluid_host_free",
+    "fluid_set_device", "fluid_host_alloc", "fluid_host_free",
     "fluid_add_source", "fluid_set_bnd", "fluid_lin_solve", "fluid_diffuse", "fluid_diffuse_blur", "fluid_advect",
     "fluid_project", "fluid_vel_step", "fluid_dens_step", "fluid_vort_confinement", "fluid_damp",
     "fluid_params_default", "fluid_ctx_create", "fluid_ctx_destroy", "fluid_ctx_clear", "fluid_ctx_upload",
     "fluid_ctx_download", "fluid_ctx_set_sources", "fluid_ctx_vel_step", "fluid_ctx_dens_step", "fluid_ctx_step",
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
+    "fluid_ctx_set_profiling", "fluid_ctx_profile",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
 ]
@@ -103,6 +104,8 @@ def lib():
     L.fluid_ctx_last_step_ms.argtypes = [_vp, ctypes.POINTER(_cf)]
     L.fluid_ctx_set_modes.argtypes = [_vp, _ci, _ci, _ci]
     L.fluid_ctx_set_coeffs.argtypes = [_vp, _cf, _cf, _cf, _cf]
+    L.fluid_ctx_set_profiling.argtypes = [_vp, _ci]
+    L.fluid_ctx_profile.argtypes = [_vp, ctypes.POINTER(_cf), ctypes.POINTER(ctypes.c_ulonglong), _ci]
     L.fluid_ctx_add_source.argtypes = [_vp, _ci, _ci, _cf]
     L.fluid_ctx_set_bnd.argtypes = [_vp, _ci, _ci]
     L.fluid_ctx_lin_solve.argtypes = [_vp, _ci, _ci, _ci, _cf, _cf]
@@ -218,6 +221,17 @@ class FluidSystem:
     def GetVelX(self, sim=0): return self.download(U, sim)
     def GetVelY(self, sim=0): return self.download(V, sim)
     def GetDensities(self, sim=0): return self.download(DENS, sim)
+
+    PROF_CLASSES = ("lin_solve", "blur", "advect", "project_aux", "add_source", "other")
+
+    def SetProfiling(self, on=True): check(lib().fluid_ctx_set_profiling(self.h, 1 if on else 0))
+
+    def Profile(self, reset=True):
+        """{class: (ms, launches)} accumulated since the last reset."""
+        ms = (_cf * 6)()
+        n = (ctypes.c_ulonglong * 6)()
+        check(lib().fluid_ctx_profile(self.h, ms, n, 1 if reset else 0))
+        return {k: (ms[i], int(n[i])) for i, k in enumerate(self.PROF_CLASSES)}
 
     # single primitives on resident fields
     def add_source(self, x, s, dt): check(lib().fluid_ctx_add_source(self.h, x, s, dt))

@@ -118,6 +118,10 @@ int fluid_set_advect_mode(int mode);
  * Default 1 = every array the reference writes is written. */
 int fluid_set_scratch_download(int on);
 
+/* CUDA device used by the host-pointer entry points and by contexts created
+ * with device = -1 on the calling thread (default: device 0). */
+int fluid_set_device(int device);
+
 /* Pinned host memory for callers that want full-speed transfers. */
 int fluid_host_alloc(void **p, size_t bytes);
 int fluid_host_free(void *p);
@@ -182,6 +186,24 @@ int fluid_ctx_last_step_ms(fluid_ctx *ctx, float *ms);
  * members of FluidSystem, FluidSystem.h:142-152). */
 int fluid_ctx_set_modes(fluid_ctx *ctx, int gs_order, int gs_iters, int advect_mode);
 int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity, float damp);
+
+/* Per-primitive device time inside fluid_ctx_step / vel_step / dens_step: when
+ * on, every primitive is bracketed by a CUDA event pair on the context's
+ * stream.  fluid_ctx_profile waits for the stream, then sums milliseconds and
+ * kernel launches per class (arrays of FLUID_PROF_COUNT) since the last reset.
+ * (The reference's only timing is the frame-level TimeAnalyse,
+ * SystemManager.cpp:246-275.) */
+typedef enum fluid_prof_class {
+	FLUID_PROF_LIN_SOLVE = 0,   /* Gauss-Seidel sweeps (wavefront or red-black) */
+	FLUID_PROF_BLUR = 1,        /* Jacobi blur passes incl. their border launches */
+	FLUID_PROF_ADVECT = 2,
+	FLUID_PROF_PROJECT_AUX = 3, /* divergence + gradient subtraction */
+	FLUID_PROF_ADD_SOURCE = 4,
+	FLUID_PROF_OTHER = 5,       /* zero fill, forcing, vorticity, damp */
+	FLUID_PROF_COUNT = 6
+} fluid_prof_class;
+int fluid_ctx_set_profiling(fluid_ctx *ctx, int on);
+int fluid_ctx_profile(fluid_ctx *ctx, float *ms, unsigned long long *launches, int reset);
 
 /* Single primitives on resident fields (x, x0 ... are fluid_field ids; every
  * ensemble member is processed).  Used by the parity tests and by bench.py's
