@@ -20,6 +20,9 @@
 #include "grid.cuh"
 #include "kernels_basic.cuh"
 #include "kernels_relax.cuh"
+#include "kernels_rb_tile.cuh"
+
+#include <map>
 
 using namespace fluid;
 
@@ -81,6 +84,11 @@ struct fluid_ctx {
 	int n_src = 0;
 	std::vector<std::vector<SourceDev>> src; // per ensemble member
 	bool src_dirty = false;
+	// red-black tile path: sweeps per tile residency (0 = one-colour-per-launch kernels), its
+	// ping-pong scratch field and the TMA descriptors of the arrays it has been asked to read
+	int rb_tile_sweeps = 2;
+	float* rb_scratch = nullptr;
+	std::map<const float*, CUtensorMap> tmaps;
 	// optional per-kernel-class device timing (CUDA event pairs on c->stream)
 	bool prof_on = false;
 	struct ProfSeg { cudaEvent_t a, b; int cls; unsigned long long launches; };
@@ -165,12 +173,98 @@ static int dev_zero_bnd(fluid_ctx* c, float* x)
 	return FLUID_OK;
 }
 
+// ---- red-black tile path ---------------------------------------------------
+constexpr int kRbRY = 64, kRbRX = 256, kRbNT = 512;
+constexpr size_t kRbSmem = (size_t) (kRbRY + 2) * kRbRX * sizeof(float);
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+				  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+				  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled is fetched through the runtime so that the library
+// has no link-time dependency on libcuda (it must load on a machine without a driver).
+static int get_encode_fn(EncodeTiledFn* out)
+{
+	static EncodeTiledFn fn = nullptr;
+	if (!fn) {
+		void* p = nullptr;
+		cudaDriverEntryPointQueryResult qres;
+		CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+		if (qres != cudaDriverEntryPointSuccess || !p) return fail(FLUID_ERR_CUDA, "driver does not provide cuTensorMapEncodeTiled");
+		fn = (EncodeTiledFn) p;
+	}
+	*out = fn;
+	return FLUID_OK;
+}
+
+// TMA descriptor of one field: 3-D tensor (pitch, NY+2, batch) of floats, box = one tile window.
+static int field_tmap(fluid_ctx* c, const float* base, const CUtensorMap** out)
+{
+	auto it = c->tmaps.find(base);
+	if (it == c->tmaps.end()) {
+		EncodeTiledFn enc;
+		FL_TRY(get_encode_fn(&enc));
+		CUtensorMap m;
+		const cuuint64_t dims[3] = { (cuuint64_t) c->g.pitch, (cuuint64_t) (c->g.NY + 2), (cuuint64_t) c->batch };
+		const cuuint64_t strides[2] = { (cuuint64_t) c->g.pitch * sizeof(float), (cuuint64_t) c->g.plane * sizeof(float) };
+		const cuuint32_t box[3] = { (cuuint32_t) kRbRX, (cuuint32_t) kRbRY, 1 };
+		const cuuint32_t estr[3] = { 1, 1, 1 };
+		CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*) base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+				 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+		if (r != CUDA_SUCCESS) return fail(FLUID_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int) r);
+		it = c->tmaps.emplace(base, m).first;
+	}
+	*out = &it->second;
+	return FLUID_OK;
+}
+
+template <int S>
+static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, float cc)
+{
+	static bool configured = false; // per template instance; attribute is per-device-function, set once per process/device
+	auto kern = k_rb_tile<S, kRbRY, kRbRX, kRbNT>;
+	if (!configured) {
+		CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kRbSmem));
+		configured = true;
+	}
+	const CUtensorMap* tm;
+	FL_TRY(field_tmap(c, in, &tm));
+	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 4 * S;
+	LAUNCH(kern, dim3(cdiv(c->g.N, TX), cdiv(c->g.NY, TY), c->batch), kRbNT, kRbSmem, c->stream, *tm, c->g, b, out, x0, a, cc);
+	return FLUID_OK;
+}
+
+// `limit` red-black sweeps as an EVEN number of tile passes of 2 or 1 sweeps,
+// ping-ponging between x and the scratch field so that the result ends in x.
+static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc, int limit)
+{
+	if (!c->rb_scratch) {
+		CU_TRY(cudaMalloc(&c->rb_scratch, c->field_bytes));
+		CU_TRY(cudaMemsetAsync(c->rb_scratch, 0, c->field_bytes, c->stream));
+	}
+	const int smax = c->rb_tile_sweeps >= 2 ? 2 : 1;
+	int n2 = smax == 2 ? limit / 2 : 0, n1 = limit - 2 * n2;
+	if ((n2 + n1) % 2) { n2 -= 1; n1 += 2; } // limit >= 2 and odd pass count imply n2 >= 1
+	const float* in = x;
+	float* out = c->rb_scratch;
+	for (int k = 0; k < n2 + n1; k++) {
+		if (k < n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, cc));
+		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, cc));
+		float* t = const_cast<float*>(in);
+		in = out;
+		out = t;
+	}
+	return FLUID_OK;
+}
+
 // LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
 static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
 {
 	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
 	const int limit = a > 0 ? c->gs_iters : 1;
-	if (c->gs_order == FLUID_GS_REDBLACK) {
+	if (c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 && b >= 0 && b <= 2) {
+		FL_TRY(rb_tile_solve(c, b, x, x0, a, cc, limit));
+	} else if (c->gs_order == FLUID_GS_REDBLACK) {
 		for (int k = 0; k < limit; k++) {
 			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 0);
 			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 1);
@@ -453,6 +547,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->stream) cudaStreamSynchronize(c->stream);
 	for (auto& p : c->f) if (p) cudaFree(p);
 	for (auto& p : c->vscr) if (p) cudaFree(p);
+	if (c->rb_scratch) cudaFree(c->rb_scratch);
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
@@ -614,6 +709,14 @@ extern "C" int fluid_ctx_set_modes(fluid_ctx* c, int gs_order, int gs_iters, int
 	c->gs_order = gs_order;
 	c->gs_iters = gs_iters;
 	c->advect_mode = advect_mode;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_tuning(fluid_ctx* c, int rb_tile_sweeps)
+{
+	CHECK_CTX(c);
+	if (rb_tile_sweeps < 0 || rb_tile_sweeps > 2) return fail(FLUID_ERR_INVALID, "rb_tile_sweeps=%d must be 0, 1 or 2", rb_tile_sweeps);
+	c->rb_tile_sweeps = rb_tile_sweeps;
 	return FLUID_OK;
 }
 

@@ -33,7 +33,7 @@ EXPORTS = [
     "fluid_params_default", "fluid_ctx_create", "fluid_ctx_destroy", "fluid_ctx_clear", "fluid_ctx_upload",
     "fluid_ctx_download", "fluid_ctx_set_sources", "fluid_ctx_vel_step", "fluid_ctx_dens_step", "fluid_ctx_step",
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
-    "fluid_ctx_set_profiling", "fluid_ctx_profile",
+    "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
 ]
@@ -104,6 +104,7 @@ def lib():
     L.fluid_ctx_last_step_ms.argtypes = [_vp, ctypes.POINTER(_cf)]
     L.fluid_ctx_set_modes.argtypes = [_vp, _ci, _ci, _ci]
     L.fluid_ctx_set_coeffs.argtypes = [_vp, _cf, _cf, _cf, _cf]
+    L.fluid_ctx_set_tuning.argtypes = [_vp, _ci]
     L.fluid_ctx_set_profiling.argtypes = [_vp, _ci]
     L.fluid_ctx_profile.argtypes = [_vp, ctypes.POINTER(_cf), ctypes.POINTER(ctypes.c_ulonglong), _ci]
     L.fluid_ctx_add_source.argtypes = [_vp, _ci, _ci, _cf]
@@ -221,6 +222,8 @@ class FluidSystem:
     def GetVelX(self, sim=0): return self.download(U, sim)
     def GetVelY(self, sim=0): return self.download(V, sim)
     def GetDensities(self, sim=0): return self.download(DENS, sim)
+
+    def SetTuning(self, rb_tile_sweeps): check(lib().fluid_ctx_set_tuning(self.h, rb_tile_sweeps))
 
     PROF_CLASSES = ("lin_solve", "blur", "advect", "project_aux", "add_source", "other")
 

@@ -186,6 +186,10 @@ int fluid_ctx_last_step_ms(fluid_ctx *ctx, float *ms);
  * members of FluidSystem, FluidSystem.h:142-152). */
 int fluid_ctx_set_modes(fluid_ctx *ctx, int gs_order, int gs_iters, int advect_mode);
 int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity, float damp);
+/* Kernel selection for FLUID_GS_REDBLACK: sweeps fused per shared-memory tile
+ * residency (2 = default, 1; 0 = one kernel launch per colour).  Results are
+ * bit-identical for every setting; only the memory traffic differs. */
+int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
 
 /* Per-primitive device time inside fluid_ctx_step / vel_step / dens_step: when
  * on, every primitive is bracketed by a CUDA event pair on the context's
