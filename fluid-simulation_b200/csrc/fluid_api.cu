@@ -229,7 +229,7 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 	}
 	const CUtensorMap* tm;
 	FL_TRY(field_tmap(c, in, &tm));
-	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 4 * S;
+	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 2 * (((2 * S + 3) / 4) * 4);
 	LAUNCH(kern, dim3(cdiv(c->g.N, TX), cdiv(c->g.NY, TY), c->batch), kRbNT, kRbSmem, c->stream, *tm, c->g, b, out, x0, a, cc);
 	return FLUID_OK;
 }
@@ -242,9 +242,15 @@ static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 		CU_TRY(cudaMalloc(&c->rb_scratch, c->field_bytes));
 		CU_TRY(cudaMemsetAsync(c->rb_scratch, 0, c->field_bytes, c->stream));
 	}
-	const int smax = c->rb_tile_sweeps >= 2 ? 2 : 1;
-	int n2 = smax == 2 ? limit / 2 : 0, n1 = limit - 2 * n2;
-	if ((n2 + n1) % 2) { n2 -= 1; n1 += 2; } // limit >= 2 and odd pass count imply n2 >= 1
+	int n2, n1; // passes of 2 sweeps and of 1 sweep; n2 + n1 must be even
+	if (c->rb_tile_sweeps >= 2) {
+		n2 = limit / 2;
+		n1 = limit % 2;
+		if ((n2 + n1) % 2) { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
+	} else {
+		n2 = limit % 2; // an odd count needs one 2-sweep pass to make the number of passes even
+		n1 = limit - 2 * n2;
+	}
 	const float* in = x;
 	float* out = c->rb_scratch;
 	for (int k = 0; k < n2 + n1; k++) {

@@ -146,10 +146,10 @@ __global__ void __launch_bounds__(256) k_divergence(GridDesc g, const float* __r
 	const float uw = __ldg(u + base - 1), ue = __ldg(u + base + 4);
 	const float fN = (float) g.N;
 	float4 r;
-	r.x = -0.5f * (uc.y - uw + vn.x - vs.x) / fN;
-	r.y = -0.5f * (uc.z - uc.x + vn.y - vs.y) / fN;
-	r.z = -0.5f * (uc.w - uc.y + vn.z - vs.z) / fN;
-	r.w = -0.5f * (ue - uc.z + vn.w - vs.w) / fN;
+	r.x = div_exact(-0.5f * (uc.y - uw + vn.x - vs.x), fN);
+	r.y = div_exact(-0.5f * (uc.z - uc.x + vn.y - vs.y), fN);
+	r.z = div_exact(-0.5f * (uc.w - uc.y + vn.z - vs.z), fN);
+	r.w = div_exact(-0.5f * (ue - uc.z + vn.w - vs.w), fN);
 	if (i0 >= 1 && i0 + 3 <= g.N) {
 		*reinterpret_cast<float4*>(dv + base) = r;
 	} else {
@@ -380,8 +380,8 @@ __global__ void __launch_bounds__(256) k_vort_dir(GridDesc g, const float* __res
 	const float len = sqrtf(gx * gx + gy * gy);
 	float fx = 0.0f, fy = 0.0f;
 	if (!(len < 0.01f)) {
-		fx = gx / len;
-		fy = gy / len;
+		fx = div_exact(gx, len);
+		fy = div_exact(gy, len);
 	}
 	(fxb + off)[id] = fx;
 	(fyb + off)[id] = fy;

@@ -70,7 +70,7 @@ __device__ __forceinline__ void rb_tile_sweeps(float* base, const float (&x0a)[K
 					       uint32_t mask1, int par, float a, float c, int b, const GridDesc& g, int i_first,
 					       int j_first)
 {
-#pragma unroll
+#pragma unroll 1
 	for (int hs = 0; hs < 2 * S; hs++) {
 		const int colour = hs & 1;
 		float* q = base + (colour ^ par); // the cell of each pair that has the active colour
@@ -104,7 +104,9 @@ __global__ void __launch_bounds__(NT, 2) k_rb_tile(const __grid_constant__ CUten
 						    float* __restrict__ xoutb, const float* __restrict__ x0b, float a,
 						    float c)
 {
-	constexpr int H = 2 * S, TY = RY - 2 * H, TX = RX - 2 * H;
+	// vertical halo 2S; the horizontal one is padded to a multiple of 4 floats because the
+	// global start address of a TMA box must be 16-byte aligned
+	constexpr int HY = 2 * S, HX = ((2 * S + 3) / 4) * 4, TY = RY - 2 * HY, TX = RX - 2 * HX;
 	constexpr int CB = RX / 32;               // 32-column blocks per window row
 	constexpr int NW = NT / 32;               // warps
 	constexpr int NB = (RY / 2) * CB;         // warp-blocks (2 rows x 32 cols)
@@ -120,7 +122,7 @@ __global__ void __launch_bounds__(NT, 2) k_rb_tile(const __grid_constant__ CUten
 	const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, sub = lane >> 4, p = lane & 15;
 	const int tx0 = blockIdx.x * TX, ty0 = blockIdx.y * TY; // output cells: i in tx0+1..tx0+TX, j in ty0+1..ty0+TY
 	const int sim = blockIdx.z;
-	const int ci0 = 1 + tx0 - H, cj0 = 1 + ty0 - H;         // interior index of window cell (0,0)
+	const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;       // interior index of window cell (0,0)
 
 	if (tid == 0) {
 		mbar_init(&bar, 1);
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(NT, 2) k_rb_tile(const __grid_constant__ CUten
 
 	// tiles that contain a wall-adjacent cell take the (block-uniform) slow path that maintains border cells
 	const bool wall = (b >= 0 && b <= 2) &&
-			  (tx0 == 0 || ty0 == 0 || tx0 + TX + H >= g.N || ty0 + TY + H >= g.NY);
+			  (tx0 == 0 || ty0 == 0 || tx0 + TX + HX >= g.N || ty0 + TY + HY >= g.NY);
 
 	mbar_wait(&bar, 0);
 
@@ -169,21 +171,20 @@ __global__ void __launch_bounds__(NT, 2) k_rb_tile(const __grid_constant__ CUten
 	float* xout = xoutb + off;
 	const bool full = (tx0 + TX <= g.N) && (ty0 + TY <= g.NY);
 	if (!wall && full) {
-		constexpr int V = (H % 4 == 0 && TX % 4 == 0) ? 4 : 2;
-		constexpr int PER_ROW = TX / V;
+		static_assert(TX % 4 == 0 && HX % 4 == 0, "float4 store path");
+		constexpr int PER_ROW = TX / 4;
 		for (int idx = tid; idx < TY * PER_ROW; idx += NT) {
 			const int r = idx / PER_ROW, cv = idx - r * PER_ROW;
-			const float* s = tile + (H + r) * RX + H + V * cv;
-			float* d = xout + cell(g, tx0 + 1 + V * cv, ty0 + 1 + r);
-			if (V == 4) *reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(s);
-			else *reinterpret_cast<float2*>(d) = *reinterpret_cast<const float2*>(s);
+			const float* s = tile + (HY + r) * RX + HX + 4 * cv;
+			float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
+			*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(s);
 		}
 	} else {
 		for (int idx = tid; idx < TY * TX; idx += NT) {
 			const int r = idx / TX, cc = idx - r * TX;
 			const int i = tx0 + 1 + cc, j = ty0 + 1 + r;
 			if (i > g.N || j > g.NY) continue;
-			const float v = tile[(H + r) * RX + H + cc];
+			const float v = tile[(HY + r) * RX + HX + cc];
 			xout[cell(g, i, j)] = v;
 			mirror_border(g, xout, b, i, j, v);
 		}
