@@ -86,6 +86,7 @@ struct fluid_ctx {
 	bool src_dirty = false;
 	// red-black tile path: sweeps per tile residency (0 = one-colour-per-launch kernels), its
 	// ping-pong scratch field and the TMA descriptors of the arrays it has been asked to read
+	int num_sms = 148;
 	int rb_tile_sweeps = 2;
 	float* rb_scratch = nullptr;
 	std::map<const float*, CUtensorMap> tmaps;
@@ -175,7 +176,7 @@ static int dev_zero_bnd(fluid_ctx* c, float* x)
 
 // ---- red-black tile path ---------------------------------------------------
 constexpr int kRbRY = 64, kRbRX = 256, kRbNT = 512;
-constexpr size_t kRbSmem = (size_t) (kRbRY + 2) * kRbRX * sizeof(float);
+constexpr size_t kRbSmem = 2 * (size_t) (kRbRY + 2) * kRbRX * sizeof(float); // double buffered
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
 				  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -202,7 +203,7 @@ static int field_tmap(fluid_ctx* c, const float* base, const CUtensorMap** out)
 {
 	auto it = c->tmaps.find(base);
 	if (it == c->tmaps.end()) {
-		EncodeTiledFn enc;
+		EncodeTiledFn enc = nullptr;
 		FL_TRY(get_encode_fn(&enc));
 		CUtensorMap m;
 		const cuuint64_t dims[3] = { (cuuint64_t) c->g.pitch, (cuuint64_t) (c->g.NY + 2), (cuuint64_t) c->batch };
@@ -230,7 +231,11 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 	const CUtensorMap* tm;
 	FL_TRY(field_tmap(c, in, &tm));
 	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 2 * (((2 * S + 3) / 4) * 4);
-	LAUNCH(kern, dim3(cdiv(c->g.N, TX), cdiv(c->g.NY, TY), c->batch), kRbNT, kRbSmem, c->stream, *tm, c->g, b, out, x0, a, cc);
+	const int ntx = cdiv(c->g.N, TX), nty = cdiv(c->g.NY, TY);
+	const long long ntiles = (long long) ntx * nty * c->batch;
+	if (ntiles > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many tiles");
+	const int grid = (int) std::min<long long>(ntiles, c->num_sms); // persistent: one CTA per SM
+	LAUNCH(kern, grid, kRbNT, kRbSmem, c->stream, *tm, c->g, b, out, x0, a, cc, ntx, nty, (int) ntiles);
 	return FLUID_OK;
 }
 
@@ -606,6 +611,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	int rc = FLUID_OK;
 	do {
 		if (cudaSetDevice(dev) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaSetDevice(%d) failed", dev); break; }
+		cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, dev);
 		if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
 		if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaEventCreate failed"); break; }
 		for (int k = 0; k < FLUID_FIELD_COUNT && rc == FLUID_OK; k++) {

@@ -62,132 +62,225 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, i
 		: "memory");
 }
 
-// The 2S colour passes of one tile residency.  WALL (block uniform) additionally
-// keeps the border cells inside the window current, i.e. SetBorder after every
-// sweep: a border cell mirrors one interior cell and is read by no other.
-template <int S, int RX, int CB, int KB, bool WALL>
-__device__ __forceinline__ void rb_tile_sweeps(float* base, const float (&x0a)[KB], const float (&x0c)[KB], uint32_t mask0,
-					       uint32_t mask1, int par, float a, float c, int b, const GridDesc& g, int i_first,
-					       int j_first)
+// x0 of one cell pair, issued early and consumed a whole tile later.  Volatile so
+// that the compiler keeps the load where it is written (ahead of the compute of
+// the previous tile) instead of sinking it to its first use.
+__device__ __forceinline__ float2 ldg_pair_early(const float* p)
 {
-#pragma unroll 1
-	for (int hs = 0; hs < 2 * S; hs++) {
-		const int colour = hs & 1;
-		float* q = base + (colour ^ par); // the cell of each pair that has the active colour
-		const uint32_t m = colour ? mask1 : mask0;
+	float2 v;
+	asm volatile("ld.global.nc.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+	return v;
+}
+
+// One colour pass over the KB cells of that colour this thread owns.
+// q points at the thread's first cell of the active colour.  MASKED: only cells
+// whose bit is set in m are real interior cells away from the window ring.
+// WALL (implies MASKED): also keep the border cells inside the window current,
+// i.e. SetBorder after every sweep -- a border cell mirrors one interior cell
+// and is read by no other.
+template <int RX, int CB, int KB, bool MASKED, bool WALL, bool SECOND>
+__device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB], uint32_t m, float a, float c, int b,
+					       const GridDesc& g, int i_first, int j_first)
+{
 #pragma unroll
-		for (int k = 0; k < KB; k++) {
-			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
-			const float v = relax(colour ? x0c[k] : x0a[k], a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], c);
-			if ((m >> k) & 1) {
-				q[o] = v;
-				if (WALL) {
-					const int i = i_first + 32 * (k % CB) + (colour ^ par), j = j_first + 2 * (k / CB);
-					const float sx = (b == 1) ? -v : v, sy = (b == 2) ? -v : v;
-					if (i == 1) q[o - 1] = sx;
-					if (i == g.N) q[o + 1] = sx;
-					if (j == 1) q[o - RX] = sy;
-					if (j == g.NY) q[o + RX] = sy;
-				}
+	for (int k = 0; k < KB; k++) {
+		const int o = 2 * (k / CB) * RX + 32 * (k % CB);
+		const float v = relax(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], c);
+		if (!MASKED) {
+			q[o] = v;
+		} else if ((m >> k) & 1) {
+			q[o] = v;
+			if (WALL) {
+				const int i = i_first + 32 * (k % CB), j = j_first + 2 * (k / CB);
+				const float sx = (b == 1) ? -v : v, sy = (b == 2) ? -v : v;
+				if (i == 1) q[o - 1] = sx;
+				if (i == g.N) q[o + 1] = sx;
+				if (j == 1) q[o - RX] = sy;
+				if (j == g.NY) q[o + RX] = sy;
 			}
 		}
+	}
+}
+
+template <int S, int RX, int CB, int KB, bool MASKED, bool WALL>
+__device__ __forceinline__ void rb_tile_sweeps(float* base, const float2 (&x0)[KB], uint32_t mask0, uint32_t mask1, int par,
+					       float a, float c, int b, const GridDesc& g, int i_first, int j_first)
+{
+	// after the conditional swap in the caller x0[k].x belongs to the red cell of pair k, .y to the black one
+	float* q0 = base + par;       // red cell (i+j even) of each pair
+	float* q1 = base + (par ^ 1); // black cell
+#pragma unroll 1
+	for (int s = 0; s < S; s++) {
+		rb_colour_pass<RX, CB, KB, MASKED, WALL, false>(q0, x0, mask0, a, c, b, g, i_first + par, j_first);
+		__syncthreads();
+		rb_colour_pass<RX, CB, KB, MASKED, WALL, true>(q1, x0, mask1, a, c, b, g, i_first + (par ^ 1), j_first);
 		__syncthreads();
 	}
 }
 
-// S  sweeps per residency (halo H = 2S);  window RY x RX floats, RX % 32 == 0 so
-// that rows r and r+1 of a 32-column block sit in the same banks and the two
-// half-warps (which work on opposite colours' columns) never collide;
-// NT threads, each owning KB = RY*RX/(2*NT) horizontally adjacent cell pairs.
+// Persistent kernel: one CTA per SM walks over tiles t = blockIdx.x, +gridDim.x, ...
+// While the CTA relaxes tile n in one shared-memory buffer, the TMA engine fills
+// the other buffer with tile n+1 and the x0 values of tile n+1 are already on
+// their way into registers, so HBM latency is hidden behind the arithmetic
+// instead of being paid at the start of every CTA (ncu on the non-persistent
+// version: long-scoreboard stalls 6 of 11 cycles per issue, DRAM at 35 %).
+//
+// S sweeps per residency; window RY x RX floats (vertical halo 2S, horizontal
+// halo padded to 4: the global start address of a TMA box must be 16-byte
+// aligned).  RX % 32 == 0 so that rows r and r+1 of a 32-column block sit in the
+// same banks and the two half-warps, which work on opposite colours' columns,
+// never collide.  NT threads, each owning KB = RY*RX/(2*NT) adjacent cell pairs.
 template <int S, int RY, int RX, int NT>
-__global__ void __launch_bounds__(NT, 2) k_rb_tile(const __grid_constant__ CUtensorMap tm_in, GridDesc g, int b,
+__global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUtensorMap tm_in, GridDesc g, int b,
 						    float* __restrict__ xoutb, const float* __restrict__ x0b, float a,
-						    float c)
+						    float c, int ntx, int nty, int ntiles)
 {
-	// vertical halo 2S; the horizontal one is padded to a multiple of 4 floats because the
-	// global start address of a TMA box must be 16-byte aligned
 	constexpr int HY = 2 * S, HX = ((2 * S + 3) / 4) * 4, TY = RY - 2 * HY, TX = RX - 2 * HX;
 	constexpr int CB = RX / 32;               // 32-column blocks per window row
 	constexpr int NW = NT / 32;               // warps
 	constexpr int NB = (RY / 2) * CB;         // warp-blocks (2 rows x 32 cols)
 	constexpr int KB = NB / NW;               // blocks per warp = pairs per thread
 	static_assert(RX % 32 == 0 && RY % 2 == 0 && NB % NW == 0, "bad tile shape");
-	static_assert(KB % CB == 0, "a warp must own whole row pairs");
+	static_assert(KB % CB == 0 && KB <= 32, "a warp must own whole row pairs; masks are 32 bits");
+	static_assert(TX % 4 == 0 && HX % 4 == 0, "float4 store path");
 	constexpr int RPW = KB / CB;              // row pairs per warp
+	constexpr int BUF = (RY + 2) * RX;        // one guard row above and below each window
 
-	extern __shared__ __align__(128) float smem[]; // (RY + 2) rows of RX: one guard row above and below
-	__shared__ __align__(8) uint64_t bar;
-	float* tile = smem + RX;
+	extern __shared__ __align__(128) float smem[]; // two buffers of BUF floats
+	__shared__ __align__(8) uint64_t bar[2];
 
 	const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, sub = lane >> 4, p = lane & 15;
-	const int tx0 = blockIdx.x * TX, ty0 = blockIdx.y * TY; // output cells: i in tx0+1..tx0+TX, j in ty0+1..ty0+TY
-	const int sim = blockIdx.z;
-	const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;       // interior index of window cell (0,0)
+	const int r_first = 2 * RPW * w + sub; // window row of this thread's first pair; later pairs add 2 per row pair
+	const int cc_first = 2 * p;            // window column of the pair; later pairs add 32 per column block
 
+	// guard rows are read by the ring cells of unmasked tiles: keep them finite
+	for (int k = tid; k < RX; k += NT) {
+		smem[k] = 0.f;
+		smem[(RY + 1) * RX + k] = 0.f;
+		smem[BUF + k] = 0.f;
+		smem[BUF + (RY + 1) * RX + k] = 0.f;
+	}
 	if (tid == 0) {
-		mbar_init(&bar, 1);
+		mbar_init(&bar[0], 1);
+		mbar_init(&bar[1], 1);
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
 	__syncthreads();
-	if (tid == 0) {
-		mbar_expect_tx(&bar, RY * RX * sizeof(float));
-		tma_load_3d(tile, &tm_in, XO + ci0, cj0, sim, &bar);
-	}
 
-	// --- x0 of this thread's cells, straight from global into registers ---
-	const long long off = (long long) sim * g.plane;
-	const float* x0 = x0b + off;
-	const int r_first = 2 * RPW * w + sub; // window row of this thread's first pair; later pairs add 2 per row pair
-	const int cc_first = 2 * p;            // window column of the pair; later pairs add 32 per column block
-	const int par = (tx0 + ty0 + r_first) & 1; // 0: the pair's first cell is red (i+j even)
-	float x0a[KB], x0c[KB];                // x0 of the cell updated in colour passes 0 / 1
-	uint32_t mask0 = 0, mask1 = 0;         // which of those cells are real interior cells inside the ring
+	// tile index -> ensemble member and window origin (interior index of window cell (0,0))
+	auto locate = [&](int t, int& sim, int& tx0, int& ty0) {
+		const int per = ntx * nty;
+		sim = t / per;
+		const int u = t - sim * per;
+		const int ty = u / ntx;
+		tx0 = (u - ty * ntx) * TX;
+		ty0 = ty * TY;
+	};
+	auto edge_tile = [&](int tx0, int ty0) { // window reaches a wall, or the tile is partial
+		return tx0 == 0 || ty0 == 0 || tx0 + TX + HX >= g.N || ty0 + TY + HY >= g.NY;
+	};
+	auto issue_tma = [&](int t, int buf) {
+		int sim, tx0, ty0;
+		locate(t, sim, tx0, ty0);
+		mbar_expect_tx(&bar[buf], RY * RX * sizeof(float));
+		tma_load_3d(smem + buf * BUF + RX, &tm_in, XO + 1 + tx0 - HX, 1 + ty0 - HY, sim, &bar[buf]);
+	};
+	auto fetch_x0 = [&](int t, float2 (&raw)[KB]) {
+		int sim, tx0, ty0;
+		locate(t, sim, tx0, ty0);
+		const float* x0 = x0b + (long long) sim * g.plane;
+		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
+		if (!edge_tile(tx0, ty0)) {
+			const float* p0 = x0 + cell(g, ci0 + cc_first, cj0 + r_first);
 #pragma unroll
-	for (int k = 0; k < KB; k++) {
-		const int r = r_first + 2 * (k / CB), cc = cc_first + 32 * (k % CB);
-		const int j = cj0 + r, i = ci0 + cc;
-		float2 v = make_float2(0.f, 0.f);
-		if (j >= 1 && j <= g.NY && i + 1 >= 1 && i <= g.N) v = __ldg(reinterpret_cast<const float2*>(x0 + cell(g, i, j)));
-		const bool rowok = (r >= 1 && r <= RY - 2 && j >= 1 && j <= g.NY);
-		const bool ok_first = rowok && cc >= 1 && i >= 1 && i <= g.N;
-		const bool ok_second = rowok && cc + 1 <= RX - 2 && i + 1 >= 1 && i + 1 <= g.N;
-		x0a[k] = par ? v.y : v.x;
-		x0c[k] = par ? v.x : v.y;
-		mask0 |= (uint32_t) (par ? ok_second : ok_first) << k;
-		mask1 |= (uint32_t) (par ? ok_first : ok_second) << k;
+			for (int k = 0; k < KB; k++) raw[k] = ldg_pair_early(p0 + (long long) (2 * (k / CB)) * g.pitch + 32 * (k % CB));
+		} else {
+#pragma unroll
+			for (int k = 0; k < KB; k++) {
+				const int j = cj0 + r_first + 2 * (k / CB), i = ci0 + cc_first + 32 * (k % CB);
+				raw[k] = make_float2(0.f, 0.f);
+				if (j >= 1 && j <= g.NY && i >= 1 && i <= g.N) raw[k] = ldg_pair_early(x0 + cell(g, i, j));
+			}
+		}
+	};
+
+	int t = blockIdx.x;
+	float2 x0[KB], x0n[KB];
+	if (t < ntiles) {
+		if (tid == 0) issue_tma(t, 0);
+		fetch_x0(t, x0);
 	}
-
-	// tiles that contain a wall-adjacent cell take the (block-uniform) slow path that maintains border cells
-	const bool wall = (b >= 0 && b <= 2) &&
-			  (tx0 == 0 || ty0 == 0 || tx0 + TX + HX >= g.N || ty0 + TY + HY >= g.NY);
-
-	mbar_wait(&bar, 0);
-
-	float* base = tile + r_first * RX + cc_first;
-	if (wall) rb_tile_sweeps<S, RX, CB, KB, true>(base, x0a, x0c, mask0, mask1, par, a, c, b, g, ci0 + cc_first, cj0 + r_first);
-	else rb_tile_sweeps<S, RX, CB, KB, false>(base, x0a, x0c, mask0, mask1, par, a, c, b, g, 0, 0);
-
-	// --- store the centre ---
-	float* xout = xoutb + off;
-	const bool full = (tx0 + TX <= g.N) && (ty0 + TY <= g.NY);
-	if (!wall && full) {
-		static_assert(TX % 4 == 0 && HX % 4 == 0, "float4 store path");
-		constexpr int PER_ROW = TX / 4;
-		for (int idx = tid; idx < TY * PER_ROW; idx += NT) {
-			const int r = idx / PER_ROW, cv = idx - r * PER_ROW;
-			const float* s = tile + (HY + r) * RX + HX + 4 * cv;
-			float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
-			*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(s);
+	for (int n = 0; t < ntiles; n++) {
+		const int buf = n & 1;
+		const int tn = t + gridDim.x;
+		if (tn < ntiles) {
+			// buffer buf^1 was last touched in iteration n-1, which ended with a proxy fence + __syncthreads
+			if (tid == 0) issue_tma(tn, buf ^ 1);
+			fetch_x0(tn, x0n);
 		}
-	} else {
-		for (int idx = tid; idx < TY * TX; idx += NT) {
-			const int r = idx / TX, cc = idx - r * TX;
-			const int i = tx0 + 1 + cc, j = ty0 + 1 + r;
-			if (i > g.N || j > g.NY) continue;
-			const float v = tile[(HY + r) * RX + HX + cc];
-			xout[cell(g, i, j)] = v;
-			mirror_border(g, xout, b, i, j, v);
+		int sim, tx0, ty0;
+		locate(t, sim, tx0, ty0);
+		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
+		const bool edge = edge_tile(tx0, ty0);
+		const bool wall = edge && (b >= 0 && b <= 2);
+		const int par = (tx0 + ty0 + r_first) & 1; // 0: the pair's first cell is red (i+j even)
+		if (par) {
+#pragma unroll
+			for (int k = 0; k < KB; k++) {
+				const float tmp = x0[k].x;
+				x0[k].x = x0[k].y;
+				x0[k].y = tmp;
+			}
 		}
+		float* tile = smem + buf * BUF + RX;
+		float* base = tile + r_first * RX + cc_first;
+
+		mbar_wait(&bar[buf], (n >> 1) & 1);
+
+		if (!edge) {
+			rb_tile_sweeps<S, RX, CB, KB, false, false>(base, x0, 0, 0, par, a, c, b, g, 0, 0);
+		} else {
+			uint32_t mask0 = 0, mask1 = 0; // real interior cells inside the ring, per colour
+#pragma unroll
+			for (int k = 0; k < KB; k++) {
+				const int r = r_first + 2 * (k / CB), cc = cc_first + 32 * (k % CB);
+				const int j = cj0 + r, i = ci0 + cc;
+				const bool rowok = (r >= 1 && r <= RY - 2 && j >= 1 && j <= g.NY);
+				const bool ok_first = rowok && cc >= 1 && i >= 1 && i <= g.N;
+				const bool ok_second = rowok && cc + 1 <= RX - 2 && i + 1 >= 1 && i + 1 <= g.N;
+				mask0 |= (uint32_t) (par ? ok_second : ok_first) << k;
+				mask1 |= (uint32_t) (par ? ok_first : ok_second) << k;
+			}
+			if (wall) rb_tile_sweeps<S, RX, CB, KB, true, true>(base, x0, mask0, mask1, par, a, c, b, g, ci0 + cc_first, cj0 + r_first);
+			else rb_tile_sweeps<S, RX, CB, KB, true, false>(base, x0, mask0, mask1, par, a, c, b, g, 0, 0);
+		}
+
+		// --- store the centre ---
+		float* xout = xoutb + (long long) sim * g.plane;
+		if (!edge) {
+			constexpr int PER_ROW = TX / 4;
+			for (int idx = tid; idx < TY * PER_ROW; idx += NT) {
+				const int r = idx / PER_ROW, cv = idx - r * PER_ROW;
+				const float* s = tile + (HY + r) * RX + HX + 4 * cv;
+				float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
+				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(s);
+			}
+		} else {
+			for (int idx = tid; idx < TY * TX; idx += NT) {
+				const int r = idx / TX, cc = idx - r * TX;
+				const int i = tx0 + 1 + cc, j = ty0 + 1 + r;
+				if (i > g.N || j > g.NY) continue;
+				const float v = tile[(HY + r) * RX + HX + cc];
+				xout[cell(g, i, j)] = v;
+				mirror_border(g, xout, b, i, j, v);
+			}
+		}
+		// order this thread's generic-proxy accesses to the buffer before the TMA write that refills it
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+		__syncthreads();
+#pragma unroll
+		for (int k = 0; k < KB; k++) x0[k] = x0n[k];
+		t = tn;
 	}
 }
 
