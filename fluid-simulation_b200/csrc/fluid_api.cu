@@ -175,7 +175,7 @@ static int dev_zero_bnd(fluid_ctx* c, float* x)
 }
 
 // ---- red-black tile path ---------------------------------------------------
-constexpr int kRbRY = 64, kRbRX = 256, kRbNT = 512;
+constexpr int kRbRY = 64, kRbRX = 256, kRbNT = 1024;
 constexpr size_t kRbSmem = 2 * (size_t) (kRbRY + 2) * kRbRX * sizeof(float); // double buffered
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,

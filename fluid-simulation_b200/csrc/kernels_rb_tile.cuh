@@ -167,27 +167,25 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	}
 	__syncthreads();
 
-	// tile index -> ensemble member and window origin (interior index of window cell (0,0))
-	auto locate = [&](int t, int& sim, int& tx0, int& ty0) {
-		const int per = ntx * nty;
-		sim = t / per;
-		const int u = t - sim * per;
-		const int ty = u / ntx;
-		tx0 = (u - ty * ntx) * TX;
-		ty0 = ty * TY;
+	// Tile coordinates (column, row, ensemble member) are advanced incrementally by
+	// gridDim.x tiles: integer division costs ~60 instructions per warp per use.
+	struct TilePos { int tx, ty, sim; };
+	auto advance = [&](TilePos p, int by) {
+		p.tx += by;
+		while (p.tx >= ntx) { p.tx -= ntx; p.ty++; }
+		while (p.ty >= nty) { p.ty -= nty; p.sim++; }
+		return p;
 	};
 	auto edge_tile = [&](int tx0, int ty0) { // window reaches a wall, or the tile is partial
 		return tx0 == 0 || ty0 == 0 || tx0 + TX + HX >= g.N || ty0 + TY + HY >= g.NY;
 	};
-	auto issue_tma = [&](int t, int buf) {
-		int sim, tx0, ty0;
-		locate(t, sim, tx0, ty0);
+	auto issue_tma = [&](TilePos tp, int buf) {
+		const int sim = tp.sim, tx0 = tp.tx * TX, ty0 = tp.ty * TY;
 		mbar_expect_tx(&bar[buf], RY * RX * sizeof(float));
 		tma_load_3d(smem + buf * BUF + RX, &tm_in, XO + 1 + tx0 - HX, 1 + ty0 - HY, sim, &bar[buf]);
 	};
-	auto fetch_x0 = [&](int t, float2 (&raw)[KB]) {
-		int sim, tx0, ty0;
-		locate(t, sim, tx0, ty0);
+	auto fetch_x0 = [&](TilePos tp, float2 (&raw)[KB]) {
+		const int sim = tp.sim, tx0 = tp.tx * TX, ty0 = tp.ty * TY;
 		const float* x0 = x0b + (long long) sim * g.plane;
 		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
 		if (!edge_tile(tx0, ty0)) {
@@ -204,22 +202,16 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		}
 	};
 
-	int t = blockIdx.x;
-	float2 x0[KB], x0n[KB];
-	if (t < ntiles) {
-		if (tid == 0) issue_tma(t, 0);
-		fetch_x0(t, x0);
-	}
-	for (int n = 0; t < ntiles; n++) {
+	// One loop iteration: relax tile t from buffer `buf` with the x0 values in `cur`
+	// (requested one iteration ago) while tile t + gridDim.x streams into the other
+	// buffer and into `nxt`.  The two register sets alternate roles (the loop below
+	// is unrolled by two) so that no value is copied: a copy, like any other use,
+	// would wait on the loads that have just been issued.  For the same reason
+	// `cur` is consumed (colour swap) BEFORE the next loads are issued -- loads that
+	// share a scoreboard slot with older ones would otherwise stall the first use.
+	auto iteration = [&](TilePos tp, TilePos tpn, bool has_next, int n, float2 (&cur)[KB], float2 (&nxt)[KB]) {
 		const int buf = n & 1;
-		const int tn = t + gridDim.x;
-		if (tn < ntiles) {
-			// buffer buf^1 was last touched in iteration n-1, which ended with a proxy fence + __syncthreads
-			if (tid == 0) issue_tma(tn, buf ^ 1);
-			fetch_x0(tn, x0n);
-		}
-		int sim, tx0, ty0;
-		locate(t, sim, tx0, ty0);
+		const int sim = tp.sim, tx0 = tp.tx * TX, ty0 = tp.ty * TY;
 		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
 		const bool edge = edge_tile(tx0, ty0);
 		const bool wall = edge && (b >= 0 && b <= 2);
@@ -227,10 +219,15 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		if (par) {
 #pragma unroll
 			for (int k = 0; k < KB; k++) {
-				const float tmp = x0[k].x;
-				x0[k].x = x0[k].y;
-				x0[k].y = tmp;
+				const float tmp = cur[k].x;
+				cur[k].x = cur[k].y;
+				cur[k].y = tmp;
 			}
+		}
+		if (has_next) {
+			// buffer buf^1 was last touched in iteration n-1, which ended with a proxy fence + __syncthreads
+			if (tid == 0) issue_tma(tpn, buf ^ 1);
+			fetch_x0(tpn, nxt);
 		}
 		float* tile = smem + buf * BUF + RX;
 		float* base = tile + r_first * RX + cc_first;
@@ -238,7 +235,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		mbar_wait(&bar[buf], (n >> 1) & 1);
 
 		if (!edge) {
-			rb_tile_sweeps<S, RX, CB, KB, false, false>(base, x0, 0, 0, par, a, c, b, g, 0, 0);
+			rb_tile_sweeps<S, RX, CB, KB, false, false>(base, cur, 0, 0, par, a, c, b, g, 0, 0);
 		} else {
 			uint32_t mask0 = 0, mask1 = 0; // real interior cells inside the ring, per colour
 #pragma unroll
@@ -251,8 +248,8 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 				mask0 |= (uint32_t) (par ? ok_second : ok_first) << k;
 				mask1 |= (uint32_t) (par ? ok_first : ok_second) << k;
 			}
-			if (wall) rb_tile_sweeps<S, RX, CB, KB, true, true>(base, x0, mask0, mask1, par, a, c, b, g, ci0 + cc_first, cj0 + r_first);
-			else rb_tile_sweeps<S, RX, CB, KB, true, false>(base, x0, mask0, mask1, par, a, c, b, g, 0, 0);
+			if (wall) rb_tile_sweeps<S, RX, CB, KB, true, true>(base, cur, mask0, mask1, par, a, c, b, g, ci0 + cc_first, cj0 + r_first);
+			else rb_tile_sweeps<S, RX, CB, KB, true, false>(base, cur, mask0, mask1, par, a, c, b, g, 0, 0);
 		}
 
 		// --- store the centre ---
@@ -278,9 +275,24 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		// order this thread's generic-proxy accesses to the buffer before the TMA write that refills it
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 		__syncthreads();
-#pragma unroll
-		for (int k = 0; k < KB; k++) x0[k] = x0n[k];
-		t = tn;
+	};
+
+	int t = blockIdx.x;
+	if (t >= ntiles) return;
+	TilePos tp = advance(TilePos{ 0, 0, 0 }, t);
+	float2 xa[KB], xb[KB];
+	if (tid == 0) issue_tma(tp, 0);
+	fetch_x0(tp, xa);
+#pragma unroll 1
+	for (int n = 0;; n += 2) {
+		TilePos tpn = advance(tp, gridDim.x);
+		iteration(tp, tpn, t + (int) gridDim.x < ntiles, n, xa, xb);
+		t += gridDim.x;
+		if (t >= ntiles) break;
+		tp = advance(tpn, gridDim.x);
+		iteration(tpn, tp, t + (int) gridDim.x < ntiles, n + 1, xb, xa);
+		t += gridDim.x;
+		if (t >= ntiles) break;
 	}
 }
 
