@@ -36,6 +36,7 @@ EXPORTS = [
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
+    "fluid_lin_solve_rb_static",
 ]
 
 
@@ -115,6 +116,7 @@ def lib():
     L.fluid_ctx_advect_velocity.argtypes = [_vp, _ci, _ci, _ci, _ci, _cf]
     L.fluid_ctx_project.argtypes = [_vp, _ci, _ci, _ci, _ci]
     L.fluid_ctx_time_kernel.argtypes = [_vp, _ci, _ci, ctypes.POINTER(_cf)]
+    L.fluid_lin_solve_rb_static.argtypes = [_ci, _ci, _vp, _vp, _cf, _cf, _ci, _vp]
     _lib = L
     return L
 

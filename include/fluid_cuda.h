@@ -227,6 +227,38 @@ typedef enum fluid_kernel_id {
 } fluid_kernel_id;
 int fluid_ctx_time_kernel(fluid_ctx *ctx, int which, int reps, float *ms);
 
+/* ---- for callers that must not allocate --------------------------------- *
+ * No counterpart in the reference (it owns all its memory as std::vector and *
+ * never allocates inside a step either).                                     *
+ *                                                                            *
+ * Red-black lin_solve (same sweeps, same results as fluid_lin_solve with     *
+ * FLUID_GS_REDBLACK) on DEVICE arrays you already own, without a single      *
+ * cudaMalloc/cudaFree: meant for real-time loops, plug-ins living inside a   *
+ * pre-sized arena, or processes whose GPU memory belongs to a pool allocator *
+ * -- places where a hidden allocation can fail late, stall the device, or is *
+ * simply forbidden.  The tile ping-pong scratch that a context would         *
+ * allocate is a fixed array compiled into the library (4.3 MiB resident on   *
+ * every GPU that loads it), hence the limit N <= FLUID_STATIC_MAX_N; larger  *
+ * N is refused with FLUID_ERR_INVALID.                                       *
+ *                                                                            *
+ * Layout of x_dev and x0_dev (16-byte aligned, on the current CUDA device):  *
+ * (N+2) rows of FLUID_STATIC_PITCH_OF(N) floats, cell (i,j) at               *
+ * j*pitch + FLUID_STATIC_XO + i; the other floats of a row are padding.      *
+ * x_dev is updated in place; x0_dev is only read.  `stream` is a             *
+ * cudaStream_t (NULL = default stream); the call only enqueues work.         *
+ *                                                                            *
+ * - The first call on each device looks up the array's device address and    *
+ *   raises the kernels' shared-memory limit; make that first call before any *
+ *   stream capture begins.                                                   *
+ * - All calls share the one array, and it keeps the previous call's data     *
+ *   (this function clears the part it is about to use).  Two calls whose GPU *
+ *   work can overlap -- different streams, different host threads -- race on *
+ *   it; keep them on one stream or serialise them yourself.                  */
+#define FLUID_STATIC_MAX_N 1024
+#define FLUID_STATIC_XO 31
+#define FLUID_STATIC_PITCH_OF(N) ((((N) + 2 + FLUID_STATIC_XO + 31) / 32) * 32)
+int fluid_lin_solve_rb_static(int N, int b, float *x_dev, const float *x0_dev, float a, float c, int iters, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
