@@ -233,14 +233,26 @@ def run_b200(args):
     order = fl.GS_REDBLACK if args.order == "redblack" else fl.GS_WAVEFRONT
     L = fl.lib()
 
-    fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local)
-    c = N // 2
-    fs.SetSources([(fl.DENS, c, c, fl.SRC_PREV_SET, 100.0), (fl.U, c, c, fl.SRC_PREV_SET, 5.0),
-                   (fl.V, c, c, fl.SRC_PREV_SET, 5.0)])
+    # N GPUs: row slabs of a global N x (N*world) grid, one slab of N rows per GPU (weak scaling, h = 1/N),
+    # halos over NCCL send/recv between neighbouring ranks (fluid_b200.slabs.NcclExchange)
+    transport = None
+    if world > 1:
+        if order != fl.GS_REDBLACK:
+            raise SystemExit("bench.py: row slabs need --order redblack")
+        from fluid_b200.slabs import NcclExchange
+        fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local, slab=(rank, world, N))
+        transport = NcclExchange(fs, rank, world, local)
+    else:
+        fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local)
+    c, cy = N // 2, (N * world) // 2
+    fs.SetSources([(fl.DENS, c, cy, fl.SRC_PREV_SET, 100.0), (fl.U, c, cy, fl.SRC_PREV_SET, 5.0),
+                   (fl.V, c, cy, fl.SRC_PREV_SET, 5.0)])
     # spin-up + warm-up (untimed)
     fs.Update(DT, max(args.warmup, 3))
     fs.Sync()
 
+    if transport is not None:
+        transport.calls = transport.bytes = 0
     sampler = ClockSampler(local)
     fs.SetProfiling(True)
     fs.Profile(reset=True)
@@ -254,6 +266,7 @@ def run_b200(args):
     wall_ms = 1e3 * (time.perf_counter() - t0)
     dev_ms = fs.LastStepMs()            # CUDA events on the launching stream, around exactly the K steps
     launches = int(L.fluid_launch_count())
+    xcalls, xbytes = (transport.calls, transport.bytes) if transport is not None else (0, 0)
     clocks = sampler.stop()
     prof = fs.Profile(reset=True)
     fs.SetProfiling(False)
@@ -285,7 +298,10 @@ def run_b200(args):
 
     e2e = None
     if not args.no_e2e:
-        e2e = measure_e2e(fl, np, N, order, max(1, min(args.steps, 5)), dist, local, world)
+        if world == 1:
+            e2e = measure_e2e(fl, np, N, order, max(1, min(args.steps, 5)), dist, local, world)
+        else:
+            e2e = measure_e2e_slabs(fl, fs, N, max(1, min(args.steps, 5)), dist, local, world)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_single()
@@ -300,7 +316,10 @@ def run_b200(args):
                                    "%s relaxation, source S1 (dens 100, u=v=5 at the centre cell each step)" % (N, args.order),
                        "N": N, "gs_order": args.order, "gs_iters": ITERS, "advect": "midpoint",
                        "l2": "inputs larger than L2 (six %.0f MB fields vs 126 MB L2), no explicit flush" % (4e-6 * (N + 2) ** 2),
-                       "parallelism": "1 GPU" if world == 1 else "%d independent N=%d simulations, one per GPU, no exchange" % (world, N)},
+                       "parallelism": "1 GPU" if world == 1 else
+                       "%d row slabs of %d rows (global grid %d x %d, h=1/%d), 48-row overlapped halos refreshed at 6 points per step "
+                       "over NCCL send/recv between neighbouring ranks (%d exchange calls, %.1f MB sent per rank per step, timed)"
+                       % (world, N, N, N * world, N, xcalls // args.steps, xbytes / args.steps / 1e6)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": roofline, "cpu_baseline": cpu,
         }
@@ -308,6 +327,37 @@ def run_b200(args):
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def measure_e2e_slabs(fl, fs, N, steps, dist, local, world):
+    """N GPUs: each rank uploads the rows it stores (u, v, dens; pinned host memory), advances one
+    step (halo exchanges included) and downloads them again, every step, through the context API."""
+    import torch
+    rows, _ = fs.LocalRows()
+    n = rows * (N + 2)
+    bufs = {}
+    for k in ("u", "v", "d"):
+        bufs[k], _ = fl.pinned_empty(n)
+        bufs[k][:] = 0
+    ids = {"u": fl.U, "v": fl.V, "d": fl.DENS}
+
+    def one():
+        for k in bufs:
+            fs.upload_local(ids[k], bufs[k])
+        fs.Update(DT, 1)
+        for k in bufs:
+            fs.download_local(ids[k], bufs[k])
+
+    one()
+    barrier_sync(dist, local)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    torch.cuda.synchronize(local)
+    dt = max_over_ranks(dist, local, time.perf_counter() - t0)
+    return {"value": float(N) * N * world * steps / dt, "unit": UNIT, "h2d_bytes_per_step": 3 * n * 4 * world,
+            "d2h_bytes_per_step": 3 * n * 4 * world, "steps": steps,
+            "api": "fluid_ctx_upload_local x3 + fluid_ctx_step + fluid_ctx_download_local x3 per rank (host pointers, pinned)"}
 
 
 def measure_e2e(fl, np, N, order, steps, dist, local, world):

@@ -87,6 +87,12 @@ struct fluid_ctx {
 	// red-black tile path: sweeps per tile residency (0 = one-colour-per-launch kernels), its
 	// ping-pong scratch field and the TMA descriptors of the arrays it has been asked to read
 	int num_sms = 148;
+	// row slab of a taller global grid (multi-GPU); slab_count == 1 means the whole grid is here
+	int slab_index = 0, slab_count = 1, slab_rows = 0, slab_halo = 0;
+	int own_lo = 1;            // local row of the first owned row
+	fluid_exchange_fn exchange = nullptr;
+	void* exchange_user = nullptr;
+	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int rb_tile_sweeps = 2;
 	float* rb_scratch = nullptr;
 	std::map<const float*, CUtensorMap> tmaps;
@@ -281,6 +287,8 @@ static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 1);
 		}
 	} else {
+		if (c->slab_count > 1)
+			return fail(FLUID_ERR_UNSUPPORTED, "the wavefront (reference-order) relaxation is a pipeline across slabs and is offered on one GPU only; use FLUID_GS_REDBLACK for row slabs");
 		constexpr int T = 64;
 		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
 		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
@@ -315,7 +323,7 @@ static int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const floa
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
-	LAUNCH(k_advect, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode);
+	LAUNCH(k_advect, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
 	return FLUID_OK;
 }
 
@@ -323,7 +331,7 @@ static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
-	LAUNCH(k_advect_velocity, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode);
+	LAUNCH(k_advect_velocity, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
 	return FLUID_OK;
 }
 
@@ -345,22 +353,49 @@ static int dev_project(fluid_ctx* c, float* u, float* v, float* p, float* div)
 // Diffuse1 (FluidSystem.cpp:810-814): a = dt*diff*N*N left to right in float.
 static inline float diffusion_a(const fluid_ctx* c, float coef, float dt) { return dt * coef * c->g.N * c->g.N; }
 
+// Halo exchange between row slabs.  The slabs overlap by slab_halo (+1) rows and every
+// kernel computes on all stored rows, so stale values creep in from the outer
+// halo edge by one row per stencil application; the fields named here are made
+// valid again over the full halo depth by asking the host's transport (NCCL
+// send/recv, peer copies ...) to refill the halo rows from the neighbours' owned
+// rows.  With a 48-row halo that is needed once per 20-sweep solve instead of
+// once per colour pass: 9 exchanges of ~3 MB per step instead of ~200 of 64 KB.
+static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> arrays)
+{
+	if (c->slab_count <= 1) return FLUID_OK;
+	if (!c->exchange) return fail(FLUID_ERR_INVALID, "this context is a row slab but no exchange callback is set (fluid_ctx_set_exchange)");
+	int ids[FLUID_FIELD_COUNT], n = 0;
+	for (const float* a : arrays)
+		for (int f = 0; f < FLUID_FIELD_COUNT; f++)
+			if (c->f[f] == a) ids[n++] = f;
+	ProfScope ps(c, FLUID_PROF_EXCHANGE);
+	CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
+	const int rc = c->exchange(c->exchange_user, n, ids);
+	if (rc != 0) return fail(FLUID_ERR_CUDA, "halo exchange callback failed with code %d", rc);
+	return FLUID_OK;
+}
+
 // VelStep1 (FluidSystem.cpp:354-376).  The four pointers are locals: the
 // reference's two Swap() calls per FlipFlopArr become local pointer swaps, so
 // the result lands in the arrays passed as u and v.
 static int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt)
 {
+	// slabs: u, v (and the source arrays, which every slab fills itself) are valid over the whole halo on entry
 	FL_TRY(dev_add_source2(c, u, u0, v, v0, dt));
 	std::swap(u, u0);
 	const float a = diffusion_a(c, visc, dt);
 	FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
 	std::swap(v, v0);
 	FL_TRY(dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a));
+	FL_TRY(halo_exchange(c, { u, v }));
 	FL_TRY(dev_project(c, u, v, u0, v0));
+	FL_TRY(halo_exchange(c, { u, v }));
 	std::swap(u, u0);
 	std::swap(v, v0);
 	FL_TRY(dev_advect_velocity(c, u, v, u0, v0, dt));
+	FL_TRY(halo_exchange(c, { u, v }));
 	FL_TRY(dev_project(c, u, v, u0, v0));
+	FL_TRY(halo_exchange(c, { u, v }));
 	return FLUID_OK;
 }
 
@@ -372,7 +407,9 @@ static int dev_dens_step(fluid_ctx* c, float* x, float* x0, const float* u, cons
 	const float a = diffusion_a(c, diff, dt);
 	FL_TRY(dev_blur(c, 0, x, x0, a, 1 + 4 * a));
 	std::swap(x, x0);
+	FL_TRY(halo_exchange(c, { x0 })); // 21 blur passes consumed 21 halo rows of the field advect samples
 	FL_TRY(dev_advect(c, 0, x, x0, u, v, dt));
+	FL_TRY(halo_exchange(c, { x }));
 	return FLUID_OK;
 }
 
@@ -446,7 +483,10 @@ static int dev_update(fluid_ctx* c, float dt)
 			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 		}
 	}
-	if (c->vorticity != 0.0f) FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
+	if (c->vorticity != 0.0f) {
+		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
+		FL_TRY(halo_exchange(c, { c->f[FLUID_U], c->f[FLUID_V] })); // three stencil phases consumed 3 halo rows
+	}
 	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], c->visc, dt));
 	FL_TRY(dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], c->diff, dt));
 	if (c->damp != 0.0f) {
@@ -559,6 +599,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& p : c->f) if (p) cudaFree(p);
 	for (auto& p : c->vscr) if (p) cudaFree(p);
 	if (c->rb_scratch) cudaFree(c->rb_scratch);
+	if (c->d_oob) cudaFree(c->d_oob);
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
@@ -580,6 +621,16 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	if (p->gs_order != FLUID_GS_WAVEFRONT && p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", p->gs_order);
 	if (p->advect_mode != FLUID_ADVECT_MIDPOINT && p->advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", p->advect_mode);
 	for (int r : p->reserved) if (r != 0) return fail(FLUID_ERR_INVALID, "reserved fields must be 0");
+	if (p->slab_count < 0 || (p->slab_count > 1 && (p->slab_index < 0 || p->slab_index >= p->slab_count)))
+		return fail(FLUID_ERR_INVALID, "slab_index=%d / slab_count=%d is not a valid slab", p->slab_index, p->slab_count);
+	if (p->slab_count > 1) {
+		const int halo = p->slab_halo > 0 ? p->slab_halo : 48;
+		if (halo < 44) return fail(FLUID_ERR_INVALID, "slab_halo=%d is too small: a projection consumes 42 halo rows (20 red-black sweeps + 2)", halo);
+		if (p->slab_rows < halo + 1) return fail(FLUID_ERR_INVALID, "slab_rows=%d must exceed the halo depth %d", p->slab_rows, halo);
+		if (p->batch != 1) return fail(FLUID_ERR_UNSUPPORTED, "row slabs and ensembles cannot be combined");
+		if (p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_UNSUPPORTED, "row slabs need FLUID_GS_REDBLACK (the reference order is a pipeline across slabs)");
+		if (p->gs_iters > 20) return fail(FLUID_ERR_UNSUPPORTED, "row slabs support gs_iters <= 20 (the halo is consumed at 2 rows per sweep)");
+	}
 
 	int ndev = 0;
 	cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -603,6 +654,22 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	c->damp = p->damp;
 	c->g.N = p->N;
 	c->g.NY = p->N;
+	c->g.j0 = 0;
+	c->g.NYG = p->N;
+	c->g.walls = 3;
+	if (p->slab_count > 1) {
+		// rank `slab_index` of `slab_count` owns `slab_rows` rows of a global N x (slab_rows*slab_count) grid
+		c->slab_index = p->slab_index;
+		c->slab_count = p->slab_count;
+		c->slab_rows = p->slab_rows;
+		c->slab_halo = p->slab_halo > 0 ? p->slab_halo : 48;
+		const bool lo_nb = c->slab_index > 0, hi_nb = c->slab_index < c->slab_count - 1;
+		c->g.NY = c->slab_rows + (lo_nb ? c->slab_halo : 0) + (hi_nb ? c->slab_halo : 0);
+		c->g.NYG = c->slab_rows * c->slab_count;
+		c->g.j0 = c->slab_index * c->slab_rows - (lo_nb ? c->slab_halo : 0);
+		c->g.walls = (lo_nb ? 0 : 1) | (hi_nb ? 0 : 2);
+		c->own_lo = lo_nb ? c->slab_halo + 1 : 1;
+	}
 	c->g.pitch = ((XO + p->N + 2 + 31) / 32) * 32;
 	c->g.plane = (long long) c->g.pitch * (c->g.NY + 2);
 	c->field_bytes = (size_t) c->g.plane * c->batch * sizeof(float);
@@ -625,6 +692,10 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 			if (e != cudaSuccess) rc = fail(FLUID_ERR_CUDA, "cudaMemset failed: %s", cudaGetErrorString(e));
 		}
 		if (rc != FLUID_OK) break;
+		if (cudaMalloc(&c->d_oob, sizeof(int)) != cudaSuccess || cudaMemsetAsync(c->d_oob, 0, sizeof(int), c->stream) != cudaSuccess) {
+			rc = fail(FLUID_ERR_NOMEM, "cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+			break;
+		}
 		c->src_dirty = true;
 		rc = sync_sources(c);
 		if (rc != FLUID_OK) break;
@@ -673,9 +744,10 @@ extern "C" int fluid_ctx_upload(fluid_ctx* c, int field, int sim, const float* h
 	FL_TRY(check_field(field));
 	if (!host) return fail(FLUID_ERR_INVALID, "null host pointer");
 	if (sim < 0 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range [0,%d)", sim, c->batch);
+	// slabs: `host` is the GLOBAL dense array; every stored row (halo included) is taken from it
 	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
-	CU_TRY(cudaMemcpy2DAsync(c->f[field] + (long long) sim * c->g.plane + XO, (size_t) c->g.pitch * sizeof(float), host, w, w,
-				 c->g.NY + 2, cudaMemcpyHostToDevice, c->stream));
+	CU_TRY(cudaMemcpy2DAsync(c->f[field] + (long long) sim * c->g.plane + XO, (size_t) c->g.pitch * sizeof(float),
+				 host + (size_t) c->g.j0 * (c->g.N + 2), w, w, c->g.NY + 2, cudaMemcpyHostToDevice, c->stream));
 	return FLUID_OK;
 }
 
@@ -685,10 +757,51 @@ extern "C" int fluid_ctx_download(fluid_ctx* c, int field, int sim, float* host)
 	FL_TRY(check_field(field));
 	if (!host) return fail(FLUID_ERR_INVALID, "null host pointer");
 	if (sim < 0 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range [0,%d)", sim, c->batch);
+	// slabs: `host` is the GLOBAL dense array; only the rows this slab owns (plus the wall rows) are written
 	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
-	CU_TRY(cudaMemcpy2DAsync(host, w, c->f[field] + (long long) sim * c->g.plane + XO, (size_t) c->g.pitch * sizeof(float), w,
-				 c->g.NY + 2, cudaMemcpyDeviceToHost, c->stream));
+	int lo = 0, n = c->g.NY + 2;
+	if (c->slab_count > 1) {
+		lo = (c->g.walls & 1) ? 0 : c->own_lo;
+		const int hi = (c->g.walls & 2) ? c->g.NY + 1 : c->own_lo + c->slab_rows - 1;
+		n = hi - lo + 1;
+	}
+	CU_TRY(cudaMemcpy2DAsync(host + (size_t) (c->g.j0 + lo) * (c->g.N + 2), w,
+				 c->f[field] + (long long) sim * c->g.plane + (long long) lo * c->g.pitch + XO,
+				 (size_t) c->g.pitch * sizeof(float), w, n, cudaMemcpyDeviceToHost, c->stream));
 	CU_TRY(cudaStreamSynchronize(c->stream));
+	return FLUID_OK;
+}
+
+// Slab-local transfers: `host` is a dense (N+2) x (NY_local+2) array of exactly the rows this
+// context stores (halo rows included); for a whole-grid context identical to upload/download.
+extern "C" int fluid_ctx_upload_local(fluid_ctx* c, int field, const float* host)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(field));
+	if (!host) return fail(FLUID_ERR_INVALID, "null host pointer");
+	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
+	CU_TRY(cudaMemcpy2DAsync(c->f[field] + XO, (size_t) c->g.pitch * sizeof(float), host, w, w, c->g.NY + 2, cudaMemcpyHostToDevice,
+				 c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_download_local(fluid_ctx* c, int field, float* host)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(field));
+	if (!host) return fail(FLUID_ERR_INVALID, "null host pointer");
+	const size_t w = (size_t) (c->g.N + 2) * sizeof(float);
+	CU_TRY(cudaMemcpy2DAsync(host, w, c->f[field] + XO, (size_t) c->g.pitch * sizeof(float), w, c->g.NY + 2, cudaMemcpyDeviceToHost,
+				 c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_local_rows(fluid_ctx* c, int* rows_stored, int* first_global_row)
+{
+	CHECK_CTX(c);
+	if (rows_stored) *rows_stored = c->g.NY + 2;
+	if (first_global_row) *first_global_row = c->g.j0;
 	return FLUID_OK;
 }
 
@@ -701,7 +814,7 @@ extern "C" int fluid_ctx_set_sources(fluid_ctx* c, int sim, int n, const fluid_s
 	for (int k = 0; k < n; k++) {
 		const fluid_source& s = src[k];
 		if (s.field < FLUID_U || s.field > FLUID_DENS) return fail(FLUID_ERR_INVALID, "source %d: field %d is not U, V or DENS", k, s.field);
-		if (s.i < 0 || s.i > c->g.N + 1 || s.j < 0 || s.j > c->g.NY + 1) return fail(FLUID_ERR_INVALID, "source %d: cell (%d,%d) outside the grid", k, s.i, s.j);
+		if (s.i < 0 || s.i > c->g.N + 1 || s.j < 0 || s.j > c->g.NYG + 1) return fail(FLUID_ERR_INVALID, "source %d: cell (%d,%d) outside the grid", k, s.i, s.j);
 		if (s.mode < FLUID_SRC_PREV_SET || s.mode > FLUID_SRC_CURR_SET) return fail(FLUID_ERR_INVALID, "source %d: unknown mode %d", k, s.mode);
 		v.push_back({ s.field, s.i, s.j, s.mode, s.value });
 	}
@@ -771,6 +884,48 @@ extern "C" int fluid_ctx_sync(fluid_ctx* c)
 	CHECK_CTX(c);
 	CU_TRY(cudaStreamSynchronize(c->stream));
 	CU_TRY(cudaGetLastError());
+	if (c->slab_count > 1) {
+		int oob = 0;
+		CU_TRY(cudaMemcpy(&oob, c->d_oob, sizeof(int), cudaMemcpyDeviceToHost));
+		if (oob) {
+			CU_TRY(cudaMemset(c->d_oob, 0, sizeof(int)));
+			return fail(FLUID_ERR_UNSUPPORTED, "advect: a backtrace reached rows that are not stored on this slab "
+							   "(dt*N*|v| exceeded the %d-row halo); results are invalid -- use a deeper slab_halo", c->slab_halo);
+		}
+	}
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_exchange(fluid_ctx* c, fluid_exchange_fn fn, void* user)
+{
+	CHECK_CTX(c);
+	c->exchange = fn;
+	c->exchange_user = user;
+	return FLUID_OK;
+}
+
+// Rows a transport must move for one field of a slab: (slab_halo + 1) whole rows of `pitch` floats each way.
+extern "C" int fluid_ctx_halo_regions(fluid_ctx* c, int field, float** send_down, float** recv_down, float** send_up, float** recv_up,
+				      size_t* count)
+{
+	CHECK_CTX(c);
+	FL_TRY(check_field(field));
+	if (!send_down || !recv_down || !send_up || !recv_up || !count) return fail(FLUID_ERR_INVALID, "null pointer");
+	*send_down = *recv_down = *send_up = *recv_up = nullptr;
+	*count = 0;
+	if (c->slab_count <= 1) return FLUID_OK;
+	const long long rows = c->slab_halo + 1, P = c->g.pitch;
+	*count = (size_t) (rows * P);
+	float* f = c->f[field];
+	if (!(c->g.walls & 1)) {
+		*recv_down = f;                                  // local rows 0 .. halo
+		*send_down = f + (long long) c->own_lo * P;      // my first halo+1 owned rows -> lower neighbour's upper halo
+	}
+	if (!(c->g.walls & 2)) {
+		const long long top = c->own_lo + c->slab_rows;  // first row above the owned ones
+		*recv_up = f + top * P;                          // local rows top .. top + halo  (= NY + 1)
+		*send_up = f + (top - rows) * P;                 // my last halo+1 owned rows -> upper neighbour's lower halo
+	}
 	return FLUID_OK;
 }
 
@@ -1194,6 +1349,9 @@ extern "C" int fluid_lin_solve_rb_static(int N, int b, float* x_dev, const float
 	g.NY = N;
 	g.pitch = ((XO + N + 2 + 31) / 32) * 32;
 	g.plane = (long long) g.pitch * (N + 2);
+	g.j0 = 0;
+	g.NYG = N;
+	g.walls = 3;
 	const int limit = a > 0 ? iters : 1;
 
 	if (limit >= 2 && b >= 0 && b <= 2) {

@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(256) k_set_bnd(GridDesc g, int b, float* __res
 		}
 		if (k <= g.N) {
 			const float lo = x[cell(g, k, 1)], hi = x[cell(g, k, g.NY)];
-			x[cell(g, k, 0)] = (b == 2) ? -lo : lo;
-			x[cell(g, k, g.NY + 1)] = (b == 2) ? -hi : hi;
+			if (g.walls & 1) x[cell(g, k, 0)] = (b == 2) ? -lo : lo;
+			if (g.walls & 2) x[cell(g, k, g.NY + 1)] = (b == 2) ? -hi : hi;
 		}
 	}
 	if (k == 1) {
@@ -97,10 +97,14 @@ __global__ void __launch_bounds__(256) k_set_bnd(GridDesc g, int b, float* __res
 			bN0 = x[cell(g, N, 0)];      bN11 = x[cell(g, N + 1, 1)];
 			bNM1 = x[cell(g, N, M + 1)]; bN1M = x[cell(g, N + 1, M)];
 		}
-		x[cell(g, 0, 0)] = 0.5f * (b10 + b01);
-		x[cell(g, 0, M + 1)] = 0.5f * (b1M1 + b0M);
-		x[cell(g, N + 1, 0)] = 0.5f * (bN0 + bN11);
-		x[cell(g, N + 1, M + 1)] = 0.5f * (bNM1 + bN1M);
+		if (g.walls & 1) {
+			x[cell(g, 0, 0)] = 0.5f * (b10 + b01);
+			x[cell(g, N + 1, 0)] = 0.5f * (bN0 + bN11);
+		}
+		if (g.walls & 2) {
+			x[cell(g, 0, M + 1)] = 0.5f * (b1M1 + b0M);
+			x[cell(g, N + 1, M + 1)] = 0.5f * (bNM1 + bN1M);
+		}
 	}
 }
 
@@ -109,8 +113,8 @@ __global__ void __launch_bounds__(256) k_zero_bnd(GridDesc g, float* __restrict_
 	float* x = xb + (long long) blockIdx.z * g.plane;
 	const int k = blockIdx.x * blockDim.x + threadIdx.x;
 	if (k <= g.N + 1) {
-		x[cell(g, k, 0)] = 0.0f;
-		x[cell(g, k, g.NY + 1)] = 0.0f;
+		if (g.walls & 1) x[cell(g, k, 0)] = 0.0f;
+		if (g.walls & 2) x[cell(g, k, g.NY + 1)] = 0.0f;
 	}
 	if (k <= g.NY + 1) {
 		x[cell(g, 0, k)] = 0.0f;
@@ -215,23 +219,32 @@ struct Bilin {
 	float s0, s1, t0, t1;
 };
 
-__device__ __forceinline__ Bilin bilin_calc(const GridDesc& g, float px, float py)
+// (px, py) are GLOBAL cell coordinates; the sampled rows are converted to local
+// ones at the end.  A sample whose rows are not stored on this slab (backtrace
+// longer than the halo) sets *oob and is clamped into the slab so that the access
+// stays legal; the host reports it as an error after the step.
+__device__ __forceinline__ Bilin bilin_calc(const GridDesc& g, float px, float py, int* oob)
 {
 	Bilin r;
 	if (px < 0.5f) px = 0.5f;
 	if (px > g.N + 0.5f) px = g.N + 0.5f;
 	int i0 = (int) px;
 	if (py < 0.5f) py = 0.5f;
-	if (py > g.NY + 0.5f) py = g.NY + 0.5f;
+	if (py > g.NYG + 0.5f) py = g.NYG + 0.5f;
 	int j0 = (int) py;
 	// a NaN coordinate makes the reference index out of bounds (undefined); keep the access in range
 	i0 = min(max(i0, 0), g.N);
-	j0 = min(max(j0, 0), g.NY);
+	j0 = min(max(j0, 0), g.NYG);
 	r.s1 = px - i0;
 	r.s0 = 1 - r.s1;
 	r.t1 = py - j0;
 	r.t0 = 1 - r.t1;
-	r.o00 = cell(g, i0, j0);
+	int jl = j0 - g.j0;
+	if (jl < 0 || jl > g.NY) {
+		if (oob) *oob = 1;
+		jl = min(max(jl, 0), g.NY);
+	}
+	r.o00 = cell(g, i0, jl);
 	return r;
 }
 
@@ -244,24 +257,26 @@ __device__ __forceinline__ float bilin_eval(const Bilin& c, const float* __restr
 
 // Backtraced sample position of cell (i,j): MidpointBackward (FluidSystem.h:185-206)
 // or EulerBack (FluidSystem.h:208-219).
+// (i, j) local; the returned position is in global coordinates.
 __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __restrict__ u, const float* __restrict__ v,
-					  int i, int j, float dtN, int mode, float& px, float& py)
+					  int i, int j, float dtN, int mode, float& px, float& py, int* oob)
 {
 	const long long id = cell(g, i, j);
 	const float uc = __ldg(u + id), vc = __ldg(v + id);
+	const int jg = j + g.j0;
 	if (mode == 1) {
 		px = i - dtN * uc;
-		py = j - dtN * vc;
+		py = jg - dtN * vc;
 	} else {
 		const float dirx = -dtN * uc;
 		const float diry = -dtN * vc;
 		const float mx = i + 0.5f * dirx;
-		const float my = j + 0.5f * diry;
-		const Bilin m = bilin_calc(g, mx, my);
+		const float my = jg + 0.5f * diry;
+		const Bilin m = bilin_calc(g, mx, my, oob);
 		const float vx = bilin_eval(m, u, g.pitch);
 		const float vy = bilin_eval(m, v, g.pitch);
 		px = i - dtN * vx;
-		py = j - dtN * vy;
+		py = jg - dtN * vy;
 	}
 }
 
@@ -271,15 +286,16 @@ __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __rest
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __restrict__ db, const float* __restrict__ d0b,
 						 const float* __restrict__ ub, const float* __restrict__ vb, float dtN,
-						 int mode)
+						 int mode, int* oob_flag, int own_lo, int own_hi)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
 	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
 	if (i > g.N || j > g.NY) return;
+	int* oob = (j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
 	float px, py;
-	backtrace(g, ub + off, vb + off, i, j, dtN, mode, px, py);
-	const Bilin c = bilin_calc(g, px, py);
+	backtrace(g, ub + off, vb + off, i, j, dtN, mode, px, py, oob);
+	const Bilin c = bilin_calc(g, px, py, oob);
 	const float val = bilin_eval(c, d0b + off, g.pitch);
 	float* d = db + off;
 	d[cell(g, i, j)] = val;
@@ -291,17 +307,18 @@ __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __rest
 // by one pass over (u0,v0): 16 B per cell instead of 2 x 12 B.
 __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
 							  const float* __restrict__ u0b, const float* __restrict__ v0b,
-							  float dtN, int mode)
+							  float dtN, int mode, int* oob_flag, int own_lo, int own_hi)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
 	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
 	if (i > g.N || j > g.NY) return;
+	int* oob = (j >= own_lo && j <= own_hi) ? oob_flag : nullptr;
 	const float* u0 = u0b + off;
 	const float* v0 = v0b + off;
 	float px, py;
-	backtrace(g, u0, v0, i, j, dtN, mode, px, py);
-	const Bilin c = bilin_calc(g, px, py);
+	backtrace(g, u0, v0, i, j, dtN, mode, px, py, oob);
+	const Bilin c = bilin_calc(g, px, py, oob);
 	const float un = bilin_eval(c, u0, g.pitch);
 	const float vn = bilin_eval(c, v0, g.pitch);
 	float* u = ub + off;
@@ -337,7 +354,9 @@ __global__ void k_apply_sources(GridDesc g, FieldPtrs f, const SourceDev* __rest
 	const long long off = (long long) sim * g.plane;
 	for (int k = first[sim]; k < first[sim + 1]; k++) {
 		const SourceDev e = src[k];
-		const long long id = off + cell(g, e.i, e.j);
+		const int jl = e.j - g.j0; // entries carry global rows; a slab applies those it stores (halo rows included)
+		if (jl < 0 || jl > g.NY + 1) continue;
+		const long long id = off + cell(g, e.i, jl);
 		if (e.mode == 0) f.prev[e.field][id] = e.value;
 		else if (e.mode == 1) f.cur[e.field][id] += e.value;
 		else f.cur[e.field][id] = e.value;

@@ -95,8 +95,8 @@ __device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB],
 				const float sx = (b == 1) ? -v : v, sy = (b == 2) ? -v : v;
 				if (i == 1) q[o - 1] = sx;
 				if (i == g.N) q[o + 1] = sx;
-				if (j == 1) q[o - RX] = sy;
-				if (j == g.NY) q[o + RX] = sy;
+				if (j == 1 && (g.walls & 1)) q[o - RX] = sy;
+				if (j == g.NY && (g.walls & 2)) q[o + RX] = sy;
 			}
 		}
 	}
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
 		const bool edge = edge_tile(tx0, ty0);
 		const bool wall = edge && (b >= 0 && b <= 2);
-		const int par = (tx0 + ty0 + r_first) & 1; // 0: the pair's first cell is red (i+j even)
+		const int par = (tx0 + ty0 + r_first + g.j0) & 1; // 0: the pair's first cell is red (i + global j even)
 		if (par) {
 #pragma unroll
 			for (int k = 0; k < KB; k++) {

@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(256) k_rb_half(GridDesc g, int b, float* __res
 	const float4 r0 = __ldg(reinterpret_cast<const float4*>(x0 + base));
 	const float xw = x[base - 1], xe = x[base + 4];
 	// lane l is updated when (i0 + l + j) has the active parity
-	const int first = (i0 + j + colour) & 1; // 0: lanes 0,2 ; 1: lanes 1,3
+	const int first = (i0 + j + g.j0 + colour) & 1; // 0: lanes 0,2 ; 1: lanes 1,3 (colour = parity of i + global j)
 	float vals[4] = { xc.x, xc.y, xc.z, xc.w };
 	if (first == 0) {
 		vals[0] = relax(r0.x, a, xw, xc.y, xs.x, xn.x, c);

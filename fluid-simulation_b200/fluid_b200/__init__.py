@@ -34,6 +34,8 @@ EXPORTS = [
     "fluid_ctx_download", "fluid_ctx_set_sources", "fluid_ctx_vel_step", "fluid_ctx_dens_step", "fluid_ctx_step",
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
+    "fluid_ctx_set_exchange", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
+    "fluid_ctx_local_rows",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
     "fluid_lin_solve_rb_static",
@@ -50,7 +52,8 @@ class Params(ctypes.Structure):
     _fields_ = [("N", ctypes.c_int), ("batch", ctypes.c_int), ("gs_iters", ctypes.c_int), ("gs_order", ctypes.c_int),
                 ("advect_mode", ctypes.c_int), ("device", ctypes.c_int), ("visc", ctypes.c_float),
                 ("diff", ctypes.c_float), ("vorticity", ctypes.c_float), ("damp", ctypes.c_float),
-                ("reserved", ctypes.c_int * 6)]
+                ("slab_index", ctypes.c_int), ("slab_count", ctypes.c_int), ("slab_rows", ctypes.c_int),
+                ("slab_halo", ctypes.c_int), ("reserved", ctypes.c_int * 2)]
 
 
 class Source(ctypes.Structure):
@@ -60,6 +63,8 @@ class Source(ctypes.Structure):
 
 _f32 = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
 _ci, _cf, _vp = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+
+EXCHANGE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int))
 
 _lib = None
 
@@ -106,6 +111,11 @@ def lib():
     L.fluid_ctx_set_modes.argtypes = [_vp, _ci, _ci, _ci]
     L.fluid_ctx_set_coeffs.argtypes = [_vp, _cf, _cf, _cf, _cf]
     L.fluid_ctx_set_tuning.argtypes = [_vp, _ci]
+    L.fluid_ctx_upload_local.argtypes = [_vp, _ci, _f32]
+    L.fluid_ctx_download_local.argtypes = [_vp, _ci, _f32]
+    L.fluid_ctx_local_rows.argtypes = [_vp, ctypes.POINTER(_ci), ctypes.POINTER(_ci)]
+    L.fluid_ctx_set_exchange.argtypes = [_vp, EXCHANGE_FN, _vp]
+    L.fluid_ctx_halo_regions.argtypes = [_vp, _ci] + [ctypes.POINTER(_vp)] * 4 + [ctypes.POINTER(ctypes.c_size_t)]
     L.fluid_ctx_set_profiling.argtypes = [_vp, _ci]
     L.fluid_ctx_profile.argtypes = [_vp, ctypes.POINTER(_cf), ctypes.POINTER(ctypes.c_ulonglong), _ci]
     L.fluid_ctx_add_source.argtypes = [_vp, _ci, _ci, _cf]
@@ -167,16 +177,52 @@ class FluidSystem:
         self.batch = 1
 
     def Setup(self, N, visc=0.0, diff=0.0, vorticity=0.0, damp=0.0, gs_order=GS_WAVEFRONT, gs_iters=20,
-              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1):
+              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1, slab=None, slab_halo=0):
+        """slab = (index, count, rows): this context is one row slab of a global N x (rows*count) grid."""
         self.close()
         p = Params()
         lib().fluid_params_default(ctypes.byref(p))
         p.N, p.batch, p.gs_iters, p.gs_order, p.advect_mode, p.device = N, batch, gs_iters, gs_order, advect_mode, device
         p.visc, p.diff, p.vorticity, p.damp = visc, diff, vorticity, damp
+        self.NYG = N
+        if slab is not None:
+            p.slab_index, p.slab_count, p.slab_rows = slab
+            p.slab_halo = slab_halo
+            self.NYG = slab[1] * slab[2]
         h = _vp()
         check(lib().fluid_ctx_create(ctypes.byref(p), ctypes.byref(h)))
         self.h, self.N, self.batch = h, N, batch
+        self._exchange_cb = None
         return self
+
+    def SetExchange(self, fn):
+        """fn(field_ids: list[int]) -> None is called at every halo exchange point (row slabs)."""
+        def thunk(_user, n, ids):
+            try:
+                fn([ids[k] for k in range(n)])
+                return 0
+            except Exception:  # never let an exception cross the C boundary
+                import traceback
+                traceback.print_exc()
+                return 1
+        self._exchange_cb = EXCHANGE_FN(thunk)  # keep a reference alive
+        check(lib().fluid_ctx_set_exchange(self.h, self._exchange_cb, None))
+
+    def LocalRows(self):
+        """(rows stored incl. halo and border rows, global row index of the first)."""
+        n, j0 = _ci(), _ci()
+        check(lib().fluid_ctx_local_rows(self.h, ctypes.byref(n), ctypes.byref(j0)))
+        return n.value, j0.value
+
+    def upload_local(self, field, host): check(lib().fluid_ctx_upload_local(self.h, field, host))
+    def download_local(self, field, host): check(lib().fluid_ctx_download_local(self.h, field, host))
+
+    def HaloRegions(self, field):
+        """(send_down, recv_down, send_up, recv_up, count_floats) device addresses (None where no neighbour)."""
+        p = [_vp() for _ in range(4)]
+        n = ctypes.c_size_t()
+        check(lib().fluid_ctx_halo_regions(self.h, field, *[ctypes.byref(q) for q in p], ctypes.byref(n)))
+        return tuple(q.value for q in p) + (n.value,)
 
     def close(self):
         if self.h:
@@ -217,7 +263,7 @@ class FluidSystem:
 
     def download(self, field, sim=0, out=None):
         if out is None:
-            out = np.empty((self.N + 2) ** 2, np.float32)
+            out = np.empty((self.N + 2) * (self.NYG + 2), np.float32)
         check(lib().fluid_ctx_download(self.h, field, sim, out))
         return out
 
@@ -227,14 +273,14 @@ class FluidSystem:
 
     def SetTuning(self, rb_tile_sweeps): check(lib().fluid_ctx_set_tuning(self.h, rb_tile_sweeps))
 
-    PROF_CLASSES = ("lin_solve", "blur", "advect", "project_aux", "add_source", "other")
+    PROF_CLASSES = ("lin_solve", "blur", "advect", "project_aux", "add_source", "other", "exchange")
 
     def SetProfiling(self, on=True): check(lib().fluid_ctx_set_profiling(self.h, 1 if on else 0))
 
     def Profile(self, reset=True):
         """{class: (ms, launches)} accumulated since the last reset."""
-        ms = (_cf * 6)()
-        n = (ctypes.c_ulonglong * 6)()
+        ms = (_cf * 7)()
+        n = (ctypes.c_ulonglong * 7)()
         check(lib().fluid_ctx_profile(self.h, ms, n, 1 if reset else 0))
         return {k: (ms[i], int(n[i])) for i, k in enumerate(self.PROF_CLASSES)}
 

@@ -1,0 +1,146 @@
+"""Host-side transports for row slabs (multi-GPU).
+
+The C library decides WHEN halos are exchanged (fluid_ctx_set_exchange); this
+module supplies HOW, twice:
+
+* ``NcclExchange``  -- one process per GPU (torchrun): torch.distributed
+  send/recv over NCCL/NVLink between neighbouring ranks.
+* ``LocalSlabGroup`` -- several slabs inside ONE process on one device, moved
+  with device copies.  It emulates the ranks (one host thread per slab, a
+  barrier at every exchange point) so that the decomposition can be tested on a
+  single GPU.
+
+``exchange_pairs`` is the pairing logic both share; it works on any torch
+tensors, so the CPU suite runs it with gloo and world_size 2.
+
+torch is plumbing here (process group, NCCL); no field arithmetic happens in Python.
+"""
+import threading
+
+from . import FluidSystem
+
+
+class _DeviceBlock:
+    """A device address range as something torch.as_tensor can wrap without copying."""
+
+    def __init__(self, ptr, nfloats):
+        self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (ptr, False), "version": 3}
+
+
+def device_tensor(ptr, nfloats, device):
+    import torch
+    return torch.as_tensor(_DeviceBlock(ptr, nfloats), device=device)
+
+
+def exchange_pairs(dist, rank, world, blocks):
+    """blocks: list of (send_down, recv_down, send_up, recv_up) tensors (None where there is
+    no neighbour), one tuple per field, in the same order on every rank.  Rank r's
+    send_up fills rank r+1's recv_down and vice versa.  Blocking."""
+    ops = []
+    for send_down, recv_down, send_up, recv_up in blocks:
+        if rank + 1 < world:
+            ops.append(dist.P2POp(dist.isend, send_up, rank + 1))
+            ops.append(dist.P2POp(dist.irecv, recv_up, rank + 1))
+        if rank > 0:
+            ops.append(dist.P2POp(dist.isend, send_down, rank - 1))
+            ops.append(dist.P2POp(dist.irecv, recv_down, rank - 1))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+
+
+class NcclExchange:
+    """Halo transport for one slab per process: torch.distributed (NCCL) send/recv."""
+
+    def __init__(self, fs, rank, world, device):
+        import torch
+        import torch.distributed as dist
+        self.fs, self.rank, self.world, self.dist, self.torch = fs, rank, world, dist, torch
+        self.device = torch.device("cuda", device)
+        self.cache = {}
+        self.calls = 0
+        self.bytes = 0
+        fs.SetExchange(self)
+
+    def _blocks(self, field):
+        if field not in self.cache:
+            sd, rd, su, ru, n = self.fs.HaloRegions(field)
+            self.cache[field] = tuple(device_tensor(p, n, self.device) if p else None for p in (sd, rd, su, ru))
+        return self.cache[field]
+
+    def __call__(self, fields):
+        blocks = [self._blocks(f) for f in fields]
+        exchange_pairs(self.dist, self.rank, self.world, blocks)
+        self.torch.cuda.synchronize(self.device)
+        self.calls += 1
+        self.bytes += sum(b.numel() * 4 for blk in blocks for b in (blk[0], blk[2]) if b is not None)
+
+
+class LocalSlabGroup:
+    """`count` slabs of `rows` rows each in one process on one device: the multi-GPU
+    code path on a single GPU.  Every slab steps in its own host thread (the
+    library's step call releases the GIL); exchange points are rendezvous."""
+
+    def __init__(self, N, count, rows, device=0, slab_halo=0, **setup):
+        import torch
+        self.torch = torch
+        self.N, self.count, self.rows = N, count, rows
+        self.device = torch.device("cuda", device)
+        self.slabs = [FluidSystem().Setup(N, device=device, slab=(k, count, rows), slab_halo=slab_halo, **setup)
+                      for k in range(count)]
+        self.barrier = threading.Barrier(count)
+        self.exchanges = 0
+        for k, fs in enumerate(self.slabs):
+            fs.SetExchange(lambda fields, k=k: self._exchange(k, fields))
+
+    def _exchange(self, k, fields):
+        self.barrier.wait()  # every slab's stream is idle and its owned rows are final
+        if k == 0:
+            for f in fields:
+                reg = [fs.HaloRegions(f) for fs in self.slabs]
+                for r in range(self.count - 1):
+                    n = reg[r][4]
+                    lower_send_up, lower_recv_up = reg[r][2], reg[r][3]
+                    upper_send_down, upper_recv_down = reg[r + 1][0], reg[r + 1][1]
+                    device_tensor(upper_recv_down, n, self.device).copy_(device_tensor(lower_send_up, n, self.device))
+                    device_tensor(lower_recv_up, n, self.device).copy_(device_tensor(upper_send_down, n, self.device))
+            self.torch.cuda.synchronize(self.device)
+            self.exchanges += 1
+        self.barrier.wait()
+
+    def SetSources(self, sources):
+        for fs in self.slabs:
+            fs.SetSources(sources)  # global coordinates; each slab keeps the entries it stores
+
+    def upload(self, field, host_global):
+        for fs in self.slabs:
+            fs.upload(field, host_global)
+
+    def download(self, field, out):
+        for fs in self.slabs:
+            fs.download(field, out=out)
+        return out
+
+    def Update(self, dt, nsteps=1):
+        errors = []
+
+        def run(fs):
+            try:
+                fs.Update(dt, nsteps)
+                fs.Sync()
+            except Exception as e:  # a failed slab must not leave the others waiting forever
+                errors.append(e)
+                self.barrier.abort()
+
+        threads = [threading.Thread(target=run, args=(fs,)) for fs in self.slabs]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        if errors:
+            self.barrier.reset()
+            raise errors[0]
+
+    def close(self):
+        for fs in self.slabs:
+            fs.close()

@@ -91,7 +91,12 @@ typedef struct fluid_params {
 	float diff;       /* FluidProps::Diff of the one fluid */
 	float vorticity;  /* 0 = confinement off (useVort=false) */
 	float damp;       /* 0 = no damping (reference default 0.1, FluidSystem.h:150) */
-	int reserved[6];  /* must be 0 */
+	/* Row slab of a taller grid (multi-GPU): this context stores rows
+	 * slab_index*slab_rows+1 .. (slab_index+1)*slab_rows of a global N x (slab_rows*slab_count)
+	 * grid, plus slab_halo halo rows towards each neighbour.  slab_count <= 1: whole grid. */
+	int slab_index, slab_count, slab_rows;
+	int slab_halo;    /* 0 = default 48 rows; >= 44 */
+	int reserved[2];  /* must be 0 */
 } fluid_params;
 
 typedef struct fluid_ctx fluid_ctx;
@@ -191,6 +196,32 @@ int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity
  * bit-identical for every setting; only the memory traffic differs. */
 int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
 
+/* ---- row slabs over several GPUs ---------------------------------------- *
+ * One context per GPU/process, each a slab (fluid_params.slab_*).  No          *
+ * counterpart in the reference (single process, single thread).  Slabs overlap *
+ * by slab_halo+1 rows and recompute the overlap, so halos are refreshed once    *
+ * per 20-sweep solve (9 times per step) rather than once per colour pass.  The  *
+ * library decides WHEN; the host supplies HOW: the callback must, for each      *
+ * listed field, move fluid_ctx_halo_regions()' send blocks into the             *
+ * neighbours' recv blocks (ncclSend/ncclRecv, cudaMemcpyPeer ...) and return 0   *
+ * only when this rank's recv blocks are complete.  The context's stream is      *
+ * idle when the callback runs.  upload/download take the GLOBAL dense array.    *
+ * Forcing entries use global rows.  FLUID_GS_REDBLACK only.                     */
+typedef int (*fluid_exchange_fn)(void *user, int nfields, const int *fields);
+int fluid_ctx_set_exchange(fluid_ctx *ctx, fluid_exchange_fn fn, void *user);
+/* Device pointers of the blocks to move for `field`; *count floats each; a
+ * pointer is NULL where there is no neighbour.  send_down -> lower neighbour's
+ * recv_up, send_up -> upper neighbour's recv_down. */
+int fluid_ctx_halo_regions(fluid_ctx *ctx, int field, float **send_down, float **recv_down, float **send_up, float **recv_up,
+			   size_t *count);
+
+/* Slab-local transfers: `host` holds exactly the rows this context stores (halo
+ * rows included), dense, (N+2) floats per row; fluid_ctx_local_rows tells how
+ * many rows that is and which global row the first one is. */
+int fluid_ctx_upload_local(fluid_ctx *ctx, int field, const float *host);
+int fluid_ctx_download_local(fluid_ctx *ctx, int field, float *host);
+int fluid_ctx_local_rows(fluid_ctx *ctx, int *rows_stored, int *first_global_row);
+
 /* Per-primitive device time inside fluid_ctx_step / vel_step / dens_step: when
  * on, every primitive is bracketed by a CUDA event pair on the context's
  * stream.  fluid_ctx_profile waits for the stream, then sums milliseconds and
@@ -204,7 +235,8 @@ typedef enum fluid_prof_class {
 	FLUID_PROF_PROJECT_AUX = 3, /* divergence + gradient subtraction */
 	FLUID_PROF_ADD_SOURCE = 4,
 	FLUID_PROF_OTHER = 5,       /* zero fill, forcing, vorticity, damp */
-	FLUID_PROF_COUNT = 6
+	FLUID_PROF_EXCHANGE = 6,    /* halo exchange between row slabs (includes the stream sync before it) */
+	FLUID_PROF_COUNT = 7
 } fluid_prof_class;
 int fluid_ctx_set_profiling(fluid_ctx *ctx, int on);
 int fluid_ctx_profile(fluid_ctx *ctx, float *ms, unsigned long long *launches, int reset);

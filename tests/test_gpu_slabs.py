@@ -1,0 +1,69 @@
+"""GPU suite: the multi-GPU row-slab path, exercised on ONE GPU by
+running every slab as its own context + host thread (fluid_b200.slabs.LocalSlabGroup;
+the exchange points, halo regions and kernels are exactly those a multi-process
+NCCL run uses).  Red-black results do not depend on the decomposition, so the
+assembled global fields must equal the CPU red-black statement bit for bit."""
+import numpy as np
+import pytest
+
+from conftest import assert_bits, rand_field
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("count,rows", [(2, 96), (3, 64), (4, 50)])
+def test_slabs_equal_single_domain_bitwise(fl, oracle, count, rows):
+    import oracle_py as op
+    from fluid_b200.slabs import LocalSlabGroup
+    N = count * rows  # square global grid so that the oracle can state it
+    steps = 3
+    rng = np.random.default_rng(count)
+    src = op.stam_sources(N) + [(2, 7, N - 3, 0, 50.0), (0, N - 5, 3, 0, -4.0), (1, 9, rows, 0, 3.0), (1, 10, rows + 1, 0, 3.0)]
+    init = {k: rand_field(rng, N, 0.5) for k in "u v d".split()}
+    f = {k: init[k].copy() for k in init}
+    f.update({k: np.zeros((N + 2) ** 2, np.float32) for k in "u0 v0 d0".split()})
+    oracle.update(N, f, src, 1e-4, 1e-4, 0.1, steps, order=op.GS_RB)
+
+    grp = LocalSlabGroup(N, count, rows, visc=1e-4, diff=1e-4, gs_order=fl.GS_REDBLACK)
+    try:
+        grp.SetSources(src)
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            grp.upload(fid, init[name])
+        grp.Update(0.1, steps)
+        assert grp.exchanges == 6 * steps  # 4 exchange points in vel_step (u,v), 2 in dens_step = 10 field transfers
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            out = np.full((N + 2) ** 2, np.nan, np.float32)
+            grp.download(fid, out)
+            assert_bits(out, f[name], "%d slabs of %d rows: %s" % (count, rows, name))
+    finally:
+        grp.close()
+
+
+def test_backtrace_longer_than_the_halo_is_reported(fl):
+    from fluid_b200.slabs import LocalSlabGroup
+    N, count, rows = 128, 2, 64
+    grp = LocalSlabGroup(N, count, rows, visc=0.0, diff=0.0, gs_order=fl.GS_REDBLACK)
+    try:
+        v = np.full((N + 2) ** 2, 60.0, np.float32)  # dt*N*v = 768 cells per step
+        grp.upload(fl.V, v)
+        with pytest.raises(fl.FluidError) as e:
+            grp.Update(0.1, 1)
+        assert "halo" in str(e.value)
+    finally:
+        grp.close()
+
+
+def test_slab_argument_checks(fl):
+    with pytest.raises(fl.FluidError):
+        fl.FluidSystem().Setup(128, gs_order=fl.GS_WAVEFRONT, slab=(0, 2, 64))  # reference order is a pipeline across slabs
+    with pytest.raises(fl.FluidError):
+        fl.FluidSystem().Setup(128, gs_order=fl.GS_REDBLACK, slab=(0, 2, 40))   # fewer rows than the halo
+    with pytest.raises(fl.FluidError):
+        fl.FluidSystem().Setup(128, gs_order=fl.GS_REDBLACK, slab=(2, 2, 64))   # index out of range
+    fs = fl.FluidSystem().Setup(128, gs_order=fl.GS_REDBLACK, slab=(1, 2, 64))
+    with pytest.raises(fl.FluidError) as e:
+        fs.Update(0.1, 1)  # no transport registered
+    assert "exchange" in str(e.value)
+    sd, rd, su, ru, n = fs.HaloRegions(fl.U)
+    assert su is None and ru is None and sd and rd and n == 49 * (((128 + 2 + 31 + 31) // 32) * 32)
+    fs.close()
