@@ -94,6 +94,10 @@ struct fluid_ctx {
 	void* exchange_user = nullptr;
 	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int rb_tile_sweeps = 2;
+	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
+	int fast_div_mode = 1; // 0 never, 1 when the solve is large enough to repay the 1.5 ms check, 2 always
+	std::map<uint32_t, DivC> divs;
+	unsigned int* d_divbins = nullptr;
 	float* rb_scratch = nullptr;
 	std::map<const float*, CUtensorMap> tmaps;
 	// optional per-kernel-class device timing (CUDA event pairs on c->stream)
@@ -181,8 +185,8 @@ static int dev_zero_bnd(fluid_ctx* c, float* x)
 }
 
 // ---- red-black tile path ---------------------------------------------------
-constexpr int kRbRY = 64, kRbRX = 256, kRbNT = 1024;
-constexpr size_t kRbSmem = 2 * (size_t) (kRbRY + 2) * kRbRX * sizeof(float); // double buffered
+constexpr int kRbRY = 64, kRbRX = 256, kRbNT = 512;
+constexpr size_t kRbSmem = (2 * (size_t) (kRbRY + 2) + kRbRY) * kRbRX * sizeof(float); // two x windows + x0 staging
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
 				  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -225,23 +229,57 @@ static int field_tmap(fluid_ctx* c, const float* base, const CUtensorMap** out)
 	return FLUID_OK;
 }
 
-template <int S>
-static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, float cc)
+// DivC for divisor cc: verified window if known / worth establishing, else range = 0 (callers use div.rn).
+static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 {
-	static bool configured = false; // per template instance; attribute is per-device-function, set once per process/device
-	auto kern = k_rb_tile<S, kRbRY, kRbRX, kRbNT>;
-	if (!configured) {
-		CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kRbSmem));
-		configured = true;
+	out->c = cc;
+	out->y = 1.0f / cc;
+	out->lo = 0;
+	out->range = 0;
+	if (!(cc > 0.0f) || !isfinite(cc) || !isfinite(out->y) || c->fast_div_mode == 0) return FLUID_OK;
+	uint32_t key;
+	memcpy(&key, &cc, sizeof key);
+	auto it = c->divs.find(key);
+	if (it != c->divs.end()) {
+		*out = it->second;
+		return FLUID_OK;
 	}
-	const CUtensorMap* tm;
+	if (c->fast_div_mode == 1 && cell_updates < 2.5e8) return FLUID_OK; // 2^31 trial divisions would cost more than they save
+	if (!c->d_divbins) CU_TRY(cudaMalloc(&c->d_divbins, 256 * sizeof(unsigned int)));
+	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), c->stream));
+	LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins);
+	unsigned int bins[256];
+	CU_TRY(cudaMemcpyAsync(bins, c->d_divbins, sizeof bins, cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	if (bins[127] == 0) {
+		int elo = 127, ehi = 127;
+		while (elo > 1 && bins[elo - 1] == 0) elo--;
+		while (ehi < 254 && bins[ehi + 1] == 0) ehi++;
+		out->lo = (uint32_t) elo << 23;
+		out->range = (uint32_t) (ehi - elo + 1) << 23;
+	}
+	c->divs[key] = *out;
+	return FLUID_OK;
+}
+
+template <int S>
+static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
+{
+	static bool configured[64] = {}; // per template instance and per device: function attributes are per device
+	auto kern = k_rb_tile<S, kRbRY, kRbRX, kRbNT>;
+	if (c->device >= 64 || !configured[c->device]) {
+		CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kRbSmem));
+		if (c->device < 64) configured[c->device] = true;
+	}
+	const CUtensorMap *tm, *tm0;
 	FL_TRY(field_tmap(c, in, &tm));
+	FL_TRY(field_tmap(c, x0, &tm0));
 	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 2 * (((2 * S + 3) / 4) * 4);
 	const int ntx = cdiv(c->g.N, TX), nty = cdiv(c->g.NY, TY);
 	const long long ntiles = (long long) ntx * nty * c->batch;
 	if (ntiles > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many tiles");
 	const int grid = (int) std::min<long long>(ntiles, c->num_sms); // persistent: one CTA per SM
-	LAUNCH(kern, grid, kRbNT, kRbSmem, c->stream, *tm, c->g, b, out, x0, a, cc, ntx, nty, (int) ntiles);
+	LAUNCH(kern, grid, kRbNT, kRbSmem, c->stream, *tm, *tm0, c->g, b, out, a, dv, ntx, nty, (int) ntiles);
 	return FLUID_OK;
 }
 
@@ -262,11 +300,13 @@ static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 		n2 = limit % 2; // an odd count needs one 2-sweep pass to make the number of passes even
 		n1 = limit - 2 * n2;
 	}
+	DivC dv;
+	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
 	const float* in = x;
 	float* out = c->rb_scratch;
 	for (int k = 0; k < n2 + n1; k++) {
-		if (k < n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, cc));
-		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, cc));
+		if (k < n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv));
+		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv));
 		float* t = const_cast<float*>(in);
 		in = out;
 		out = t;
@@ -600,6 +640,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& p : c->vscr) if (p) cudaFree(p);
 	if (c->rb_scratch) cudaFree(c->rb_scratch);
 	if (c->d_oob) cudaFree(c->d_oob);
+	if (c->d_divbins) cudaFree(c->d_divbins);
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
@@ -842,6 +883,35 @@ extern "C" int fluid_ctx_set_tuning(fluid_ctx* c, int rb_tile_sweeps)
 	CHECK_CTX(c);
 	if (rb_tile_sweeps < 0 || rb_tile_sweeps > 2) return fail(FLUID_ERR_INVALID, "rb_tile_sweeps=%d must be 0, 1 or 2", rb_tile_sweeps);
 	c->rb_tile_sweeps = rb_tile_sweeps;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_fast_division(fluid_ctx* c, int mode)
+{
+	CHECK_CTX(c);
+	if (mode < 0 || mode > 2) return fail(FLUID_ERR_INVALID, "fast division mode %d must be 0 (never), 1 (auto) or 2 (always)", mode);
+	c->fast_div_mode = mode;
+	return FLUID_OK;
+}
+
+// Exponent window [2^lo_exp, 2^(hi_exp+1)) of dividends for which the short division by `divisor` was proven exact.
+extern "C" int fluid_ctx_division_window(fluid_ctx* c, float divisor, int* lo_exp, int* hi_exp)
+{
+	CHECK_CTX(c);
+	if (!lo_exp || !hi_exp) return fail(FLUID_ERR_INVALID, "null pointer");
+	const int keep = c->fast_div_mode;
+	c->fast_div_mode = 2;
+	DivC dv;
+	const int rc = division_for(c, divisor, 0, &dv);
+	c->fast_div_mode = keep;
+	FL_TRY(rc);
+	if (dv.range == 0) {
+		*lo_exp = 0;
+		*hi_exp = -1;
+	} else {
+		*lo_exp = (int) (dv.lo >> 23) - 127;
+		*hi_exp = (int) ((dv.lo + dv.range) >> 23) - 128;
+	}
 	return FLUID_OK;
 }
 
@@ -1319,13 +1389,17 @@ static int encode_static_tmap(const float* base, const GridDesc& g, CUtensorMap*
 }
 
 template <int S>
-static void static_tile_pass(const StaticSetup* st, const GridDesc& g, int b, const CUtensorMap& tm_in, float* out, const float* x0,
-			     float a, float cc, cudaStream_t stream)
+static void static_tile_pass(const StaticSetup* st, const GridDesc& g, int b, const CUtensorMap& tm_in, float* out,
+			     const CUtensorMap& tm_x0, float a, float cc, cudaStream_t stream)
 {
 	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 2 * (((2 * S + 3) / 4) * 4);
 	const int ntx = cdiv(g.N, TX), nty = cdiv(g.NY, TY), ntiles = ntx * nty;
-	LAUNCH((k_rb_tile<S, kRbRY, kRbRX, kRbNT>), std::min(ntiles, st->num_sms), kRbNT, kRbSmem, stream, tm_in, g, b, out, x0, a, cc,
-	       ntx, nty, ntiles);
+	DivC dv; // plain IEEE division: establishing a verified window would need a device buffer
+	dv.c = cc;
+	dv.y = 0.0f;
+	dv.lo = dv.range = 0;
+	LAUNCH((k_rb_tile<S, kRbRY, kRbRX, kRbNT>), std::min(ntiles, st->num_sms), kRbNT, kRbSmem, stream, tm_in, tm_x0, g, b, out, a,
+	       dv, ntx, nty, ntiles);
 }
 
 extern "C" int fluid_lin_solve_rb_static(int N, int b, float* x_dev, const float* x0_dev, float a, float cc, int iters, void* stream_)
@@ -1359,17 +1433,18 @@ extern "C" int fluid_lin_solve_rb_static(int N, int b, float* x_dev, const float
 		// every cell they later read, but the pad columns would keep stale values; start from zeros
 		// like a freshly created context does.
 		CU_TRY(cudaMemsetAsync(st->scratch, 0, (size_t) g.plane * sizeof(float), stream));
-		CUtensorMap tm_x, tm_s;
+		CUtensorMap tm_x, tm_s, tm_0;
 		FL_TRY(encode_static_tmap(x_dev, g, &tm_x));
 		FL_TRY(encode_static_tmap(st->scratch, g, &tm_s));
+		FL_TRY(encode_static_tmap(x0_dev, g, &tm_0));
 		int n2 = limit / 2, n1 = limit % 2; // passes of two sweeps and of one; their number must be even
 		if ((n2 + n1) % 2) { n2 -= 1; n1 += 2; }
 		bool in_is_x = true;
 		for (int k = 0; k < n2 + n1; k++) {
 			const CUtensorMap& tm = in_is_x ? tm_x : tm_s;
 			float* out = in_is_x ? st->scratch : x_dev;
-			if (k < n2) static_tile_pass<2>(st, g, b, tm, out, x0_dev, a, cc, stream);
-			else static_tile_pass<1>(st, g, b, tm, out, x0_dev, a, cc, stream);
+			if (k < n2) static_tile_pass<2>(st, g, b, tm, out, tm_0, a, cc, stream);
+			else static_tile_pass<1>(st, g, b, tm, out, tm_0, a, cc, stream);
 			in_is_x = !in_is_x;
 		}
 	} else {

@@ -62,16 +62,6 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, i
 		: "memory");
 }
 
-// x0 of one cell pair, issued early and consumed a whole tile later.  Volatile so
-// that the compiler keeps the load where it is written (ahead of the compute of
-// the previous tile) instead of sinking it to its first use.
-__device__ __forceinline__ float2 ldg_pair_early(const float* p)
-{
-	float2 v;
-	asm volatile("ld.global.nc.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
-	return v;
-}
-
 // One colour pass over the KB cells of that colour this thread owns.
 // q points at the thread's first cell of the active colour.  MASKED: only cells
 // whose bit is set in m are real interior cells away from the window ring.
@@ -80,8 +70,20 @@ __device__ __forceinline__ float2 ldg_pair_early(const float* p)
 // and is read by no other.
 template <int RX, int CB, int KB, bool MASKED, bool WALL, bool SECOND>
 __device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB], uint32_t m, float a, float c, int b,
-					       const GridDesc& g, int i_first, int j_first)
+					       const GridDesc& g, int i_first, int j_first, const DivC& dv)
 {
+	if (!MASKED && dv.range != 0) {
+		// verified short division; a warp that meets a dividend outside the verified window (subnormal
+		// fringe of the field, overflow) redoes its cells exactly -- the inputs are the other colour's
+		// cells and x0, which this pass does not modify.
+		bool bad = false;
+#pragma unroll
+		for (int k = 0; k < KB; k++) {
+			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
+			q[o] = relax_fast(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], dv, bad);
+		}
+		if (!bad) return;
+	}
 #pragma unroll
 	for (int k = 0; k < KB; k++) {
 		const int o = 2 * (k / CB) * RX + 32 * (k % CB);
@@ -104,36 +106,42 @@ __device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB],
 
 template <int S, int RX, int CB, int KB, bool MASKED, bool WALL>
 __device__ __forceinline__ void rb_tile_sweeps(float* base, const float2 (&x0)[KB], uint32_t mask0, uint32_t mask1, int par,
-					       float a, float c, int b, const GridDesc& g, int i_first, int j_first)
+					       float a, float c, int b, const GridDesc& g, int i_first, int j_first,
+					       const DivC& dv)
 {
 	// after the conditional swap in the caller x0[k].x belongs to the red cell of pair k, .y to the black one
 	float* q0 = base + par;       // red cell (i+j even) of each pair
 	float* q1 = base + (par ^ 1); // black cell
 #pragma unroll 1
 	for (int s = 0; s < S; s++) {
-		rb_colour_pass<RX, CB, KB, MASKED, WALL, false>(q0, x0, mask0, a, c, b, g, i_first + par, j_first);
+		rb_colour_pass<RX, CB, KB, MASKED, WALL, false>(q0, x0, mask0, a, c, b, g, i_first + par, j_first, dv);
 		__syncthreads();
-		rb_colour_pass<RX, CB, KB, MASKED, WALL, true>(q1, x0, mask1, a, c, b, g, i_first + (par ^ 1), j_first);
+		rb_colour_pass<RX, CB, KB, MASKED, WALL, true>(q1, x0, mask1, a, c, b, g, i_first + (par ^ 1), j_first, dv);
 		__syncthreads();
 	}
 }
 
 // Persistent kernel: one CTA per SM walks over tiles t = blockIdx.x, +gridDim.x, ...
 // While the CTA relaxes tile n in one shared-memory buffer, the TMA engine fills
-// the other buffer with tile n+1 and the x0 values of tile n+1 are already on
-// their way into registers, so HBM latency is hidden behind the arithmetic
-// instead of being paid at the start of every CTA (ncu on the non-persistent
-// version: long-scoreboard stalls 6 of 11 cycles per issue, DRAM at 35 %).
+// the other x buffer and the x0 staging buffer with tile n+1, so HBM latency is
+// hidden behind the arithmetic instead of being paid at the start of every CTA
+// (ncu on the non-persistent version: long-scoreboard stalls 6 of 11 cycles per
+// issue, DRAM at 35 %).  x0 of the thread's own cells is copied from the staging
+// buffer into registers at the start of a tile, which frees the staging buffer
+// for the next TMA at once and keeps the register budget for the relaxation loop
+// (an earlier version prefetched x0 with ld.global into a second register set:
+// 64 pinned registers, spills inside the hot loop, two copies of the loop body).
 //
 // S sweeps per residency; window RY x RX floats (vertical halo 2S, horizontal
 // halo padded to 4: the global start address of a TMA box must be 16-byte
 // aligned).  RX % 32 == 0 so that rows r and r+1 of a 32-column block sit in the
 // same banks and the two half-warps, which work on opposite colours' columns,
 // never collide.  NT threads, each owning KB = RY*RX/(2*NT) adjacent cell pairs.
+// Shared memory: 2 x (RY+2) x RX (x, one guard row above and below) + RY x RX (x0).
 template <int S, int RY, int RX, int NT>
-__global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUtensorMap tm_in, GridDesc g, int b,
-						    float* __restrict__ xoutb, const float* __restrict__ x0b, float a,
-						    float c, int ntx, int nty, int ntiles)
+__global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUtensorMap tm_in,
+						    const __grid_constant__ CUtensorMap tm_x0, GridDesc g, int b,
+						    float* __restrict__ xoutb, float a, DivC dv, int ntx, int nty, int ntiles)
 {
 	constexpr int HY = 2 * S, HX = ((2 * S + 3) / 4) * 4, TY = RY - 2 * HY, TX = RX - 2 * HX;
 	constexpr int CB = RX / 32;               // 32-column blocks per window row
@@ -145,9 +153,11 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	static_assert(TX % 4 == 0 && HX % 4 == 0, "float4 store path");
 	constexpr int RPW = KB / CB;              // row pairs per warp
 	constexpr int BUF = (RY + 2) * RX;        // one guard row above and below each window
+	const float c = dv.c;
 
-	extern __shared__ __align__(128) float smem[]; // two buffers of BUF floats
-	__shared__ __align__(8) uint64_t bar[2];
+	extern __shared__ __align__(128) float smem[]; // [2][BUF] x windows, then [RY*RX] x0 staging
+	__shared__ __align__(8) uint64_t bar[3];       // x buffer 0, x buffer 1, x0 staging
+	float* x0s = smem + 2 * BUF;
 
 	const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, sub = lane >> 4, p = lane & 15;
 	const int r_first = 2 * RPW * w + sub; // window row of this thread's first pair; later pairs add 2 per row pair
@@ -163,6 +173,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	if (tid == 0) {
 		mbar_init(&bar[0], 1);
 		mbar_init(&bar[1], 1);
+		mbar_init(&bar[2], 1);
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
 	__syncthreads();
@@ -170,72 +181,58 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	// Tile coordinates (column, row, ensemble member) are advanced incrementally by
 	// gridDim.x tiles: integer division costs ~60 instructions per warp per use.
 	struct TilePos { int tx, ty, sim; };
-	auto advance = [&](TilePos p, int by) {
-		p.tx += by;
-		while (p.tx >= ntx) { p.tx -= ntx; p.ty++; }
-		while (p.ty >= nty) { p.ty -= nty; p.sim++; }
-		return p;
+	auto advance = [&](TilePos q, int by) {
+		q.tx += by;
+		while (q.tx >= ntx) { q.tx -= ntx; q.ty++; }
+		while (q.ty >= nty) { q.ty -= nty; q.sim++; }
+		return q;
 	};
 	auto edge_tile = [&](int tx0, int ty0) { // window reaches a wall, or the tile is partial
 		return tx0 == 0 || ty0 == 0 || tx0 + TX + HX >= g.N || ty0 + TY + HY >= g.NY;
 	};
+	// both boxes of a tile: same window, one from x (into x buffer `buf`), one from x0 (staging)
 	auto issue_tma = [&](TilePos tp, int buf) {
-		const int sim = tp.sim, tx0 = tp.tx * TX, ty0 = tp.ty * TY;
+		const int cx = XO + 1 + tp.tx * TX - HX, cy = 1 + tp.ty * TY - HY;
 		mbar_expect_tx(&bar[buf], RY * RX * sizeof(float));
-		tma_load_3d(smem + buf * BUF + RX, &tm_in, XO + 1 + tx0 - HX, 1 + ty0 - HY, sim, &bar[buf]);
-	};
-	auto fetch_x0 = [&](TilePos tp, float2 (&raw)[KB]) {
-		const int sim = tp.sim, tx0 = tp.tx * TX, ty0 = tp.ty * TY;
-		const float* x0 = x0b + (long long) sim * g.plane;
-		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
-		if (!edge_tile(tx0, ty0)) {
-			const float* p0 = x0 + cell(g, ci0 + cc_first, cj0 + r_first);
-#pragma unroll
-			for (int k = 0; k < KB; k++) raw[k] = ldg_pair_early(p0 + (long long) (2 * (k / CB)) * g.pitch + 32 * (k % CB));
-		} else {
-#pragma unroll
-			for (int k = 0; k < KB; k++) {
-				const int j = cj0 + r_first + 2 * (k / CB), i = ci0 + cc_first + 32 * (k % CB);
-				raw[k] = make_float2(0.f, 0.f);
-				if (j >= 1 && j <= g.NY && i >= 1 && i <= g.N) raw[k] = ldg_pair_early(x0 + cell(g, i, j));
-			}
-		}
+		tma_load_3d(smem + buf * BUF + RX, &tm_in, cx, cy, tp.sim, &bar[buf]);
+		mbar_expect_tx(&bar[2], RY * RX * sizeof(float));
+		tma_load_3d(x0s, &tm_x0, cx, cy, tp.sim, &bar[2]);
 	};
 
-	// One loop iteration: relax tile t from buffer `buf` with the x0 values in `cur`
-	// (requested one iteration ago) while tile t + gridDim.x streams into the other
-	// buffer and into `nxt`.  The two register sets alternate roles (the loop below
-	// is unrolled by two) so that no value is copied: a copy, like any other use,
-	// would wait on the loads that have just been issued.  For the same reason
-	// `cur` is consumed (colour swap) BEFORE the next loads are issued -- loads that
-	// share a scoreboard slot with older ones would otherwise stall the first use.
-	auto iteration = [&](TilePos tp, TilePos tpn, bool has_next, int n, float2 (&cur)[KB], float2 (&nxt)[KB]) {
+	int t = blockIdx.x;
+	if (t >= ntiles) return;
+	TilePos tp = advance(TilePos{ 0, 0, 0 }, t);
+	if (tid == 0) issue_tma(tp, 0);
+
+#pragma unroll 1
+	for (int n = 0; t < ntiles; n++, t += gridDim.x) {
 		const int buf = n & 1;
-		const int sim = tp.sim, tx0 = tp.tx * TX, ty0 = tp.ty * TY;
-		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;
+		const int tx0 = tp.tx * TX, ty0 = tp.ty * TY, sim = tp.sim;
+		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;   // interior index of window cell (0,0)
 		const bool edge = edge_tile(tx0, ty0);
 		const bool wall = edge && (b >= 0 && b <= 2);
-		const int par = (tx0 + ty0 + r_first + g.j0) & 1; // 0: the pair's first cell is red (i + global j even)
-		if (par) {
-#pragma unroll
-			for (int k = 0; k < KB; k++) {
-				const float tmp = cur[k].x;
-				cur[k].x = cur[k].y;
-				cur[k].y = tmp;
-			}
-		}
-		if (has_next) {
-			// buffer buf^1 was last touched in iteration n-1, which ended with a proxy fence + __syncthreads
-			if (tid == 0) issue_tma(tpn, buf ^ 1);
-			fetch_x0(tpn, nxt);
-		}
+		const int par = (tx0 + ty0 + r_first + g.j0) & 1;   // 0: the pair's first cell is red (i + global j even)
 		float* tile = smem + buf * BUF + RX;
 		float* base = tile + r_first * RX + cc_first;
+
+		// x0 of this thread's cells: staging buffer -> registers; .x = red cell, .y = black cell
+		mbar_wait(&bar[2], n & 1);
+		float2 x0[KB];
+#pragma unroll
+		for (int k = 0; k < KB; k++) {
+			const float2 v = *reinterpret_cast<const float2*>(x0s + (r_first + 2 * (k / CB)) * RX + cc_first + 32 * (k % CB));
+			x0[k] = par ? make_float2(v.y, v.x) : v;
+		}
+		// staging buffer and the other x buffer (stored from in iteration n-1) are free: refill them
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+		__syncthreads();
+		const TilePos tpn = advance(tp, gridDim.x);
+		if (tid == 0 && t + (int) gridDim.x < ntiles) issue_tma(tpn, buf ^ 1);
 
 		mbar_wait(&bar[buf], (n >> 1) & 1);
 
 		if (!edge) {
-			rb_tile_sweeps<S, RX, CB, KB, false, false>(base, cur, 0, 0, par, a, c, b, g, 0, 0);
+			rb_tile_sweeps<S, RX, CB, KB, false, false>(base, x0, 0, 0, par, a, c, b, g, 0, 0, dv);
 		} else {
 			uint32_t mask0 = 0, mask1 = 0; // real interior cells inside the ring, per colour
 #pragma unroll
@@ -248,8 +245,8 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 				mask0 |= (uint32_t) (par ? ok_second : ok_first) << k;
 				mask1 |= (uint32_t) (par ? ok_first : ok_second) << k;
 			}
-			if (wall) rb_tile_sweeps<S, RX, CB, KB, true, true>(base, cur, mask0, mask1, par, a, c, b, g, ci0 + cc_first, cj0 + r_first);
-			else rb_tile_sweeps<S, RX, CB, KB, true, false>(base, cur, mask0, mask1, par, a, c, b, g, 0, 0);
+			if (wall) rb_tile_sweeps<S, RX, CB, KB, true, true>(base, x0, mask0, mask1, par, a, c, b, g, ci0 + cc_first, cj0 + r_first, dv);
+			else rb_tile_sweeps<S, RX, CB, KB, true, false>(base, x0, mask0, mask1, par, a, c, b, g, 0, 0, dv);
 		}
 
 		// --- store the centre ---
@@ -258,9 +255,9 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 			constexpr int PER_ROW = TX / 4;
 			for (int idx = tid; idx < TY * PER_ROW; idx += NT) {
 				const int r = idx / PER_ROW, cv = idx - r * PER_ROW;
-				const float* s = tile + (HY + r) * RX + HX + 4 * cv;
+				const float* sp = tile + (HY + r) * RX + HX + 4 * cv;
 				float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
-				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(s);
+				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(sp);
 			}
 		} else {
 			for (int idx = tid; idx < TY * TX; idx += NT) {
@@ -275,24 +272,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		// order this thread's generic-proxy accesses to the buffer before the TMA write that refills it
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 		__syncthreads();
-	};
-
-	int t = blockIdx.x;
-	if (t >= ntiles) return;
-	TilePos tp = advance(TilePos{ 0, 0, 0 }, t);
-	float2 xa[KB], xb[KB];
-	if (tid == 0) issue_tma(tp, 0);
-	fetch_x0(tp, xa);
-#pragma unroll 1
-	for (int n = 0;; n += 2) {
-		TilePos tpn = advance(tp, gridDim.x);
-		iteration(tp, tpn, t + (int) gridDim.x < ntiles, n, xa, xb);
-		t += gridDim.x;
-		if (t >= ntiles) break;
-		tp = advance(tpn, gridDim.x);
-		iteration(tpn, tp, t + (int) gridDim.x < ntiles, n + 1, xb, xa);
-		t += gridDim.x;
-		if (t >= ntiles) break;
+		tp = tpn;
 	}
 }
 

@@ -158,6 +158,8 @@ __global__ void __launch_bounds__(256) k_blur_pass(GridDesc g, int b, float* __r
 	vals[3] = relax(xc.w, a, xc.z, xe, xs.w, xn.w, c);
 	const bool full = (i0 >= 1 && i0 + 3 <= g.N);
 	if (full) *reinterpret_cast<float4*>(dst + base) = make_float4(vals[0], vals[1], vals[2], vals[3]);
+	// only the groups along the walls have border cells to write (one test per thread, not per cell)
+	if (full && !(i0 == 1 || i0 + 3 == g.N || j == 1 || j == g.NY)) return;
 #pragma unroll
 	for (int l = 0; l < 4; l++) {
 		const int i = i0 + l;

@@ -195,6 +195,16 @@ int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity
  * residency (2 = default, 1; 0 = one kernel launch per colour).  Results are
  * bit-identical for every setting; only the memory traffic differs. */
 int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
+/* The red-black tile kernel divides by the same c for a whole solve.  For a
+ * given c the library can PROVE, by trying all 2^31 non-negative finite
+ * dividends on the GPU (~1.5 ms, cached per context), over which exponent range
+ * a 3-instruction multiply/fma sequence equals the IEEE quotient bit for bit, and
+ * then uses it there (div.rn elsewhere).  mode 0 = never, 1 = when the solve is
+ * large enough to repay the check (default), 2 = always.  Results never change. */
+int fluid_ctx_set_fast_division(fluid_ctx *ctx, int mode);
+/* The proven window for `divisor`: dividends with 2^lo_exp <= |t| < 2^(hi_exp+1)
+ * (hi_exp < lo_exp: none).  Runs the proof if it has not been run yet. */
+int fluid_ctx_division_window(fluid_ctx *ctx, float divisor, int *lo_exp, int *hi_exp);
 
 /* ---- row slabs over several GPUs ---------------------------------------- *
  * One context per GPU/process, each a slab (fluid_params.slab_*).  No          *

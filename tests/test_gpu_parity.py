@@ -365,3 +365,30 @@ def test_errors_are_status_codes(fl):
     with pytest.raises(fl.FluidError):
         fs.SetSources([(0, 99, 1, 0, 1.0)])
     fs.close()
+
+
+def test_verified_division_windows_and_results(fl, oracle):
+    """The short division sequence is only used where an exhaustive on-GPU comparison with
+    div.rn.f32 (all 2^31 non-negative finite dividends) found no mismatch; results must be
+    unchanged with it forced on, including fields with zeros, subnormals and huge values."""
+    import oracle_py as op
+    fs = fl.FluidSystem().Setup(300, gs_order=fl.GS_REDBLACK, gs_iters=6)
+    fs.SetFastDivision(2)
+    lo, hi = fs.DivisionWindow(4.0)
+    assert lo <= -100 and hi >= 100, (lo, hi)          # a power of two: exact wherever nothing under/overflows
+    for c in (np.float32(42.943043), np.float32(1.0004), np.float32(3.0), np.float32(1e6)):
+        lo, hi = fs.DivisionWindow(float(c))
+        assert hi < lo or (lo <= -20 and hi >= 20), (c, lo, hi)
+    rng = np.random.default_rng(99)
+    N = 300
+    for scale in (1.0, 1e-38, 1e30, 0.0):
+        x, x0 = rand_field(rng, N, scale), rand_field(rng, N, scale)
+        x0[rng.integers(0, x0.size, x0.size // 3)] = 0.0   # exact zeros, +0 and -0
+        x0[rng.integers(0, x0.size, x0.size // 7)] = -0.0
+        a = np.float32(10.49)
+        fs.upload(fl.U, x)
+        fs.upload(fl.V, x0)
+        fs.lin_solve(1, fl.U, fl.V, a, 1 + 4 * a)
+        oracle.lin_solve(N, 1, x, x0, a, 1 + 4 * a, 6, op.GS_RB)
+        assert_bits(fs.download(fl.U), x, "fast division, field scale %g" % scale)
+    fs.close()
