@@ -348,10 +348,12 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	int limit = a > 0 ? c->gs_iters : 1;
 	if (limit % 2 == 0) limit += 1;
 	float *dst = x, *src = x0;
+	DivC dv;
+	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
 	FL_TRY(dev_set_bnd(c, b, src));
 	for (int k = 0; k < limit; k++) {
 		if (k > 0) std::swap(dst, src);
-		LAUNCH(k_blur_pass, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, dst, src, a, cc,
+		LAUNCH(k_blur_pass, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, dst, src, a, dv,
 		       k + 1 < limit ? 1 : 0);
 	}
 	FL_TRY(dev_zero_bnd(c, dst));

@@ -81,6 +81,7 @@ class Oracle:
         L.oracle_lin_solve_rb.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int]
         L.oracle_diffuse.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, c_int]
         L.oracle_diffuse_blur.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int]
+        L.oracle_blur.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int]
         L.oracle_advect.argtypes = [c_int, c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_int]
         L.oracle_project.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int, c_int]
         L.oracle_vel_step.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_float, c_int, c_int, c_int]
@@ -106,6 +107,9 @@ class Oracle:
 
     def diffuse_blur(self, N, b, x, x0, diff, dt, iters=20):
         self.L.oracle_diffuse_blur(N, b, x, x0, diff, dt, iters)
+
+    def blur(self, N, b, x, x0, a, c, iters=20):
+        self.L.oracle_blur(N, b, x, x0, a, c, iters)
 
     def advect(self, N, b, d, d0, u, v, dt, mode=ADV_MIDPOINT):
         self.L.oracle_advect(N, b, d, d0, u, v, dt, mode)

@@ -391,4 +391,13 @@ def test_verified_division_windows_and_results(fl, oracle):
         fs.lin_solve(1, fl.U, fl.V, a, 1 + 4 * a)
         oracle.lin_solve(N, 1, x, x0, a, 1 + 4 * a, 6, op.GS_RB)
         assert_bits(fs.download(fl.U), x, "fast division, field scale %g" % scale)
+        # the Jacobi blur passes use the same verified division
+        x, x0 = rand_field(rng, N, scale), rand_field(rng, N, scale)
+        x0[rng.integers(0, x0.size, x0.size // 3)] = 0.0
+        fs.upload(fl.U, x)
+        fs.upload(fl.V, x0)
+        fs.blur(0, fl.U, fl.V, a, 1 + 4 * a)
+        oracle.blur(N, 0, x, x0, a, 1 + 4 * a, 6)
+        assert_bits(fs.download(fl.U), x, "fast division in blur, field scale %g" % scale)
+        assert_bits(fs.download(fl.V), x0, "blur penultimate iterate")
     fs.close()
