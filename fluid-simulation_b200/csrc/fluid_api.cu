@@ -92,6 +92,8 @@ struct fluid_ctx {
 	int own_lo = 1;            // local row of the first owned row
 	fluid_exchange_fn exchange = nullptr;
 	void* exchange_user = nullptr;
+	bool exchange_stream_ordered = false; // the transport enqueues on c->stream; no host sync around it
+	cudaStream_t own_stream = nullptr;    // the stream created with the context (c->stream may be the caller's)
 	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int rb_tile_sweeps = 2;
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
@@ -411,7 +413,7 @@ static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> array
 		for (int f = 0; f < FLUID_FIELD_COUNT; f++)
 			if (c->f[f] == a) ids[n++] = f;
 	ProfScope ps(c, FLUID_PROF_EXCHANGE);
-	CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
+	if (!c->exchange_stream_ordered) CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
 	const int rc = c->exchange(c->exchange_user, n, ids);
 	if (rc != 0) return fail(FLUID_ERR_CUDA, "halo exchange callback failed with code %d", rc);
 	return FLUID_OK;
@@ -649,7 +651,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);
-	if (c->stream) cudaStreamDestroy(c->stream);
+	if (c->own_stream) cudaStreamDestroy(c->own_stream);
 	delete c;
 	return FLUID_OK;
 }
@@ -723,6 +725,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 		if (cudaSetDevice(dev) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaSetDevice(%d) failed", dev); break; }
 		cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, dev);
 		if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+		c->own_stream = c->stream;
 		if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaEventCreate failed"); break; }
 		for (int k = 0; k < FLUID_FIELD_COUNT && rc == FLUID_OK; k++) {
 			e = cudaMalloc(&c->f[k], c->field_bytes);
@@ -973,6 +976,15 @@ extern "C" int fluid_ctx_set_exchange(fluid_ctx* c, fluid_exchange_fn fn, void* 
 	CHECK_CTX(c);
 	c->exchange = fn;
 	c->exchange_user = user;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_stream(fluid_ctx* c, void* stream, int exchange_stream_ordered)
+{
+	CHECK_CTX(c);
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	c->stream = stream ? (cudaStream_t) stream : c->own_stream;
+	c->exchange_stream_ordered = exchange_stream_ordered != 0;
 	return FLUID_OK;
 }
 

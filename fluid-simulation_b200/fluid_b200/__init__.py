@@ -35,7 +35,7 @@ EXPORTS = [
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_set_fast_division", "fluid_ctx_division_window",
-    "fluid_ctx_set_exchange", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
+    "fluid_ctx_set_exchange", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
     "fluid_ctx_local_rows",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
@@ -118,6 +118,7 @@ def lib():
     L.fluid_ctx_download_local.argtypes = [_vp, _ci, _f32]
     L.fluid_ctx_local_rows.argtypes = [_vp, ctypes.POINTER(_ci), ctypes.POINTER(_ci)]
     L.fluid_ctx_set_exchange.argtypes = [_vp, EXCHANGE_FN, _vp]
+    L.fluid_ctx_set_stream.argtypes = [_vp, _vp, _ci]
     L.fluid_ctx_halo_regions.argtypes = [_vp, _ci] + [ctypes.POINTER(_vp)] * 4 + [ctypes.POINTER(ctypes.c_size_t)]
     L.fluid_ctx_set_profiling.argtypes = [_vp, _ci]
     L.fluid_ctx_profile.argtypes = [_vp, ctypes.POINTER(_cf), ctypes.POINTER(ctypes.c_ulonglong), _ci]
@@ -219,6 +220,9 @@ class FluidSystem:
 
     def upload_local(self, field, host): check(lib().fluid_ctx_upload_local(self.h, field, host))
     def download_local(self, field, host): check(lib().fluid_ctx_download_local(self.h, field, host))
+
+    def SetStream(self, stream_handle, exchange_stream_ordered=False):
+        check(lib().fluid_ctx_set_stream(self.h, stream_handle, 1 if exchange_stream_ordered else 0))
 
     def HaloRegions(self, field):
         """(send_down, recv_down, send_up, recv_up, count_floats) device addresses (None where no neighbour)."""

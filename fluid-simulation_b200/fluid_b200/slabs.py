@@ -50,16 +50,26 @@ def exchange_pairs(dist, rank, world, blocks):
 
 
 class NcclExchange:
-    """Halo transport for one slab per process: torch.distributed (NCCL) send/recv."""
+    """Halo transport for one slab per process: torch.distributed (NCCL) send/recv.
 
-    def __init__(self, fs, rank, world, device):
+    stream_ordered=True (default): the context runs on torch's current stream and the
+    sends/receives are enqueued in stream order (torch makes the NCCL stream wait for the
+    current stream, and ``wait()`` makes the current stream wait for NCCL), so a step is
+    one uninterrupted stream of device work.  False: the library drains its stream before
+    every exchange and the transport blocks the host until the halos have arrived."""
+
+    def __init__(self, fs, rank, world, device, stream_ordered=True):
         import torch
         import torch.distributed as dist
         self.fs, self.rank, self.world, self.dist, self.torch = fs, rank, world, dist, torch
         self.device = torch.device("cuda", device)
+        self.stream_ordered = stream_ordered
         self.cache = {}
         self.calls = 0
         self.bytes = 0
+        if stream_ordered:
+            self.stream = torch.cuda.Stream(device=self.device)
+            fs.SetStream(self.stream.cuda_stream, True)
         fs.SetExchange(self)
 
     def _blocks(self, field):
@@ -70,8 +80,12 @@ class NcclExchange:
 
     def __call__(self, fields):
         blocks = [self._blocks(f) for f in fields]
-        exchange_pairs(self.dist, self.rank, self.world, blocks)
-        self.torch.cuda.synchronize(self.device)
+        if self.stream_ordered:
+            with self.torch.cuda.stream(self.stream):
+                exchange_pairs(self.dist, self.rank, self.world, blocks)  # wait() = stream-level wait on CUDA tensors
+        else:
+            exchange_pairs(self.dist, self.rank, self.world, blocks)
+            self.torch.cuda.synchronize(self.device)
         self.calls += 1
         self.bytes += sum(b.numel() * 4 for blk in blocks for b in (blk[0], blk[2]) if b is not None)
 

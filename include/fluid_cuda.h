@@ -219,6 +219,12 @@ int fluid_ctx_division_window(fluid_ctx *ctx, float divisor, int *lo_exp, int *h
  * Forcing entries use global rows.  FLUID_GS_REDBLACK only.                     */
 typedef int (*fluid_exchange_fn)(void *user, int nfields, const int *fields);
 int fluid_ctx_set_exchange(fluid_ctx *ctx, fluid_exchange_fn fn, void *user);
+/* Run the context on the caller's stream (a cudaStream_t; NULL = back to the
+ * context's own).  With exchange_stream_ordered != 0 the library does not wait for
+ * the stream before calling the exchange callback: the transport must then enqueue
+ * its transfers in stream order (e.g. NCCL on that stream), and the whole step stays
+ * asynchronous -- no host round trip per halo exchange. */
+int fluid_ctx_set_stream(fluid_ctx *ctx, void *stream, int exchange_stream_ordered);
 /* Device pointers of the blocks to move for `field`; *count floats each; a
  * pointer is NULL where there is no neighbour.  send_down -> lower neighbour's
  * recv_up, send_up -> upper neighbour's recv_down. */
