@@ -96,6 +96,7 @@ struct fluid_ctx {
 	cudaStream_t own_stream = nullptr;    // the stream created with the context (c->stream may be the caller's)
 	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int rb_tile_sweeps = 2;
+	int rb_rx = 256; // tile window width, see choose_rb_rx
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
 	int fast_div_mode = 1; // 0 never, 1 when the solve is large enough to repay the 1.5 ms check, 2 always
 	std::map<uint32_t, DivC> divs;
@@ -220,7 +221,7 @@ static int field_tmap(fluid_ctx* c, const float* base, const CUtensorMap** out)
 		CUtensorMap m;
 		const cuuint64_t dims[3] = { (cuuint64_t) c->g.pitch, (cuuint64_t) (c->g.NY + 2), (cuuint64_t) c->batch };
 		const cuuint64_t strides[2] = { (cuuint64_t) c->g.pitch * sizeof(float), (cuuint64_t) c->g.plane * sizeof(float) };
-		const cuuint32_t box[3] = { (cuuint32_t) kRbRX, (cuuint32_t) kRbRY, 1 };
+		const cuuint32_t box[3] = { (cuuint32_t) c->rb_rx, (cuuint32_t) kRbRY, 1 };
 		const cuuint32_t estr[3] = { 1, 1, 1 };
 		CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*) base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 				 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -264,25 +265,49 @@ static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	return FLUID_OK;
 }
 
-template <int S>
-static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
+template <int S, int RX>
+static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
 {
 	static bool configured[64] = {}; // per template instance and per device: function attributes are per device
-	auto kern = k_rb_tile<S, kRbRY, kRbRX, kRbNT>;
+	constexpr size_t smem = (2 * (size_t) (kRbRY + 2) + kRbRY) * RX * sizeof(float); // two x windows + x0 staging
+	auto kern = k_rb_tile<S, kRbRY, RX, kRbNT>;
 	if (c->device >= 64 || !configured[c->device]) {
-		CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kRbSmem));
+		CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 		if (c->device < 64) configured[c->device] = true;
 	}
 	const CUtensorMap *tm, *tm0;
 	FL_TRY(field_tmap(c, in, &tm));
 	FL_TRY(field_tmap(c, x0, &tm0));
-	constexpr int TY = kRbRY - 4 * S, TX = kRbRX - 2 * (((2 * S + 3) / 4) * 4);
+	constexpr int TY = kRbRY - 4 * S, TX = RX - 2 * (((2 * S + 3) / 4) * 4);
 	const int ntx = cdiv(c->g.N, TX), nty = cdiv(c->g.NY, TY);
 	const long long ntiles = (long long) ntx * nty * c->batch;
 	if (ntiles > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many tiles");
 	const int grid = (int) std::min<long long>(ntiles, c->num_sms); // persistent: one CTA per SM
-	LAUNCH(kern, grid, kRbNT, kRbSmem, c->stream, *tm, *tm0, c->g, b, out, a, dv, ntx, nty, (int) ntiles);
+	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, ntx, nty, (int) ntiles);
 	return FLUID_OK;
+}
+
+// The window width is chosen per context so that ceil(N / (RX-8)) windows waste the fewest columns
+// (N=512: 3 x 192 instead of 3 x 256; N <= 120: one 128-wide window instead of a 256-wide one).
+template <int S>
+static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
+{
+	switch (c->rb_rx) {
+	case 128: return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv);
+	case 192: return rb_tile_pass_rx<S, 192>(c, b, in, out, x0, a, dv);
+	default: return rb_tile_pass_rx<S, 256>(c, b, in, out, x0, a, dv);
+	}
+}
+
+static int choose_rb_rx(int N)
+{
+	int best = 256;
+	long long best_cost = -1;
+	for (int rx : { 256, 192, 128 }) {
+		const long long cost = (long long) cdiv(N, rx - 8) * rx;
+		if (best_cost < 0 || cost < best_cost) { best = rx; best_cost = cost; }
+	}
+	return best;
 }
 
 // `limit` red-black sweeps as an EVEN number of tile passes of 2 or 1 sweeps,
@@ -717,6 +742,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	}
 	c->g.pitch = ((XO + p->N + 2 + 31) / 32) * 32;
 	c->g.plane = (long long) c->g.pitch * (c->g.NY + 2);
+	c->rb_rx = choose_rb_rx(p->N);
 	c->field_bytes = (size_t) c->g.plane * c->batch * sizeof(float);
 	c->src.resize(c->batch);
 

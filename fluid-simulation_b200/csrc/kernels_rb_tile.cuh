@@ -72,34 +72,48 @@ template <int RX, int CB, int KB, bool MASKED, bool WALL, bool SECOND>
 __device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB], uint32_t m, float a, float c, int b,
 					       const GridDesc& g, int i_first, int j_first, const DivC& dv)
 {
-	if (!MASKED && dv.range != 0) {
-		// verified short division; a warp that meets a dividend outside the verified window (subnormal
-		// fringe of the field, overflow) redoes its cells exactly -- the inputs are the other colour's
-		// cells and x0, which this pass does not modify.
-		bool bad = false;
+	// Cells this thread really updates (bit k): everything for an unmasked tile.
+	const uint32_t live = MASKED ? m : 0xffffffffu;
+	uint32_t redo = live; // cells still to be computed with the exact division
+	if (dv.range != 0) {
+		// verified short division first; a cell whose dividend lies outside the verified window (the
+		// subnormal fringe of a field, overflow) stays in `redo` and is recomputed exactly below.  Its
+		// inputs are the other colour's cells, x0 and -- along a wall -- border cells, none of which
+		// this loop modifies (border cells are written at the very end).
+		uint32_t bad = 0;
 #pragma unroll
 		for (int k = 0; k < KB; k++) {
 			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
-			q[o] = relax_fast(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], dv, bad);
+			bool kbad = false;
+			const float v = relax_fast(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], dv, kbad);
+			if (!MASKED || ((m >> k) & 1)) q[o] = v;
+			bad |= (uint32_t) kbad << k;
 		}
-		if (!bad) return;
+		redo &= bad;
 	}
+	if (redo) {
 #pragma unroll
-	for (int k = 0; k < KB; k++) {
-		const int o = 2 * (k / CB) * RX + 32 * (k % CB);
-		const float v = relax(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], c);
-		if (!MASKED) {
-			q[o] = v;
-		} else if ((m >> k) & 1) {
-			q[o] = v;
-			if (WALL) {
-				const int i = i_first + 32 * (k % CB), j = j_first + 2 * (k / CB);
-				const float sx = (b == 1) ? -v : v, sy = (b == 2) ? -v : v;
-				if (i == 1) q[o - 1] = sx;
-				if (i == g.N) q[o + 1] = sx;
-				if (j == 1 && (g.walls & 1)) q[o - RX] = sy;
-				if (j == g.NY && (g.walls & 2)) q[o + RX] = sy;
-			}
+		for (int k = 0; k < KB; k++) {
+			if (!((redo >> k) & 1)) continue;
+			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
+			q[o] = relax(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], c);
+		}
+	}
+	if (WALL) {
+		// SetBorder inside the window: a border cell mirrors one interior cell and is read by no other
+#pragma unroll
+		for (int k = 0; k < KB; k++) {
+			if (!((live >> k) & 1)) continue;
+			const int i = i_first + 32 * (k % CB), j = j_first + 2 * (k / CB);
+			const bool L = (i == 1), R = (i == g.N), B = (j == 1 && (g.walls & 1)), T = (j == g.NY && (g.walls & 2));
+			if (!(L || R || B || T)) continue;
+			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
+			const float v = q[o];
+			const float sx = (b == 1) ? -v : v, sy = (b == 2) ? -v : v;
+			if (L) q[o - 1] = sx;
+			if (R) q[o + 1] = sx;
+			if (B) q[o - RX] = sy;
+			if (T) q[o + RX] = sy;
 		}
 	}
 }
@@ -260,13 +274,37 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(sp);
 			}
 		} else {
-			for (int idx = tid; idx < TY * TX; idx += NT) {
-				const int r = idx / TX, cc = idx - r * TX;
-				const int i = tx0 + 1 + cc, j = ty0 + 1 + r;
-				if (i > g.N || j > g.NY) continue;
-				const float v = tile[(HY + r) * RX + HX + cc];
-				xout[cell(g, i, j)] = v;
-				mirror_border(g, xout, b, i, j, v);
+			// edge tile: the rows/columns that lie inside the grid, vectorised where whole float4 groups
+			// are inside, then the border cells that mirror the wall-adjacent cells of this tile
+			const int rows_in = min(TY, g.NY - ty0), cols_in = min(TX, g.N - tx0);
+			const int groups = cols_in / 4;
+			for (int idx = tid; idx < rows_in * groups; idx += NT) {
+				const int r = idx / groups, cv = idx - r * groups;
+				const float* sp = tile + (HY + r) * RX + HX + 4 * cv;
+				float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
+				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(sp);
+			}
+			const int tail = cols_in - 4 * groups; // 0..3 leftover columns at the right wall
+			for (int idx = tid; idx < rows_in * tail; idx += NT) {
+				const int r = idx / tail, cc = 4 * groups + (idx - r * tail);
+				xout[cell(g, tx0 + 1 + cc, ty0 + 1 + r)] = tile[(HY + r) * RX + HX + cc];
+			}
+			// walls: left/right columns and bottom/top rows of the grid that fall into this tile
+			const bool wl = (tx0 == 0), wr = (tx0 + cols_in == g.N), wb = (ty0 == 0), wt = (ty0 + rows_in == g.NY);
+			if (wl || wr) {
+				for (int r = tid; r < rows_in; r += NT) {
+					const int j = ty0 + 1 + r;
+					if (wl) mirror_border(g, xout, b, 1, j, tile[(HY + r) * RX + HX]);
+					if (wr && g.N > 1) mirror_border(g, xout, b, g.N, j, tile[(HY + r) * RX + HX + cols_in - 1]);
+				}
+			}
+			if (wb || wt) {
+				for (int cc = tid; cc < cols_in; cc += NT) {
+					const int i = tx0 + 1 + cc;
+					if (i == 1 || i == g.N) continue; // corners' cells were handled by the column loop above
+					if (wb) mirror_border(g, xout, b, i, 1, tile[HY * RX + HX + cc]);
+					if (wt && g.NY > 1) mirror_border(g, xout, b, i, g.NY, tile[(HY + rows_in - 1) * RX + HX + cc]);
+				}
 			}
 		}
 		// order this thread's generic-proxy accesses to the buffer before the TMA write that refills it

@@ -1,0 +1,15 @@
+import sys, os
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "fluid-simulation_b200"))
+import fluid_b200 as fl
+for N, batch in ((512, 512), (512, 64), (256, 512), (1024, 64)):
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=1, batch=batch)
+    fs.SetFastDivision(2)
+    for b in range(batch):
+        cx, cy = 1 + (37 * b) % N, 1 + (101 * b) % N
+        fs.SetSources([(2, cx, cy, 0, 100.0), (0, cx, cy, 0, 5.0), (1, cx, cy, 0, 5.0)], sim=b)
+    fs.Update(0.1, 3); fs.Sync()
+    fs.SetProfiling(True); fs.Profile()
+    fs.Update(0.1, 5); fs.Sync()
+    ms = fs.LastStepMs() / 5
+    print("N=%d batch=%d: %.3f ms/step %.3e cell-updates/s" % (N, batch, ms, N * N * batch / ms * 1e3), {k: round(v[0] / 5, 3) for k, v in fs.Profile().items()})
+    fs.close()
