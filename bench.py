@@ -361,25 +361,21 @@ def measure_e2e_slabs(fl, fs, N, steps, dist, local, world):
 
 
 def measure_e2e(fl, np, N, order, steps, dist, local, world):
-    """Same metric through the reference-facing host-pointer calls (fluid_vel_step +
-    fluid_dens_step, Stam signatures) with HOST buffers: every step uploads its
-    inputs from pinned memory and downloads u, v, dens; copies are inside the timing."""
+    """Same metric through the reference-facing host-pointer call fluid_update (= FluidSystem::Update,
+    the reference's public per-frame API) with HOST buffers: every step uploads u, v, dens from pinned
+    memory, runs the step and downloads them again; the copies are inside the timing."""
     import torch
     n = (N + 2) ** 2
     bufs = {}
-    for k in ("u", "v", "d", "u0", "v0", "d0"):
+    for k in ("u", "v", "d"):
         bufs[k], _ = fl.pinned_empty(n)
         bufs[k][:] = 0
-    fl.set_modes(gs_order=order, gs_iters=ITERS, scratch_download=False)
+    fl.set_modes(gs_order=order, gs_iters=ITERS)
     c = N // 2
-    idx = c + (N + 2) * c
+    src = [(fl.DENS, c, c, fl.SRC_PREV_SET, 100.0), (fl.U, c, c, fl.SRC_PREV_SET, 5.0), (fl.V, c, c, fl.SRC_PREV_SET, 5.0)]
 
     def one():
-        for k in ("u0", "v0", "d0"):
-            bufs[k][:] = 0          # FluidSystem::Update's zero fill + forcing, done by the host as in the reference
-        bufs["d0"][idx], bufs["u0"][idx], bufs["v0"][idx] = 100.0, 5.0, 5.0
-        fl.vel_step(N, bufs["u"], bufs["v"], bufs["u0"], bufs["v0"], VISC, DT)
-        fl.dens_step(N, bufs["d"], bufs["d0"], bufs["u"], bufs["v"], DIFF, DT)
+        fl.update(N, bufs["u"], bufs["v"], bufs["d"], src, VISC, DIFF, DT)
 
     one()  # warm-up: creates the library's cached context
     barrier_sync(dist, local)
@@ -390,9 +386,9 @@ def measure_e2e(fl, np, N, order, steps, dist, local, world):
     dt = time.perf_counter() - t0
     dt = max_over_ranks(dist, local, dt)
     fl.set_modes()
-    return {"value": float(N) * N * world * steps / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * n * 4 * world,
+    return {"value": float(N) * N * world * steps / dt, "unit": UNIT, "h2d_bytes_per_step": 3 * n * 4 * world,
             "d2h_bytes_per_step": 3 * n * 4 * world, "steps": steps,
-            "api": "fluid_vel_step + fluid_dens_step (host pointers, pinned), scratch download off"}
+            "api": "fluid_update (FluidSystem::Update on host pointers, pinned): 3 fields up, step, 3 fields down"}
 
 
 if __name__ == "__main__":

@@ -890,8 +890,18 @@ extern "C" int fluid_ctx_set_sources(fluid_ctx* c, int sim, int n, const fluid_s
 		if (s.mode < FLUID_SRC_PREV_SET || s.mode > FLUID_SRC_CURR_SET) return fail(FLUID_ERR_INVALID, "source %d: unknown mode %d", k, s.mode);
 		v.push_back({ s.field, s.i, s.j, s.mode, s.value });
 	}
-	if (sim < 0) for (auto& e : c->src) e = v;
-	else c->src[sim] = v;
+	auto same = [](const std::vector<SourceDev>& a, const std::vector<SourceDev>& b) {
+		return a.size() == b.size() && (a.empty() || memcmp(a.data(), b.data(), a.size() * sizeof(SourceDev)) == 0);
+	};
+	bool changed = false;
+	if (sim < 0) {
+		for (auto& e : c->src)
+			if (!same(e, v)) { e = v; changed = true; }
+	} else if (!same(c->src[sim], v)) {
+		c->src[sim] = v;
+		changed = true;
+	}
+	if (!changed) return FLUID_OK; // a per-frame caller re-sending the same forcing costs nothing
 	c->src_dirty = true;
 	CU_TRY(cudaStreamSynchronize(c->stream)); // the old list may still be in use
 	return sync_sources(c);
@@ -1335,6 +1345,29 @@ extern "C" int fluid_dens_step(int N, float* x, float* x0, const float* u, const
 	FL_TRY(dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], diff, dt));
 	FL_TRY(down_async(c, FLUID_DENS, x));
 	if (t_scratch_download) FL_TRY(down_async(c, FLUID_DENS_PREV, x0));
+	return finish(c);
+}
+
+// FluidSystem::Update (FluidSystem.cpp:101-128) on host arrays: the reference's public per-frame call.
+// Only the three fields cross the bus; the source arrays are zero-filled and forced on the device.
+extern "C" int fluid_update(int N, float* u, float* v, float* dens, int nsrc, const fluid_source* src, float visc, float diff,
+			    float vorticity, float damp, float dt)
+{
+	NEED(u); NEED(v); NEED(dens);
+	fluid_ctx* c;
+	FL_TRY(host_ctx(N, &c));
+	FL_TRY(fluid_ctx_set_sources(c, -1, nsrc, src));
+	c->visc = visc;
+	c->diff = diff;
+	c->vorticity = vorticity;
+	c->damp = damp;
+	FL_TRY(up(c, FLUID_U, u));
+	FL_TRY(up(c, FLUID_V, v));
+	FL_TRY(up(c, FLUID_DENS, dens));
+	FL_TRY(dev_update(c, dt));
+	FL_TRY(down_async(c, FLUID_U, u));
+	FL_TRY(down_async(c, FLUID_V, v));
+	FL_TRY(down_async(c, FLUID_DENS, dens));
 	return finish(c);
 }
 

@@ -29,7 +29,7 @@ EXPORTS = [
     "fluid_set_gs_order", "fluid_set_gs_iters", "fluid_set_advect_mode", "fluid_set_scratch_download",
     "fluid_set_device", "fluid_host_alloc", "fluid_host_free",
     "fluid_add_source", "fluid_set_bnd", "fluid_lin_solve", "fluid_diffuse", "fluid_diffuse_blur", "fluid_advect",
-    "fluid_project", "fluid_vel_step", "fluid_dens_step", "fluid_vort_confinement", "fluid_damp",
+    "fluid_project", "fluid_vel_step", "fluid_dens_step", "fluid_update", "fluid_vort_confinement", "fluid_damp",
     "fluid_params_default", "fluid_ctx_create", "fluid_ctx_destroy", "fluid_ctx_clear", "fluid_ctx_upload",
     "fluid_ctx_download", "fluid_ctx_set_sources", "fluid_ctx_vel_step", "fluid_ctx_dens_step", "fluid_ctx_step",
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
@@ -94,6 +94,7 @@ def lib():
     L.fluid_project.argtypes = [_ci, _f32, _f32, _f32, _f32]
     L.fluid_vel_step.argtypes = [_ci, _f32, _f32, _f32, _f32, _cf, _cf]
     L.fluid_dens_step.argtypes = [_ci, _f32, _f32, _f32, _f32, _cf, _cf]
+    L.fluid_update.argtypes = [_ci, _f32, _f32, _f32, _ci, _vp, _cf, _cf, _cf, _cf, _cf]
     L.fluid_vort_confinement.argtypes = [_ci, _f32, _f32, _cf]
     L.fluid_damp.argtypes = [_ci, _f32, _cf, _cf]
     L.fluid_params_default.argtypes = [ctypes.POINTER(Params)]
@@ -159,6 +160,13 @@ def advect(N, b, d, d0, u, v, dt): check(lib().fluid_advect(N, b, d, d0, u, v, d
 def project(N, u, v, p, div): check(lib().fluid_project(N, u, v, p, div))
 def vel_step(N, u, v, u0, v0, visc, dt): check(lib().fluid_vel_step(N, u, v, u0, v0, visc, dt))
 def dens_step(N, x, x0, u, v, diff, dt): check(lib().fluid_dens_step(N, x, x0, u, v, diff, dt))
+def update(N, u, v, dens, sources, visc, diff, dt, vorticity=0.0, damp=0.0):
+    """FluidSystem::Update on host arrays; sources = [(field, i, j, mode, value), ...]."""
+    sources = list(sources)
+    arr = (Source * max(1, len(sources)))(*[Source(*s) for s in sources])
+    check(lib().fluid_update(N, u, v, dens, len(sources), ctypes.cast(arr, _vp), visc, diff, vorticity, damp, dt))
+
+
 def vort_confinement(N, u, v, vorticity): check(lib().fluid_vort_confinement(N, u, v, vorticity))
 def damp(N, vel, amount, dt): check(lib().fluid_damp(N, vel, amount, dt))
 

@@ -156,6 +156,12 @@ int fluid_project(int N, float *u, float *v, float *p, float *div);
 int fluid_vel_step(int N, float *u, float *v, float *u0, float *v0, float visc, float dt);
 /* DensStep1 (one fluid), FluidSystem.cpp:289-299; x0 = source in, scratch out. */
 int fluid_dens_step(int N, float *x, float *x0, const float *u, const float *v, float diff, float dt);
+/* FluidSystem::Update, FluidSystem.cpp:101-128 -- the reference's public per-frame call
+ * (FSType::ORIGINAL, one fluid): zero the source arrays, apply the forcing list (what the
+ * updaters do, FluidSystem.cpp:118,278-287), [vorticity], vel step, dens step, [damp].
+ * Only u, v and dens cross the bus (3 arrays up, 3 down). */
+int fluid_update(int N, float *u, float *v, float *dens, int nsrc, const fluid_source *src, float visc, float diff,
+		 float vorticity, float damp, float dt);
 /* VortConfinement, FluidSystem.cpp:1124-1175. */
 int fluid_vort_confinement(int N, float *u, float *v, float vorticity);
 /* Damp, FluidSystem.cpp:1177-1183: vel *= powf(1-amount, dt), factor computed on the host. */

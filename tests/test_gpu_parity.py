@@ -166,6 +166,24 @@ def test_vel_and_dens_step(fl, oracle, N, order):
         assert_bits(p, q, "%s N=%d order=%d" % (name, N, order))
 
 
+@pytest.mark.parametrize("order", [0, 1])
+def test_frame_level_host_call(fl, oracle, order):
+    """fluid_update = FluidSystem::Update on host arrays, incl. vorticity confinement and damping."""
+    import oracle_py as op
+    N = 90
+    rng = np.random.default_rng(order)
+    src = op.stam_sources(N) + op.blower_sources(N)
+    f = {k: rand_field(rng, N, 0.3) for k in "u v d".split()}
+    f.update({k: np.zeros((N + 2) ** 2, np.float32) for k in "u0 v0 d0".split()})
+    g = {k: f[k].copy() for k in "u v d".split()}
+    fl.set_modes(gs_order=order)
+    for _ in range(3):
+        fl.update(N, g["u"], g["v"], g["d"], src, 2e-4, 1e-4, 0.1, vorticity=0.4, damp=0.1)
+    oracle.update(N, f, src, 2e-4, 1e-4, 0.1, 3, order=order, vorticity=0.4, damp=0.1)
+    for k in "u v d".split():
+        assert_bits(g[k], f[k], "fluid_update %s order=%d" % (k, order))
+
+
 def test_golden_primitive_fields(fl, golden_fields):
     """The committed fixtures made by the unmodified reference (tests/golden/make_golden.py)."""
     G = golden_fields
