@@ -21,6 +21,7 @@
 #include "kernels_basic.cuh"
 #include "kernels_relax.cuh"
 #include "kernels_rb_tile.cuh"
+#include "kernels_small.cuh"
 
 #include <map>
 
@@ -95,6 +96,7 @@ struct fluid_ctx {
 	bool exchange_stream_ordered = false; // the transport enqueues on c->stream; no host sync around it
 	cudaStream_t own_stream = nullptr;    // the stream created with the context (c->stream may be the caller's)
 	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
+	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
@@ -341,12 +343,36 @@ static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 	return FLUID_OK;
 }
 
+static inline bool use_small_kernels(const fluid_ctx* c)
+{
+	return c->small_kernels && c->slab_count == 1 && c->g.N <= kSmallMaxN && c->g.NY == c->g.N;
+}
+
+static int small_configure(fluid_ctx* c)
+{
+	static bool configured[64] = {};
+	if (c->device >= 64 || !configured[c->device]) {
+		const int bytes = (int) small_smem_bytes(kSmallMaxN);
+		CU_TRY(cudaFuncSetAttribute(k_small_lin_solve<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+		CU_TRY(cudaFuncSetAttribute(k_small_lin_solve<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+		CU_TRY(cudaFuncSetAttribute(k_small_blur, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+		if (c->device < 64) configured[c->device] = true;
+	}
+	return FLUID_OK;
+}
+
 // LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
 static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
 {
 	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
 	const int limit = a > 0 ? c->gs_iters : 1;
-	if (c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 && b >= 0 && b <= 2) {
+	if (use_small_kernels(c)) {
+		FL_TRY(small_configure(c));
+		if (c->gs_order == FLUID_GS_REDBLACK)
+			LAUNCH(k_small_lin_solve<true>, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
+		else
+			LAUNCH(k_small_lin_solve<false>, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
+	} else if (c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 && b >= 0 && b <= 2) {
 		FL_TRY(rb_tile_solve(c, b, x, x0, a, cc, limit));
 	} else if (c->gs_order == FLUID_GS_REDBLACK) {
 		for (int k = 0; k < limit; k++) {
@@ -374,6 +400,12 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	ProfScope ps(c, FLUID_PROF_BLUR);
 	int limit = a > 0 ? c->gs_iters : 1;
 	if (limit % 2 == 0) limit += 1;
+	if (use_small_kernels(c)) {
+		FL_TRY(small_configure(c));
+		LAUNCH(k_small_blur, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
+		CU_TRY(cudaGetLastError());
+		return FLUID_OK;
+	}
 	float *dst = x, *src = x0;
 	DivC dv;
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
@@ -924,6 +956,13 @@ extern "C" int fluid_ctx_set_tuning(fluid_ctx* c, int rb_tile_sweeps)
 	CHECK_CTX(c);
 	if (rb_tile_sweeps < 0 || rb_tile_sweeps > 2) return fail(FLUID_ERR_INVALID, "rb_tile_sweeps=%d must be 0, 1 or 2", rb_tile_sweeps);
 	c->rb_tile_sweeps = rb_tile_sweeps;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_small_grid_kernels(fluid_ctx* c, int on)
+{
+	CHECK_CTX(c);
+	c->small_kernels = on != 0;
 	return FLUID_OK;
 }
 

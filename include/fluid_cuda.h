@@ -201,6 +201,10 @@ int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity
  * residency (2 = default, 1; 0 = one kernel launch per colour).  Results are
  * bit-identical for every setting; only the memory traffic differs. */
 int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
+/* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur
+ * (all passes) as ONE single-CTA launch per ensemble member, from shared memory.  on = 0
+ * forces the large-grid kernels (identical results; used by the tests). */
+int fluid_ctx_set_small_grid_kernels(fluid_ctx *ctx, int on);
 /* The red-black tile kernel divides by the same c for a whole solve.  For a
  * given c the library can PROVE, by trying all 2^31 non-negative finite
  * dividends on the GPU (~1.5 ms, cached per context), over which exponent range

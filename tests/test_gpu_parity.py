@@ -88,6 +88,7 @@ def test_redblack_kernel_variants_identical(fl, oracle, N, tile_sweeps):
     for iters in (2, 3, 5, 6, 20):
         fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_REDBLACK, gs_iters=iters)
         fs.SetTuning(tile_sweeps)
+        fs.SetSmallGridKernels(False)  # this test is about the large-grid kernels, also on tiny grids
         for b in (0, 1, 2):
             x, x0 = rand_field(rng, N), rand_field(rng, N)
             a = np.float32(0.8)
@@ -383,6 +384,36 @@ def test_errors_are_status_codes(fl):
     with pytest.raises(fl.FluidError):
         fs.SetSources([(0, 99, 1, 0, 1.0)])
     fs.close()
+
+
+@pytest.mark.parametrize("small", [True, False])
+@pytest.mark.parametrize("N", [1, 2, 9, 64, 65, 127, 128])
+def test_small_grid_kernels_match_large_grid_kernels(fl, oracle, N, small):
+    """N <= 128: one single-CTA launch per solve / per blur (hyperplane wavefront or colour passes in
+    shared memory) against the oracle, and the large-grid kernels forced onto the same sizes."""
+    import oracle_py as op
+    rng = np.random.default_rng(700 + N)
+    for order in (0, 1):
+        for iters in (1, 4, 20):
+            fs = fl.FluidSystem().Setup(N, gs_order=order, gs_iters=iters)
+            fs.SetSmallGridKernels(small)
+            for b in (0, 1, 2, 3):
+                for a in (np.float32(0.0), np.float32(0.7)):
+                    x, x0 = rand_field(rng, N), rand_field(rng, N)
+                    fs.upload(fl.U, x)
+                    fs.upload(fl.V, x0)
+                    fs.lin_solve(b, fl.U, fl.V, a, 1 + 4 * a)
+                    oracle.lin_solve(N, b, x, x0, a, 1 + 4 * a, iters, order)
+                    assert_bits(fs.download(fl.U), x, "lin_solve N=%d order=%d iters=%d b=%d a=%g" % (N, order, iters, b, a))
+                    if order == 0:
+                        x, x0 = rand_field(rng, N), rand_field(rng, N)
+                        fs.upload(fl.U, x)
+                        fs.upload(fl.V, x0)
+                        fs.blur(b, fl.U, fl.V, a, 1 + 4 * a)
+                        oracle.blur(N, b, x, x0, a, 1 + 4 * a, iters)
+                        assert_bits(fs.download(fl.U), x, "blur N=%d iters=%d b=%d a=%g" % (N, iters, b, a))
+                        assert_bits(fs.download(fl.V), x0, "blur scratch N=%d" % N)
+            fs.close()
 
 
 def test_verified_division_windows_and_results(fl, oracle):
