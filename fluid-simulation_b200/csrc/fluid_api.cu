@@ -96,12 +96,14 @@ struct fluid_ctx {
 	bool exchange_stream_ordered = false; // the transport enqueues on c->stream; no host sync around it
 	cudaStream_t own_stream = nullptr;    // the stream created with the context (c->stream may be the caller's)
 	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
+	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
 	int fast_div_mode = 1; // 0 never, 1 when the solve is large enough to repay the 1.5 ms check, 2 always
 	std::map<uint32_t, DivC> divs;
+	std::map<uint32_t, double> div_work; // cell updates seen per not-yet-verified divisor
 	unsigned int* d_divbins = nullptr;
 	float* rb_scratch = nullptr;
 	std::map<const float*, CUtensorMap> tmaps;
@@ -249,7 +251,14 @@ static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 		*out = it->second;
 		return FLUID_OK;
 	}
-	if (c->fast_div_mode == 1 && cell_updates < 2.5e8) return FLUID_OK; // 2^31 trial divisions would cost more than they save
+	// 2^31 trial divisions cost about as much as 2.5e8 cell updates: run the proof once that much work
+	// has been (or is about to be) done with this divisor -- at once for a large grid, after a few
+	// steps for a medium one, never for a divisor that changes every frame on a small grid
+	if (c->fast_div_mode == 1) {
+		double& seen = c->div_work[key];
+		seen += cell_updates;
+		if (seen < 2.5e8) return FLUID_OK;
+	}
 	if (!c->d_divbins) CU_TRY(cudaMalloc(&c->d_divbins, 256 * sizeof(unsigned int)));
 	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), c->stream));
 	LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins);
@@ -382,12 +391,16 @@ static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 	} else {
 		if (c->slab_count > 1)
 			return fail(FLUID_ERR_UNSUPPORTED, "the wavefront (reference-order) relaxation is a pipeline across slabs and is offered on one GPU only; use FLUID_GS_REDBLACK for row slabs");
-		constexpr int T = 64;
+		// small tiles: a launch is bound by the latency of one tile (2T-1 dependent steps), not by throughput.
+		// Measured ms/step (T=16/32/64): N=1024 8.6/10.0/13.8, N=2048 14.5/14.0/17.4, N=8192 77/57/68.
+		const int T = (c->wavefront_tile > 0) ? c->wavefront_tile : (c->g.N < 2048 ? 16 : 32);
 		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
 		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
-		for (int s = 0; s <= last; s++)
-			LAUNCH(k_gs_wavefront<T>, dim3(ntx, limit, c->batch), T, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx,
-			       nty);
+		for (int s = 0; s <= last; s++) {
+			if (T == 16) LAUNCH(k_gs_wavefront<16>, dim3(ntx, limit, c->batch), 16, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
+			else if (T == 32) LAUNCH(k_gs_wavefront<32>, dim3(ntx, limit, c->batch), 32, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
+			else LAUNCH(k_gs_wavefront<64>, dim3(ntx, limit, c->batch), 64, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
+		}
 	}
 	CU_TRY(cudaGetLastError());
 	return FLUID_OK;
@@ -956,6 +969,14 @@ extern "C" int fluid_ctx_set_tuning(fluid_ctx* c, int rb_tile_sweeps)
 	CHECK_CTX(c);
 	if (rb_tile_sweeps < 0 || rb_tile_sweeps > 2) return fail(FLUID_ERR_INVALID, "rb_tile_sweeps=%d must be 0, 1 or 2", rb_tile_sweeps);
 	c->rb_tile_sweeps = rb_tile_sweeps;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_wavefront_tile(fluid_ctx* c, int tile)
+{
+	CHECK_CTX(c);
+	if (tile != 0 && tile != 16 && tile != 32 && tile != 64) return fail(FLUID_ERR_INVALID, "wavefront tile %d must be 0 (automatic), 16, 32 or 64", tile);
+	c->wavefront_tile = tile;
 	return FLUID_OK;
 }
 

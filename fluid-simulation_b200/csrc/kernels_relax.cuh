@@ -44,13 +44,68 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 	const int w = min(T, g.N - i0 + 1), h = min(T, g.NY - j0 + 1);
 	const int r = threadIdx.x;
 
-	for (int rr = 0; rr < h + 2; rr++) {
-		const long long row = cell(g, i0 - 1, j0 - 1 + rr);
-		for (int cc = r; cc < w + 2; cc += T) sx[rr * PS + cc] = x[row + cc];
-	}
-	for (int rr = 0; rr < h; rr++) {
-		const long long row = cell(g, i0, j0 + rr);
-		for (int cc = r; cc < w; cc += T) s0[rr * PS + cc] = __ldg(x0 + row + cc);
+	if (w == T) {
+		// full-width tile: the interior of a row is T/4 aligned float4 groups (i0 sits on a 128-byte line);
+		// T/4 threads per row, 4 rows per step, plus the two halo columns.  All loads are issued before
+		// the first value is used: a tile lives for a few microseconds and must not pay one memory
+		// latency per row.
+		constexpr int GPR = T / 4, RPS = 4;          // groups per row, rows per step
+		constexpr int NX = (T + 2 + RPS - 1) / RPS;  // x rows per thread (incl. the two halo rows)
+		constexpr int N0 = T / RPS;                  // x0 rows per thread
+		const int q4 = r % GPR, rsub = r / GPR;
+		float4 vx[NX], v0[N0];
+		float hl[(T + 2 + T - 1) / T], hr[(T + 2 + T - 1) / T];
+#pragma unroll
+		for (int it = 0; it < NX; it++) {
+			const int rr = rsub + RPS * it;
+			if (rr < h + 2) vx[it] = *reinterpret_cast<const float4*>(x + cell(g, i0 + 4 * q4, j0 - 1 + rr));
+		}
+#pragma unroll
+		for (int it = 0; it < N0; it++) {
+			const int rr = rsub + RPS * it;
+			if (rr < h) v0[it] = __ldg(reinterpret_cast<const float4*>(x0 + cell(g, i0 + 4 * q4, j0 + rr)));
+		}
+#pragma unroll
+		for (int it = 0; it < (T + 2 + T - 1) / T; it++) {
+			const int rr = r + T * it;
+			if (rr < h + 2) {
+				hl[it] = x[cell(g, i0 - 1, j0 - 1 + rr)];
+				hr[it] = x[cell(g, i0 + T, j0 - 1 + rr)];
+			}
+		}
+#pragma unroll
+		for (int it = 0; it < NX; it++) {
+			const int rr = rsub + RPS * it;
+			if (rr < h + 2) {
+				float* d = &sx[rr * PS + 1 + 4 * q4];
+				d[0] = vx[it].x; d[1] = vx[it].y; d[2] = vx[it].z; d[3] = vx[it].w;
+			}
+		}
+#pragma unroll
+		for (int it = 0; it < N0; it++) {
+			const int rr = rsub + RPS * it;
+			if (rr < h) {
+				float* d = &s0[rr * PS + 4 * q4];
+				d[0] = v0[it].x; d[1] = v0[it].y; d[2] = v0[it].z; d[3] = v0[it].w;
+			}
+		}
+#pragma unroll
+		for (int it = 0; it < (T + 2 + T - 1) / T; it++) {
+			const int rr = r + T * it;
+			if (rr < h + 2) {
+				sx[rr * PS] = hl[it];
+				sx[rr * PS + T + 1] = hr[it];
+			}
+		}
+	} else {
+		for (int rr = 0; rr < h + 2; rr++) {
+			const long long row = cell(g, i0 - 1, j0 - 1 + rr);
+			for (int cc = r; cc < w + 2; cc += T) sx[rr * PS + cc] = x[row + cc];
+		}
+		for (int rr = 0; rr < h; rr++) {
+			const long long row = cell(g, i0, j0 + rr);
+			for (int cc = r; cc < w; cc += T) s0[rr * PS + cc] = __ldg(x0 + row + cc);
+		}
 	}
 	__syncthreads();
 
@@ -59,19 +114,29 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 	for (int d = 0; d < nd; d++) {
 		const int col = d - r;
 		if (r < h && col >= 0 && col < w) {
-			const float v = relax(s0[r * PS + col], a, me[col - 1], me[col + 1], me[col - PS], me[col + PS], c);
-			me[col] = v;
+			// plain IEEE division: this loop is bound by the latency of the dependent chain, and the part of
+			// div.rn that depends on the dividend is as short as the verified sequence (measured: no gain)
+			me[col] = relax(s0[r * PS + col], a, me[col - 1], me[col + 1], me[col - PS], me[col + PS], c);
 		}
 		__syncthreads();
 	}
 
-	for (int rr = 0; rr < h; rr++) {
-		const int j = j0 + rr;
-		const long long row = cell(g, i0, j);
-		for (int cc = r; cc < w; cc += T) {
-			const float v = sx[(rr + 1) * PS + cc + 1];
-			x[row + cc] = v;
-			mirror_border(g, x, b, i0 + cc, j, v);
+	if (w == T && !(I == 0 || J == 0 || i0 + T - 1 == g.N || j0 + h - 1 == g.NY)) {
+		constexpr int GPR = T / 4, RPS = 4;
+		const int q4 = r % GPR, rsub = r / GPR;
+		for (int rr = rsub; rr < h; rr += RPS) {
+			const float* sp = &sx[(rr + 1) * PS + 1 + 4 * q4];
+			*reinterpret_cast<float4*>(x + cell(g, i0 + 4 * q4, j0 + rr)) = make_float4(sp[0], sp[1], sp[2], sp[3]);
+		}
+	} else {
+		for (int rr = 0; rr < h; rr++) {
+			const int j = j0 + rr;
+			const long long row = cell(g, i0, j);
+			for (int cc = r; cc < w; cc += T) {
+				const float v = sx[(rr + 1) * PS + cc + 1];
+				x[row + cc] = v;
+				mirror_border(g, x, b, i0 + cc, j, v);
+			}
 		}
 	}
 }

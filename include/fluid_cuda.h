@@ -201,6 +201,8 @@ int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity
  * residency (2 = default, 1; 0 = one kernel launch per colour).  Results are
  * bit-identical for every setting; only the memory traffic differs. */
 int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
+/* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
+int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur
  * (all passes) as ONE single-CTA launch per ensemble member, from shared memory.  on = 0
  * forces the large-grid kernels (identical results; used by the tests). */

@@ -386,6 +386,24 @@ def test_errors_are_status_codes(fl):
     fs.close()
 
 
+@pytest.mark.parametrize("tile", [16, 32, 64])
+def test_wavefront_tile_sizes_bitwise(fl, oracle, tile):
+    import oracle_py as op
+    rng = np.random.default_rng(tile)
+    for N in (130, 257, 320):
+        fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=7)
+        fs.SetWavefrontTile(tile)
+        for b in (0, 1, 2, 3):
+            x, x0 = rand_field(rng, N), rand_field(rng, N)
+            a = np.float32(0.6)
+            fs.upload(fl.U, x)
+            fs.upload(fl.V, x0)
+            fs.lin_solve(b, fl.U, fl.V, a, 1 + 4 * a)
+            oracle.lin_solve(N, b, x, x0, a, 1 + 4 * a, 7, op.GS_LEX)
+            assert_bits(fs.download(fl.U), x, "wavefront tile %d N=%d b=%d" % (tile, N, b))
+        fs.close()
+
+
 @pytest.mark.parametrize("small", [True, False])
 @pytest.mark.parametrize("N", [1, 2, 9, 64, 65, 127, 128])
 def test_small_grid_kernels_match_large_grid_kernels(fl, oracle, N, small):
