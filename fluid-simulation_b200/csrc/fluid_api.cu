@@ -95,7 +95,9 @@ struct fluid_ctx {
 	void* exchange_user = nullptr;
 	bool exchange_stream_ordered = false; // the transport enqueues on c->stream; no host sync around it
 	cudaStream_t own_stream = nullptr;    // the stream created with the context (c->stream may be the caller's)
-	int* d_oob = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
+	int* d_oob = nullptr;
+	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
+	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
@@ -715,6 +717,8 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->rb_scratch) cudaFree(c->rb_scratch);
 	if (c->d_oob) cudaFree(c->d_oob);
 	if (c->d_divbins) cudaFree(c->d_divbins);
+	if (c->d_pixels) cudaFree(c->d_pixels);
+	if (c->d_lines) cudaFree(c->d_lines);
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
@@ -969,6 +973,27 @@ extern "C" int fluid_ctx_set_tuning(fluid_ctx* c, int rb_tile_sweeps)
 	CHECK_CTX(c);
 	if (rb_tile_sweeps < 0 || rb_tile_sweeps > 2) return fail(FLUID_ERR_INVALID, "rb_tile_sweeps=%d must be 0, 1 or 2", rb_tile_sweeps);
 	c->rb_tile_sweeps = rb_tile_sweeps;
+	return FLUID_OK;
+}
+
+// FluidRenderer::DoBuffer without a window: colourise + velocity lines of ensemble member `sim` into
+// device buffers, then (optionally) to dense host arrays.
+extern "C" int fluid_ctx_render(fluid_ctx* c, int sim, const float* color_rgb, float* host_pixels, float* host_lines)
+{
+	CHECK_CTX(c);
+	if (!color_rgb || !host_pixels) return fail(FLUID_ERR_INVALID, "null pointer");
+	if (sim < 0 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range [0,%d)", sim, c->batch);
+	if (c->slab_count > 1) return fail(FLUID_ERR_UNSUPPORTED, "render a slab by downloading it; the display buffer is per whole grid");
+	const size_t cells = (size_t) (c->g.N + 2) * (c->g.NY + 2);
+	if (!c->d_pixels) CU_TRY(cudaMalloc(&c->d_pixels, cells * 3 * sizeof(float)));
+	if (host_lines && !c->d_lines) CU_TRY(cudaMalloc(&c->d_lines, cells * 4 * sizeof(float)));
+	const long long off = (long long) sim * c->g.plane;
+	LAUNCH(k_colourise, dim3(cdiv(c->g.N + 2, 32), cdiv(c->g.NY + 2, 8), 1), kBlk2D, 0, c->stream, c->g, c->f[FLUID_DENS] + off,
+	       c->f[FLUID_U] + off, c->f[FLUID_V] + off, color_rgb[0], color_rgb[1], color_rgb[2], c->d_pixels,
+	       host_lines ? c->d_lines : nullptr);
+	CU_TRY(cudaMemcpyAsync(host_pixels, c->d_pixels, cells * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	if (host_lines) CU_TRY(cudaMemcpyAsync(host_lines, c->d_lines, cells * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
 	return FLUID_OK;
 }
 

@@ -428,4 +428,55 @@ __global__ void __launch_bounds__(256) k_vort_apply(GridDesc g, float* __restric
 	mirror_border(g, v, 0, i, j, vn);
 }
 
+// ---------------------------------------------------------------------------
+// Headless stand-in for the display path: the per-cell colourise loop and the
+// velocity line list of FluidRenderer::DoBuffer (FluidRenderer.cpp:56-84, 97-132) for one fluid,
+// written to dense device buffers instead of a GL texture / vertex buffer (graphics APIs are
+// unavailable on this box).  Cells of the grid's outer ring are not FLUID after ResetCellInfo
+// (FluidSystem.cpp:1215-1232) and come out green; there are no OBJECT cells on the ORIGINAL path.
+// pixels: (N+2)^2 x 3 floats, lines: (N+2)^2 x 4 floats (x0, y0, x1, y1), both indexed by ID(i,j).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_colourise(GridDesc g, const float* __restrict__ db, const float* __restrict__ ub,
+						    const float* __restrict__ vb, float cr, float cg, float cb,
+						    float* __restrict__ pixels, float* __restrict__ lines)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	const int j = blockIdx.y * blockDim.y + threadIdx.y;
+	if (i > g.N + 1 || j > g.NY + 1) return;
+	const long long id = cell(g, i, j);
+	const long long out = (long long) i + (long long) (g.N + 2) * j;
+	float r = 0.f, gg = 0.f, b = 0.f;
+	if (i >= 1 && i <= g.N && j >= 1 && j <= g.NY) {
+		const float d = __ldg(db + id);
+		float d_total = 0.f;
+		d_total += d;
+		r += cr * d;
+		gg += cg * d;
+		b += cb * d;
+		if (d_total > 1) {
+			r = div_exact(r, d_total);
+			gg = div_exact(gg, d_total);
+			b = div_exact(b, d_total);
+		}
+	} else {
+		gg = 1.f;
+	}
+	pixels[3 * out + 0] = r;
+	pixels[3 * out + 1] = gg;
+	pixels[3 * out + 2] = b;
+	if (lines) {
+		const float vx0 = __ldg(ub + id), vy0 = __ldg(vb + id);
+		const float mag = sqrtf(vx0 * vx0 + vy0 * vy0);
+		const int N2 = g.N + 2;
+		const float s = N2 * 1.05f;
+		float vx = (vx0 / mag) / s, vy = (vy0 / mag) / s;
+		if ((double) mag < 0.000000000001) vx = vy = 0.f;
+		const float lx = (i + 0.5f) / (float) N2, ly = (j + 0.5f) / (float) N2;
+		lines[4 * out + 0] = lx;
+		lines[4 * out + 1] = ly;
+		lines[4 * out + 2] = lx + vx;
+		lines[4 * out + 3] = ly + vy;
+	}
+}
+
 } // namespace fluid

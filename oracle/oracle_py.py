@@ -90,6 +90,7 @@ class Oracle:
         L.oracle_damp.argtypes = [c_int, _f32p, c_float, c_float]
         L.oracle_update.argtypes = [c_int] + [_f32p] * 6 + [c_int, c_void_p, c_float, c_float, c_float, c_int, c_int,
                                                            c_int, c_float, c_float, c_int]
+        L.oracle_render.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, _f32p, _f32p]
         L.oracle_total_inner_mass.argtypes = [c_int, _f32p]
         L.oracle_total_inner_mass.restype = c_float
 
@@ -141,6 +142,12 @@ class Oracle:
 
     def total_inner_mass(self, N, d):
         return float(self.L.oracle_total_inner_mass(N, d))
+
+    def render(self, N, dens, u, v, color):
+        n = (N + 2) ** 2
+        px, ln = np.empty(n * 3, np.float32), np.empty(n * 4, np.float32)
+        self.L.oracle_render(N, dens, u, v, np.asarray(color, np.float32), px, ln)
+        return px.reshape(n, 3), ln.reshape(n, 4)
 
 
 class Ref:

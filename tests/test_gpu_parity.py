@@ -468,3 +468,27 @@ def test_verified_division_windows_and_results(fl, oracle):
         assert_bits(fs.download(fl.U), x, "fast division in blur, field scale %g" % scale)
         assert_bits(fs.download(fl.V), x0, "blur penultimate iterate")
     fs.close()
+
+
+def test_headless_render_matches_restated_renderer_loop(fl, oracle):
+    """SURVEY 8(f) row 2: FluidRenderer::DoBuffer's colourise loop and velocity line list on the device
+    (no graphics API).  The oracle for this row is a restatement only (the renderer cannot be compiled
+    here), so parity with the real reference is unpinned; the CUDA kernel equals the restatement bitwise."""
+    N = 77
+    rng = np.random.default_rng(21)
+    d = np.abs(rand_field(rng, N, 2.5))   # some cells above 1 (normalised), some below
+    u, v = rand_field(rng, N), rand_field(rng, N)
+    u[::7] = 0.0
+    v[::7] = 0.0                          # zero-speed cells: the reference's 0/0 then override path
+    fs = fl.FluidSystem().Setup(N)
+    fs.upload(fl.DENS, d)
+    fs.upload(fl.U, u)
+    fs.upload(fl.V, v)
+    color = (0.05, 0.05, 1.0)             # the first fluid of the shipped scene, SystemManager.cpp:104
+    px, ln = fs.Render(color)
+    want_px, want_ln = oracle.render(N, d, u, v, color)
+    assert_bits(px, want_px, "pixels")
+    assert_bits(ln, want_ln, "velocity lines")
+    g = px.reshape(N + 2, N + 2, 3)
+    assert np.all(g[0, :, 1] == 1) and np.all(g[0, :, 0] == 0)  # outer ring is green
+    fs.close()
