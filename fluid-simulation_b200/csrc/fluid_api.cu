@@ -439,7 +439,10 @@ static int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const floa
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
-	LAUNCH(k_advect, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	if (c->slab_count > 1)
+		LAUNCH(k_advect<true>, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	else
+		LAUNCH(k_advect<false>, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode, c->d_oob, 1, 0);
 	return FLUID_OK;
 }
 
@@ -447,7 +450,10 @@ static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
-	LAUNCH(k_advect_velocity, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	if (c->slab_count > 1)
+		LAUNCH(k_advect_velocity<true>, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	else
+		LAUNCH(k_advect_velocity<false>, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode, c->d_oob, 1, 0);
 	return FLUID_OK;
 }
 

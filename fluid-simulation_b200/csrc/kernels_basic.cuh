@@ -219,30 +219,31 @@ struct Bilin {
 	float s0, s1, t0, t1;
 };
 
-// (px, py) are GLOBAL cell coordinates; the sampled rows are converted to local
-// ones at the end.  A sample whose rows are not stored on this slab (backtrace
-// longer than the halo) sets *oob and is clamped into the slab so that the access
-// stays legal; the host reports it as an error after the step.
+// (px, py) are GLOBAL cell coordinates; the sampled rows are converted to local ones at the end.
+// The reference clamps with `if (i < 0.5f) i = 0.5f; if (i > N + 0.5f) i = N + 0.5f` (FluidCode.h:95-103);
+// fmaxf/fminf give the same value for every non-NaN input in two instructions, and map a NaN
+// coordinate (for which the reference indexes out of bounds) to the lower clamp.
+// SLAB: a sample whose rows are not stored on this slab (backtrace longer than the halo) sets *oob
+// and is clamped into the slab so that the access stays legal; the host reports it after the step.
+template <bool SLAB>
 __device__ __forceinline__ Bilin bilin_calc(const GridDesc& g, float px, float py, int* oob)
 {
 	Bilin r;
-	if (px < 0.5f) px = 0.5f;
-	if (px > g.N + 0.5f) px = g.N + 0.5f;
-	int i0 = (int) px;
-	if (py < 0.5f) py = 0.5f;
-	if (py > g.NYG + 0.5f) py = g.NYG + 0.5f;
-	int j0 = (int) py;
-	// a NaN coordinate makes the reference index out of bounds (undefined); keep the access in range
-	i0 = min(max(i0, 0), g.N);
-	j0 = min(max(j0, 0), g.NYG);
+	px = fminf(fmaxf(px, 0.5f), g.N + 0.5f);
+	py = fminf(fmaxf(py, 0.5f), g.NYG + 0.5f);
+	const int i0 = (int) px;
+	const int j0 = (int) py;
 	r.s1 = px - i0;
 	r.s0 = 1 - r.s1;
 	r.t1 = py - j0;
 	r.t0 = 1 - r.t1;
-	int jl = j0 - g.j0;
-	if (jl < 0 || jl > g.NY) {
-		if (oob) *oob = 1;
-		jl = min(max(jl, 0), g.NY);
+	int jl = j0;
+	if (SLAB) {
+		jl = j0 - g.j0;
+		if (jl < 0 || jl > g.NY) {
+			if (oob) *oob = 1;
+			jl = min(max(jl, 0), g.NY);
+		}
 	}
 	r.o00 = cell(g, i0, jl);
 	return r;
@@ -258,12 +259,13 @@ __device__ __forceinline__ float bilin_eval(const Bilin& c, const float* __restr
 // Backtraced sample position of cell (i,j): MidpointBackward (FluidSystem.h:185-206)
 // or EulerBack (FluidSystem.h:208-219).
 // (i, j) local; the returned position is in global coordinates.
+template <bool SLAB>
 __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __restrict__ u, const float* __restrict__ v,
 					  int i, int j, float dtN, int mode, float& px, float& py, int* oob)
 {
 	const long long id = cell(g, i, j);
 	const float uc = __ldg(u + id), vc = __ldg(v + id);
-	const int jg = j + g.j0;
+	const int jg = SLAB ? j + g.j0 : j;
 	if (mode == 1) {
 		px = i - dtN * uc;
 		py = jg - dtN * vc;
@@ -272,7 +274,7 @@ __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __rest
 		const float diry = -dtN * vc;
 		const float mx = i + 0.5f * dirx;
 		const float my = jg + 0.5f * diry;
-		const Bilin m = bilin_calc(g, mx, my, oob);
+		const Bilin m = bilin_calc<SLAB>(g, mx, my, oob);
 		const float vx = bilin_eval(m, u, g.pitch);
 		const float vy = bilin_eval(m, v, g.pitch);
 		px = i - dtN * vx;
@@ -284,6 +286,7 @@ __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __rest
 // Advect1 (FluidSystem.cpp:850-862) for one scalar field, SetBorder fused.
 // Gather kernel: u,v,d0 read, d written = 16 B per cell algorithmic.
 // ---------------------------------------------------------------------------
+template <bool SLAB>
 __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __restrict__ db, const float* __restrict__ d0b,
 						 const float* __restrict__ ub, const float* __restrict__ vb, float dtN,
 						 int mode, int* oob_flag, int own_lo, int own_hi)
@@ -292,10 +295,10 @@ __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __rest
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
 	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
 	if (i > g.N || j > g.NY) return;
-	int* oob = (j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
+	int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
 	float px, py;
-	backtrace(g, ub + off, vb + off, i, j, dtN, mode, px, py, oob);
-	const Bilin c = bilin_calc(g, px, py, oob);
+	backtrace<SLAB>(g, ub + off, vb + off, i, j, dtN, mode, px, py, oob);
+	const Bilin c = bilin_calc<SLAB>(g, px, py, oob);
 	const float val = bilin_eval(c, d0b + off, g.pitch);
 	float* d = db + off;
 	d[cell(g, i, j)] = val;
@@ -305,6 +308,7 @@ __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __rest
 // VelStep1's self-advection (FluidSystem.cpp:372-373): Advect1(1,u,u0,u0,v0) and
 // Advect1(2,v,v0,u0,v0) share the backtrace, so both components are produced
 // by one pass over (u0,v0): 16 B per cell instead of 2 x 12 B.
+template <bool SLAB>
 __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
 							  const float* __restrict__ u0b, const float* __restrict__ v0b,
 							  float dtN, int mode, int* oob_flag, int own_lo, int own_hi)
@@ -313,12 +317,12 @@ __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __re
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
 	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
 	if (i > g.N || j > g.NY) return;
-	int* oob = (j >= own_lo && j <= own_hi) ? oob_flag : nullptr;
+	int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr;
 	const float* u0 = u0b + off;
 	const float* v0 = v0b + off;
 	float px, py;
-	backtrace(g, u0, v0, i, j, dtN, mode, px, py, oob);
-	const Bilin c = bilin_calc(g, px, py, oob);
+	backtrace<SLAB>(g, u0, v0, i, j, dtN, mode, px, py, oob);
+	const Bilin c = bilin_calc<SLAB>(g, px, py, oob);
 	const float un = bilin_eval(c, u0, g.pitch);
 	const float vn = bilin_eval(c, v0, g.pitch);
 	float* u = ub + off;

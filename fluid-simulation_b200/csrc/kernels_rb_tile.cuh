@@ -266,12 +266,14 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		// --- store the centre ---
 		float* xout = xoutb + (long long) sim * g.plane;
 		if (!edge) {
+			// a warp per row, a lane per float4: no index division, one 64-bit address per row
 			constexpr int PER_ROW = TX / 4;
-			for (int idx = tid; idx < TY * PER_ROW; idx += NT) {
-				const int r = idx / PER_ROW, cv = idx - r * PER_ROW;
-				const float* sp = tile + (HY + r) * RX + HX + 4 * cv;
-				float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
-				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(sp);
+			for (int r = w; r < TY; r += NW) {
+				const float* sp = tile + (HY + r) * RX + HX;
+				float* d = xout + cell(g, tx0 + 1, ty0 + 1 + r);
+#pragma unroll
+				for (int cv = lane; cv < PER_ROW; cv += 32)
+					*reinterpret_cast<float4*>(d + 4 * cv) = *reinterpret_cast<const float4*>(sp + 4 * cv);
 			}
 		} else {
 			// edge tile: the rows/columns that lie inside the grid, vectorised where whole float4 groups
