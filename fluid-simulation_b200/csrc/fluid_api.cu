@@ -78,7 +78,11 @@ struct fluid_ctx {
 	int gs_iters = 20, gs_order = FLUID_GS_WAVEFRONT, advect_mode = FLUID_ADVECT_MIDPOINT;
 	float visc = 0, diff = 0, vorticity = 0, damp = 0;
 	size_t field_bytes = 0;   // one field, all ensemble members
-	float* f[FLUID_FIELD_COUNT] = {}; // field id -> device array (ids are fixed; steps swap locals)
+	static constexpr int kMaxFields = FLUID_FIELD_COUNT + 2 * (FLUID_MAX_FLUIDS - 1);
+	float* f[kMaxFields] = {}; // field id -> device array (ids are fixed; steps swap locals)
+	int n_fluids = 1, n_fields = FLUID_FIELD_COUNT;
+	float fl_diff[FLUID_MAX_FLUIDS] = {}, fl_visc[FLUID_MAX_FLUIDS] = {};
+	bool fl_set[FLUID_MAX_FLUIDS] = {}; // fluid k has its own coefficients (else it follows fluid 0)
 	float* vscr[4] = {};      // vorticity scratch, allocated on first use
 	SourceDev* d_src = nullptr;
 	int* d_first = nullptr;
@@ -486,9 +490,9 @@ static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> array
 {
 	if (c->slab_count <= 1) return FLUID_OK;
 	if (!c->exchange) return fail(FLUID_ERR_INVALID, "this context is a row slab but no exchange callback is set (fluid_ctx_set_exchange)");
-	int ids[FLUID_FIELD_COUNT], n = 0;
+	int ids[fluid_ctx::kMaxFields], n = 0;
 	for (const float* a : arrays)
-		for (int f = 0; f < FLUID_FIELD_COUNT; f++)
+		for (int f = 0; f < c->n_fields; f++)
 			if (c->f[f] == a) ids[n++] = f;
 	ProfScope ps(c, FLUID_PROF_EXCHANGE);
 	if (!c->exchange_stream_ordered) CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
@@ -588,6 +592,18 @@ static int sync_sources(fluid_ctx* c)
 	return FLUID_OK;
 }
 
+static inline float fluid_diff(const fluid_ctx* c, int fl) { return c->fl_set[fl] ? c->fl_diff[fl] : c->diff; }
+
+// visc_avg, FluidSystem.cpp:26-30: float sum over the fluids, divided by the count
+static inline float visc_avg(const fluid_ctx* c)
+{
+	if (c->n_fluids == 1) return c->visc;
+	float v = 0;
+	for (int fl = 0; fl < c->n_fluids; fl++) v += c->fl_set[fl] ? c->fl_visc[fl] : c->visc;
+	v /= (float) c->n_fluids;
+	return v;
+}
+
 // FluidSystem::Update (FluidSystem.cpp:101-128) for FSType::ORIGINAL.
 static int dev_update(fluid_ctx* c, float dt)
 {
@@ -595,12 +611,16 @@ static int dev_update(fluid_ctx* c, float dt)
 		ProfScope ps(c, FLUID_PROF_OTHER);
 		CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));
 		CU_TRY(cudaMemsetAsync(c->f[FLUID_V_PREV], 0, c->field_bytes, c->stream));
-		CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV], 0, c->field_bytes, c->stream));
+		for (int fl = 0; fl < c->n_fluids; fl++) CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV_OF(fl)], 0, c->field_bytes, c->stream));
 		if (c->n_src > 0) {
-			FieldPtrs fp;
-			for (int k = 0; k < 3; k++) {
-				fp.cur[k] = c->f[k];
-				fp.prev[k] = c->f[k + 3];
+			FieldPtrs fp = {};
+			fp.cur[0] = c->f[FLUID_U];
+			fp.prev[0] = c->f[FLUID_U_PREV];
+			fp.cur[1] = c->f[FLUID_V];
+			fp.prev[1] = c->f[FLUID_V_PREV];
+			for (int fl = 0; fl < c->n_fluids; fl++) {
+				fp.cur[2 + fl] = c->f[FLUID_DENS_OF(fl)];
+				fp.prev[2 + fl] = c->f[FLUID_DENS_PREV_OF(fl)];
 			}
 			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 		}
@@ -609,8 +629,9 @@ static int dev_update(fluid_ctx* c, float dt)
 		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
 		FL_TRY(halo_exchange(c, { c->f[FLUID_U], c->f[FLUID_V] })); // three stencil phases consumed 3 halo rows
 	}
-	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], c->visc, dt));
-	FL_TRY(dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], c->diff, dt));
+	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt));
+	for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
+		FL_TRY(dev_dens_step(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], fluid_diff(c, fl), dt));
 	if (c->damp != 0.0f) {
 		FL_TRY(dev_damp(c, c->f[FLUID_U], c->damp, dt));
 		FL_TRY(dev_damp(c, c->f[FLUID_V], c->damp, dt));
@@ -746,6 +767,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	if (p->gs_order != FLUID_GS_WAVEFRONT && p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", p->gs_order);
 	if (p->advect_mode != FLUID_ADVECT_MIDPOINT && p->advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", p->advect_mode);
 	for (int r : p->reserved) if (r != 0) return fail(FLUID_ERR_INVALID, "reserved fields must be 0");
+	if (p->n_fluids < 0 || p->n_fluids > FLUID_MAX_FLUIDS) return fail(FLUID_ERR_INVALID, "n_fluids=%d out of range [1,%d]", p->n_fluids, FLUID_MAX_FLUIDS);
 	if (p->slab_count < 0 || (p->slab_count > 1 && (p->slab_index < 0 || p->slab_index >= p->slab_count)))
 		return fail(FLUID_ERR_INVALID, "slab_index=%d / slab_count=%d is not a valid slab", p->slab_index, p->slab_count);
 	if (p->slab_count > 1) {
@@ -777,6 +799,8 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	c->diff = p->diff;
 	c->vorticity = p->vorticity;
 	c->damp = p->damp;
+	c->n_fluids = p->n_fluids > 0 ? p->n_fluids : 1;
+	c->n_fields = FLUID_FIELD_COUNT + 2 * (c->n_fluids - 1);
 	c->g.N = p->N;
 	c->g.NY = p->N;
 	c->g.j0 = 0;
@@ -808,7 +832,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 		if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
 		c->own_stream = c->stream;
 		if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "cudaEventCreate failed"); break; }
-		for (int k = 0; k < FLUID_FIELD_COUNT && rc == FLUID_OK; k++) {
+		for (int k = 0; k < c->n_fields && rc == FLUID_OK; k++) {
 			e = cudaMalloc(&c->f[k], c->field_bytes);
 			if (e != cudaSuccess) {
 				rc = fail(FLUID_ERR_NOMEM, "cudaMalloc of %zu bytes failed: %s", c->field_bytes, cudaGetErrorString(e));
@@ -845,13 +869,14 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 		FL_TRY(ctx_bind(c));                                                                              \
 	} while (0)
 
-static int check_field(int f) { return (f >= 0 && f < FLUID_FIELD_COUNT) ? FLUID_OK : fail(FLUID_ERR_INVALID, "field id %d out of range", f); }
+static int check_field_n(int f, int n) { return (f >= 0 && f < n) ? FLUID_OK : fail(FLUID_ERR_INVALID, "field id %d out of range [0,%d)", f, n); }
+#define check_field(f) check_field_n((f), c->n_fields)
 
-static int check_distinct(std::initializer_list<int> ids)
+static int check_distinct_n(int n_fields, std::initializer_list<int> ids)
 {
 	std::vector<int> v(ids);
 	for (size_t a = 0; a < v.size(); a++) {
-		FL_TRY(check_field(v[a]));
+		FL_TRY(check_field_n(v[a], n_fields));
 		for (size_t b = a + 1; b < v.size(); b++)
 			if (v[a] == v[b]) return fail(FLUID_ERR_INVALID, "field %d passed twice where distinct arrays are required", v[a]);
 	}
@@ -861,7 +886,7 @@ static int check_distinct(std::initializer_list<int> ids)
 extern "C" int fluid_ctx_clear(fluid_ctx* c)
 {
 	CHECK_CTX(c);
-	for (auto& p : c->f) CU_TRY(cudaMemsetAsync(p, 0, c->field_bytes, c->stream));
+	for (int k = 0; k < c->n_fields; k++) CU_TRY(cudaMemsetAsync(c->f[k], 0, c->field_bytes, c->stream));
 	return FLUID_OK;
 }
 
@@ -940,10 +965,14 @@ extern "C" int fluid_ctx_set_sources(fluid_ctx* c, int sim, int n, const fluid_s
 	std::vector<SourceDev> v;
 	for (int k = 0; k < n; k++) {
 		const fluid_source& s = src[k];
-		if (s.field < FLUID_U || s.field > FLUID_DENS) return fail(FLUID_ERR_INVALID, "source %d: field %d is not U, V or DENS", k, s.field);
+		int slot = -1; // 0 = u, 1 = v, 2 + fluid = a density field
+		if (s.field == FLUID_U || s.field == FLUID_V) slot = s.field;
+		for (int fl = 0; fl < c->n_fluids; fl++)
+			if (s.field == FLUID_DENS_OF(fl)) slot = 2 + fl;
+		if (slot < 0) return fail(FLUID_ERR_INVALID, "source %d: field %d is not U, V or a density field of this context", k, s.field);
 		if (s.i < 0 || s.i > c->g.N + 1 || s.j < 0 || s.j > c->g.NYG + 1) return fail(FLUID_ERR_INVALID, "source %d: cell (%d,%d) outside the grid", k, s.i, s.j);
 		if (s.mode < FLUID_SRC_PREV_SET || s.mode > FLUID_SRC_CURR_SET) return fail(FLUID_ERR_INVALID, "source %d: unknown mode %d", k, s.mode);
-		v.push_back({ s.field, s.i, s.j, s.mode, s.value });
+		v.push_back({ slot, s.i, s.j, s.mode, s.value });
 	}
 	auto same = [](const std::vector<SourceDev>& a, const std::vector<SourceDev>& b) {
 		return a.size() == b.size() && (a.empty() || memcmp(a.data(), b.data(), a.size() * sizeof(SourceDev)) == 0);
@@ -1052,6 +1081,7 @@ extern "C" int fluid_ctx_set_coeffs(fluid_ctx* c, float visc, float diff, float 
 	CHECK_CTX(c);
 	c->visc = visc;
 	c->diff = diff;
+	c->fl_set[0] = false; // fluid 0 follows these again
 	c->vorticity = vorticity;
 	c->damp = damp;
 	return FLUID_OK;
@@ -1060,13 +1090,25 @@ extern "C" int fluid_ctx_set_coeffs(fluid_ctx* c, float visc, float diff, float 
 extern "C" int fluid_ctx_vel_step(fluid_ctx* c, float dt)
 {
 	CHECK_CTX(c);
-	return dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], c->visc, dt);
+	return dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt);
 }
 
 extern "C" int fluid_ctx_dens_step(fluid_ctx* c, float dt)
 {
 	CHECK_CTX(c);
-	return dev_dens_step(c, c->f[FLUID_DENS], c->f[FLUID_DENS_PREV], c->f[FLUID_U], c->f[FLUID_V], c->diff, dt);
+	for (int fl = 0; fl < c->n_fluids; fl++)
+		FL_TRY(dev_dens_step(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], fluid_diff(c, fl), dt));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_fluid(fluid_ctx* c, int k, float diff, float visc)
+{
+	CHECK_CTX(c);
+	if (k < 0 || k >= c->n_fluids) return fail(FLUID_ERR_INVALID, "fluid %d out of range [0,%d)", k, c->n_fluids);
+	c->fl_diff[k] = diff;
+	c->fl_visc[k] = visc;
+	c->fl_set[k] = true;
+	return FLUID_OK;
 }
 
 extern "C" int fluid_ctx_step(fluid_ctx* c, float dt, int nsteps)
@@ -1179,7 +1221,7 @@ extern "C" int fluid_ctx_profile(fluid_ctx* c, float* ms, unsigned long long* la
 extern "C" int fluid_ctx_add_source(fluid_ctx* c, int x, int s, float dt)
 {
 	CHECK_CTX(c);
-	FL_TRY(check_distinct({ x, s }));
+	FL_TRY(check_distinct_n(c->n_fields, { x, s }));
 	return dev_add_source(c, c->f[x], c->f[s], dt);
 }
 
@@ -1193,14 +1235,14 @@ extern "C" int fluid_ctx_set_bnd(fluid_ctx* c, int b, int x)
 extern "C" int fluid_ctx_lin_solve(fluid_ctx* c, int b, int x, int x0, float a, float cc)
 {
 	CHECK_CTX(c);
-	FL_TRY(check_distinct({ x, x0 }));
+	FL_TRY(check_distinct_n(c->n_fields, { x, x0 }));
 	return dev_lin_solve(c, b, c->f[x], c->f[x0], a, cc);
 }
 
 extern "C" int fluid_ctx_blur(fluid_ctx* c, int b, int x, int x0, float a, float cc)
 {
 	CHECK_CTX(c);
-	FL_TRY(check_distinct({ x, x0 }));
+	FL_TRY(check_distinct_n(c->n_fields, { x, x0 }));
 	return dev_blur(c, b, c->f[x], c->f[x0], a, cc);
 }
 
@@ -1208,7 +1250,7 @@ extern "C" int fluid_ctx_advect(fluid_ctx* c, int b, int d, int d0, int u, int v
 {
 	CHECK_CTX(c);
 	FL_TRY(check_field(d0));
-	FL_TRY(check_distinct({ d, u, v }));
+	FL_TRY(check_distinct_n(c->n_fields, { d, u, v }));
 	if (d == d0) return fail(FLUID_ERR_INVALID, "advect: d and d0 must be different arrays");
 	return dev_advect(c, b, c->f[d], c->f[d0], c->f[u], c->f[v], dt);
 }
@@ -1216,14 +1258,14 @@ extern "C" int fluid_ctx_advect(fluid_ctx* c, int b, int d, int d0, int u, int v
 extern "C" int fluid_ctx_advect_velocity(fluid_ctx* c, int u, int v, int u0, int v0, float dt)
 {
 	CHECK_CTX(c);
-	FL_TRY(check_distinct({ u, v, u0, v0 }));
+	FL_TRY(check_distinct_n(c->n_fields, { u, v, u0, v0 }));
 	return dev_advect_velocity(c, c->f[u], c->f[v], c->f[u0], c->f[v0], dt);
 }
 
 extern "C" int fluid_ctx_project(fluid_ctx* c, int u, int v, int p, int div)
 {
 	CHECK_CTX(c);
-	FL_TRY(check_distinct({ u, v, p, div }));
+	FL_TRY(check_distinct_n(c->n_fields, { u, v, p, div }));
 	return dev_project(c, c->f[u], c->f[v], c->f[p], c->f[div]);
 }
 

@@ -345,9 +345,10 @@ struct SourceDev {
 	float value;
 };
 
+// index 0 = u, 1 = v, 2 + k = density of fluid k
 struct FieldPtrs {
-	float* cur[3];
-	float* prev[3];
+	float* cur[2 + 8];
+	float* prev[2 + 8];
 };
 
 __global__ void k_apply_sources(GridDesc g, FieldPtrs f, const SourceDev* __restrict__ src,

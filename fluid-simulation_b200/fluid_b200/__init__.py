@@ -32,7 +32,7 @@ EXPORTS = [
     "fluid_project", "fluid_vel_step", "fluid_dens_step", "fluid_update", "fluid_vort_confinement", "fluid_damp",
     "fluid_params_default", "fluid_ctx_create", "fluid_ctx_destroy", "fluid_ctx_clear", "fluid_ctx_upload",
     "fluid_ctx_download", "fluid_ctx_set_sources", "fluid_ctx_vel_step", "fluid_ctx_dens_step", "fluid_ctx_step",
-    "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs",
+    "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs", "fluid_ctx_set_fluid",
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_set_fast_division", "fluid_ctx_division_window", "fluid_ctx_set_small_grid_kernels",
     "fluid_ctx_set_wavefront_tile", "fluid_ctx_render",
@@ -55,7 +55,7 @@ class Params(ctypes.Structure):
                 ("advect_mode", ctypes.c_int), ("device", ctypes.c_int), ("visc", ctypes.c_float),
                 ("diff", ctypes.c_float), ("vorticity", ctypes.c_float), ("damp", ctypes.c_float),
                 ("slab_index", ctypes.c_int), ("slab_count", ctypes.c_int), ("slab_rows", ctypes.c_int),
-                ("slab_halo", ctypes.c_int), ("reserved", ctypes.c_int * 2)]
+                ("slab_halo", ctypes.c_int), ("n_fluids", ctypes.c_int), ("reserved", ctypes.c_int * 1)]
 
 
 class Source(ctypes.Structure):
@@ -113,6 +113,7 @@ def lib():
     L.fluid_ctx_last_step_ms.argtypes = [_vp, ctypes.POINTER(_cf)]
     L.fluid_ctx_set_modes.argtypes = [_vp, _ci, _ci, _ci]
     L.fluid_ctx_set_coeffs.argtypes = [_vp, _cf, _cf, _cf, _cf]
+    L.fluid_ctx_set_fluid.argtypes = [_vp, _ci, _cf, _cf]
     L.fluid_ctx_set_tuning.argtypes = [_vp, _ci]
     L.fluid_ctx_set_fast_division.argtypes = [_vp, _ci]
     L.fluid_ctx_set_small_grid_kernels.argtypes = [_vp, _ci]
@@ -138,6 +139,15 @@ def lib():
     L.fluid_lin_solve_rb_static.argtypes = [_ci, _ci, _vp, _vp, _cf, _cf, _ci, _vp]
     _lib = L
     return L
+
+
+def dens_of(k):
+    """Field id of the density of fluid k (FLUID_DENS_OF in the header)."""
+    return DENS if k == 0 else 4 + 2 * k
+
+
+def dens_prev_of(k):
+    return DENS_PREV if k == 0 else 5 + 2 * k
 
 
 def check(rc):
@@ -193,13 +203,14 @@ class FluidSystem:
         self.batch = 1
 
     def Setup(self, N, visc=0.0, diff=0.0, vorticity=0.0, damp=0.0, gs_order=GS_WAVEFRONT, gs_iters=20,
-              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1, slab=None, slab_halo=0):
+              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1, slab=None, slab_halo=0, n_fluids=1):
         """slab = (index, count, rows): this context is one row slab of a global N x (rows*count) grid."""
         self.close()
         p = Params()
         lib().fluid_params_default(ctypes.byref(p))
         p.N, p.batch, p.gs_iters, p.gs_order, p.advect_mode, p.device = N, batch, gs_iters, gs_order, advect_mode, device
         p.visc, p.diff, p.vorticity, p.damp = visc, diff, vorticity, damp
+        p.n_fluids = n_fluids
         self.NYG = N
         if slab is not None:
             p.slab_index, p.slab_count, p.slab_rows = slab
@@ -273,6 +284,10 @@ class FluidSystem:
 
     def SetModes(self, gs_order, gs_iters=20, advect_mode=ADVECT_MIDPOINT):
         check(lib().fluid_ctx_set_modes(self.h, gs_order, gs_iters, advect_mode))
+
+    def SetFluid(self, k, diff, visc):
+        """FluidProps of fluid k (its viscosity enters through visc_avg, FluidSystem.cpp:26-30)."""
+        check(lib().fluid_ctx_set_fluid(self.h, k, diff, visc))
 
     def SetCoeffs(self, visc, diff, vorticity=0.0, damp=0.0):
         check(lib().fluid_ctx_set_coeffs(self.h, visc, diff, vorticity, damp))

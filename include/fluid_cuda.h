@@ -61,6 +61,11 @@ typedef enum fluid_field {
 	FLUID_U_PREV = 3, FLUID_V_PREV = 4, FLUID_DENS_PREV = 5,
 	FLUID_FIELD_COUNT = 6
 } fluid_field;
+/* More than one fluid (fluid_params.n_fluids, the reference's densList, FluidSystem.h:160): the
+ * Curr / Prev density fields of fluid k >= 1 have the ids below; fluid 0 keeps FLUID_DENS(_PREV). */
+#define FLUID_MAX_FLUIDS 8
+#define FLUID_DENS_OF(k) ((k) == 0 ? (int) FLUID_DENS : 4 + 2 * (k))
+#define FLUID_DENS_PREV_OF(k) ((k) == 0 ? (int) FLUID_DENS_PREV : 5 + 2 * (k))
 
 /* How a forcing entry is applied each step (between the zero fill of the Prev
  * arrays and the velocity step, i.e. where FluidSystem::Update calls its
@@ -96,7 +101,8 @@ typedef struct fluid_params {
 	 * grid, plus slab_halo halo rows towards each neighbour.  slab_count <= 1: whole grid. */
 	int slab_index, slab_count, slab_rows;
 	int slab_halo;    /* 0 = default 48 rows; >= 44 */
-	int reserved[2];  /* must be 0 */
+	int n_fluids;     /* density fields advanced by dens_step (fluid_count, FluidSystem.cpp:21); 0 = 1 */
+	int reserved[1];  /* must be 0 */
 } fluid_params;
 
 typedef struct fluid_ctx fluid_ctx;
@@ -197,6 +203,10 @@ int fluid_ctx_last_step_ms(fluid_ctx *ctx, float *ms);
  * members of FluidSystem, FluidSystem.h:142-152). */
 int fluid_ctx_set_modes(fluid_ctx *ctx, int gs_order, int gs_iters, int advect_mode);
 int fluid_ctx_set_coeffs(fluid_ctx *ctx, float visc, float diff, float vorticity, float damp);
+/* FluidProps of fluid k (FluidCode.h:46-59): its diffusion coefficient, and its viscosity, which
+ * enters the velocity step through visc_avg = mean over the fluids (FluidSystem.cpp:26-30).
+ * fluid_ctx_set_coeffs / fluid_params set fluid 0 and are copied to the others until this is called. */
+int fluid_ctx_set_fluid(fluid_ctx *ctx, int k, float diff, float visc);
 /* Kernel selection for FLUID_GS_REDBLACK: sweeps fused per shared-memory tile
  * residency (2 = default, 1; 0 = one kernel launch per colour).  Results are
  * bit-identical for every setting; only the memory traffic differs. */

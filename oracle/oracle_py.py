@@ -157,6 +157,10 @@ class Ref:
         L = self.L = ctypes.CDLL(path)
         L.ref_create.restype = c_void_p
         L.ref_create.argtypes = [c_int, c_float, c_float, c_float, c_int, c_int, c_float]
+        L.ref_create_multi.restype = c_void_p
+        L.ref_create_multi.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_int, c_int, c_float]
+        L.ref_density.restype = ctypes.POINTER(c_float)
+        L.ref_density.argtypes = [c_void_p, c_int, c_int]
         L.ref_destroy.argtypes = [c_void_p]
         L.ref_set_sources.argtypes = [c_void_p, c_int] + [c_void_p] * 5
         L.ref_field.restype = ctypes.POINTER(c_float)
@@ -178,9 +182,18 @@ class Ref:
         L.ref_project.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int]
 
     class Sim:
-        def __init__(self, ref, N, visc, diff, vorticity=0.0, iters=20, damp=0.0):
+        def __init__(self, ref, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None):
+            """fluids: optional list of (diff, visc) per fluid (source field ids 2+k address fluid k)."""
             self.ref, self.N = ref, N
-            self.h = ref.L.ref_create(N, visc, diff, vorticity, iters, 1 if vorticity != 0.0 else 0, damp)
+            if fluids:
+                d = np.array([f[0] for f in fluids], np.float32)
+                v = np.array([f[1] for f in fluids], np.float32)
+                self.h = ref.L.ref_create_multi(N, len(fluids), d, v, vorticity, iters, 1 if vorticity != 0.0 else 0, damp)
+            else:
+                self.h = ref.L.ref_create(N, visc, diff, vorticity, iters, 1 if vorticity != 0.0 else 0, damp)
+
+        def density(self, fluid, prev=False):
+            return np.ctypeslib.as_array(self.ref.L.ref_density(self.h, fluid, 1 if prev else 0), ((self.N + 2) ** 2,))
 
         def set_sources(self, sources):
             n = len(sources)
@@ -210,5 +223,5 @@ class Ref:
                 self.ref.L.ref_destroy(self.h)
                 self.h = None
 
-    def sim(self, N, visc, diff, vorticity=0.0, iters=20, damp=0.0):
-        return Ref.Sim(self, N, visc, diff, vorticity, iters, damp)
+    def sim(self, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None):
+        return Ref.Sim(self, N, visc, diff, vorticity, iters, damp, fluids)

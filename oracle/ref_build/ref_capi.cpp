@@ -41,7 +41,7 @@ struct SourceEntry { int field, i, j, mode; float value; };
 
 // Synthetic forcing, injected the way the reference's own updaters are
 // (Tools::UpdatableR<bool, FluidUpdate>, FluidSystem.cpp:278-287).
-// field: 0=u 1=v 2=dens;  mode: 0 = write Prev (Stam-style source, relies on
+// field: 0=u 1=v 2+k=density of fluid k;  mode: 0 = write Prev (Stam-style source, relies on
 // Update's zero fill, FluidSystem.cpp:104-109), 1 = Curr +=, 2 = Curr =
 // (the last two are what Blower/AddFluid do, FluidSystem.cpp:250-257).
 class SourceUpdater : public Tools::UpdatableR<bool, FluidUpdate> {
@@ -52,7 +52,7 @@ public:
 		if (fu.type != FluidUpdate::VEL) return true;
 		FluidSystem* fs = fu.fs;
 		for (const SourceEntry& e : entries) {
-			FlipFlopArr<real>& f = e.field == 0 ? fs->vX : (e.field == 1 ? fs->vY : fs->densList[0]);
+			FlipFlopArr<real>& f = e.field == 0 ? fs->vX : (e.field == 1 ? fs->vY : fs->densList[e.field - 2]);
 			int id = fs->ID(e.i, e.j);
 			if (e.mode == 0) f.Prev()[id] = e.value;
 			else if (e.mode == 1) f.Curr()[id] += e.value;
@@ -98,6 +98,31 @@ void* ref_create(int N, float visc, float diff, float vorticity, int steps, int 
 	s->src = new SourceUpdater();
 	s->fs.AddUpdater(s->src);
 	return s;
+}
+
+// Several fluids, each with its own FluidProps (FluidCode.h:46-59): what the shipped scene sets up
+// (SystemManager.cpp:103-108), but on the ORIGINAL pipeline.
+void* ref_create_multi(int N, int nfluids, const float* diffs, const float* viscs, float vorticity, int steps, int use_vort,
+		       float damp)
+{
+	RefSim* s = new RefSim();
+	std::vector<FluidProps> props;
+	for (int k = 0; k < nfluids; k++) props.push_back({ { diffs[k], viscs[k] }, { 1.0f, 1.0f, 1.0f } });
+	s->fs.Setup(N, vorticity, props, FluidSystem::FSType::ORIGINAL);
+	s->fs.steps = steps;
+	s->fs.useVort = use_vort != 0;
+	s->fs.damp = damp;
+	s->fs.Clear();
+	std::fill(s->fs.p.begin(), s->fs.p.end(), 0.0f);
+	s->src = new SourceUpdater();
+	s->fs.AddUpdater(s->src);
+	return s;
+}
+
+float* ref_density(void* h, int fluid, int prev)
+{
+	RefSim* s = (RefSim*) h;
+	return prev ? s->fs.densList[fluid].Prev().data() : s->fs.densList[fluid].Curr().data();
 }
 
 void ref_destroy(void* h)

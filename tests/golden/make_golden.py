@@ -107,7 +107,25 @@ def fields():
     return z
 
 
+def multifluid():
+    """Two fluids with the shipped scene's properties (SystemManager.cpp:103-106) on the ORIGINAL
+    pipeline: visc_avg couples them through the velocity step, each diffuses with its own coefficient."""
+    N, steps = 48, 12
+    fluids = [(0.000001, 0.0001), (0.0001, 0.0003)]  # (diff, visc)
+    c = N // 2
+    # source field ids: 0=u 1=v 2=fluid 0 3=fluid 1
+    src = [(2, c, c, 0, 100.0), (3, c - 7, c + 5, 0, 60.0), (0, c, c, 0, 5.0), (1, c, c, 0, 5.0), (3, 4, 4, 1, 0.9)]
+    sim = R.sim(N, 0, 0, 0.0, 20, 0.0, fluids=fluids)
+    sim.set_sources(src)
+    sim.update(0.1, steps)
+    z = dict(N=np.int32(N), steps=np.int32(steps), fluids=np.array(fluids, np.float32), sources=np.array(src, np.float64),
+             u=sim.field(0).copy(), v=sim.field(1).copy(), d0=sim.density(0).copy(), d1=sim.density(1).copy())
+    sim.close()
+    return z
+
+
 if __name__ == "__main__":
+    np.savez_compressed(os.path.join(HERE, "golden_multifluid.npz"), **multifluid())
     json.dump(dict(generator="tests/golden/make_golden.py", reference="surajiyer/Fluid-Simulation FluidSystem.cpp (unmodified)",
                    compiler="g++ -std=c++20 -O2 -ffp-contract=off", frames=frames()),
               open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1)

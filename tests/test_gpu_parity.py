@@ -492,3 +492,33 @@ def test_headless_render_matches_restated_renderer_loop(fl, oracle):
     g = px.reshape(N + 2, N + 2, 3)
     assert np.all(g[0, :, 1] == 1) and np.all(g[0, :, 0] == 0)  # outer ring is green
     fs.close()
+
+
+@pytest.mark.parametrize("order", [0, 1])
+def test_two_fluids_resident_context(fl, oracle, order):
+    """n_fluids = 2 (the reference's densList): visc_avg couples the fluids, each diffuses with its own
+    coefficient.  Reference order vs the golden file made by the unmodified reference; red-black vs the
+    oracle construction that test_oracle.py pins against the same file."""
+    import os
+    from conftest import GOLDEN
+    from test_oracle import multifluid_expected
+    G = np.load(os.path.join(GOLDEN, "golden_multifluid.npz"))
+    N, steps = int(G["N"]), int(G["steps"])
+    fluids = [tuple(map(float, row)) for row in G["fluids"]]
+    fs = fl.FluidSystem().Setup(N, gs_order=order, n_fluids=2)
+    for k, (diff, visc) in enumerate(fluids):
+        fs.SetFluid(k, diff, visc)
+    src = []
+    for s in G["sources"]:
+        fid = int(s[0]) if s[0] < 2 else fl.dens_of(int(s[0]) - 2)
+        src.append((fid, int(s[1]), int(s[2]), int(s[3]), float(s[4])))
+    fs.SetSources(src)
+    fs.Update(0.1, steps)
+    want = {k: G[k] for k in ("u", "v", "d0", "d1")} if order == 0 else multifluid_expected(oracle, N, steps, fluids, G["sources"], order=1)
+    assert_bits(fs.GetVelX(), want["u"], "u")
+    assert_bits(fs.GetVelY(), want["v"], "v")
+    assert_bits(fs.download(fl.dens_of(0)), want["d0"], "fluid 0")
+    assert_bits(fs.download(fl.dens_of(1)), want["d1"], "fluid 1")
+    with pytest.raises(fl.FluidError):
+        fs.SetFluid(2, 0.0, 0.0)
+    fs.close()

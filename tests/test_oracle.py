@@ -166,3 +166,38 @@ def test_projection_reduces_divergence(oracle):
     p, dv = np.zeros_like(u), np.zeros_like(u)
     oracle.project(N, u, v, p, dv, 200)
     assert div_norm(u, v) < 0.2 * before
+
+
+def _visc_avg(fluids):
+    """visc_avg as the reference computes it (FluidSystem.cpp:26-30): float sum, then float division."""
+    v = np.float32(0)
+    for _, visc in fluids:
+        v = np.float32(v + np.float32(visc))
+    return np.float32(v / np.float32(len(fluids)))
+
+
+def multifluid_expected(oracle, N, steps, fluids, sources, order=0):
+    """On the ORIGINAL pipeline the fluids only interact through visc_avg (DensStep1 loops over them,
+    FluidSystem.cpp:289-299; VelStep1 never reads a density), so fluid k's density is what a one-fluid
+    run with visc = visc_avg, diff = diff_k and fluid k's density sources produces."""
+    va = _visc_avg(fluids)
+    out = {}
+    for k, (diff, _) in enumerate(fluids):
+        src = [(2 if s[0] >= 2 else int(s[0]), int(s[1]), int(s[2]), int(s[3]), float(s[4])) for s in sources
+               if s[0] < 2 or int(s[0]) == 2 + k]
+        f = {n: np.zeros((N + 2) ** 2, np.float32) for n in "u v d u0 v0 d0".split()}
+        oracle.update(N, f, src, float(va), float(diff), 0.1, steps, order=order)
+        out["d%d" % k] = f["d"]
+        out["u"], out["v"] = f["u"], f["v"]
+    return out
+
+
+def test_multifluid_golden_from_the_reference(oracle):
+    import os
+    from conftest import GOLDEN
+    G = np.load(os.path.join(GOLDEN, "golden_multifluid.npz"))
+    N, steps = int(G["N"]), int(G["steps"])
+    fluids = [tuple(map(float, row)) for row in G["fluids"]]
+    want = multifluid_expected(oracle, N, steps, fluids, G["sources"])
+    for k in ("u", "v", "d0", "d1"):
+        assert_bits(want[k], G[k], "two fluids, " + k)
