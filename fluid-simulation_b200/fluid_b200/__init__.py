@@ -41,6 +41,8 @@ EXPORTS = [
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
     "fluid_lin_solve_rb_static",
+    "fluid_multi_create", "fluid_multi_destroy", "fluid_multi_count", "fluid_multi_set_sources", "fluid_multi_upload",
+    "fluid_multi_download", "fluid_multi_step", "fluid_multi_sync", "fluid_multi_last_step_ms",
 ]
 
 
@@ -137,6 +139,15 @@ def lib():
     L.fluid_ctx_project.argtypes = [_vp, _ci, _ci, _ci, _ci]
     L.fluid_ctx_time_kernel.argtypes = [_vp, _ci, _ci, ctypes.POINTER(_cf)]
     L.fluid_lin_solve_rb_static.argtypes = [_ci, _ci, _vp, _vp, _cf, _cf, _ci, _vp]
+    L.fluid_multi_create.argtypes = [ctypes.POINTER(Params), _ci, ctypes.POINTER(_ci), ctypes.POINTER(_vp)]
+    L.fluid_multi_destroy.argtypes = [_vp]
+    L.fluid_multi_count.argtypes = [_vp]
+    L.fluid_multi_set_sources.argtypes = [_vp, _ci, _vp]
+    L.fluid_multi_upload.argtypes = [_vp, _ci, _f32]
+    L.fluid_multi_download.argtypes = [_vp, _ci, _f32]
+    L.fluid_multi_step.argtypes = [_vp, _cf, _ci]
+    L.fluid_multi_sync.argtypes = [_vp]
+    L.fluid_multi_last_step_ms.argtypes = [_vp, ctypes.POINTER(_cf)]
     _lib = L
     return L
 
@@ -350,3 +361,45 @@ class FluidSystem:
         ms = _cf()
         check(lib().fluid_ctx_time_kernel(self.h, which, reps, ctypes.byref(ms)))
         return ms.value
+
+
+class FluidMulti:
+    """fluid_multi_*: several GPUs (or several slabs on one GPU) from one process, peer-copy halos."""
+
+    def __init__(self, N, rows, devices, visc=0.0, diff=0.0, gs_iters=20, advect_mode=ADVECT_MIDPOINT, slab_halo=0):
+        self.h = None
+        p = Params()
+        lib().fluid_params_default(ctypes.byref(p))
+        p.N, p.gs_iters, p.gs_order, p.advect_mode = N, gs_iters, GS_REDBLACK, advect_mode
+        p.visc, p.diff, p.slab_rows, p.slab_halo = visc, diff, rows, slab_halo
+        dev = (ctypes.c_int * len(devices))(*devices)
+        h = _vp()
+        check(lib().fluid_multi_create(ctypes.byref(p), len(devices), dev, ctypes.byref(h)))
+        self.h, self.N, self.NYG = h, N, rows * len(devices)
+
+    def SetSources(self, sources):
+        sources = list(sources)
+        arr = (Source * max(1, len(sources)))(*[Source(*s) for s in sources])
+        check(lib().fluid_multi_set_sources(self.h, len(sources), ctypes.cast(arr, _vp)))
+
+    def upload(self, field, host_global): check(lib().fluid_multi_upload(self.h, field, host_global))
+
+    def download(self, field):
+        out = np.zeros((self.N + 2) * (self.NYG + 2), np.float32)
+        check(lib().fluid_multi_download(self.h, field, out))
+        return out
+
+    def Update(self, dt, nsteps=1): check(lib().fluid_multi_step(self.h, dt, nsteps))
+    def Sync(self): check(lib().fluid_multi_sync(self.h))
+
+    def LastStepMs(self):
+        ms = _cf()
+        check(lib().fluid_multi_last_step_ms(self.h, ctypes.byref(ms)))
+        return ms.value
+
+    def close(self):
+        if self.h:
+            lib().fluid_multi_destroy(self.h)
+            self.h = None
+
+    __del__ = close

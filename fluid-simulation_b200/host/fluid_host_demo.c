@@ -5,7 +5,8 @@
  * out.  It owns the loop and the forcing and calls only the extern "C" layer
  * of include/fluid_cuda.h -- this is what "host code stays in C" looks like.
  *
- * usage: fluid_host_demo [N=64] [steps=100] [visc=1e-4] [diff=1e-4] [order=0|1] [batch=1]
+ * usage: fluid_host_demo [N=64] [steps=100] [visc=1e-4] [diff=1e-4] [order=0|1] [batch=1] [gpus=1]
+ *        gpus > 1: N rows per GPU (global grid N x N*gpus), red-black, peer-copy halos (fluid_multi_*)
  */
 #include <stdint.h>
 #include <stdio.h>
@@ -32,6 +33,35 @@ static uint64_t fnv1a64(const void *p, size_t n)
 		}                                                                          \
 	} while (0)
 
+/* several GPUs from this one C process: row slabs, halos by peer copies */
+static int run_multi(fluid_params p, int steps, int gpus)
+{
+	int dev[64];
+	if (gpus > 64) gpus = 64;
+	for (int k = 0; k < gpus; k++) dev[k] = k;
+	p.slab_rows = p.N;
+	p.batch = 1;
+	fluid_multi *m;
+	CHECK(fluid_multi_create(&p, gpus, dev, &m));
+	const int cx = p.N / 2, cy = p.N * gpus / 2;
+	fluid_source src[3] = {
+		{ FLUID_DENS, cx, cy, FLUID_SRC_PREV_SET, 100.0f },
+		{ FLUID_U, cx, cy, FLUID_SRC_PREV_SET, 5.0f },
+		{ FLUID_V, cx, cy, FLUID_SRC_PREV_SET, 5.0f },
+	};
+	CHECK(fluid_multi_set_sources(m, 3, src));
+	CHECK(fluid_multi_step(m, 0.1f, 3)); /* warm-up */
+	CHECK(fluid_multi_sync(m));
+	CHECK(fluid_multi_step(m, 0.1f, steps));
+	CHECK(fluid_multi_sync(m));
+	float ms = 0;
+	CHECK(fluid_multi_last_step_ms(m, &ms));
+	printf("N=%d x %d rows on %d GPUs, steps=%d red-black: %.3f ms/step, %.4g cell-updates/s\n", p.N, p.N * gpus, gpus, steps,
+	       ms / (steps > 0 ? steps : 1), steps > 0 ? (double) p.N * p.N * gpus * steps / (ms * 1e-3) : 0.0);
+	CHECK(fluid_multi_destroy(m));
+	return 0;
+}
+
 int main(int argc, char **argv)
 {
 	fluid_params p;
@@ -42,6 +72,8 @@ int main(int argc, char **argv)
 	p.diff = argc > 4 ? (float) atof(argv[4]) : 1e-4f;
 	p.gs_order = argc > 5 ? atoi(argv[5]) : FLUID_GS_WAVEFRONT;
 	p.batch = argc > 6 ? atoi(argv[6]) : 1;
+	const int gpus = argc > 7 ? atoi(argv[7]) : 1;
+	if (gpus > 1) return run_multi(p, steps, gpus);
 
 	fluid_ctx *ctx;
 	CHECK(fluid_ctx_create(&p, &ctx));

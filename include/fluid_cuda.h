@@ -253,6 +253,23 @@ int fluid_ctx_set_stream(fluid_ctx *ctx, void *stream, int exchange_stream_order
 int fluid_ctx_halo_regions(fluid_ctx *ctx, int field, float **send_down, float **recv_down, float **send_up, float **recv_up,
 			   size_t *count);
 
+/* Several GPUs from one plain-C process: `ndev` row slabs of p->slab_rows rows each (global grid
+ * N x slab_rows*ndev) on devices[0..ndev), stepped together; halos move by peer copies
+ * (cudaMemcpyPeerAsync over NVLink) ordered by CUDA events only -- no stream is drained and the
+ * host never waits for the device.  A device may be listed more than once (used by the tests to
+ * run the multi-GPU path on one GPU).  upload/download take the GLOBAL dense array, forcing
+ * entries use global rows, relaxation is FLUID_GS_REDBLACK.  No counterpart in the reference. */
+typedef struct fluid_multi fluid_multi;
+int fluid_multi_create(const fluid_params *p, int ndev, const int *devices, fluid_multi **out);
+int fluid_multi_destroy(fluid_multi *m);
+int fluid_multi_count(fluid_multi *m);
+int fluid_multi_set_sources(fluid_multi *m, int n, const fluid_source *src);
+int fluid_multi_upload(fluid_multi *m, int field, const float *host_global);
+int fluid_multi_download(fluid_multi *m, int field, float *host_global);
+int fluid_multi_step(fluid_multi *m, float dt, int nsteps);   /* returns when the work is enqueued */
+int fluid_multi_sync(fluid_multi *m);
+int fluid_multi_last_step_ms(fluid_multi *m, float *ms);     /* slowest device */
+
 /* Slab-local transfers: `host` holds exactly the rows this context stores (halo
  * rows included), dense, (N+2) floats per row; fluid_ctx_local_rows tells how
  * many rows that is and which global row the first one is. */
