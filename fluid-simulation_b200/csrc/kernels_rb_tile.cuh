@@ -192,13 +192,22 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	}
 	__syncthreads();
 
-	// Tile coordinates (column, row, ensemble member) are advanced incrementally by
-	// gridDim.x tiles: integer division costs ~60 instructions per warp per use.
+	// Tile coordinates (column, row, ensemble member), advanced by gridDim.x tiles per iteration with
+	// two divisions by small constants-per-launch (a subtract loop took 49 rounds per step on an
+	// ensemble of 3-tile-wide grids; decoding the linear index afresh costs three divisions).
 	struct TilePos { int tx, ty, sim; };
 	auto advance = [&](TilePos q, int by) {
 		q.tx += by;
-		while (q.tx >= ntx) { q.tx -= ntx; q.ty++; }
-		while (q.ty >= nty) { q.ty -= nty; q.sim++; }
+		if (q.tx >= ntx) {
+			const int carry = q.tx / ntx;
+			q.tx -= carry * ntx;
+			q.ty += carry;
+			if (q.ty >= nty) {
+				const int c2 = q.ty / nty;
+				q.ty -= c2 * nty;
+				q.sim += c2;
+			}
+		}
 		return q;
 	};
 	auto edge_tile = [&](int tx0, int ty0) { // window reaches a wall, or the tile is partial
@@ -280,16 +289,13 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 			// are inside, then the border cells that mirror the wall-adjacent cells of this tile
 			const int rows_in = min(TY, g.NY - ty0), cols_in = min(TX, g.N - tx0);
 			const int groups = cols_in / 4;
-			for (int idx = tid; idx < rows_in * groups; idx += NT) {
-				const int r = idx / groups, cv = idx - r * groups;
-				const float* sp = tile + (HY + r) * RX + HX + 4 * cv;
-				float* d = xout + cell(g, tx0 + 1 + 4 * cv, ty0 + 1 + r);
-				*reinterpret_cast<float4*>(d) = *reinterpret_cast<const float4*>(sp);
-			}
-			const int tail = cols_in - 4 * groups; // 0..3 leftover columns at the right wall
-			for (int idx = tid; idx < rows_in * tail; idx += NT) {
-				const int r = idx / tail, cc = 4 * groups + (idx - r * tail);
-				xout[cell(g, tx0 + 1 + cc, ty0 + 1 + r)] = tile[(HY + r) * RX + HX + cc];
+			for (int r = w; r < rows_in; r += NW) { // a warp per row, a lane per float4 / per leftover column
+				const float* sp = tile + (HY + r) * RX + HX;
+				float* d = xout + cell(g, tx0 + 1, ty0 + 1 + r);
+				for (int cv = lane; cv < groups; cv += 32)
+					*reinterpret_cast<float4*>(d + 4 * cv) = *reinterpret_cast<const float4*>(sp + 4 * cv);
+				const int cc = 4 * groups + lane; // 0..3 leftover columns at the right wall
+				if (cc < cols_in) d[cc] = sp[cc];
 			}
 			// walls: left/right columns and bottom/top rows of the grid that fall into this tile
 			const bool wl = (tx0 == 0), wr = (tx0 + cols_in == g.N), wb = (ty0 == 0), wt = (ty0 + rows_in == g.NY);
