@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 
 // ---------------------------------------------------------------------------
 // Red-black Gauss-Seidel, one colour per launch (baseline fast path; the
-// temporally blocked kernel in kernels_rb_tma.cuh supersedes it where it
+// temporally blocked kernel in kernels_rb_tile.cuh supersedes it where it
 // applies).  colour 0 = (i+j) even.  One thread = one float4 group of a row:
 // two cells of the active colour.  Border cells are rewritten by the thread
 // that updates the cell they mirror, which is equivalent to SetBorder after
