@@ -39,6 +39,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=8192, help="interior cells per side per GPU (BASELINE config 3: 8192)")
     ap.add_argument("--order", default="redblack", choices=["redblack", "wavefront"])
+    ap.add_argument("--strong", action="store_true", help="N>1 GPUs: split ONE N x N grid into row slabs (strong scaling) "
+                    "instead of N rows per GPU (weak scaling, the default)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -240,11 +242,15 @@ def run_b200(args):
         if order != fl.GS_REDBLACK:
             raise SystemExit("bench.py: row slabs need --order redblack")
         from fluid_b200.slabs import NcclExchange
-        fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local, slab=(rank, world, N))
+        rows = N // world if args.strong else N
+        if args.strong and N % world:
+            raise SystemExit("bench.py --strong: N must be divisible by the number of GPUs")
+        fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local, slab=(rank, world, rows))
         transport = NcclExchange(fs, rank, world, local)
     else:
         fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local)
-    c, cy = N // 2, (N * world) // 2
+    rows_per_gpu = (N // world) if (world > 1 and args.strong) else N
+    c, cy = N // 2, (rows_per_gpu * world) // 2
     fs.SetSources([(fl.DENS, c, cy, fl.SRC_PREV_SET, 100.0), (fl.U, c, cy, fl.SRC_PREV_SET, 5.0),
                    (fl.V, c, cy, fl.SRC_PREV_SET, 5.0)])
     # spin-up + warm-up (untimed)
@@ -272,7 +278,7 @@ def run_b200(args):
     fs.SetProfiling(False)
     ms = max_over_ranks(dist, local, dev_ms)
     wall_ms = max_over_ranks(dist, local, wall_ms)
-    cells = float(N) * N * world
+    cells = float(N) * rows_per_gpu * world
     value = cells * args.steps / (ms * 1e-3)
 
     # roofline of the dominant kernel class (Gauss-Seidel sweeps), measured inside the timed region
@@ -301,7 +307,7 @@ def run_b200(args):
         if world == 1:
             e2e = measure_e2e(fl, np, N, order, max(1, min(args.steps, 5)), dist, local, world)
         else:
-            e2e = measure_e2e_slabs(fl, fs, N, max(1, min(args.steps, 5)), dist, local, world)
+            e2e = measure_e2e_slabs(fl, fs, N, rows_per_gpu, max(1, min(args.steps, 5)), dist, local, world)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_single()
@@ -310,7 +316,7 @@ def run_b200(args):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and args.strong) else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "N=%d single-GPU throughput run (BASELINE config 3): dt=0.1 visc=diff=1e-4, 20 GS iterations, "
                                    "%s relaxation, source S1 (dens 100, u=v=5 at the centre cell each step)" % (N, args.order),
@@ -319,7 +325,7 @@ def run_b200(args):
                        "parallelism": "1 GPU" if world == 1 else
                        "%d row slabs of %d rows (global grid %d x %d, h=1/%d), 48-row overlapped halos refreshed at 6 points per step "
                        "over NCCL send/recv between neighbouring ranks (%d exchange calls, %.1f MB sent per rank per step, timed)"
-                       % (world, N, N, N * world, N, xcalls // args.steps, xbytes / args.steps / 1e6)},
+                       % (world, rows_per_gpu, N, rows_per_gpu * world, N, xcalls // args.steps, xbytes / args.steps / 1e6)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": roofline, "cpu_baseline": cpu,
         }
@@ -329,7 +335,7 @@ def run_b200(args):
     return 0
 
 
-def measure_e2e_slabs(fl, fs, N, steps, dist, local, world):
+def measure_e2e_slabs(fl, fs, N, rows_per_gpu, steps, dist, local, world):
     """N GPUs: each rank uploads the rows it stores (u, v, dens; pinned host memory), advances one
     step (halo exchanges included) and downloads them again, every step, through the context API."""
     import torch
@@ -355,7 +361,7 @@ def measure_e2e_slabs(fl, fs, N, steps, dist, local, world):
         one()
     torch.cuda.synchronize(local)
     dt = max_over_ranks(dist, local, time.perf_counter() - t0)
-    return {"value": float(N) * N * world * steps / dt, "unit": UNIT, "h2d_bytes_per_step": 3 * n * 4 * world,
+    return {"value": float(N) * rows_per_gpu * world * steps / dt, "unit": UNIT, "h2d_bytes_per_step": 3 * n * 4 * world,
             "d2h_bytes_per_step": 3 * n * 4 * world, "steps": steps,
             "api": "fluid_ctx_upload_local x3 + fluid_ctx_step + fluid_ctx_download_local x3 per rank (host pointers, pinned)"}
 

@@ -768,6 +768,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	if (p->advect_mode != FLUID_ADVECT_MIDPOINT && p->advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", p->advect_mode);
 	for (int r : p->reserved) if (r != 0) return fail(FLUID_ERR_INVALID, "reserved fields must be 0");
 	if (p->n_fluids < 0 || p->n_fluids > FLUID_MAX_FLUIDS) return fail(FLUID_ERR_INVALID, "n_fluids=%d out of range [1,%d]", p->n_fluids, FLUID_MAX_FLUIDS);
+	if (p->slab_rows < 0 || p->slab_rows > 1048576) return fail(FLUID_ERR_INVALID, "slab_rows=%d out of range", p->slab_rows);
 	if (p->slab_count < 0 || (p->slab_count > 1 && (p->slab_index < 0 || p->slab_index >= p->slab_count)))
 		return fail(FLUID_ERR_INVALID, "slab_index=%d / slab_count=%d is not a valid slab", p->slab_index, p->slab_count);
 	if (p->slab_count > 1) {
@@ -806,6 +807,11 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	c->g.j0 = 0;
 	c->g.NYG = p->N;
 	c->g.walls = 3;
+	if (p->slab_count <= 1 && p->slab_rows > 0) {
+		// a whole (non-square) grid of N columns x slab_rows rows on one device; h = 1/N as for slabs
+		c->g.NY = p->slab_rows;
+		c->g.NYG = p->slab_rows;
+	}
 	if (p->slab_count > 1) {
 		// rank `slab_index` of `slab_count` owns `slab_rows` rows of a global N x (slab_rows*slab_count) grid
 		c->slab_index = p->slab_index;
@@ -1816,10 +1822,9 @@ extern "C" int fluid_multi_create(const fluid_params* p, int ndev, const int* de
 		q.slab_index = k;
 		q.slab_count = ndev;
 		q.gs_order = FLUID_GS_REDBLACK;
-		if (ndev == 1) { // a single device: an ordinary context over N x slab_rows is not expressible (square only): require N == rows
-			if (p->slab_rows != p->N) { rc = fail(FLUID_ERR_UNSUPPORTED, "one device: slab_rows must equal N"); break; }
+		if (ndev == 1) { // a single device: one whole grid of N x slab_rows
 			q.slab_count = 0;
-			q.slab_index = q.slab_rows = q.slab_halo = 0;
+			q.slab_index = q.slab_halo = 0;
 		}
 		rc = fluid_ctx_create(&q, &m->slab[k]);
 		if (rc != FLUID_OK) break;

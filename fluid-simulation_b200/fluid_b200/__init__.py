@@ -215,7 +215,8 @@ class FluidSystem:
 
     def Setup(self, N, visc=0.0, diff=0.0, vorticity=0.0, damp=0.0, gs_order=GS_WAVEFRONT, gs_iters=20,
               advect_mode=ADVECT_MIDPOINT, batch=1, device=-1, slab=None, slab_halo=0, n_fluids=1):
-        """slab = (index, count, rows): this context is one row slab of a global N x (rows*count) grid."""
+        """slab = (index, count, rows): this context is one row slab of a global N x (rows*count) grid;
+        slab = (0, 1, rows): a whole non-square grid of N x rows."""
         self.close()
         p = Params()
         lib().fluid_params_default(ctypes.byref(p))

@@ -98,7 +98,9 @@ typedef struct fluid_params {
 	float damp;       /* 0 = no damping (reference default 0.1, FluidSystem.h:150) */
 	/* Row slab of a taller grid (multi-GPU): this context stores rows
 	 * slab_index*slab_rows+1 .. (slab_index+1)*slab_rows of a global N x (slab_rows*slab_count)
-	 * grid, plus slab_halo halo rows towards each neighbour.  slab_count <= 1: whole grid. */
+	 * grid, plus slab_halo halo rows towards each neighbour.  slab_count <= 1: whole grid -- square
+	 * (slab_rows = 0) or N columns x slab_rows rows (the reference is square-only; the scale factors
+	 * dt*N, /N, 0.5*N, dt*diff*N*N keep using N, i.e. h = 1/N). */
 	int slab_index, slab_count, slab_rows;
 	int slab_halo;    /* 0 = default 48 rows; >= 44 */
 	int n_fluids;     /* density fields advanced by dens_step (fluid_count, FluidSystem.cpp:21); 0 = 1 */

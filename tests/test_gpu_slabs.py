@@ -67,3 +67,37 @@ def test_slab_argument_checks(fl):
     sd, rd, su, ru, n = fs.HaloRegions(fl.U)
     assert su is None and ru is None and sd and rd and n == 49 * (((128 + 2 + 31 + 31) // 32) * 32)
     fs.close()
+
+
+@pytest.mark.parametrize("order", [0, 1])
+def test_non_square_single_context(fl, order):
+    """N x NY grids (what a multi-GPU weak-scaling run is globally).  The oracle is square-only, so
+    the check is internal consistency: red-black on one context == the slab decomposition (which is
+    itself pinned to the oracle on square grids); the reference order runs and stays finite."""
+    from fluid_b200.slabs import LocalSlabGroup
+    N, rows, count, steps = 150, 60, 3, 2
+    NY = rows * count
+    rng = np.random.default_rng(31)
+    init = {k: (rng.uniform(-1, 1, (N + 2) * (NY + 2)) * 0.4).astype(np.float32) for k in "uvd"}
+    src = [(2, N // 2, NY // 2, 0, 100.0), (0, N // 2, NY // 2, 0, 5.0), (1, 7, rows, 0, 5.0)]
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=order, slab=(0, 1, NY))
+    fs.SetSources(src)
+    for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+        fs.upload(fid, init[name])
+    fs.Update(0.1, steps)
+    one = {name: fs.download(fid) for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS))}
+    fs.close()
+    assert all(np.isfinite(a).all() and a.size == (N + 2) * (NY + 2) for a in one.values())
+    if order == 1:
+        grp = LocalSlabGroup(N, count, rows, visc=1e-4, diff=1e-4, gs_order=fl.GS_REDBLACK)
+        try:
+            grp.SetSources(src)
+            for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+                grp.upload(fid, init[name])
+            grp.Update(0.1, steps)
+            for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+                out = np.zeros((N + 2) * (NY + 2), np.float32)
+                grp.download(fid, out)
+                assert_bits(out, one[name], "non-square %s: slabs vs one context" % name)
+        finally:
+            grp.close()
