@@ -20,6 +20,7 @@
 #include "grid.cuh"
 #include "kernels_basic.cuh"
 #include "kernels_relax.cuh"
+#include "kernels_rb_stream.cuh"
 #include "kernels_rb_tile.cuh"
 #include "kernels_small.cuh"
 
@@ -105,6 +106,9 @@ struct fluid_ctx {
 	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
+	bool rb_stream = true;     // interior of large grids by the register-resident streaming kernel (k_rb_stream)
+	int* d_redo = nullptr;     // [0] = count, [1..] = stream tasks the tile kernel must recompute
+	int redo_capacity = 0;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
 	int fast_div_mode = 1; // 0 never, 1 when the solve is large enough to repay the 1.5 ms check, 2 always
@@ -282,8 +286,77 @@ static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	return FLUID_OK;
 }
 
+// Geometry of one pass of S sweeps: the tile grid, which tiles are left to the tile kernel (the frame)
+// and the rectangle the streaming kernel produces.
+struct PassGeom {
+	int TX, TY, ntx, nty;
+	int ftx0, ftx1, fty1; // interior tiles: ftx0 <= tx < ftx1, 1 <= ty < fty1; ftx1 = 0: no interior, tile kernel does everything
+	StreamRect rc;
+};
+
+template <int S>
+static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
+{
+	PassGeom pg{};
+	pg.TY = kRbRY - 4 * S;
+	pg.TX = c->rb_rx - 2 * (((2 * S + 3) / 4) * 4);
+	pg.ntx = cdiv(c->g.N, pg.TX);
+	pg.nty = cdiv(c->g.NY, pg.TY);
+	pg.ftx0 = pg.ftx1 = pg.fty1 = 0;
+	if (!c->rb_stream || !have_fast_division) return pg; // the streaming kernel only knows the verified division
+	constexpr int L = StreamGeom<S>::L, HALO = StreamGeom<S>::HALO;
+	if (StreamGeom<S>::OUT > pg.TX) return pg;             // a redo tile must cover a strip's width
+	// Rows: the streamed rectangle keeps one tile row below and above (bottom and top walls stay with the
+	// tile kernel) and must find its 2S halo rows inside the stored rows 0..NY+1.
+	int fy = pg.nty - 1;
+	while (fy > 1 && pg.TY * fy + L > c->g.NY + 1) fy--;
+	if (fy <= 1) return pg;
+	// Columns: the streaming kernel handles the left and right walls itself when a row is a whole number of
+	// float4 groups; otherwise it keeps one tile column away from them as well.
+	int fx0, fx1;
+	if (c->g.N % 4 == 0 && c->g.N >= 2 * StreamGeom<S>::OUT) {
+		fx0 = 0;
+		fx1 = pg.ntx;
+	} else {
+		fx0 = 1;
+		fx1 = pg.ntx - 1;
+		while (fx1 > 1 && pg.TX * fx1 + HALO > c->g.N + 1) fx1--;
+		if (fx1 <= 1) return pg;
+	}
+	const long long width = (fx0 == 0) ? c->g.N : (long long) (fx1 - 1) * pg.TX;
+	if (width * (fy - 1) * pg.TY * c->batch < (1LL << 22)) return pg; // too little interior to bother
+	pg.ftx0 = fx0;
+	pg.ftx1 = fx1;
+	pg.fty1 = fy;
+	pg.rc.col0 = (fx0 == 0) ? XO + 1 : XO + 1 + pg.TX;
+	pg.rc.col1 = (fx0 == 0) ? XO + 1 + c->g.N : XO + 1 + pg.TX * fx1;
+	pg.rc.row0 = 1 + pg.TY;
+	pg.rc.row1 = 1 + pg.TY * fy;
+	pg.rc.nstrips = cdiv(pg.rc.col1 - pg.rc.col0, StreamGeom<S>::OUT);
+	const int rows = pg.rc.row1 - pg.rc.row0;
+	// chunks of about 256 rows, nudged so that the warp tasks fill whole waves of resident warps
+	int nchunks = std::max(1, cdiv(rows, 256));
+	// resident warps per SM of k_rb_stream<S> (register bound: 167 / 115 / 89 registers per thread)
+	const long long slots = (long long) c->num_sms * (S >= 4 ? 12 : (S == 2 ? 16 : 20));
+	constexpr int kWallSplit = 2; // wall strips: tasks of half the rows
+	const bool walls = (fx0 == 0);
+	const long long per_chunk = (long long) (pg.rc.nstrips + (walls ? 2 * (kWallSplit - 1) : 0)) * c->batch;
+	if (per_chunk * nchunks > slots / 2) {
+		const long long waves = std::max(1LL, (per_chunk * nchunks + slots / 2) / slots);
+		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
+	}
+	const int unit = 2 * kWallSplit; // chunk and wall task both an even number of rows: one colour phase per launch
+	pg.rc.chunk_rows = (cdiv(rows, nchunks) + unit - 1) / unit * unit;
+	pg.rc.nchunks = cdiv(rows, pg.rc.chunk_rows);
+	pg.rc.wall_rows = walls ? pg.rc.chunk_rows / kWallSplit : 0;
+	pg.rc.wall_chunks = walls ? cdiv(rows, pg.rc.wall_rows) : 0;
+	pg.rc.per_sim = 2 * pg.rc.wall_chunks + (pg.rc.nstrips - (walls ? 2 : 0)) * pg.rc.nchunks;
+	return pg;
+}
+
 template <int S, int RX>
-static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
+static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv,
+			   const PassGeom& pg)
 {
 	static bool configured[64] = {}; // per template instance and per device: function attributes are per device
 	constexpr size_t smem = (2 * (size_t) (kRbRY + 2) + kRbRY) * RX * sizeof(float); // two x windows + x0 staging
@@ -295,24 +368,41 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 	const CUtensorMap *tm, *tm0;
 	FL_TRY(field_tmap(c, in, &tm));
 	FL_TRY(field_tmap(c, x0, &tm0));
-	constexpr int TY = kRbRY - 4 * S, TX = RX - 2 * (((2 * S + 3) / 4) * 4);
-	const int ntx = cdiv(c->g.N, TX), nty = cdiv(c->g.NY, TY);
-	const long long ntiles = (long long) ntx * nty * c->batch;
+	long long ntiles = (long long) pg.ntx * pg.nty;
+	if (pg.ftx1 > 0) ntiles -= (long long) (pg.ftx1 - pg.ftx0) * (pg.fty1 - 1); // the frame only
+	ntiles *= c->batch;
 	if (ntiles > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many tiles");
 	const int grid = (int) std::min<long long>(ntiles, c->num_sms); // persistent: one CTA per SM
-	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, ntx, nty, (int) ntiles);
+	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, pg.ntx, pg.nty, (int) ntiles, pg.ftx0, pg.ftx1,
+	       pg.fty1, c->d_redo, pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
 	return FLUID_OK;
 }
 
-// The window width is chosen per context so that ceil(N / (RX-8)) windows waste the fewest columns
-// (N=512: 3 x 192 instead of 3 x 256; N <= 120: one 128-wide window instead of a 256-wide one).
+// One pass of S red-black sweeps, in -> out: the streaming kernel on the interior rectangle (if the grid
+// is large enough to have one) and the tile kernel on the frame of tiles around it, or on everything.
+// The window width of the tile kernel is chosen per context so that ceil(N / (RX-8)) windows waste the
+// fewest columns (N=512: 3 x 192 instead of 3 x 256; N <= 120: one 128-wide window instead of 256).
 template <int S>
 static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
 {
+	// the streaming kernel relies on the proven window reaching the largest finite float
+	const bool stream_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
+	const PassGeom pg = pass_geometry<S>(c, stream_ok);
+	if (pg.ftx1 > 0) {
+		const int ntasks = pg.rc.per_sim * c->batch;
+		if (ntasks + 1 > c->redo_capacity) {
+			if (c->d_redo) CU_TRY(cudaFree(c->d_redo));
+			c->d_redo = nullptr;
+			CU_TRY(cudaMalloc(&c->d_redo, sizeof(int) * (size_t) (ntasks + 1)));
+			c->redo_capacity = ntasks + 1;
+		}
+		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
+		LAUNCH(k_rb_stream<S>, cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
+	}
 	switch (c->rb_rx) {
-	case 128: return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv);
-	case 192: return rb_tile_pass_rx<S, 192>(c, b, in, out, x0, a, dv);
-	default: return rb_tile_pass_rx<S, 256>(c, b, in, out, x0, a, dv);
+	case 128: return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv, pg);
+	case 192: return rb_tile_pass_rx<S, 192>(c, b, in, out, x0, a, dv, pg);
+	default: return rb_tile_pass_rx<S, 256>(c, b, in, out, x0, a, dv, pg);
 	}
 }
 
@@ -335,21 +425,30 @@ static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 		CU_TRY(cudaMalloc(&c->rb_scratch, c->field_bytes));
 		CU_TRY(cudaMemsetAsync(c->rb_scratch, 0, c->field_bytes, c->stream));
 	}
-	int n2, n1; // passes of 2 sweeps and of 1 sweep; n2 + n1 must be even
+	DivC dv;
+	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
+	int n4 = 0, n2, n1; // passes of 4, 2 and 1 sweeps; their number must be even
 	if (c->rb_tile_sweeps >= 2) {
-		n2 = limit / 2;
-		n1 = limit % 2;
-		if ((n2 + n1) % 2) { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
+		int rest = limit;
+		if (c->rb_stream && pass_geometry<4>(c, dv.range != 0 && (dv.lo + dv.range) == (255u << 23)).ftx1 > 0) { // 4 sweeps per pass pay off where the streaming kernel runs
+			n4 = rest / 4;
+			rest -= 4 * n4;
+		}
+		n2 = rest / 2;
+		n1 = rest % 2;
+		if ((n4 + n2 + n1) % 2) {
+			if (n4 > 0) { n4 -= 1; n2 += 2; }
+			else { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
+		}
 	} else {
 		n2 = limit % 2; // an odd count needs one 2-sweep pass to make the number of passes even
 		n1 = limit - 2 * n2;
 	}
-	DivC dv;
-	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
 	const float* in = x;
 	float* out = c->rb_scratch;
-	for (int k = 0; k < n2 + n1; k++) {
-		if (k < n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv));
+	for (int k = 0; k < n4 + n2 + n1; k++) {
+		if (k < n4) FL_TRY(rb_tile_pass<4>(c, b, in, out, x0, a, dv));
+		else if (k < n4 + n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv));
 		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv));
 		float* t = const_cast<float*>(in);
 		in = out;
@@ -744,6 +843,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->rb_scratch) cudaFree(c->rb_scratch);
 	if (c->d_oob) cudaFree(c->d_oob);
 	if (c->d_divbins) cudaFree(c->d_divbins);
+	if (c->d_redo) cudaFree(c->d_redo);
 	if (c->d_pixels) cudaFree(c->d_pixels);
 	if (c->d_lines) cudaFree(c->d_lines);
 	if (c->d_src) cudaFree(c->d_src);
@@ -1035,6 +1135,13 @@ extern "C" int fluid_ctx_render(fluid_ctx* c, int sim, const float* color_rgb, f
 	CU_TRY(cudaMemcpyAsync(host_pixels, c->d_pixels, cells * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
 	if (host_lines) CU_TRY(cudaMemcpyAsync(host_lines, c->d_lines, cells * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
 	CU_TRY(cudaStreamSynchronize(c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_stream_kernel(fluid_ctx* c, int on)
+{
+	CHECK_CTX(c);
+	c->rb_stream = on != 0;
 	return FLUID_OK;
 }
 
@@ -1611,7 +1718,7 @@ static void static_tile_pass(const StaticSetup* st, const GridDesc& g, int b, co
 	dv.y = 0.0f;
 	dv.lo = dv.range = 0;
 	LAUNCH((k_rb_tile<S, kRbRY, kRbRX, kRbNT>), std::min(ntiles, st->num_sms), kRbNT, kRbSmem, stream, tm_in, tm_x0, g, b, out, a,
-	       dv, ntx, nty, ntiles);
+	       dv, ntx, nty, ntiles, 0, 0, 0, nullptr, StreamRect{}, 0, 0);
 }
 
 extern "C" int fluid_lin_solve_rb_static(int N, int b, float* x_dev, const float* x0_dev, float a, float cc, int iters, void* stream_)

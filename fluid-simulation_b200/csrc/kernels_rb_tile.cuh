@@ -22,6 +22,7 @@
 #include <cuda.h> // CUtensorMap (types only; the encode function is fetched at run time)
 
 #include "grid.cuh"
+#include "kernels_rb_stream.cuh"
 
 namespace fluid {
 
@@ -155,7 +156,9 @@ __device__ __forceinline__ void rb_tile_sweeps(float* base, const float2 (&x0)[K
 template <int S, int RY, int RX, int NT>
 __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUtensorMap tm_in,
 						    const __grid_constant__ CUtensorMap tm_x0, GridDesc g, int b,
-						    float* __restrict__ xoutb, float a, DivC dv, int ntx, int nty, int ntiles)
+						    float* __restrict__ xoutb, float a, DivC dv, int ntx, int nty, int ntiles,
+						    int ftx0, int ftx1, int fty1, const int* __restrict__ redo, StreamRect rc,
+						    int stream_out, int stream_halo)
 {
 	constexpr int HY = 2 * S, HX = ((2 * S + 3) / 4) * 4, TY = RY - 2 * HY, TX = RX - 2 * HX;
 	constexpr int CB = RX / 32;               // 32-column blocks per window row
@@ -195,7 +198,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	// Tile coordinates (column, row, ensemble member), advanced by gridDim.x tiles per iteration with
 	// two divisions by small constants-per-launch (a subtract loop took 49 rounds per step on an
 	// ensemble of 3-tile-wide grids; decoding the linear index afresh costs three divisions).
-	struct TilePos { int tx, ty, sim; };
+	struct TilePos { int tx, ty, sim, tx0, ty0; }; // tile grid position and the cell offsets of its output
 	auto advance = [&](TilePos q, int by) {
 		q.tx += by;
 		if (q.tx >= ntx) {
@@ -208,6 +211,48 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 				q.sim += c2;
 			}
 		}
+		q.tx0 = q.tx * TX;
+		q.ty0 = q.ty * TY;
+		return q;
+	};
+	// Frame mode (ftx1 > 0): the tiles with ftx0 <= tx < ftx1 and 1 <= ty < fty1 belong to k_rb_stream; this
+	// launch enumerates only the frame around them -- bottom tile row, top tile rows, left column and
+	// right columns -- from a linear index (few tiles, so the divisions do not matter).
+	const int frame_mid = ftx0 + (ntx - ftx1), frame_top = nty - fty1;
+	const int frame_per_sim = ntx + ntx * frame_top + frame_mid * (fty1 - 1);
+	// After the frame tiles come the rectangles k_rb_stream could not finish with the short division
+	// (redo[0] of them, task ids in redo[1..]): `redo_rt` tiles stacked over each rectangle.  A redo tile
+	// is wider than the rectangle and may overlap finished neighbours; it stores the same values there.
+	const int redo_rt = (ftx1 > 0) ? (rc.chunk_rows + TY - 1) / TY : 0;
+	if (ftx1 > 0) ntiles += redo_rt * redo[0]; // written by the preceding kernel in stream order
+	auto frame_pos = [&](int t) {
+		TilePos q;
+		const int nframe = frame_per_sim * (int) (g.plane ? 1 : 1);
+		(void) nframe;
+		q.tx = q.ty = 0;
+		const int frame_total = ntiles - redo_rt * redo[0];
+		if (t >= frame_total) { // a redo tile
+			const int e = (t - frame_total) / redo_rt, k = (t - frame_total) - e * redo_rt;
+			const StreamTask st = stream_task(rc, redo[1 + e]);
+			q.sim = st.sim;
+			q.tx0 = rc.col0 + st.strip * stream_out - (XO + 1);
+			// tiles past the rectangle's last row repeat the last useful one (same values, and inside the grid)
+			q.ty0 = min(st.out_lo - 1 + k * TY, max(st.out_lo - 1, st.out_hi - TY));
+			(void) stream_halo;
+			return q;
+		}
+		q.sim = t / frame_per_sim;
+		int k = t - q.sim * frame_per_sim;
+		if (k < ntx) { q.tx = k; q.ty = 0; }
+		else if (k - ntx < ntx * frame_top) { k -= ntx; q.ty = fty1 + k / ntx; q.tx = k - (q.ty - fty1) * ntx; }
+		else {
+			k -= ntx + ntx * frame_top;
+			q.ty = 1 + k / frame_mid;
+			const int m = k - (q.ty - 1) * frame_mid;
+			q.tx = (m < ftx0) ? m : ftx1 + (m - ftx0);
+		}
+		q.tx0 = q.tx * TX;
+		q.ty0 = q.ty * TY;
 		return q;
 	};
 	auto edge_tile = [&](int tx0, int ty0) { // window reaches a wall, or the tile is partial
@@ -215,7 +260,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 	};
 	// both boxes of a tile: same window, one from x (into x buffer `buf`), one from x0 (staging)
 	auto issue_tma = [&](TilePos tp, int buf) {
-		const int cx = XO + 1 + tp.tx * TX - HX, cy = 1 + tp.ty * TY - HY;
+		const int cx = XO + 1 + tp.tx0 - HX, cy = 1 + tp.ty0 - HY;
 		mbar_expect_tx(&bar[buf], RY * RX * sizeof(float));
 		tma_load_3d(smem + buf * BUF + RX, &tm_in, cx, cy, tp.sim, &bar[buf]);
 		mbar_expect_tx(&bar[2], RY * RX * sizeof(float));
@@ -224,13 +269,13 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 
 	int t = blockIdx.x;
 	if (t >= ntiles) return;
-	TilePos tp = advance(TilePos{ 0, 0, 0 }, t);
+	TilePos tp = (ftx1 > 0) ? frame_pos(t) : advance(TilePos{ 0, 0, 0, 0, 0 }, t);
 	if (tid == 0) issue_tma(tp, 0);
 
 #pragma unroll 1
 	for (int n = 0; t < ntiles; n++, t += gridDim.x) {
 		const int buf = n & 1;
-		const int tx0 = tp.tx * TX, ty0 = tp.ty * TY, sim = tp.sim;
+		const int tx0 = tp.tx0, ty0 = tp.ty0, sim = tp.sim;
 		const int ci0 = 1 + tx0 - HX, cj0 = 1 + ty0 - HY;   // interior index of window cell (0,0)
 		const bool edge = edge_tile(tx0, ty0);
 		const bool wall = edge && (b >= 0 && b <= 2);
@@ -249,7 +294,7 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		// staging buffer and the other x buffer (stored from in iteration n-1) are free: refill them
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 		__syncthreads();
-		const TilePos tpn = advance(tp, gridDim.x);
+		const TilePos tpn = (ftx1 > 0) ? frame_pos(min(t + (int) gridDim.x, ntiles - 1)) : advance(tp, gridDim.x);
 		if (tid == 0 && t + (int) gridDim.x < ntiles) issue_tma(tpn, buf ^ 1);
 
 		mbar_wait(&bar[buf], (n >> 1) & 1);

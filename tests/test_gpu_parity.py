@@ -522,3 +522,28 @@ def test_two_fluids_resident_context(fl, oracle, order):
     with pytest.raises(fl.FluidError):
         fs.SetFluid(2, 0.0, 0.0)
     fs.close()
+
+
+@pytest.mark.parametrize("N,stream", [(2500, True), (2500, False), (2502, True), (2524, True)])
+def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
+    """Large grids: the rows away from the bottom and top walls are relaxed by the register-resident
+    streaming kernel (4, 2 or 1 sweeps per pass) -- including the left and right walls when N is a multiple
+    of 4 (2500, 2524 = 28 mod 32, where lanes fold back onto the border column), one tile column away from
+    them otherwise (2502) -- the rest by the tile kernel.  Mixed pass schedules (20 = 4x4+2x2,
+    7 = 4+2+1 -> 4+1+1+1, 6, 2) against the CPU red-black statement, and the tile-only path on the same inputs."""
+    import oracle_py as op
+    rng = np.random.default_rng(N)
+    for iters, b, a in ((20, 1, np.float32(10.49)), (7, 2, np.float32(1.0)), (6, 0, np.float32(0.3)), (2, 1, np.float32(0.3)),
+                        (4, 3, np.float32(0.7))):
+        fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_REDBLACK, gs_iters=iters)
+        fs.SetStreamKernel(stream)
+        fs.SetFastDivision(2)
+        x, x0 = rand_field(rng, N), rand_field(rng, N)
+        x0[rng.integers(0, x0.size, x0.size // 5)] = 0.0
+        c = np.float32(4.0) if a == 1 else 1 + 4 * a
+        fs.upload(fl.U, x)
+        fs.upload(fl.V, x0)
+        fs.lin_solve(b, fl.U, fl.V, a, c)
+        oracle.lin_solve(N, b, x, x0, a, c, iters, op.GS_RB)
+        assert_bits(fs.download(fl.U), x, "N=%d iters=%d b=%d stream=%s" % (N, iters, b, stream))
+        fs.close()
