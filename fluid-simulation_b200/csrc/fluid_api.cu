@@ -290,7 +290,7 @@ static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 // and the rectangle the streaming kernel produces.
 struct PassGeom {
 	int TX, TY, ntx, nty;
-	int ftx0, ftx1, fty1; // interior tiles: ftx0 <= tx < ftx1, 1 <= ty < fty1; ftx1 = 0: no interior, tile kernel does everything
+	int ftx0, ftx1, fty0, fty1; // streamed tiles: ftx0 <= tx < ftx1, fty0 <= ty < fty1; ftx1 = 0: none, the tile kernel does everything
 	StreamRect rc;
 };
 
@@ -302,15 +302,14 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
 	pg.TX = c->rb_rx - 2 * (((2 * S + 3) / 4) * 4);
 	pg.ntx = cdiv(c->g.N, pg.TX);
 	pg.nty = cdiv(c->g.NY, pg.TY);
-	pg.ftx0 = pg.ftx1 = pg.fty1 = 0;
+	pg.ftx0 = pg.ftx1 = pg.fty0 = pg.fty1 = 0;
 	if (!c->rb_stream || !have_fast_division) return pg; // the streaming kernel only knows the verified division
 	constexpr int L = StreamGeom<S>::L, HALO = StreamGeom<S>::HALO;
 	if (StreamGeom<S>::OUT > pg.TX) return pg;             // a redo tile must cover a strip's width
-	// Rows: the streamed rectangle keeps one tile row below and above (bottom and top walls stay with the
-	// tile kernel) and must find its 2S halo rows inside the stored rows 0..NY+1.
-	int fy = pg.nty - 1;
-	while (fy > 1 && pg.TY * fy + L > c->g.NY + 1) fy--;
-	if (fy <= 1) return pg;
+	// Rows: all of them; the streaming kernel does the bottom and top walls' set_bnd (or, for a slab that
+	// ends in a neighbour's rows, treats the row beyond as fixed, like the tile kernel).
+	if (c->g.NY < 8 * L) return pg;
+	const int fy = pg.nty;
 	// Columns: the streaming kernel handles the left and right walls itself when a row is a whole number of
 	// float4 groups; otherwise it keeps one tile column away from them as well.
 	int fx0, fx1;
@@ -324,14 +323,14 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
 		if (fx1 <= 1) return pg;
 	}
 	const long long width = (fx0 == 0) ? c->g.N : (long long) (fx1 - 1) * pg.TX;
-	if (width * (fy - 1) * pg.TY * c->batch < (1LL << 22)) return pg; // too little interior to bother
+	if (width * c->g.NY * c->batch < (1LL << 22)) return pg; // too little to bother
 	pg.ftx0 = fx0;
 	pg.ftx1 = fx1;
 	pg.fty1 = fy;
 	pg.rc.col0 = (fx0 == 0) ? XO + 1 : XO + 1 + pg.TX;
 	pg.rc.col1 = (fx0 == 0) ? XO + 1 + c->g.N : XO + 1 + pg.TX * fx1;
-	pg.rc.row0 = 1 + pg.TY;
-	pg.rc.row1 = 1 + pg.TY * fy;
+	pg.rc.row0 = 1;
+	pg.rc.row1 = c->g.NY + 1;
 	pg.rc.nstrips = cdiv(pg.rc.col1 - pg.rc.col0, StreamGeom<S>::OUT);
 	const int rows = pg.rc.row1 - pg.rc.row0;
 	// chunks of about 256 rows, nudged so that the warp tasks fill whole waves of resident warps
@@ -346,10 +345,15 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
 		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
 	}
 	const int unit = 2 * kWallSplit; // chunk and wall task both an even number of rows: one colour phase per launch
-	pg.rc.chunk_rows = (cdiv(rows, nchunks) + unit - 1) / unit * unit;
-	pg.rc.nchunks = cdiv(rows, pg.rc.chunk_rows);
+	// the bottom and top chunks run ~3S slower row steps next to their wall: make them that much shorter
+	const int shift = (nchunks > 2) ? 12 * S : 0;
+	pg.rc.row_shift = shift;
+	pg.rc.chunk_rows = (cdiv(rows + 2 * shift, nchunks) + unit - 1) / unit * unit;
+	pg.rc.nchunks = cdiv(rows + shift, pg.rc.chunk_rows);
 	pg.rc.wall_rows = walls ? pg.rc.chunk_rows / kWallSplit : 0;
-	pg.rc.wall_chunks = walls ? cdiv(rows, pg.rc.wall_rows) : 0;
+	pg.rc.wall_chunks = walls ? cdiv(rows + shift, pg.rc.wall_rows) : 0;
+	pg.rc.seg_rows = pg.TY;
+	pg.rc.segs = cdiv(pg.rc.chunk_rows, pg.TY);
 	pg.rc.per_sim = 2 * pg.rc.wall_chunks + (pg.rc.nstrips - (walls ? 2 : 0)) * pg.rc.nchunks;
 	return pg;
 }
@@ -369,12 +373,13 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 	FL_TRY(field_tmap(c, in, &tm));
 	FL_TRY(field_tmap(c, x0, &tm0));
 	long long ntiles = (long long) pg.ntx * pg.nty;
-	if (pg.ftx1 > 0) ntiles -= (long long) (pg.ftx1 - pg.ftx0) * (pg.fty1 - 1); // the frame only
+	if (pg.ftx1 > 0) ntiles -= (long long) (pg.ftx1 - pg.ftx0) * (pg.fty1 - pg.fty0); // the frame only, possibly nothing
 	ntiles *= c->batch;
 	if (ntiles > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many tiles");
-	const int grid = (int) std::min<long long>(ntiles, c->num_sms); // persistent: one CTA per SM
+	// persistent: one CTA per SM; behind the streaming kernel the redo list adds tiles the host cannot count
+	const int grid = (pg.ftx1 > 0) ? c->num_sms : (int) std::min<long long>(ntiles, c->num_sms);
 	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, pg.ntx, pg.nty, (int) ntiles, pg.ftx0, pg.ftx1,
-	       pg.fty1, c->d_redo, pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
+	       pg.fty0, pg.fty1, c->d_redo, pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
 	return FLUID_OK;
 }
 
@@ -389,12 +394,14 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 	const bool stream_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
 	const PassGeom pg = pass_geometry<S>(c, stream_ok);
 	if (pg.ftx1 > 0) {
-		const int ntasks = pg.rc.per_sim * c->batch;
-		if (ntasks + 1 > c->redo_capacity) {
+		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch, entries = ntasks_ll * pg.rc.segs + 1;
+		if (entries > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many streaming tasks");
+		const int ntasks = (int) ntasks_ll;
+		if (entries > c->redo_capacity) {
 			if (c->d_redo) CU_TRY(cudaFree(c->d_redo));
 			c->d_redo = nullptr;
-			CU_TRY(cudaMalloc(&c->d_redo, sizeof(int) * (size_t) (ntasks + 1)));
-			c->redo_capacity = ntasks + 1;
+			CU_TRY(cudaMalloc(&c->d_redo, sizeof(int) * (size_t) entries));
+			c->redo_capacity = (int) entries;
 		}
 		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
 		LAUNCH(k_rb_stream<S>, cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
@@ -1718,7 +1725,7 @@ static void static_tile_pass(const StaticSetup* st, const GridDesc& g, int b, co
 	dv.y = 0.0f;
 	dv.lo = dv.range = 0;
 	LAUNCH((k_rb_tile<S, kRbRY, kRbRX, kRbNT>), std::min(ntiles, st->num_sms), kRbNT, kRbSmem, stream, tm_in, tm_x0, g, b, out, a,
-	       dv, ntx, nty, ntiles, 0, 0, 0, nullptr, StreamRect{}, 0, 0);
+	       dv, ntx, nty, ntiles, 0, 0, 0, 0, nullptr, StreamRect{}, 0, 0);
 }
 
 extern "C" int fluid_lin_solve_rb_static(int N, int b, float* x_dev, const float* x0_dev, float a, float cc, int iters, void* stream_)

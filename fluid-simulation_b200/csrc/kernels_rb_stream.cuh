@@ -17,9 +17,9 @@
 // extra rows below and above, and a strip 2S (rounded up to a lane) extra columns left and right.
 // Redundant arithmetic: 128/112 * (CY+16)/CY for S = 4; HBM traffic: 13 B per cell per FOUR sweeps.
 //
-// The kernel handles the rows that are at least one tile away from the bottom and top walls
-// (k_rb_tile keeps those two bands and the corners) and, when rows are whole float4 groups, the full
-// width including the left and right walls' set_bnd.  Values are bit-identical to
+// The kernel handles all rows including the bottom and top walls' set_bnd and, when rows are whole
+// float4 groups, the full width including the left and right walls and the corners (otherwise
+// k_rb_tile keeps one tile column along each side wall).  Values are bit-identical to
 // oracle_lin_solve_rb: same expression per cell, same neighbours.
 #pragma once
 #include <type_traits>
@@ -42,6 +42,9 @@ struct StreamRect {
 	// shorter tasks: wall_chunks tasks of wall_rows rows for each of the two; 0 = no strip touches a wall.
 	int wall_rows, wall_chunks;
 	int per_sim;    // tasks per ensemble member
+	int row_shift;  // the first and last chunk are this much shorter: their wall handling costs extra row steps
+	int seg_rows;   // a task reports trouble per segment of this many rows (the tile kernel's tile height)
+	int segs;       // segments per task at most; a redo entry is task * segs + segment
 };
 
 struct StreamTask { int sim, strip, out_lo, out_hi; bool wall; };
@@ -57,16 +60,17 @@ __device__ __forceinline__ StreamTask stream_task(const StreamRect& rc, int task
 		const int side = q / rc.wall_chunks, sub = q - side * rc.wall_chunks;
 		k.strip = side ? rc.nstrips - 1 : 0;
 		rows = rc.wall_rows;
-		k.out_lo = rc.row0 + sub * rows;
+		k.out_lo = rc.row0 - rc.row_shift + sub * rows;
 	} else {
 		q -= 2 * rc.wall_chunks;
 		const int first = rc.wall_chunks ? 1 : 0, inner = rc.nstrips - 2 * first;
 		const int chunk = q / inner;
 		k.strip = first + q - chunk * inner;
 		rows = rc.chunk_rows;
-		k.out_lo = rc.row0 + chunk * rows;
+		k.out_lo = rc.row0 - rc.row_shift + chunk * rows;
 	}
 	k.out_hi = min(k.out_lo + rows, rc.row1) - 1;
+	k.out_lo = max(k.out_lo, rc.row0);
 	return k;
 }
 
@@ -95,17 +99,21 @@ __device__ __forceinline__ float stream_relax(float x0, float a, float w, float 
 }
 
 // One warp task: rows [out_lo, out_hi] x storage columns [lane0_col + HALO, ... + OUT) of one member,
-// with the verified short division.  Returns (warp-uniform) whether some dividend fell outside the
-// proven window; the caller then hands the task's rectangle to the tile kernel.
+// with the verified short division.  Segments of rows in which some dividend fell outside the proven
+// window (the subnormal fringe of a field, an overflow) may have been stored wrong: they go on the redo
+// list and the tile kernel -- which spreads such slow cells over 16 warps per tile and balances tiles
+// dynamically -- recomputes them with IEEE division right after this kernel.  A dividend met while
+// segment k was being stored belongs to a row at most 2S ahead of the stored one, so it can spoil
+// segments k and k+1, never an earlier one.
 // WALL: the strip contains the left and/or the right wall of the grid.  The border cell next to a wall
 // cell mirrors it (SetBorder: negated for b == 1) and sits in the neighbouring lane, so after every
 // colour pass that updated the wall cell its new value is shuffled across and written into the border
 // cell; in the other passes the border cell -- which the plain update has just treated like an interior
 // cell -- gets its previous value back.  The border column is stored with the rows.
 template <int S, bool WALL>
-__device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* __restrict__ xin, const float* __restrict__ x0g,
+__device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* __restrict__ xin, const float* __restrict__ x0g,
 					       float* __restrict__ xout, float a, const DivC& dv, int lane0_col, int out_lo,
-					       int out_hi, int col_lo, int col_hi, int b, float* ring)
+					       int out_hi, int col_lo, int col_hi, int b, float* ring, int* __restrict__ redo, int redo_base, int seg_rows)
 {
 	constexpr int L = StreamGeom<S>::L, W = StreamGeom<S>::W;
 	const int lane = threadIdx.x & 31;
@@ -113,7 +121,12 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 	// are folded back (they are farther than HALO from every produced column, so what they compute
 	// never matters, but their loads must stay inside the array)
 	const int col = min(lane0_col + 4 * lane, g.pitch - 4);
-	const int row_lo = out_lo - L, row_hi = out_hi + L;    // rows that are loaded
+	// Rows that pass through the window.  At the bottom and top of the grid the range runs past the stored
+	// rows 0..NY+1: those row steps are virtual -- nothing is fetched, no pass applies -- and keep every
+	// task on the same schedule (and the same colour phase).
+	const int row_lo = out_lo - L, row_hi = out_hi + L;
+	const int ylo = max(row_lo + 1, 1), yhi = min(row_hi - 1, g.NY); // rows that receive colour passes
+	const bool botw = (out_lo == 1), topw = (out_hi == g.NY);         // the task reaches the bottom / top row
 	const bool store_lane = (col >= col_lo) && (col + 4 <= col_hi) && (lane >= StreamGeom<S>::HALO / 4) &&
 				(lane < 32 - StreamGeom<S>::HALO / 4);
 	// colour of cell (i, y) is (i + y + j0) & 1 with i = storage column - XO; col is a multiple of 4
@@ -121,14 +134,34 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 	// lanes holding the border cells: left border i = 0 is component .w of the lane before the one with i = 1;
 	// right border i = N+1 (N % 4 == 0) is component .x of the lane after the one whose .w is i = N
 	const bool mirror = (b >= 0 && b <= 2);
+	// bottom / top border rows mirror rows 1 / NY the same way (negated for b == 2) where the slab ends in a wall
+	const bool wallB = botw && (g.walls & 1), wallT = topw && (g.walls & 2);
 	const bool ghostL = WALL && (col + 3 == XO);
 	const bool ghostR = WALL && (lane0_col + 4 * lane == XO + g.N + 1); // not a folded-back lane
 	const float* pin = xin + (long long) row_lo * g.pitch + col;
 	const float* p0 = x0g + (long long) row_lo * g.pitch + col;
 	float* pout = xout + (long long) out_lo * g.pitch + col;
 	float4 x[W], r[W];
+	// Rows below the first loaded one do not exist, but the fast blocks apply every pass from the first row
+	// step on (no per-row conditions): give the empty slots harmless values.  What is computed from them
+	// stays within the 2S untrusted rows, like everything else that depends on the missing neighbours.
+#pragma unroll
+	for (int i = 0; i < W; i++) {
+		x[i] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+		r[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+	}
 	uint32_t low = 0xffffffffu;
-	bool bad = false;
+	bool bad = false, bad_before = false;
+	int seg = 0, seg_left = seg_rows;
+	auto close_segment = [&]() {
+		const bool now = __any_sync(0xffffffffu, bad || (low < 2u * dv.lo - 1u));
+		if ((now || bad_before) && lane == 0) redo[1 + atomicAdd(&redo[0], 1)] = redo_base + seg;
+		bad_before = now;
+		bad = false;
+		low = 0xffffffffu;
+		seg++;
+		seg_left = seg_rows;
+	};
 	// Rows arrive through a small per-lane ring in shared memory filled by cp.async kDepth rows ahead of
 	// their use: DRAM latency is covered without holding the rows in flight in registers (one row ahead
 	// in registers left the warps waiting on the loads for a third of their time).  A lane reads back only
@@ -136,9 +169,11 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 	constexpr int kDepth = kStreamDepth;
 	constexpr int B = (S >= 4) ? STREAM_B4 : W; // row steps per unrolled block
 	const uint32_t ring_base = (uint32_t) __cvta_generic_to_shared(ring) + 16u * lane;
-	auto fetch = [&](int slot) { // next row of x and x0 into ring slot `slot`; always one group
-		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_base + 1024u * slot), "l"(pin) : "memory");
-		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_base + 1024u * slot + 512u), "l"(p0) : "memory");
+	auto fetch = [&](int slot, bool real) { // next row of x and x0 into ring slot `slot`
+		if (real) {
+			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_base + 1024u * slot), "l"(pin) : "memory");
+			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_base + 1024u * slot + 512u), "l"(p0) : "memory");
+		}
 		pin += g.pitch;
 		p0 += g.pitch;
 	};
@@ -146,19 +181,34 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 #pragma unroll
 	for (int d = 0; d < kDepth; d++) {
 		if (issued <= row_hi) {
-			fetch(d);
+			fetch(d, issued >= 0 && issued <= g.NY + 1);
 			issued++;
 		}
 		asm volatile("cp.async.commit_group;" ::: "memory");
 	}
+	// border row next to row 1 / NY, written when that row is final; the corners average their two
+	// neighbouring border cells (SetBorder, FluidSystem.cpp:496-499), whatever b is
+	auto store_border_row = [&](const float4& vg, const float4& vi, int y, bool is_wall) {
+		float4 v = vg;
+		if (WALL && is_wall) {
+			const float h1 = __shfl_down_sync(0xffffffffu, vg.x, 1); // border-row cell above/below i = 1
+			const float hN = __shfl_up_sync(0xffffffffu, vg.w, 1);   // ... i = N
+			if (ghostL) v.w = 0.5f * (h1 + vi.w);
+			if (ghostR) v.x = 0.5f * (hN + vi.x);
+		}
+		float* pb = xout + (long long) y * g.pitch + col;
+		if (store_lane) *reinterpret_cast<float4*>(pb) = v;
+		if (WALL && ghostL) pb[3] = v.w;
+		if (WALL && ghostR) pb[0] = v.x;
+	};
 	int slot = 0;
 
 	// B row steps with compile-time register slots.  Unrolling all W steps needs no register moves, but for
 	// S = 4 that loop is 35 KB of code, more than the 32 KB instruction cache level that 12 warps at 12
 	// different places in the loop can share -- ncu showed more warps waiting for instructions than
 	// issuing.  Four steps and one rotation of the window (80 moves, +9 % instructions) fit: 1.81 -> 1.60 ms
-	// per 20-sweep solve at N = 8192 (six steps: 1.64, two: 1.62).  STEADY: the window is full and stays inside the
-	// chunk, so every pass applies and every finished row is stored -- no per-row conditions at all.
+	// per 20-sweep solve at N = 8192 (six steps: 1.64, two: 1.62).  STEADY: every pass applies and
+	// every row is fetched unconditionally; the only condition left is whether the finished row is stored.
 	// In steady blocks the colour phase of every row step is a compile-time constant as well (W is even, so
 	// all blocks of a task start on the same parity, P0): half the code, and -- the host makes chunks an
 	// even number of rows -- every warp of the launch runs the SAME half, which is what keeps the unrolled
@@ -177,7 +227,7 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 				asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r[u].x), "=f"(r[u].y), "=f"(r[u].z), "=f"(r[u].w) : "r"(sa + 512u) : "memory");
 			}
 			if (STEADY || issued <= row_hi) { // refill the slot just read
-				fetch(slot);
+				fetch(slot, STEADY || (issued >= 0 && issued <= g.NY + 1));
 				issued++;
 			}
 			asm volatile("cp.async.commit_group;" ::: "memory");
@@ -185,7 +235,7 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 			const int ph = STEADY ? ((P0 + u) & 1) : ((par0 + t) & 1); // parity of (column + row t)
 #pragma unroll
 			for (int h = 1; h <= L; h++) {
-				if (!STEADY && t - h <= row_lo) continue; // the chunk's first row has no lower neighbour
+				if (!STEADY && (t - h < ylo || t - h > yhi)) continue; // no such row, or it lacks a neighbour
 				constexpr int WW = 4 * W;
 				const int sy = (u - h + WW) % W, sn = (u - h + 1 + WW) % W, ss = (u - h - 1 + WW) % W;
 				// row y = t - h, colour (h - 1) & 1: (par0 + y + colour) & 1 = (ph + h + h - 1) & 1 = (ph + 1) & 1,
@@ -200,6 +250,16 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 						const float v1 = __shfl_down_sync(0xffffffffu, x[sy].x, 1); // cell i = 1 was updated
 						if (ghostL && mirror) x[sy].w = (b == 1) ? -v1 : v1;
 					}
+					if (!STEADY && mirror) {
+						if (wallB && t - h == 1) {
+							x[ss].x = (b == 2) ? -x[sy].x : x[sy].x;
+							x[ss].z = (b == 2) ? -x[sy].z : x[sy].z;
+						}
+						if (wallT && t - h == g.NY) {
+							x[sn].x = (b == 2) ? -x[sy].x : x[sy].x;
+							x[sn].z = (b == 2) ? -x[sy].z : x[sy].z;
+						}
+					}
 				} else {  // cells .y and .w
 					const float er = __shfl_down_sync(0xffffffffu, x[sy].x, 1);
 					const float keep = x[sy].w;
@@ -210,15 +270,28 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 						const float vN = __shfl_up_sync(0xffffffffu, x[sy].w, 1);   // cell i = N was updated
 						if (ghostR && mirror) x[sy].x = (b == 1) ? -vN : vN;
 					}
+					if (!STEADY && mirror) {
+						if (wallB && t - h == 1) {
+							x[ss].y = (b == 2) ? -x[sy].y : x[sy].y;
+							x[ss].w = (b == 2) ? -x[sy].w : x[sy].w;
+						}
+						if (wallT && t - h == g.NY) {
+							x[sn].y = (b == 2) ? -x[sy].y : x[sy].y;
+							x[sn].w = (b == 2) ? -x[sy].w : x[sy].w;
+						}
+					}
 				}
 			}
-			if (STEADY || (t - L >= out_lo && t - L <= out_hi)) { // this row has now received all L passes
+			if (STEADY ? (t - L >= out_lo) : (t - L >= out_lo && t - L <= out_hi)) { // this row has now received all L passes
 				const float4 v = x[(u - L + 4 * W) % W];
 				bad = bad || !(v.x == v.x) || !(v.y == v.y) || !(v.z == v.z) || !(v.w == v.w);
 				if (store_lane) *reinterpret_cast<float4*>(pout) = v;
 				if (WALL && ghostL) pout[3] = v.w;
 				if (WALL && ghostR) pout[0] = v.x;
 				pout += g.pitch;
+				if (--seg_left == 0 || (!STEADY && t - L == out_hi)) close_segment();
+				if (!STEADY && botw && t - L == 1) store_border_row(x[(u - L - 1 + 4 * W) % W], v, 0, wallB);
+				if (!STEADY && topw && t - L == g.NY) store_border_row(x[(u - L + 1 + 4 * W) % W], v, g.NY + 1, wallT);
 			}
 		}
 		if (B != W) { // rotate the window so that the next block starts at slot 0 again
@@ -238,16 +311,16 @@ __device__ __forceinline__ bool rb_stream_task(const GridDesc& g, const float* _
 	static_assert(B % 2 == 0 && B <= W, "blocks must start on one parity");
 	const int phase0 = (par0 + row_lo) & 1;
 	for (int t0 = row_lo; t0 <= row_hi; t0 += B) {
-		if (t0 >= row_lo + 2 * L && t0 + B - 1 + kDepth <= row_hi) {
+		// steady: every row up to the one fetched now is real, no border row to mirror or store -- the whole
+		// task except its last few rows and, in the bottom and top chunks, the rows next to the wall
+		if ((!botw || t0 > row_lo + 2 * L) && t0 + B - 1 + kDepth <= min(row_hi, g.NY + 1)) {
 			if (phase0) block(t0, std::true_type{}, std::integral_constant<int, 1>{});
 			else block(t0, std::true_type{}, std::integral_constant<int, 0>{});
 		} else block(t0, std::false_type{}, std::integral_constant<int, 0>{});
 	}
-	bad = bad || (low < 2u * dv.lo - 1u);
-	return __any_sync(0xffffffffu, bad);
 }
 
-// redo[0] counts, redo[1..] lists the tasks whose rectangle the tile kernel must recompute exactly.
+// redo[0] counts, redo[1..] lists the (task, segment) rectangles the tile kernel must recompute exactly.
 template <int S>
 __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g, StreamRect rc, const float* __restrict__ xinb,
 							const float* __restrict__ x0b, float* __restrict__ xoutb, float a, DivC dv,
@@ -260,12 +333,8 @@ __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g,
 	const StreamTask k = stream_task(rc, task);
 	const long long off = (long long) k.sim * g.plane;
 	const int lane0_col = rc.col0 + k.strip * StreamGeom<S>::OUT - StreamGeom<S>::HALO;
-	const bool bad = k.wall ? rb_stream_task<S, true>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring)
-				: rb_stream_task<S, false>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring);
-	// A dividend outside the proven window (the subnormal fringe of a field, an overflow): what this warp
-	// stored may be wrong.  The tile kernel, which spreads such slow cells over 16 warps per tile and
-	// balances tiles dynamically, recomputes the rectangle with IEEE division right after this kernel.
-	if (bad && (threadIdx.x & 31) == 0) redo[1 + atomicAdd(&redo[0], 1)] = task;
+	if (k.wall) rb_stream_task<S, true>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	else rb_stream_task<S, false>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 }
 
 } // namespace fluid

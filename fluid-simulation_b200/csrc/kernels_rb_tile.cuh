@@ -97,7 +97,9 @@ __device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB],
 		for (int k = 0; k < KB; k++) {
 			if (!((redo >> k) & 1)) continue;
 			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
-			q[o] = relax(SECOND ? x0[k].y : x0[k].x, a, q[o - 1], q[o + 1], q[o - RX], q[o + RX], c);
+			// a verified divisor is positive and finite: the cells left over are the subnormal fringe, cheaper in double
+			const float t = (SECOND ? x0[k].y : x0[k].x) + a * (((q[o - 1] + q[o + 1]) + q[o - RX]) + q[o + RX]);
+			q[o] = (dv.range != 0) ? div_wide(t, c) : div_exact(t, c);
 		}
 	}
 	if (WALL) {
@@ -157,7 +159,7 @@ template <int S, int RY, int RX, int NT>
 __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUtensorMap tm_in,
 						    const __grid_constant__ CUtensorMap tm_x0, GridDesc g, int b,
 						    float* __restrict__ xoutb, float a, DivC dv, int ntx, int nty, int ntiles,
-						    int ftx0, int ftx1, int fty1, const int* __restrict__ redo, StreamRect rc,
+						    int ftx0, int ftx1, int fty0, int fty1, const int* __restrict__ redo, StreamRect rc,
 						    int stream_out, int stream_halo)
 {
 	constexpr int HY = 2 * S, HX = ((2 * S + 3) / 4) * 4, TY = RY - 2 * HY, TX = RX - 2 * HX;
@@ -215,15 +217,15 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		q.ty0 = q.ty * TY;
 		return q;
 	};
-	// Frame mode (ftx1 > 0): the tiles with ftx0 <= tx < ftx1 and 1 <= ty < fty1 belong to k_rb_stream; this
-	// launch enumerates only the frame around them -- bottom tile row, top tile rows, left column and
-	// right columns -- from a linear index (few tiles, so the divisions do not matter).
-	const int frame_mid = ftx0 + (ntx - ftx1), frame_top = nty - fty1;
-	const int frame_per_sim = ntx + ntx * frame_top + frame_mid * (fty1 - 1);
+	// Frame mode (ftx1 > 0): the tiles with ftx0 <= tx < ftx1 and fty0 <= ty < fty1 belong to k_rb_stream; this
+	// launch enumerates only the frame around them -- bottom tile rows, top tile rows, left columns and
+	// right columns, possibly none at all -- from a linear index (few tiles, so the divisions do not matter).
+	const int frame_mid = ftx0 + (ntx - ftx1), frame_bot = fty0 * ntx, frame_top = (nty - fty1) * ntx;
+	const int frame_per_sim = frame_bot + frame_top + frame_mid * (fty1 - fty0);
 	// After the frame tiles come the rectangles k_rb_stream could not finish with the short division
 	// (redo[0] of them, task ids in redo[1..]): `redo_rt` tiles stacked over each rectangle.  A redo tile
 	// is wider than the rectangle and may overlap finished neighbours; it stores the same values there.
-	const int redo_rt = (ftx1 > 0) ? (rc.chunk_rows + TY - 1) / TY : 0;
+	const int redo_rt = (ftx1 > 0) ? 1 : 0; // one tile per listed (task, segment): segments are TY rows
 	if (ftx1 > 0) ntiles += redo_rt * redo[0]; // written by the preceding kernel in stream order
 	auto frame_pos = [&](int t) {
 		TilePos q;
@@ -233,22 +235,23 @@ __global__ void __launch_bounds__(NT, 1) k_rb_tile(const __grid_constant__ CUten
 		const int frame_total = ntiles - redo_rt * redo[0];
 		if (t >= frame_total) { // a redo tile
 			const int e = (t - frame_total) / redo_rt, k = (t - frame_total) - e * redo_rt;
-			const StreamTask st = stream_task(rc, redo[1 + e]);
+			const int entry = redo[1 + e], k_seg = entry % rc.segs;
+			const StreamTask st = stream_task(rc, entry / rc.segs);
 			q.sim = st.sim;
 			q.tx0 = rc.col0 + st.strip * stream_out - (XO + 1);
 			// tiles past the rectangle's last row repeat the last useful one (same values, and inside the grid)
-			q.ty0 = min(st.out_lo - 1 + k * TY, max(st.out_lo - 1, st.out_hi - TY));
+			q.ty0 = min(st.out_lo - 1 + (k + k_seg) * TY, max(st.out_lo - 1, st.out_hi - TY));
 			(void) stream_halo;
 			return q;
 		}
 		q.sim = t / frame_per_sim;
 		int k = t - q.sim * frame_per_sim;
-		if (k < ntx) { q.tx = k; q.ty = 0; }
-		else if (k - ntx < ntx * frame_top) { k -= ntx; q.ty = fty1 + k / ntx; q.tx = k - (q.ty - fty1) * ntx; }
+		if (k < frame_bot) { q.ty = k / ntx; q.tx = k - q.ty * ntx; }
+		else if (k - frame_bot < frame_top) { k -= frame_bot; q.ty = fty1 + k / ntx; q.tx = k - (q.ty - fty1) * ntx; }
 		else {
-			k -= ntx + ntx * frame_top;
-			q.ty = 1 + k / frame_mid;
-			const int m = k - (q.ty - 1) * frame_mid;
+			k -= frame_bot + frame_top;
+			q.ty = fty0 + k / frame_mid;
+			const int m = k - (q.ty - fty0) * frame_mid;
 			q.tx = (m < ftx0) ? m : ftx1 + (m - ftx0);
 		}
 		q.tx0 = q.tx * TX;
