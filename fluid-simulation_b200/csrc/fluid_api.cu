@@ -22,6 +22,7 @@
 #include "kernels_relax.cuh"
 #include "kernels_rb_stream.cuh"
 #include "kernels_rb_tile.cuh"
+#include "kernels_blur_stream.cuh"
 #include "kernels_small.cuh"
 
 #include <map>
@@ -286,6 +287,19 @@ static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	return FLUID_OK;
 }
 
+// The list of rectangles a streaming kernel hands to its exact fallback: [0] = count, [1..] = entries.
+static int redo_reserve(fluid_ctx* c, long long entries)
+{
+	if (entries > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many streaming tasks");
+	if (entries > c->redo_capacity) {
+		if (c->d_redo) CU_TRY(cudaFree(c->d_redo));
+		c->d_redo = nullptr;
+		CU_TRY(cudaMalloc(&c->d_redo, sizeof(int) * (size_t) entries));
+		c->redo_capacity = (int) entries;
+	}
+	return FLUID_OK;
+}
+
 // Geometry of one pass of S sweeps: the tile grid, which tiles are left to the tile kernel (the frame)
 // and the rectangle the streaming kernel produces.
 struct PassGeom {
@@ -323,7 +337,7 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
 		if (fx1 <= 1) return pg;
 	}
 	const long long width = (fx0 == 0) ? c->g.N : (long long) (fx1 - 1) * pg.TX;
-	if (width * c->g.NY * c->batch < (1LL << 22)) return pg; // too little to bother
+	if (width * c->g.NY * c->batch < (1LL << 21)) return pg; // too little to bother
 	pg.ftx0 = fx0;
 	pg.ftx1 = fx1;
 	pg.fty1 = fy;
@@ -394,15 +408,9 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 	const bool stream_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
 	const PassGeom pg = pass_geometry<S>(c, stream_ok);
 	if (pg.ftx1 > 0) {
-		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch, entries = ntasks_ll * pg.rc.segs + 1;
-		if (entries > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many streaming tasks");
+		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch;
+		FL_TRY(redo_reserve(c, ntasks_ll * pg.rc.segs + 1));
 		const int ntasks = (int) ntasks_ll;
-		if (entries > c->redo_capacity) {
-			if (c->d_redo) CU_TRY(cudaFree(c->d_redo));
-			c->d_redo = nullptr;
-			CU_TRY(cudaMalloc(&c->d_redo, sizeof(int) * (size_t) entries));
-			c->redo_capacity = (int) entries;
-		}
 		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
 		LAUNCH(k_rb_stream<S>, cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
 	}
@@ -520,6 +528,43 @@ static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 
 // Blur (FluidSystem.cpp:722-743).  x and x0 are the caller's two buffers; on
 // return the result is in x and the penultimate iterate in x0.
+// Blur, L passes per launch (kernels_blur_stream.cuh): the task geometry, or false when the grid does not
+// qualify (rows must be whole float4 groups and at least two strips wide; small grids have their own kernel).
+constexpr int kBlurL = 5, kBlurSeg = 32;
+
+static bool blur_stream_geometry(const fluid_ctx* c, StreamRect* rc)
+{
+	constexpr int OUT = BlurGeom<kBlurL>::OUT;
+	const GridDesc& g = c->g;
+	if (!c->rb_stream || g.N % 4 != 0 || g.N < 2 * OUT || g.NY < 8 * kBlurL) return false;
+	if ((long long) g.N * g.NY * c->batch < (1LL << 21)) return false;
+	*rc = StreamRect{};
+	rc->col0 = XO + 1;
+	rc->col1 = XO + 1 + g.N;
+	rc->row0 = 1;
+	rc->row1 = g.NY + 1;
+	rc->nstrips = cdiv(g.N, OUT);
+	const int rows = g.NY;
+	int nchunks = std::max(1, cdiv(rows, 256));
+	const long long slots = (long long) c->num_sms * 16; // 4 CTAs of 4 warps per SM
+	constexpr int kWallSplit = 2;
+	const long long per_chunk = (long long) (rc->nstrips + 2 * (kWallSplit - 1)) * c->batch;
+	if (per_chunk * nchunks > slots / 2) {
+		const long long waves = std::max(1LL, (per_chunk * nchunks + slots / 2) / slots);
+		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
+	}
+	const int shift = (nchunks > 2) ? 6 * kBlurL : 0;
+	rc->row_shift = shift;
+	rc->chunk_rows = (cdiv(rows + 2 * shift, nchunks) + kWallSplit - 1) / kWallSplit * kWallSplit;
+	rc->nchunks = cdiv(rows + shift, rc->chunk_rows);
+	rc->wall_rows = rc->chunk_rows / kWallSplit;
+	rc->wall_chunks = cdiv(rows + shift, rc->wall_rows);
+	rc->seg_rows = kBlurSeg;
+	rc->segs = cdiv(rc->chunk_rows, kBlurSeg);
+	rc->per_sim = 2 * rc->wall_chunks + (rc->nstrips - 2) * rc->nchunks;
+	return true;
+}
+
 static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 {
 	ProfScope ps(c, FLUID_PROF_BLUR);
@@ -535,7 +580,24 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	DivC dv;
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
 	FL_TRY(dev_set_bnd(c, b, src));
-	for (int k = 0; k < limit; k++) {
+	// kBlurL passes per launch while an even number of such launches fits (the result must land in x with the
+	// penultimate iterate in x0, as the pass-per-launch sequence leaves them); single passes for the rest
+	int done = 0;
+	StreamRect rc;
+	const bool window_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
+	if (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc)) {
+		const int launches = 2 * ((limit - 1) / (2 * kBlurL));
+		const long long ntasks = (long long) rc.per_sim * c->batch;
+		FL_TRY(redo_reserve(c, ntasks * rc.segs + 1));
+		for (int l = 0; l < launches; l++) {
+			if (l > 0) std::swap(dst, src);
+			CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
+			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo, b);
+			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), c->num_sms, 256, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo, b);
+		}
+		done = launches * kBlurL;
+	}
+	for (int k = done; k < limit; k++) {
 		if (k > 0) std::swap(dst, src);
 		LAUNCH(k_blur_pass, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, dst, src, a, dv,
 		       k + 1 < limit ? 1 : 0);

@@ -547,3 +547,31 @@ def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
         oracle.lin_solve(N, b, x, x0, a, c, iters, op.GS_RB)
         assert_bits(fs.download(fl.U), x, "N=%d iters=%d b=%d stream=%s" % (N, iters, b, stream))
         fs.close()
+
+
+@pytest.mark.parametrize("N,stream", [(2048, True), (2500, True), (2048, False)])
+def test_streamed_blur_bitwise(fl, oracle, N, stream):
+    """Blur on large grids runs five Jacobi passes per launch in a register-resident window (an even number
+    of such launches, single passes for the rest: 21 = 4x5+1, 11 = 2x5+1, 31 = 6x5+1, 7 = single passes only),
+    walls and corners included; rectangles whose dividends leave the verified division window -- the field
+    has a subnormal patch and an all-zero patch -- are recomputed by the exact fallback kernel.  Result and
+    penultimate iterate against the CPU statement, bit for bit."""
+    rng = np.random.default_rng(N + 7)
+    W = N + 2
+    for iters, b, a in ((20, 0, np.float32(671.0886)), (10, 1, np.float32(0.37)), (30, 2, np.float32(2.5)), (6, 0, np.float32(1.0))):
+        fs = fl.FluidSystem().Setup(N, gs_iters=iters)
+        fs.SetStreamKernel(stream)
+        fs.SetFastDivision(2)
+        x, x0 = rand_field(rng, N), rand_field(rng, N)
+        g0 = x0.reshape(W, W)
+        g0[300:420, 100:400] *= np.float32(1e-38)   # products and quotients in the subnormal range
+        g0[900:1100, 1500:1900] = 0.0
+        g0[1:40, 1:60] *= np.float32(1e-36)         # ... next to two walls
+        c = 1 + 4 * a
+        fs.upload(fl.U, x)
+        fs.upload(fl.V, x0)
+        fs.blur(b, fl.U, fl.V, a, c)
+        oracle.blur(N, b, x, x0, a, c, iters)
+        assert_bits(fs.download(fl.U), x, "blur N=%d iters=%d b=%d stream=%s" % (N, iters, b, stream))
+        assert_bits(fs.download(fl.V), x0, "blur penultimate iterate N=%d iters=%d b=%d" % (N, iters, b))
+        fs.close()

@@ -39,6 +39,33 @@ def test_slabs_equal_single_domain_bitwise(fl, oracle, count, rows):
         grp.close()
 
 
+def test_large_slabs_use_the_streaming_kernels_bitwise(fl, oracle):
+    """Two slabs of 2048 x 1024 cells are large enough for the register-resident streaming kernels
+    (red-black relaxation and Blur); there the slab's inner end is not a wall -- the row beyond belongs
+    to the neighbour and stays as exchanged -- while its outer end is."""
+    import oracle_py as op
+    from fluid_b200.slabs import LocalSlabGroup
+    N, count, rows = 2048, 2, 1024
+    rng = np.random.default_rng(77)
+    src = op.stam_sources(N) + [(2, 7, N - 3, 0, 50.0), (1, 9, rows, 0, 3.0), (1, 10, rows + 1, 0, 3.0)]
+    init = {k: rand_field(rng, N, 0.5) for k in "u v d".split()}
+    f = {k: init[k].copy() for k in init}
+    f.update({k: np.zeros((N + 2) ** 2, np.float32) for k in "u0 v0 d0".split()})
+    oracle.update(N, f, src, 1e-4, 1e-4, 0.1, 1, order=op.GS_RB)
+    grp = LocalSlabGroup(N, count, rows, visc=1e-4, diff=1e-4, gs_order=fl.GS_REDBLACK)
+    try:
+        grp.SetSources(src)
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            grp.upload(fid, init[name])
+        grp.Update(0.1, 1)
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            out = np.full((N + 2) ** 2, np.nan, np.float32)
+            grp.download(fid, out)
+            assert_bits(out, f[name], "2 slabs of 1024 rows, N=2048: %s" % name)
+    finally:
+        grp.close()
+
+
 def test_backtrace_longer_than_the_halo_is_reported(fl):
     from fluid_b200.slabs import LocalSlabGroup
     N, count, rows = 128, 2, 64
