@@ -81,7 +81,7 @@ struct fluid_ctx {
 	float visc = 0, diff = 0, vorticity = 0, damp = 0;
 	size_t field_bytes = 0;   // one field, all ensemble members
 	static constexpr int kMaxFields = FLUID_FIELD_COUNT + 2 * (FLUID_MAX_FLUIDS - 1);
-	float* f[kMaxFields] = {}; // field id -> device array (ids are fixed; steps swap locals)
+	float* f[kMaxFields] = {}; // field id -> device array (ids are fixed; steps swap locals; rb_tile_solve may trade an array with rb_scratch)
 	int n_fluids = 1, n_fields = FLUID_FIELD_COUNT;
 	float fl_diff[FLUID_MAX_FLUIDS] = {}, fl_visc[FLUID_MAX_FLUIDS] = {};
 	bool fl_set[FLUID_MAX_FLUIDS] = {}; // fluid k has its own coefficients (else it follows fluid 0)
@@ -432,10 +432,16 @@ static int choose_rb_rx(int N)
 	return best;
 }
 
-// `limit` red-black sweeps as an EVEN number of tile passes of 2 or 1 sweeps,
-// ping-ponging between x and the scratch field so that the result ends in x.
-static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc, int limit)
+// `limit` red-black sweeps as passes of 4, 2 or 1 sweeps, ping-ponging between x and the scratch field.
+// After an odd number of passes the result sits in the scratch array: if x is the storage of a context
+// field, that field and the scratch simply trade arrays (c->f is the only place that maps field ids to
+// storage, and x is updated for the caller) -- 20 sweeps are then five 4-sweep passes instead of four and
+// two 2-sweep passes.  For any other array the number of passes is made even.
+static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, int limit)
 {
+	int field = -1;
+	for (int f = 0; f < c->n_fields; f++)
+		if (c->f[f] == x) field = f;
 	if (!c->rb_scratch) {
 		CU_TRY(cudaMalloc(&c->rb_scratch, c->field_bytes));
 		CU_TRY(cudaMemsetAsync(c->rb_scratch, 0, c->field_bytes, c->stream));
@@ -451,12 +457,12 @@ static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 		}
 		n2 = rest / 2;
 		n1 = rest % 2;
-		if ((n4 + n2 + n1) % 2) {
+		if (field < 0 && (n4 + n2 + n1) % 2) {
 			if (n4 > 0) { n4 -= 1; n2 += 2; }
 			else { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
 		}
 	} else {
-		n2 = limit % 2; // an odd count needs one 2-sweep pass to make the number of passes even
+		n2 = (field < 0) ? limit % 2 : 0; // an odd count needs one 2-sweep pass to make the number of passes even
 		n1 = limit - 2 * n2;
 	}
 	const float* in = x;
@@ -468,6 +474,11 @@ static int rb_tile_solve(fluid_ctx* c, int b, float* x, const float* x0, float a
 		float* t = const_cast<float*>(in);
 		in = out;
 		out = t;
+	}
+	if (in != x) { // odd number of passes: the field's values are in the scratch array now
+		c->f[field] = c->rb_scratch;
+		c->rb_scratch = x;
+		x = c->f[field];
 	}
 	return FLUID_OK;
 }
@@ -491,7 +502,8 @@ static int small_configure(fluid_ctx* c)
 }
 
 // LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
-static int dev_lin_solve(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
+// x may come back pointing at another array (rb_tile_solve); callers keep using x, not a copy made before.
+static int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc)
 {
 	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
 	const int limit = a > 0 ? c->gs_iters : 1;
@@ -630,7 +642,7 @@ static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0
 }
 
 // Project (FluidSystem.cpp:982-1007).
-static int dev_project(fluid_ctx* c, float* u, float* v, float* p, float* div)
+static int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
 {
 	{
 		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
@@ -1418,7 +1430,8 @@ extern "C" int fluid_ctx_lin_solve(fluid_ctx* c, int b, int x, int x0, float a, 
 {
 	CHECK_CTX(c);
 	FL_TRY(check_distinct_n(c->n_fields, { x, x0 }));
-	return dev_lin_solve(c, b, c->f[x], c->f[x0], a, cc);
+	float* px = c->f[x];
+	return dev_lin_solve(c, b, px, c->f[x0], a, cc);
 }
 
 extern "C" int fluid_ctx_blur(fluid_ctx* c, int b, int x, int x0, float a, float cc)
@@ -1448,7 +1461,8 @@ extern "C" int fluid_ctx_project(fluid_ctx* c, int u, int v, int p, int div)
 {
 	CHECK_CTX(c);
 	FL_TRY(check_distinct_n(c->n_fields, { u, v, p, div }));
-	return dev_project(c, c->f[u], c->f[v], c->f[p], c->f[div]);
+	float* pp = c->f[p];
+	return dev_project(c, c->f[u], c->f[v], pp, c->f[div]);
 }
 
 extern "C" int fluid_ctx_time_kernel(fluid_ctx* c, int which, int reps, float* ms)
@@ -1456,10 +1470,11 @@ extern "C" int fluid_ctx_time_kernel(fluid_ctx* c, int which, int reps, float* m
 	CHECK_CTX(c);
 	if (!ms || reps < 1) return fail(FLUID_ERR_INVALID, "bad arguments");
 	const float a = diffusion_a(c, c->visc > 0 ? c->visc : 1e-4f, 0.1f);
-	float *U = c->f[FLUID_U], *V = c->f[FLUID_V], *D = c->f[FLUID_DENS];
-	float *U0 = c->f[FLUID_U_PREV], *V0 = c->f[FLUID_V_PREV], *D0 = c->f[FLUID_DENS_PREV];
 	CU_TRY(cudaEventRecord(c->ev0, c->stream));
 	for (int r = 0; r < reps; r++) {
+		// (a red-black solve may move a field to another array, so the table is read afresh every time)
+		float *U = c->f[FLUID_U], *V = c->f[FLUID_V], *D = c->f[FLUID_DENS];
+		float *U0 = c->f[FLUID_U_PREV], *V0 = c->f[FLUID_V_PREV], *D0 = c->f[FLUID_DENS_PREV];
 		switch (which) {
 		case FLUID_K_LIN_SOLVE: FL_TRY(dev_lin_solve(c, 1, U0, U, a, 1 + 4 * a)); break;
 		case FLUID_K_BLUR: FL_TRY(dev_blur(c, 0, D0, D, a, 1 + 4 * a)); break;
@@ -1558,7 +1573,8 @@ extern "C" int fluid_lin_solve(int N, int b, float* x, const float* x0, float a,
 	FL_TRY(host_ctx(N, &c));
 	FL_TRY(up(c, 0, x));
 	FL_TRY(up(c, 1, x0));
-	FL_TRY(dev_lin_solve(c, b, c->f[0], c->f[1], a, cc));
+	float* px = c->f[0];
+	FL_TRY(dev_lin_solve(c, b, px, c->f[1], a, cc));
 	FL_TRY(down_async(c, 0, x));
 	return finish(c);
 }
@@ -1572,7 +1588,8 @@ extern "C" int fluid_diffuse(int N, int b, float* x, const float* x0, float diff
 	FL_TRY(up(c, 0, x));
 	FL_TRY(up(c, 1, x0));
 	const float a = diffusion_a(c, diff, dt);
-	FL_TRY(dev_lin_solve(c, b, c->f[0], c->f[1], a, 1 + 4 * a));
+	float* px = c->f[0];
+	FL_TRY(dev_lin_solve(c, b, px, c->f[1], a, 1 + 4 * a));
 	FL_TRY(down_async(c, 0, x));
 	return finish(c);
 }
@@ -1619,7 +1636,8 @@ extern "C" int fluid_project(int N, float* u, float* v, float* p, float* div)
 	FL_TRY(up(c, 0, u));
 	FL_TRY(up(c, 1, v));
 	FL_TRY(up(c, 3, div)); // div's border cells survive the call (FluidSystem.cpp:986-990 write the interior only)
-	FL_TRY(dev_project(c, c->f[0], c->f[1], c->f[2], c->f[3]));
+	float* pp = c->f[2];
+	FL_TRY(dev_project(c, c->f[0], c->f[1], pp, c->f[3]));
 	FL_TRY(down_async(c, 0, u));
 	FL_TRY(down_async(c, 1, v));
 	if (t_scratch_download) {

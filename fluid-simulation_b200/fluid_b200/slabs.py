@@ -73,10 +73,12 @@ class NcclExchange:
         fs.SetExchange(self)
 
     def _blocks(self, field):
-        if field not in self.cache:
-            sd, rd, su, ru, n = self.fs.HaloRegions(field)
-            self.cache[field] = tuple(device_tensor(p, n, self.device) if p else None for p in (sd, rd, su, ru))
-        return self.cache[field]
+        # asked afresh every time: a red-black solve may move a field to another device array
+        sd, rd, su, ru, n = self.fs.HaloRegions(field)
+        key = (sd, rd, su, ru, n)
+        if key not in self.cache:
+            self.cache[key] = tuple(device_tensor(p, n, self.device) if p else None for p in (sd, rd, su, ru))
+        return self.cache[key]
 
     def __call__(self, fields):
         blocks = [self._blocks(f) for f in fields]
