@@ -217,7 +217,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -329,7 +329,7 @@ def run_b200(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": roofline, "cpu_baseline": cpu,
         }
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0
@@ -397,6 +397,16 @@ def measure_e2e(fl, np, N, order, steps, dist, local, world):
             "api": "fluid_update (FluidSystem::Update on host pointers, pinned): 3 fields up, step, 3 fields down"}
 
 
+def emit(line):
+    """The ONE line of stdout."""
+    os.write(_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 if __name__ == "__main__":
     a = parse()
+    # Libraries write to the process's stdout behind Python's back (NCCL prints its version banner there when
+    # NCCL_DEBUG asks for it): everything but the result line goes to stderr, the result to the real stdout.
+    sys.stdout.flush()
+    _STDOUT = os.dup(1)
+    os.dup2(2, 1)
     sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

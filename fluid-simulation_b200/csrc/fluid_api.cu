@@ -117,7 +117,7 @@ struct fluid_ctx {
 	std::map<uint32_t, double> div_work; // cell updates seen per not-yet-verified divisor
 	unsigned int* d_divbins = nullptr;
 	float* rb_scratch = nullptr;
-	std::map<const float*, CUtensorMap> tmaps;
+	std::map<std::pair<const float*, int>, CUtensorMap> tmaps; // (array, window width) -> descriptor
 	// optional per-kernel-class device timing (CUDA event pairs on c->stream)
 	bool prof_on = false;
 	struct ProfSeg { cudaEvent_t a, b; int cls; unsigned long long launches; };
@@ -227,21 +227,21 @@ static int get_encode_fn(EncodeTiledFn* out)
 }
 
 // TMA descriptor of one field: 3-D tensor (pitch, NY+2, batch) of floats, box = one tile window.
-static int field_tmap(fluid_ctx* c, const float* base, const CUtensorMap** out)
+static int field_tmap(fluid_ctx* c, const float* base, int rx, const CUtensorMap** out)
 {
-	auto it = c->tmaps.find(base);
+	auto it = c->tmaps.find({ base, rx });
 	if (it == c->tmaps.end()) {
 		EncodeTiledFn enc = nullptr;
 		FL_TRY(get_encode_fn(&enc));
 		CUtensorMap m;
 		const cuuint64_t dims[3] = { (cuuint64_t) c->g.pitch, (cuuint64_t) (c->g.NY + 2), (cuuint64_t) c->batch };
 		const cuuint64_t strides[2] = { (cuuint64_t) c->g.pitch * sizeof(float), (cuuint64_t) c->g.plane * sizeof(float) };
-		const cuuint32_t box[3] = { (cuuint32_t) c->rb_rx, (cuuint32_t) kRbRY, 1 };
+		const cuuint32_t box[3] = { (cuuint32_t) rx, (cuuint32_t) kRbRY, 1 };
 		const cuuint32_t estr[3] = { 1, 1, 1 };
 		CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*) base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 				 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 		if (r != CUDA_SUCCESS) return fail(FLUID_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int) r);
-		it = c->tmaps.emplace(base, m).first;
+		it = c->tmaps.emplace(std::make_pair(base, rx), m).first;
 	}
 	*out = &it->second;
 	return FLUID_OK;
@@ -384,8 +384,8 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 		if (c->device < 64) configured[c->device] = true;
 	}
 	const CUtensorMap *tm, *tm0;
-	FL_TRY(field_tmap(c, in, &tm));
-	FL_TRY(field_tmap(c, x0, &tm0));
+	FL_TRY(field_tmap(c, in, RX, &tm));
+	FL_TRY(field_tmap(c, x0, RX, &tm0));
 	long long ntiles = (long long) pg.ntx * pg.nty;
 	if (pg.ftx1 > 0) ntiles -= (long long) (pg.ftx1 - pg.ftx0) * (pg.fty1 - pg.fty0); // the frame only, possibly nothing
 	ntiles *= c->batch;
@@ -413,6 +413,14 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 		const int ntasks = (int) ntasks_ll;
 		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
 		LAUNCH(k_rb_stream<S>, cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
+	}
+	// nothing but listed rectangles to do: the narrowest window covers a strip (112 columns) and has the
+	// shortest colour passes -- a redo launch lasts as long as one tile does
+	if (pg.ftx1 > 0 && pg.ftx0 == 0 && pg.ftx1 == pg.ntx && pg.fty0 == 0 && pg.fty1 == pg.nty && StreamGeom<S>::OUT <= 128 - 2 * StreamGeom<S>::HALO) {
+		PassGeom narrow = pg;
+		narrow.TX = 128 - 2 * StreamGeom<S>::HALO;
+		narrow.ntx = narrow.ftx1 = cdiv(c->g.N, narrow.TX);
+		return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv, narrow);
 	}
 	switch (c->rb_rx) {
 	case 128: return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv, pg);
@@ -605,7 +613,8 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 			if (l > 0) std::swap(dst, src);
 			CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
 			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo, b);
-			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), c->num_sms, 256, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo, b);
+			// few entries, each a chain of 2L barrier-separated phases over ~5000 cells: wide CTAs keep the chain short
+			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo, b);
 		}
 		done = launches * kBlurL;
 	}

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(128, 4) k_blur_stream(GridDesc g, StreamRect r
 // The listed (task, segment) rectangles again, with exact division: one CTA per entry does the L passes on
 // the rectangle plus L cells all round in shared memory.  SEG is the segment height (rc.seg_rows).
 template <int L, int SEG>
-__global__ void __launch_bounds__(256) k_blur_redo(GridDesc g, StreamRect rc, const float* __restrict__ xinb, float* __restrict__ xoutb,
+__global__ void __launch_bounds__(1024) k_blur_redo(GridDesc g, StreamRect rc, const float* __restrict__ xinb, float* __restrict__ xoutb,
 						    float a, float c, const int* __restrict__ redo, int b)
 {
 	constexpr int OUT = BlurGeom<L>::OUT, WW = OUT + 2 * L, WH = SEG + 2 * L, P = WW + 1;
