@@ -101,6 +101,9 @@ struct fluid_ctx {
 	void* exchange_user = nullptr;
 	bool exchange_stream_ordered = false; // the transport enqueues on c->stream; no host sync around it
 	cudaStream_t own_stream = nullptr;    // the stream created with the context (c->stream may be the caller's)
+	// fluid_update overlaps its bus transfers with the step: second stream + the two events that order them
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t ev_dens_up = nullptr, ev_vel_done = nullptr;
 	int* d_oob = nullptr;
 	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
@@ -794,7 +797,9 @@ static inline float visc_avg(const fluid_ctx* c)
 }
 
 // FluidSystem::Update (FluidSystem.cpp:101-128) for FSType::ORIGINAL.
-static int dev_update(fluid_ctx* c, float dt)
+// FluidSystem::Update (FluidSystem.cpp:101-128) in two halves: forcing + vorticity + VelStep, then DensStep +
+// damping.  fluid_update() slips bus transfers in between; everybody else calls dev_update.
+static int dev_update_velocity(fluid_ctx* c, float dt)
 {
 	{
 		ProfScope ps(c, FLUID_PROF_OTHER);
@@ -818,7 +823,11 @@ static int dev_update(fluid_ctx* c, float dt)
 		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
 		FL_TRY(halo_exchange(c, { c->f[FLUID_U], c->f[FLUID_V] })); // three stencil phases consumed 3 halo rows
 	}
-	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt));
+	return dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt);
+}
+
+static int dev_update_density(fluid_ctx* c, float dt)
+{
 	for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
 		FL_TRY(dev_dens_step(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], fluid_diff(c, fl), dt));
 	if (c->damp != 0.0f) {
@@ -826,6 +835,12 @@ static int dev_update(fluid_ctx* c, float dt)
 		FL_TRY(dev_damp(c, c->f[FLUID_V], c->damp, dt));
 	}
 	return FLUID_OK;
+}
+
+static int dev_update(fluid_ctx* c, float dt)
+{
+	FL_TRY(dev_update_velocity(c, dt));
+	return dev_update_density(c, dt);
 }
 
 // ---------------------------------------------------------------------------
@@ -942,6 +957,9 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);
+	if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+	if (c->ev_dens_up) cudaEventDestroy(c->ev_dens_up);
+	if (c->ev_vel_done) cudaEventDestroy(c->ev_vel_done);
 	if (c->own_stream) cudaStreamDestroy(c->own_stream);
 	delete c;
 	return FLUID_OK;
@@ -1703,13 +1721,49 @@ extern "C" int fluid_update(int N, float* u, float* v, float* dens, int nsrc, co
 	c->diff = diff;
 	c->vorticity = vorticity;
 	c->damp = damp;
-	FL_TRY(up(c, FLUID_U, u));
-	FL_TRY(up(c, FLUID_V, v));
-	FL_TRY(up(c, FLUID_DENS, dens));
-	FL_TRY(dev_update(c, dt));
-	FL_TRY(down_async(c, FLUID_U, u));
-	FL_TRY(down_async(c, FLUID_V, v));
-	FL_TRY(down_async(c, FLUID_DENS, dens));
+	// The density is not needed before DensStep and the velocity is final after VelStep (no damping): with
+	// pinned host arrays the density goes up while VelStep runs and the velocity comes down while DensStep
+	// runs, on a second stream.  Forcing that writes the current density needs it on the device first.
+	bool overlap = (damp == 0.0f);
+	for (int k = 0; k < nsrc; k++)
+		if (src[k].mode != FLUID_SRC_PREV_SET && src[k].field >= FLUID_DENS) overlap = false;
+	if (!overlap) {
+		FL_TRY(up(c, FLUID_U, u));
+		FL_TRY(up(c, FLUID_V, v));
+		FL_TRY(up(c, FLUID_DENS, dens));
+		FL_TRY(dev_update(c, dt));
+		FL_TRY(down_async(c, FLUID_U, u));
+		FL_TRY(down_async(c, FLUID_V, v));
+		FL_TRY(down_async(c, FLUID_DENS, dens));
+		return finish(c);
+	}
+	if (!c->copy_stream) {
+		CU_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+		CU_TRY(cudaEventCreateWithFlags(&c->ev_dens_up, cudaEventDisableTiming));
+		CU_TRY(cudaEventCreateWithFlags(&c->ev_vel_done, cudaEventDisableTiming));
+	}
+	const size_t w = (size_t) (c->g.N + 2) * sizeof(float), dp = (size_t) c->g.pitch * sizeof(float);
+	auto enqueue = [&]() -> int {
+		FL_TRY(up(c, FLUID_U, u));
+		FL_TRY(up(c, FLUID_V, v));
+		CU_TRY(cudaMemcpy2DAsync(c->f[FLUID_DENS] + XO, dp, dens, w, w, c->g.NY + 2, cudaMemcpyHostToDevice, c->copy_stream));
+		CU_TRY(cudaEventRecord(c->ev_dens_up, c->copy_stream));
+		FL_TRY(dev_update_velocity(c, dt));
+		CU_TRY(cudaEventRecord(c->ev_vel_done, c->stream));
+		CU_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_vel_done, 0));
+		CU_TRY(cudaMemcpy2DAsync(u, w, c->f[FLUID_U] + XO, dp, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->copy_stream));
+		CU_TRY(cudaMemcpy2DAsync(v, w, c->f[FLUID_V] + XO, dp, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->copy_stream));
+		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_dens_up, 0));
+		FL_TRY(dev_update_density(c, dt));
+		return down_async(c, FLUID_DENS, dens);
+	};
+	const int rc = enqueue();
+	if (rc != FLUID_OK) { // nothing may still be writing the caller's arrays when the error is returned
+		cudaStreamSynchronize(c->copy_stream);
+		cudaStreamSynchronize(c->stream);
+		return rc;
+	}
+	CU_TRY(cudaStreamSynchronize(c->copy_stream));
 	return finish(c);
 }
 
