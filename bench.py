@@ -281,22 +281,36 @@ def run_b200(args):
     cells = float(N) * rows_per_gpu * world
     value = cells * args.steps / (ms * 1e-3)
 
-    # roofline of the dominant kernel class (Gauss-Seidel sweeps), measured inside the timed region
+    # roofline of the dominant kernel (the red-black relaxation), measured inside the timed region
     peak, peak_src = peaks()
     gs_ms, gs_launches = prof["lin_solve"]
-    gs_bytes = B_GS_SWEEP * float(N) * N * GS_SWEEPS_PER_STEP * args.steps
+    gs_bytes = B_GS_SWEEP * float(N) * rows_per_gpu * GS_SWEEPS_PER_STEP * args.steps
     achieved = gs_bytes / (gs_ms * 1e-3) / 1e9 if gs_ms > 0 else 0.0
-    traffic = None
+    traffic = tkernel = None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get("traffic_bytes_per_launch")
-    step_gbs = B_CELL_UPDATE * float(N) * N * args.steps / (ms * 1e-3) / 1e9
+        tj = json.load(open(tpath))
+        traffic, tkernel = tj.get("traffic_bytes_per_launch"), tj.get("kernel")
+    # large grids: a pass is k_rb_stream<4> (4 sweeps) followed by the launch that recomputes the rectangles it
+    # listed -- two launches; the pair is the unit below.  Otherwise every launch of the class is a unit.
+    passes4 = GS_SWEEPS_PER_STEP * args.steps // 4
+    if args.order == "redblack" and gs_launches == 2 * passes4:
+        units, unit_name = passes4, "k_rb_stream<4> + redo launch = one pass of 4 red-black sweeps"
+    else:
+        units, unit_name, traffic = max(1, gs_launches), "one launch of the relaxation kernels (%s)" % args.order, None
+    step_gbs = B_CELL_UPDATE * float(N) * rows_per_gpu * args.steps / (ms * 1e-3) / 1e9
+    ms_unit = gs_ms / units
     roofline = {
-        "bound": "hbm", "kernel": "Gauss-Seidel relaxation (%s), %d launches in the timed region" % (args.order, gs_launches),
+        "bound": "hbm", "kernel": "%s; %d launches in the timed region" % (unit_name, gs_launches),
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-        "traffic": traffic,
-        "algorithmic_bytes_per_launch": gs_bytes / max(1, gs_launches),
-        "ms_per_launch": gs_ms / max(1, gs_launches),
+        "traffic": traffic, "traffic_kernel": tkernel,
+        "algorithmic_bytes_per_launch": gs_bytes / units,
+        "ms_per_launch": ms_unit,
+        "dram_gbs": (traffic / (ms_unit * 1e-3) / 1e9) if traffic else None,
+        "note": "algorithmic bytes charge every sweep one pass over x0 and x (12 B per cell); the streaming kernel keeps rows "
+                "in registers for 4 sweeps, so its DRAM traffic (`traffic`) is ~3.3x smaller and achieved exceeds the HBM "
+                "peak: frac > 1 is the gain of temporal blocking over the per-sweep roofline.  The kernel itself is bound "
+                "by instruction issue (profiles/README.md), at dram_gbs of real traffic",
         "share_of_step": gs_ms / max(1e-9, sum(v[0] for v in prof.values())),
         "whole_step": {"achieved": step_gbs, "frac": step_gbs / peak, "bytes_per_cell_update": B_CELL_UPDATE},
         "classes_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},

@@ -635,10 +635,14 @@ static int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const floa
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
-	if (c->slab_count > 1)
-		LAUNCH(k_advect<true>, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
-	else
-		LAUNCH(k_advect<false>, cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->advect_mode, c->d_oob, 1, 0);
+	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	if (c->slab_count > 1) {
+		if (euler) LAUNCH((k_advect<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+		else LAUNCH((k_advect<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	} else {
+		if (euler) LAUNCH((k_advect<false, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, 1, 0);
+		else LAUNCH((k_advect<false, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, 1, 0);
+	}
 	return FLUID_OK;
 }
 
@@ -646,10 +650,14 @@ static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
-	if (c->slab_count > 1)
-		LAUNCH(k_advect_velocity<true>, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
-	else
-		LAUNCH(k_advect_velocity<false>, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->advect_mode, c->d_oob, 1, 0);
+	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	if (c->slab_count > 1) {
+		if (euler) LAUNCH((k_advect_velocity<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+		else LAUNCH((k_advect_velocity<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	} else {
+		if (euler) LAUNCH((k_advect_velocity<false, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0);
+		else LAUNCH((k_advect_velocity<false, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0);
+	}
 	return FLUID_OK;
 }
 
@@ -1035,6 +1043,10 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	}
 	c->g.pitch = ((XO + p->N + 2 + 31) / 32) * 32;
 	c->g.plane = (long long) c->g.pitch * (c->g.NY + 2);
+	if (c->g.plane >= (1LL << 31)) { // kernels index one member's plane with 32-bit offsets
+		delete c;
+		return fail(FLUID_ERR_UNSUPPORTED, "a field of %d x %d cells has 2^31 floats or more; split it into row slabs", p->N, c->g.NY);
+	}
 	c->rb_rx = choose_rb_rx(p->N);
 	c->field_bytes = (size_t) c->g.plane * c->batch * sizeof(float);
 	c->src.resize(c->batch);

@@ -214,10 +214,14 @@ __global__ void __launch_bounds__(256) k_subtract_gradient(GridDesc g, float* __
 // ---------------------------------------------------------------------------
 // BilinearCoeffs::calc + Eval (FluidCode.h:91-112), generalised to NY rows.
 // ---------------------------------------------------------------------------
+// Offsets inside one member's plane are 32-bit (the context refuses planes of 2^31 floats or more): the
+// gathers were spending more instructions on 64-bit address arithmetic than on the interpolation.
 struct Bilin {
-	long long o00; // offset of (i0,j0); (i1,j0)=+1, (i0,j1)=+pitch
+	int o00; // offset of (i0,j0); (i1,j0)=+1, (i0,j1)=+pitch
 	float s0, s1, t0, t1;
 };
+
+__device__ __forceinline__ int celli(const GridDesc& g, int i, int j) { return j * g.pitch + (XO + i); }
 
 // (px, py) are GLOBAL cell coordinates; the sampled rows are converted to local ones at the end.
 // The reference clamps with `if (i < 0.5f) i = 0.5f; if (i > N + 0.5f) i = N + 0.5f` (FluidCode.h:95-103);
@@ -245,28 +249,36 @@ __device__ __forceinline__ Bilin bilin_calc(const GridDesc& g, float px, float p
 			jl = min(max(jl, 0), g.NY);
 		}
 	}
-	r.o00 = cell(g, i0, jl);
+	r.o00 = celli(g, i0, jl);
 	return r;
 }
 
-__device__ __forceinline__ float bilin_eval(const Bilin& c, const float* __restrict__ f, int pitch)
+// `fc` points at the THREAD'S OWN cell (offset `id`) of the field, the sample is addressed relative to it:
+// a per-thread 64-bit pointer plus a 32-bit difference is one IMAD.WIDE, whereas kernel-parameter base +
+// member offset + cell offset made the compiler rebuild a 64-bit sum (shifts, carries: ~5 instructions) for
+// every one of the 12-16 gathers of a cell -- more integer work than the interpolation has arithmetic.
+// (opaque_ptr: left to itself the compiler folds the pointer back into base + index and does the 64-bit sum again)
+__device__ __forceinline__ void opaque_ptr(const float*& p) { asm("" : "+l"(p)); }
+
+__device__ __forceinline__ float bilin_eval(const Bilin& c, const float* __restrict__ fc, int id, int pitch)
 {
-	const float d00 = __ldg(f + c.o00), d10 = __ldg(f + c.o00 + 1);
-	const float d01 = __ldg(f + c.o00 + pitch), d11 = __ldg(f + c.o00 + pitch + 1);
+	const float* r0 = fc + (c.o00 - id);
+	const float* r1 = r0 + pitch;
+	const float d00 = __ldg(r0), d10 = __ldg(r0 + 1);
+	const float d01 = __ldg(r1), d11 = __ldg(r1 + 1);
 	return c.s0 * (c.t0 * d00 + c.t1 * d01) + c.s1 * (c.t0 * d10 + c.t1 * d11);
 }
 
 // Backtraced sample position of cell (i,j): MidpointBackward (FluidSystem.h:185-206)
 // or EulerBack (FluidSystem.h:208-219).
 // (i, j) local; the returned position is in global coordinates.
-template <bool SLAB>
-__device__ __forceinline__ void backtrace(const GridDesc& g, const float* __restrict__ u, const float* __restrict__ v,
-					  int i, int j, float dtN, int mode, float& px, float& py, int* oob)
+template <bool SLAB, int MODE>
+__device__ __forceinline__ void backtrace(const GridDesc& g, const float* __restrict__ uc_p, const float* __restrict__ vc_p,
+					  int i, int j, int id, float dtN, float& px, float& py, int* oob)
 {
-	const long long id = cell(g, i, j);
-	const float uc = __ldg(u + id), vc = __ldg(v + id);
+	const float uc = __ldg(uc_p), vc = __ldg(vc_p); // pointers at the thread's own cell
 	const int jg = SLAB ? j + g.j0 : j;
-	if (mode == 1) {
+	if (MODE == 1) {
 		px = i - dtN * uc;
 		py = jg - dtN * vc;
 	} else {
@@ -275,8 +287,8 @@ __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __rest
 		const float mx = i + 0.5f * dirx;
 		const float my = jg + 0.5f * diry;
 		const Bilin m = bilin_calc<SLAB>(g, mx, my, oob);
-		const float vx = bilin_eval(m, u, g.pitch);
-		const float vy = bilin_eval(m, v, g.pitch);
+		const float vx = bilin_eval(m, uc_p, id, g.pitch);
+		const float vy = bilin_eval(m, vc_p, id, g.pitch);
 		px = i - dtN * vx;
 		py = jg - dtN * vy;
 	}
@@ -286,10 +298,10 @@ __device__ __forceinline__ void backtrace(const GridDesc& g, const float* __rest
 // Advect1 (FluidSystem.cpp:850-862) for one scalar field, SetBorder fused.
 // Gather kernel: u,v,d0 read, d written = 16 B per cell algorithmic.
 // ---------------------------------------------------------------------------
-template <bool SLAB>
+template <bool SLAB, int MODE>
 __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __restrict__ db, const float* __restrict__ d0b,
 						 const float* __restrict__ ub, const float* __restrict__ vb, float dtN,
-						 int mode, int* oob_flag, int own_lo, int own_hi)
+						 int* oob_flag, int own_lo, int own_hi)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
@@ -297,39 +309,55 @@ __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __rest
 	if (i > g.N || j > g.NY) return;
 	int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
 	float px, py;
-	backtrace<SLAB>(g, ub + off, vb + off, i, j, dtN, mode, px, py, oob);
+	const int id = celli(g, i, j);
+	const long long mine = off + id;
+	const float* d0c = d0b + mine;
+	const float* uc = ub + mine;
+	const float* vc = vb + mine;
+	opaque_ptr(d0c);
+	opaque_ptr(uc);
+	opaque_ptr(vc);
+	// The sample of d0 is taken three dependent memory round trips from now, most often within a cell or two
+	// of this one: touch the two lines now, together with the loads of u and v.  Nothing uses the values, and
+	// a prefetch hint or an unused load ends up scheduled right before the sample (or removed), so they are
+	// tied into the address of the mid-point gathers through a term that is always zero (g.walls < 4) but that the
+	// compiler cannot evaluate.
+	const int warm = (__float_as_int(__ldg(d0c)) | __float_as_int(__ldg(d0c + g.pitch))) & (g.walls >> 2);
+	backtrace<SLAB, MODE>(g, uc, vc, i, j, id + warm, dtN, px, py, oob); // (id only offsets the mid-point gathers)
 	const Bilin c = bilin_calc<SLAB>(g, px, py, oob);
-	const float val = bilin_eval(c, d0b + off, g.pitch);
-	float* d = db + off;
-	d[cell(g, i, j)] = val;
-	mirror_border(g, d, b, i, j, val);
+	const float val = bilin_eval(c, d0c, id, g.pitch);
+	db[mine] = val;
+	mirror_border(g, db + off, b, i, j, val);
 }
 
 // VelStep1's self-advection (FluidSystem.cpp:372-373): Advect1(1,u,u0,u0,v0) and
 // Advect1(2,v,v0,u0,v0) share the backtrace, so both components are produced
 // by one pass over (u0,v0): 16 B per cell instead of 2 x 12 B.
-template <bool SLAB>
+template <bool SLAB, int MODE>
 __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
 							  const float* __restrict__ u0b, const float* __restrict__ v0b,
-							  float dtN, int mode, int* oob_flag, int own_lo, int own_hi)
+							  float dtN, int* oob_flag, int own_lo, int own_hi)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
 	const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
 	if (i > g.N || j > g.NY) return;
 	int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr;
-	const float* u0 = u0b + off;
-	const float* v0 = v0b + off;
 	float px, py;
-	backtrace<SLAB>(g, u0, v0, i, j, dtN, mode, px, py, oob);
+	const int id = celli(g, i, j);
+	const long long mine = off + id;
+	const float* u0c = u0b + mine;
+	const float* v0c = v0b + mine;
+	opaque_ptr(u0c);
+	opaque_ptr(v0c);
+	backtrace<SLAB, MODE>(g, u0c, v0c, i, j, id, dtN, px, py, oob);
 	const Bilin c = bilin_calc<SLAB>(g, px, py, oob);
-	const float un = bilin_eval(c, u0, g.pitch);
-	const float vn = bilin_eval(c, v0, g.pitch);
+	const float un = bilin_eval(c, u0c, id, g.pitch);
+	const float vn = bilin_eval(c, v0c, id, g.pitch);
 	float* u = ub + off;
 	float* v = vb + off;
-	const long long id = cell(g, i, j);
-	u[id] = un;
-	v[id] = vn;
+	ub[mine] = un;
+	vb[mine] = vn;
 	mirror_border(g, u, 1, i, j, un);
 	mirror_border(g, v, 2, i, j, vn);
 }
