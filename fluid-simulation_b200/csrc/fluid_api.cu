@@ -111,6 +111,21 @@ struct fluid_ctx {
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
 	bool rb_stream = true;     // interior of large grids by the register-resident streaming kernel (k_rb_stream)
+	// Feedback for the streaming kernels ([0] relaxation, [1] blur).  They hand every segment that met a
+	// dividend outside the verified window to an exact fallback; on fields that are mostly fringe (an ensemble
+	// of small grids, each with its own front decaying through the subnormals) most segments come back and the
+	// streaming pass was wasted.  The count of the last launch of a solve is copied to pinned memory; when it
+	// has arrived (no waiting) and says more than a twelfth of the segments were redone -- an exact tile costs
+	// about ten times its share of a streaming pass, measured break-even 8-12 % -- the next solves use the
+	// pass-per-launch kernels, and streaming is tried again after kStreamHoldoff of them.  Results are
+	// bit-identical either way.
+	struct StreamFeedback {
+		int* h_count = nullptr; // pinned
+		cudaEvent_t arrived = nullptr;
+		bool pending = false;
+		long long segments = 0; // segments of the launch whose count is in flight
+		int holdoff = 0;
+	} feedback[2];
 	int* d_redo = nullptr;     // [0] = count, [1..] = stream tasks the tile kernel must recompute
 	int redo_capacity = 0;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
@@ -290,6 +305,40 @@ static int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	return FLUID_OK;
 }
 
+constexpr int kStreamHoldoff = 64;
+
+// May this solve use the streaming kernel?  Consumes the count of an earlier launch if it has arrived.
+static bool stream_allowed(fluid_ctx* c, int which)
+{
+	auto& fb = c->feedback[which];
+	if (fb.pending && cudaEventQuery(fb.arrived) == cudaSuccess) {
+		fb.pending = false;
+		if (getenv("FLUID_DEBUG_FEEDBACK")) fprintf(stderr, "feedback[%d]: %d of %lld segments redone\n", which, *fb.h_count, fb.segments);
+		if (fb.segments > 0 && (long long) *fb.h_count * 12 > fb.segments) fb.holdoff = kStreamHoldoff;
+	}
+	if (fb.holdoff > 0) {
+		fb.holdoff--;
+		return false;
+	}
+	return c->rb_stream;
+}
+
+// After the last streaming launch of a solve: send its redo count home (asynchronously).
+static int stream_report(fluid_ctx* c, int which, long long segments)
+{
+	auto& fb = c->feedback[which];
+	if (fb.pending) return FLUID_OK; // an earlier count is still in flight; one at a time
+	if (!fb.h_count) {
+		CU_TRY(cudaMallocHost(&fb.h_count, sizeof(int)));
+		CU_TRY(cudaEventCreateWithFlags(&fb.arrived, cudaEventDisableTiming));
+	}
+	CU_TRY(cudaMemcpyAsync(fb.h_count, c->d_redo, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaEventRecord(fb.arrived, c->stream));
+	fb.segments = segments;
+	fb.pending = true;
+	return FLUID_OK;
+}
+
 // The list of rectangles a streaming kernel hands to its exact fallback: [0] = count, [1..] = entries.
 static int redo_reserve(fluid_ctx* c, long long entries)
 {
@@ -312,7 +361,7 @@ struct PassGeom {
 };
 
 template <int S>
-static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
+static PassGeom pass_geometry(const fluid_ctx* c, bool stream_ok) // stream_ok: verified division at hand and streaming allowed
 {
 	PassGeom pg{};
 	pg.TY = kRbRY - 4 * S;
@@ -320,7 +369,7 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool have_fast_division)
 	pg.ntx = cdiv(c->g.N, pg.TX);
 	pg.nty = cdiv(c->g.NY, pg.TY);
 	pg.ftx0 = pg.ftx1 = pg.fty0 = pg.fty1 = 0;
-	if (!c->rb_stream || !have_fast_division) return pg; // the streaming kernel only knows the verified division
+	if (!stream_ok) return pg; // the streaming kernel only knows the verified division
 	constexpr int L = StreamGeom<S>::L, HALO = StreamGeom<S>::HALO;
 	if (StreamGeom<S>::OUT > pg.TX) return pg;             // a redo tile must cover a strip's width
 	// Rows: all of them; the streaming kernel does the bottom and top walls' set_bnd (or, for a slab that
@@ -405,13 +454,14 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 // The window width of the tile kernel is chosen per context so that ceil(N / (RX-8)) windows waste the
 // fewest columns (N=512: 3 x 192 instead of 3 x 256; N <= 120: one 128-wide window instead of 256).
 template <int S>
-static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv)
+static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv, bool streaming,
+			long long* segments)
 {
-	// the streaming kernel relies on the proven window reaching the largest finite float
-	const bool stream_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
-	const PassGeom pg = pass_geometry<S>(c, stream_ok);
+	const PassGeom pg = pass_geometry<S>(c, streaming);
+	*segments = 0;
 	if (pg.ftx1 > 0) {
 		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch;
+		*segments = ntasks_ll * pg.rc.segs;
 		FL_TRY(redo_reserve(c, ntasks_ll * pg.rc.segs + 1));
 		const int ntasks = (int) ntasks_ll;
 		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
@@ -459,10 +509,12 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 	}
 	DivC dv;
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
+	// the streaming kernel relies on the proven window reaching the largest finite float
+	const bool streaming = dv.range != 0 && (dv.lo + dv.range) == (255u << 23) && stream_allowed(c, 0);
 	int n4 = 0, n2, n1; // passes of 4, 2 and 1 sweeps; their number must be even
 	if (c->rb_tile_sweeps >= 2) {
 		int rest = limit;
-		if (c->rb_stream && pass_geometry<4>(c, dv.range != 0 && (dv.lo + dv.range) == (255u << 23)).ftx1 > 0) { // 4 sweeps per pass pay off where the streaming kernel runs
+		if (pass_geometry<4>(c, streaming).ftx1 > 0) { // 4 sweeps per pass pay off where the streaming kernel runs
 			n4 = rest / 4;
 			rest -= 4 * n4;
 		}
@@ -478,14 +530,16 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 	}
 	const float* in = x;
 	float* out = c->rb_scratch;
+	long long segments = 0;
 	for (int k = 0; k < n4 + n2 + n1; k++) {
-		if (k < n4) FL_TRY(rb_tile_pass<4>(c, b, in, out, x0, a, dv));
-		else if (k < n4 + n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv));
-		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv));
+		if (k < n4) FL_TRY(rb_tile_pass<4>(c, b, in, out, x0, a, dv, streaming, &segments));
+		else if (k < n4 + n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv, streaming, &segments));
+		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv, streaming, &segments));
 		float* t = const_cast<float*>(in);
 		in = out;
 		out = t;
 	}
+	if (segments > 0) FL_TRY(stream_report(c, 0, segments)); // how much of the last pass had to be redone
 	if (in != x) { // odd number of passes: the field's values are in the scratch array now
 		c->f[field] = c->rb_scratch;
 		c->rb_scratch = x;
@@ -608,7 +662,7 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	int done = 0;
 	StreamRect rc;
 	const bool window_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
-	if (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc)) {
+	if (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc) && stream_allowed(c, 1)) {
 		const int launches = 2 * ((limit - 1) / (2 * kBlurL));
 		const long long ntasks = (long long) rc.per_sim * c->batch;
 		FL_TRY(redo_reserve(c, ntasks * rc.segs + 1));
@@ -620,6 +674,7 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo, b);
 		}
 		done = launches * kBlurL;
+		FL_TRY(stream_report(c, 1, ntasks * rc.segs));
 	}
 	for (int k = done; k < limit; k++) {
 		if (k > 0) std::swap(dst, src);
@@ -965,6 +1020,10 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);
+	for (auto& fb : c->feedback) {
+		if (fb.h_count) cudaFreeHost(fb.h_count);
+		if (fb.arrived) cudaEventDestroy(fb.arrived);
+	}
 	if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
 	if (c->ev_dens_up) cudaEventDestroy(c->ev_dens_up);
 	if (c->ev_vel_done) cudaEventDestroy(c->ev_vel_done);
