@@ -455,21 +455,23 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 // fewest columns (N=512: 3 x 192 instead of 3 x 256; N <= 120: one 128-wide window instead of 256).
 template <int S>
 static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv, bool streaming,
-			long long* segments)
+			bool pow2, long long* segments)
 {
 	const PassGeom pg = pass_geometry<S>(c, streaming);
 	*segments = 0;
+	const bool whole = pg.ftx1 > 0 && pg.ftx0 == 0 && pg.ftx1 == pg.ntx && pg.fty0 == 0 && pg.fty1 == pg.nty; // the streaming kernel covers the grid
+	(void) pow2;
 	if (pg.ftx1 > 0) {
 		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch;
 		*segments = ntasks_ll * pg.rc.segs;
 		FL_TRY(redo_reserve(c, ntasks_ll * pg.rc.segs + 1));
 		const int ntasks = (int) ntasks_ll;
 		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
-		LAUNCH(k_rb_stream<S>, cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
+		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
 	}
 	// nothing but listed rectangles to do: the narrowest window covers a strip (112 columns) and has the
 	// shortest colour passes -- a redo launch lasts as long as one tile does
-	if (pg.ftx1 > 0 && pg.ftx0 == 0 && pg.ftx1 == pg.ntx && pg.fty0 == 0 && pg.fty1 == pg.nty && StreamGeom<S>::OUT <= 128 - 2 * StreamGeom<S>::HALO) {
+	if (whole && StreamGeom<S>::OUT <= 128 - 2 * StreamGeom<S>::HALO) {
 		PassGeom narrow = pg;
 		narrow.TX = 128 - 2 * StreamGeom<S>::HALO;
 		narrow.ntx = narrow.ftx1 = cdiv(c->g.N, narrow.TX);
@@ -493,12 +495,50 @@ static int choose_rb_rx(int N)
 	return best;
 }
 
+// The streaming kernel covers the whole grid (rows are float4 groups, the grid is large): no tile kernel involved.
+template <int S>
+static bool stream_covers(const fluid_ctx* c, StreamRect* rc)
+{
+	const PassGeom pg = pass_geometry<S>(c, c->rb_stream);
+	*rc = pg.rc;
+	return pg.ftx1 > 0 && pg.ftx0 == 0 && pg.ftx1 == pg.ntx && pg.fty0 == 0 && pg.fty1 == pg.nty;
+}
+
+// a == 1 and c a power of two (Project's pressure solve, c = 4): the division is a multiplication, exact for
+// every operand -- no verified window, no redo list, and five instead of twelve instructions per update, which
+// makes the pass HBM-bound.
+static bool is_pow2_solve(float a, float cc)
+{
+	int e = 0;
+	return a == 1.0f && cc > 0.0f && isfinite(cc) && frexpf(cc, &e) == 0.5f && (1.0f / cc) >= 1.17549435e-38f;
+}
+
+template <int S>
+static int rb_stream_pass_pow2(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv, bool x_is_zero)
+{
+	StreamRect rc;
+	if (!stream_covers<S>(c, &rc)) return fail(FLUID_ERR_CUDA, "internal: streaming pass on a grid it does not cover");
+	const int ntasks = (int) ((long long) rc.per_sim * c->batch);
+	if (x_is_zero) LAUNCH((k_rb_stream<S, true, true>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
+	else LAUNCH((k_rb_stream<S, true, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
+	return FLUID_OK;
+}
+
+// Will a solve with these coefficients start with a pass that can be told "x is zero"?  (dev_project asks before
+// it decides not to write p = 0.)
+static bool solve_accepts_zero_x(const fluid_ctx* c, float a, float cc, int limit)
+{
+	StreamRect rc;
+	if (!(c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps >= 2 && limit >= 4 && is_pow2_solve(a, cc))) return false;
+	return stream_covers<4>(c, &rc);
+}
+
 // `limit` red-black sweeps as passes of 4, 2 or 1 sweeps, ping-ponging between x and the scratch field.
 // After an odd number of passes the result sits in the scratch array: if x is the storage of a context
 // field, that field and the scratch simply trade arrays (c->f is the only place that maps field ids to
 // storage, and x is updated for the caller) -- 20 sweeps are then five 4-sweep passes instead of four and
 // two 2-sweep passes.  For any other array the number of passes is made even.
-static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, int limit)
+static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, int limit, bool x_is_zero)
 {
 	int field = -1;
 	for (int f = 0; f < c->n_fields; f++)
@@ -509,10 +549,23 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 	}
 	DivC dv;
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
-	// the streaming kernel relies on the proven window reaching the largest finite float
+	const bool pow2 = is_pow2_solve(a, cc);
+	// otherwise the streaming kernel relies on the proven window reaching the largest finite float
 	const bool streaming = dv.range != 0 && (dv.lo + dv.range) == (255u << 23) && stream_allowed(c, 0);
-	int n4 = 0, n2, n1; // passes of 4, 2 and 1 sweeps; their number must be even
-	if (c->rb_tile_sweeps >= 2) {
+	// power-of-two solves first take as many whole-grid streaming passes of 5 and 4 sweeps as fit
+	int p5 = 0, p4 = 0;
+	StreamRect rc_unused;
+	if (pow2 && c->rb_tile_sweeps >= 2) {
+		// (5 sweeps per pass were tried: 260 us per pass against 148 us for 4 -- ten dependent levels per row step
+		// leave three warps per scheduler too little to overlap, and the strips shrink to 104 columns)
+		if (limit >= 4 && stream_covers<4>(c, &rc_unused)) p4 = limit / 4;
+	}
+	if (x_is_zero && p5 + p4 == 0) return fail(FLUID_ERR_CUDA, "internal: zero-x hint given to a solve that cannot use it");
+	limit -= 5 * p5 + 4 * p4;
+	int n4 = 0, n2 = 0, n1 = 0; // passes of 4, 2 and 1 sweeps; the total number of passes must be even
+	if (limit == 0) {
+		if (field < 0 && (p5 + p4) % 2) return fail(FLUID_ERR_CUDA, "internal: odd pass count on an array that is not a field");
+	} else if (c->rb_tile_sweeps >= 2) {
 		int rest = limit;
 		if (pass_geometry<4>(c, streaming).ftx1 > 0) { // 4 sweeps per pass pay off where the streaming kernel runs
 			n4 = rest / 4;
@@ -520,21 +573,27 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 		}
 		n2 = rest / 2;
 		n1 = rest % 2;
-		if (field < 0 && (n4 + n2 + n1) % 2) {
+		if (field < 0 && (p5 + p4 + n4 + n2 + n1) % 2) {
 			if (n4 > 0) { n4 -= 1; n2 += 2; }
 			else { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
 		}
 	} else {
-		n2 = (field < 0) ? limit % 2 : 0; // an odd count needs one 2-sweep pass to make the number of passes even
+		n2 = (field < 0) ? (limit + p5 + p4) % 2 : 0; // an odd count needs one 2-sweep pass to make the number of passes even
 		n1 = limit - 2 * n2;
 	}
 	const float* in = x;
 	float* out = c->rb_scratch;
 	long long segments = 0;
+	for (int k = 0; k < p5 + p4; k++) {
+		FL_TRY(rb_stream_pass_pow2<4>(c, b, in, out, x0, a, dv, x_is_zero && k == 0));
+		float* t = const_cast<float*>(in);
+		in = out;
+		out = t;
+	}
 	for (int k = 0; k < n4 + n2 + n1; k++) {
-		if (k < n4) FL_TRY(rb_tile_pass<4>(c, b, in, out, x0, a, dv, streaming, &segments));
-		else if (k < n4 + n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv, streaming, &segments));
-		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv, streaming, &segments));
+		if (k < n4) FL_TRY(rb_tile_pass<4>(c, b, in, out, x0, a, dv, streaming, pow2, &segments));
+		else if (k < n4 + n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv, streaming, pow2, &segments));
+		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv, streaming, pow2, &segments));
 		float* t = const_cast<float*>(in);
 		in = out;
 		out = t;
@@ -568,7 +627,7 @@ static int small_configure(fluid_ctx* c)
 
 // LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
 // x may come back pointing at another array (rb_tile_solve); callers keep using x, not a copy made before.
-static int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc)
+static int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, bool x_is_zero = false)
 {
 	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
 	const int limit = a > 0 ? c->gs_iters : 1;
@@ -579,7 +638,7 @@ static int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 		else
 			LAUNCH(k_small_lin_solve<false>, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
 	} else if (c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 && b >= 0 && b <= 2) {
-		FL_TRY(rb_tile_solve(c, b, x, x0, a, cc, limit));
+		FL_TRY(rb_tile_solve(c, b, x, x0, a, cc, limit, x_is_zero));
 	} else if (c->gs_order == FLUID_GS_REDBLACK) {
 		for (int k = 0; k < limit; k++) {
 			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 0);
@@ -719,11 +778,16 @@ static int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0
 // Project (FluidSystem.cpp:982-1007).
 static int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
 {
+	// p = 0 is the solve's starting guess.  Where the first pass of the solve can simply be told so, the zeros
+	// are neither written here nor read there (2 x 268 MB at N = 8192).
+	const int limit = c->gs_iters; // a = 1 > 0
+	const bool skip_zero = !use_small_kernels(c) && c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 &&
+			       solve_accepts_zero_x(c, 1.0f, 4.0f, limit);
 	{
 		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
-		LAUNCH(k_divergence, rowgroup_grid(c, c->g.NY + 2), kBlk2D, 0, c->stream, c->g, u, v, div, p);
+		LAUNCH(k_divergence, rowgroup_grid(c, c->g.NY + 2), kBlk2D, 0, c->stream, c->g, u, v, div, skip_zero ? (float*) nullptr : p);
 	}
-	FL_TRY(dev_lin_solve(c, 0, p, div, 1.0f, 4.0f));
+	FL_TRY(dev_lin_solve(c, 0, p, div, 1.0f, 4.0f, skip_zero));
 	{
 		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
 		LAUNCH(k_subtract_gradient, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, u, v, p);

@@ -136,12 +136,12 @@ __global__ void __launch_bounds__(256) k_divergence(GridDesc g, const float* __r
 	const float* u = ub + off;
 	const float* v = vb + off;
 	float* dv = divb + off;
-	float* p = pb + off;
 	const int q = blockIdx.x * blockDim.x + threadIdx.x; // float4 group in the row
 	const int j = blockIdx.y * blockDim.y + threadIdx.y; // row 0..NY+1
 	if (q * 4 >= g.pitch || j > g.NY + 1) return;
 	const long long base = (long long) j * g.pitch + q * 4;
-	*reinterpret_cast<float4*>(p + base) = make_float4(0.f, 0.f, 0.f, 0.f);
+	// (pb == nullptr: the solve that follows has been told that p is zero and will not read it)
+	if (pb) *reinterpret_cast<float4*>(pb + off + base) = make_float4(0.f, 0.f, 0.f, 0.f);
 	const int i0 = q * 4 - XO; // interior index of lane 0
 	if (j < 1 || j > g.NY || i0 + 3 < 1 || i0 > g.N) return;
 	const float4 vn = __ldg(reinterpret_cast<const float4*>(v + base + g.pitch));
