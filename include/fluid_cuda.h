@@ -238,7 +238,7 @@ int fluid_ctx_division_window(fluid_ctx *ctx, float divisor, int *lo_exp, int *h
  * One context per GPU/process, each a slab (fluid_params.slab_*).  No          *
  * counterpart in the reference (single process, single thread).  Slabs overlap *
  * by slab_halo+1 rows and recompute the overlap, so halos are refreshed once    *
- * per 20-sweep solve (9 times per step) rather than once per colour pass.  The  *
+ * per 20-sweep solve (6 times per step) rather than once per colour pass.  The  *
  * library decides WHEN; the host supplies HOW: the callback must, for each      *
  * listed field, move fluid_ctx_halo_regions()' send blocks into the             *
  * neighbours' recv blocks (ncclSend/ncclRecv, cudaMemcpyPeer ...) and return 0   *
@@ -255,7 +255,10 @@ int fluid_ctx_set_exchange(fluid_ctx *ctx, fluid_exchange_fn fn, void *user);
 int fluid_ctx_set_stream(fluid_ctx *ctx, void *stream, int exchange_stream_ordered);
 /* Device pointers of the blocks to move for `field`; *count floats each; a
  * pointer is NULL where there is no neighbour.  send_down -> lower neighbour's
- * recv_up, send_up -> upper neighbour's recv_down. */
+ * recv_up, send_up -> upper neighbour's recv_down.  Ask at every exchange: a
+ * red-black solve may leave a field in another device array than before (it
+ * trades arrays with the solver's scratch field instead of copying), so pointers
+ * obtained earlier can be stale. */
 int fluid_ctx_halo_regions(fluid_ctx *ctx, int field, float **send_down, float **recv_down, float **send_up, float **recv_up,
 			   size_t *count);
 

@@ -1,0 +1,32 @@
+"""CPU check of the arithmetic fact behind `div_wide` (csrc/grid.cuh): dividing two binary32 numbers in binary64
+and rounding the quotient to binary32 gives the correctly rounded binary32 quotient -- double rounding is
+innocuous when the wide format has at least 2*24+2 bits -- including subnormal results.  The GPU kernels use it
+as their exact fallback for dividends outside the verified window (tests/test_gpu_parity.py checks those bitwise
+against the oracle); here numpy's float32 division is the judge."""
+import numpy as np
+
+
+def test_division_through_double_is_correctly_rounded():
+    rng = np.random.default_rng(20261107)
+    n = 2_000_000
+    anywhere = rng.integers(0, 0x7F800000, n, dtype=np.uint32).view(np.float32)      # every finite magnitude
+    tiny = rng.integers(0, 0x04000000, n, dtype=np.uint32).view(np.float32)          # subnormals and their neighbours
+    for c in (np.float32(4.0), np.float32(2685.3542), np.float32(1.0004), np.float32(42.96), np.float32(3.0), np.float32(1e-3)):
+        for t in (anywhere, tiny, -tiny):
+            with np.errstate(all="ignore"):
+                q32 = (t / c).astype(np.float32)
+                q64 = (t.astype(np.float64) / np.float64(c)).astype(np.float32)
+            assert np.array_equal(q32.view(np.uint32), q64.view(np.uint32)), float(c)
+
+
+def test_division_by_a_power_of_two_is_a_multiplication():
+    """The pressure solve divides by 4: t / 4 and t * 0.25 are the same real number rounded once, subnormals included."""
+    rng = np.random.default_rng(4)
+    t = rng.integers(0, 0x7F800000, 2_000_000, dtype=np.uint32).view(np.float32)
+    small = rng.integers(0, 0x02000000, 2_000_000, dtype=np.uint32).view(np.float32)
+    for x in (t, -t, small, -small):
+        for c, y in ((np.float32(4.0), np.float32(0.25)), (np.float32(2.0), np.float32(0.5)), (np.float32(64.0), np.float32(1 / 64))):
+            with np.errstate(all="ignore"):
+                assert np.array_equal((x / c).view(np.uint32), (x * y).view(np.uint32))
+    one = np.float32(1.0)
+    assert np.array_equal((one * t).view(np.uint32), t.view(np.uint32))  # a = 1: a * s is s
