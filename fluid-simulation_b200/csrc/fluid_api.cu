@@ -1167,8 +1167,9 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	c->g.pitch = ((XO + p->N + 2 + 31) / 32) * 32;
 	c->g.plane = (long long) c->g.pitch * (c->g.NY + 2);
 	if (c->g.plane >= (1LL << 31)) { // kernels index one member's plane with 32-bit offsets
+		const int rows = c->g.NY;
 		delete c;
-		return fail(FLUID_ERR_UNSUPPORTED, "a field of %d x %d cells has 2^31 floats or more; split it into row slabs", p->N, c->g.NY);
+		return fail(FLUID_ERR_UNSUPPORTED, "a field of %d x %d cells has 2^31 floats or more; split it into row slabs", p->N, rows);
 	}
 	c->rb_rx = choose_rb_rx(p->N);
 	c->field_bytes = (size_t) c->g.plane * c->batch * sizeof(float);
