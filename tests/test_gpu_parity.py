@@ -306,6 +306,28 @@ def test_ensemble_members_are_independent(fl, oracle):
         fs.close()
 
 
+def test_ensemble_on_the_streaming_kernels_bitwise(fl, oracle):
+    """Eight members of N=512 are enough cells for the register-resident streaming kernels, which then work on
+    member planes (strips and chunks per member, wall strips in every member).  Three steps, so that the redo
+    feedback may also switch a solve back to the tile kernels on the way: every member equals its own CPU run."""
+    import oracle_py as op
+    N, B, steps = 512, 8, 3
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, batch=B)
+    fs.SetFastDivision(2)
+    srcs = []
+    for b in range(B):
+        cx, cy = 1 + (37 * b) % N, 1 + (101 * b) % N
+        srcs.append([(2, cx, cy, 0, 100.0), (0, cx, cy, 0, 5.0), (1, cx, cy, 0, 5.0)])
+        fs.SetSources(srcs[-1], sim=b)
+    fs.Update(0.1, steps)
+    for b in range(B):
+        f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+        oracle.update(N, f, srcs[b], 1e-4, 1e-4, 0.1, steps, order=op.GS_RB)
+        assert_bits(fs.GetVelX(b), f["u"], "member %d u" % b)
+        assert_bits(fs.GetDensities(b), f["d"], "member %d dens" % b)
+    fs.close()
+
+
 def test_vorticity_and_damp(fl, oracle):
     N = 45
     rng = np.random.default_rng(9)
