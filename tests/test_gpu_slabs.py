@@ -96,13 +96,15 @@ def test_slab_argument_checks(fl):
     fs.close()
 
 
-@pytest.mark.parametrize("order", [0, 1])
-def test_non_square_single_context(fl, order):
+@pytest.mark.parametrize("order,N,rows,count", [(0, 150, 60, 3), (1, 150, 60, 3), (1, 2048, 512, 2)])
+def test_non_square_single_context(fl, order, N, rows, count):
     """N x NY grids (what a multi-GPU weak-scaling run is globally).  The oracle is square-only, so
     the check is internal consistency: red-black on one context == the slab decomposition (which is
-    itself pinned to the oracle on square grids); the reference order runs and stays finite."""
+    itself pinned to the oracle on square grids); the reference order runs and stays finite.
+    2048 x 1024: the single context is large enough for the streaming kernels, its two slabs are not,
+    so this also sets the two red-black implementations against each other on a non-square grid."""
     from fluid_b200.slabs import LocalSlabGroup
-    N, rows, count, steps = 150, 60, 3, 2
+    steps = 2
     NY = rows * count
     rng = np.random.default_rng(31)
     init = {k: (rng.uniform(-1, 1, (N + 2) * (NY + 2)) * 0.4).astype(np.float32) for k in "uvd"}
