@@ -37,7 +37,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=8192, help="interior cells per side per GPU (BASELINE config 3: 8192)")
+    ap.add_argument("--n", "--size", dest="n", type=int, default=8192,
+                    help="interior cells per side per GPU (BASELINE config 3: 8192); under torchrun spell it --size "
+                         "(torchrun's own parser claims --n as an abbreviation)")
     ap.add_argument("--order", default="redblack", choices=["redblack", "wavefront"])
     ap.add_argument("--strong", action="store_true", help="N>1 GPUs: split ONE N x N grid into row slabs (strong scaling) "
                     "instead of N rows per GPU (weak scaling, the default)")
