@@ -43,8 +43,9 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 	const int col = min(lane0_col + 4 * lane, g.pitch - 4); // lanes past the row are folded back (see kernels_rb_stream.cuh)
 	const int row_lo = out_lo - L, row_hi = out_hi + L;     // rows that pass through the window; some may be virtual
 	const int ylo = max(row_lo + 1, 1), yhi = min(row_hi - 1, g.NY); // rows that are computed
-	const bool botw = (out_lo == 1), topw = (out_hi == g.NY);
-	const bool wallB = botw && (g.walls & 1), wallT = topw && (g.walls & 2);
+	// border rows inside the window (the chunk that owns row 1 / NY, and a neighbour whose halo reaches them)
+	const bool has_bot = (row_lo <= 0), has_top = (row_hi >= g.NY + 1);
+	const bool wallB = has_bot && (g.walls & 1), wallT = has_top && (g.walls & 2);
 	const bool store_lane = (col >= col_lo) && (col + 4 <= col_hi) && (lane >= BlurGeom<L>::HALO / 4) && (lane < 32 - BlurGeom<L>::HALO / 4);
 	const bool ghostL = WALL && (col + 3 == XO);
 	const bool ghostR = WALL && (lane0_col + 4 * lane == XO + g.N + 1);
@@ -139,7 +140,7 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 				// Top border row of iterate h-1 >= 1: the mirror of row NY, or the stored row where the slab goes
 				// on.  It cannot be kept in the ring like the bottom one: its position is still occupied by
 				// row NY-2, which the next level reads in this very row step.
-				if (!STEADY && topw && y == g.NY && h > 1) n4 = wallT ? mirror_y(c4) : lev[0][sn];
+				if (!STEADY && has_top && y == g.NY && h > 1) n4 = wallT ? mirror_y(c4) : lev[0][sn];
 				const float wl = __shfl_up_sync(0xffffffffu, c4.w, 1);
 				const float er = __shfl_down_sync(0xffffffffu, c4.x, 1);
 				float4 o;
@@ -151,7 +152,7 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 				if (h < L) {
 					lev[h < L ? h : 0][sy] = o;
 					if (!STEADY) { // the bottom border row of this iterate: mirrored at a wall, unchanged where the slab goes on
-						if (botw && y == 1) lev[h < L ? h : 0][ss] = wallB ? mirror_y(o) : s4;
+						if (has_bot && y == 1) lev[h < L ? h : 0][ss] = wallB ? mirror_y(o) : s4;
 					}
 				} else if (STEADY ? (y >= out_lo) : (y >= out_lo && y <= out_hi)) {
 					bad = bad || !(o.x == o.x) || !(o.y == o.y) || !(o.z == o.z) || !(o.w == o.w);
@@ -166,7 +167,7 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 	};
 	for (int t0 = row_lo; t0 <= row_hi; t0 += 3) {
 		// steady: every row up to the one fetched now is real, and no border row is involved
-		if ((!botw || t0 > row_lo + 2 * L) && t0 + 2 + kDepth <= min(row_hi, g.NY + 1)) block(t0, std::true_type{});
+		if ((!has_bot || t0 > row_lo + 2 * L) && t0 + 2 + kDepth <= min(row_hi, g.NY + 1)) block(t0, std::true_type{});
 		else block(t0, std::false_type{});
 	}
 }
@@ -182,7 +183,8 @@ __global__ void __launch_bounds__(128, 4) k_blur_stream(GridDesc g, StreamRect r
 	const StreamTask k = stream_task(rc, task);
 	const long long off = (long long) k.sim * g.plane;
 	const int lane0_col = rc.col0 + k.strip * BlurGeom<L>::OUT - BlurGeom<L>::HALO;
-	if (k.wall) blur_stream_task<L, true>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	const bool wall = k.wall || lane0_col <= XO || lane0_col + 128 > XO + g.N + 1; // lanes reach a border column
+	if (wall) blur_stream_task<L, true>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 	else blur_stream_task<L, false>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 }
 

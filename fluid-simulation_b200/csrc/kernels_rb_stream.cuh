@@ -132,7 +132,10 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 	// task on the same schedule (and the same colour phase).
 	const int row_lo = out_lo - L, row_hi = out_hi + L;
 	const int ylo = max(row_lo + 1, 1), yhi = min(row_hi - 1, g.NY); // rows that receive colour passes
-	const bool botw = (out_lo == 1), topw = (out_hi == g.NY);         // the task reaches the bottom / top row
+	const bool botw = (out_lo == 1), topw = (out_hi == g.NY);         // the task owns the bottom / top row (and stores the border row)
+	// The border row itself may also lie in the halo of the NEXT chunk (edge chunks are short): every task whose
+	// window contains it must keep it mirrored, or its halo goes wrong from the wall inwards.
+	const bool has_bot = (row_lo <= 0), has_top = (row_hi >= g.NY + 1);
 	const bool store_lane = (col >= col_lo) && (col + 4 <= col_hi) && (lane >= StreamGeom<S>::HALO / 4) &&
 				(lane < 32 - StreamGeom<S>::HALO / 4);
 	// colour of cell (i, y) is (i + y + j0) & 1 with i = storage column - XO; col is a multiple of 4
@@ -141,7 +144,7 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 	// right border i = N+1 (N % 4 == 0) is component .x of the lane after the one whose .w is i = N
 	const bool mirror = (b >= 0 && b <= 2);
 	// bottom / top border rows mirror rows 1 / NY the same way (negated for b == 2) where the slab ends in a wall
-	const bool wallB = botw && (g.walls & 1), wallT = topw && (g.walls & 2);
+	const bool wallB = has_bot && (g.walls & 1), wallT = has_top && (g.walls & 2);
 	const bool ghostL = WALL && (col + 3 == XO);
 	const bool ghostR = WALL && (lane0_col + 4 * lane == XO + g.N + 1); // not a folded-back lane
 	const float* pin = xin + (long long) row_lo * g.pitch + col;
@@ -320,7 +323,7 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 	for (int t0 = row_lo; t0 <= row_hi; t0 += B) {
 		// steady: every row up to the one fetched now is real, no border row to mirror or store -- the whole
 		// task except its last few rows and, in the bottom and top chunks, the rows next to the wall
-		if ((!botw || t0 > row_lo + 2 * L) && t0 + B - 1 + kDepth <= min(row_hi, g.NY + 1)) {
+		if ((!has_bot || t0 > row_lo + 2 * L) && t0 + B - 1 + kDepth <= min(row_hi, g.NY + 1)) {
 			if (phase0) block(t0, std::true_type{}, std::integral_constant<int, 1>{});
 			else block(t0, std::true_type{}, std::integral_constant<int, 0>{});
 		} else block(t0, std::false_type{}, std::integral_constant<int, 0>{});
@@ -340,7 +343,10 @@ __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g,
 	const StreamTask k = stream_task(rc, task);
 	const long long off = (long long) k.sim * g.plane;
 	const int lane0_col = rc.col0 + k.strip * StreamGeom<S>::OUT - StreamGeom<S>::HALO;
-	if (k.wall) rb_stream_task<S, true, POW2, XZERO>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	// the wall variant for every strip whose lanes reach a border column: the first and the last strip, and the
+	// last but one when the last is narrower than the halo
+	const bool wall = k.wall || lane0_col <= XO || lane0_col + 128 > XO + g.N + 1;
+	if (wall) rb_stream_task<S, true, POW2, XZERO>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 	else rb_stream_task<S, false, POW2, XZERO>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 }
 

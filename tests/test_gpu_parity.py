@@ -597,3 +597,59 @@ def test_streamed_blur_bitwise(fl, oracle, N, stream):
         assert_bits(fs.download(fl.U), x, "blur N=%d iters=%d b=%d stream=%s" % (N, iters, b, stream))
         assert_bits(fs.download(fl.V), x0, "blur penultimate iterate N=%d iters=%d b=%d" % (N, iters, b))
         fs.close()
+
+
+def test_streaming_and_tile_paths_agree_on_random_shapes(fl):
+    """The streaming kernels cut a grid into strips, chunks, shorter edge chunks, half-height wall tasks and
+    redo segments; the tile kernels into TMA windows.  Both are pinned to the oracle at a few sizes; here they
+    are set against each other (bitwise) on random widths -- multiples of 4 and not --, heights, ensemble
+    sizes, boundary modes, sweep counts and coefficients, with zero and subnormal patches in the fields."""
+    rng = np.random.default_rng(20261107)
+    # flat members (few chunks, edge chunks that are both first and last) and many of them
+    # ... and widths whose last strip is narrower than the halo (N mod 112 <= 8: the last strip but one reaches the wall)
+    fixed = [(512, 512, 8), (1024, 300, 8), (2048, 130, 8), (256, 1100, 8), (228, 90, 104), (232, 81, 112), (2248, 940, 1),
+             (1124, 2000, 1), (1348, 1557, 1)]
+    for case in range(24 + len(fixed)):
+        if case < len(fixed):
+            N, NY, batch = fixed[case]
+        else:
+            batch = int(rng.choice([1, 1, 2, 3]))
+            N = int(rng.integers(1400, 2600)) if batch == 1 else int(rng.integers(900, 1500))
+            if rng.random() < 0.6:
+                N -= N % 4
+            NY = int(rng.integers(max(600, (1 << 21) // (N * batch) + 1), 2300))
+        b = int(rng.integers(0, 3))
+        iters = int(rng.choice([4, 5, 8, 11, 20]))
+        a = np.float32(rng.choice([0.3, 1.0, 23.5, 671.0886]))
+        c = np.float32(4.0) if a == 1 else np.float32(1 + 4 * a)
+        W, H = N + 2, NY + 2
+        fields = []
+        for _ in range(2 * batch):
+            f = rng.uniform(-1, 1, (H, W)).astype(np.float32)
+            y0, x0 = int(rng.integers(1, max(2, NY - 120))), int(rng.integers(1, max(2, N - 200)))
+            f[y0:y0 + 100, x0:x0 + 180] = 0.0
+            y1, x1 = int(rng.integers(1, max(2, NY - 80))), int(rng.integers(1, max(2, N - 150)))
+            f[y1:y1 + 60, x1:x1 + 140] *= np.float32(1e-38)
+            fields.append(f.ravel())
+        got = {}
+        for stream in (True, False):
+            fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_REDBLACK, gs_iters=iters, batch=batch, slab=(0, 1, NY))
+            fs.SetStreamKernel(stream)
+            fs.SetFastDivision(2)
+            out = []
+            for kind in ("lin_solve", "blur"):
+                for m in range(batch):
+                    fs.upload(fl.U, fields[2 * m], sim=m)
+                    fs.upload(fl.V, fields[2 * m + 1], sim=m)
+                if kind == "lin_solve":
+                    fs.lin_solve(b, fl.U, fl.V, a, c)
+                else:
+                    fs.blur(b, fl.U, fl.V, a, c)
+                for m in range(batch):
+                    out.append(fs.download(fl.U, sim=m).copy())
+                    out.append(fs.download(fl.V, sim=m).copy())
+            got[stream] = out
+            fs.close()
+        what = "case %d: N=%d NY=%d batch=%d b=%d iters=%d a=%g" % (case, N, NY, batch, b, iters, a)
+        for k, (p, q) in enumerate(zip(got[True], got[False])):
+            assert_bits(p, q, "%s, array %d" % (what, k))
