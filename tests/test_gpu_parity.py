@@ -653,3 +653,45 @@ def test_streaming_and_tile_paths_agree_on_random_shapes(fl):
         what = "case %d: N=%d NY=%d batch=%d b=%d iters=%d a=%g" % (case, N, NY, batch, b, iters, a)
         for k, (p, q) in enumerate(zip(got[True], got[False])):
             assert_bits(p, q, "%s, array %d" % (what, k))
+
+
+def test_whole_steps_agree_with_and_without_streaming(fl):
+    """Whole frames (forcing, VelStep with both projections, DensStep) on random shapes and parameters, the
+    large-grid kernels on and off: the pressure solve's exact power-of-two division with its unwritten zero
+    guess, fields trading arrays with the scratch field after odd pass counts, Blur's multi-pass launches, the
+    redo lists and their feedback must all be invisible in the results."""
+    rng = np.random.default_rng(7)
+    for case in range(10):
+        batch = int(rng.choice([1, 1, 1, 2]))
+        N = int(rng.integers(1450, 2300)) if batch == 1 else int(rng.integers(1024, 1500))
+        if rng.random() < 0.7:
+            N -= N % 4
+        NY = int(rng.integers((1 << 21) // (N * batch) + 1, 2200))
+        iters = int(rng.choice([3, 4, 7, 10, 20]))
+        visc = float(rng.choice([0.0, 1e-6, 1e-4]))
+        diff = float(rng.choice([0.0, 1e-6, 1e-4]))
+        vort = float(rng.choice([0.0, 0.0, 0.55]))
+        steps = 2
+        W, H = N + 2, NY + 2
+        init = [(rng.uniform(-1, 1, (H, W)) * 0.3).astype(np.float32) for _ in range(3 * batch)]
+        for f in init:
+            y0, x0 = int(rng.integers(1, NY - 300)), int(rng.integers(1, N - 300))
+            f[y0:y0 + 280, x0:x0 + 280] = 0.0
+            f[y0 + 290:y0 + 299, :] *= np.float32(1e-37)
+        src = [(2, int(rng.integers(1, N)), int(rng.integers(1, NY)), 0, 100.0), (0, int(rng.integers(1, N)), int(rng.integers(1, NY)), 0, 5.0),
+               (1, int(rng.integers(1, N)), int(rng.integers(1, NY)), 0, -5.0), (2, 3, 3, 1, 2.0)]
+        got = {}
+        for stream in (True, False):
+            fs = fl.FluidSystem().Setup(N, visc, diff, vorticity=vort, gs_order=fl.GS_REDBLACK, gs_iters=iters, batch=batch, slab=(0, 1, NY))
+            fs.SetStreamKernel(stream)
+            fs.SetFastDivision(2)
+            for m in range(batch):
+                fs.SetSources(src, sim=m)
+                for k, fid in enumerate((fl.U, fl.V, fl.DENS)):
+                    fs.upload(fid, init[3 * m + k].ravel(), sim=m)
+            fs.Update(0.1, steps)
+            got[stream] = [fs.download(fid, sim=m).copy() for m in range(batch) for fid in (fl.U, fl.V, fl.DENS)]
+            fs.close()
+        what = "case %d: N=%d NY=%d batch=%d iters=%d visc=%g diff=%g vort=%g" % (case, N, NY, batch, iters, visc, diff, vort)
+        for k, (p, q) in enumerate(zip(got[True], got[False])):
+            assert_bits(p, q, "%s, array %d" % (what, k))
