@@ -25,6 +25,7 @@
 #include "kernels_blur_stream.cuh"
 #include "kernels_small.cuh"
 
+#include <functional>
 #include <map>
 
 using namespace fluid;
@@ -126,8 +127,15 @@ struct fluid_ctx {
 		long long segments = 0; // segments of the launch whose count is in flight
 		int holdoff = 0;
 	} feedback[2];
-	int* d_redo = nullptr;     // [0] = count, [1..] = stream tasks the tile kernel must recompute
-	int redo_capacity = 0;
+	// redo lists of the two streaming kernels: [0] = count, [1..] = (task, segment) entries.  One per kernel
+	// family (0 relaxation, 1 blur): the density diffusion may run on the side stream while VelStep runs
+	int* d_redo[2] = { nullptr, nullptr };
+	int redo_capacity[2] = { 0, 0 };
+	// Update(): add_source + Blur of the densities do not depend on the velocity, so they run on a second stream
+	// beside VelStep and fill the tails of its launches (single-GPU contexts; slabs keep one stream)
+	cudaStream_t side_stream = nullptr;
+	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+	bool overlap_density = true;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
 	int fast_div_mode = 1; // 0 never, 1 when the solve is large enough to repay the 1.5 ms check, 2 always
@@ -332,7 +340,7 @@ static int stream_report(fluid_ctx* c, int which, long long segments)
 		CU_TRY(cudaMallocHost(&fb.h_count, sizeof(int)));
 		CU_TRY(cudaEventCreateWithFlags(&fb.arrived, cudaEventDisableTiming));
 	}
-	CU_TRY(cudaMemcpyAsync(fb.h_count, c->d_redo, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaMemcpyAsync(fb.h_count, c->d_redo[which], sizeof(int), cudaMemcpyDeviceToHost, c->stream));
 	CU_TRY(cudaEventRecord(fb.arrived, c->stream));
 	fb.segments = segments;
 	fb.pending = true;
@@ -340,14 +348,14 @@ static int stream_report(fluid_ctx* c, int which, long long segments)
 }
 
 // The list of rectangles a streaming kernel hands to its exact fallback: [0] = count, [1..] = entries.
-static int redo_reserve(fluid_ctx* c, long long entries)
+static int redo_reserve(fluid_ctx* c, int which, long long entries)
 {
 	if (entries > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many streaming tasks");
-	if (entries > c->redo_capacity) {
-		if (c->d_redo) CU_TRY(cudaFree(c->d_redo));
-		c->d_redo = nullptr;
-		CU_TRY(cudaMalloc(&c->d_redo, sizeof(int) * (size_t) entries));
-		c->redo_capacity = (int) entries;
+	if (entries > c->redo_capacity[which]) {
+		if (c->d_redo[which]) CU_TRY(cudaFree(c->d_redo[which]));
+		c->d_redo[which] = nullptr;
+		CU_TRY(cudaMalloc(&c->d_redo[which], sizeof(int) * (size_t) entries));
+		c->redo_capacity[which] = (int) entries;
 	}
 	return FLUID_OK;
 }
@@ -445,7 +453,7 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 	// persistent: one CTA per SM; behind the streaming kernel the redo list adds tiles the host cannot count
 	const int grid = (pg.ftx1 > 0) ? c->num_sms : (int) std::min<long long>(ntiles, c->num_sms);
 	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, pg.ntx, pg.nty, (int) ntiles, pg.ftx0, pg.ftx1,
-	       pg.fty0, pg.fty1, c->d_redo, pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
+	       pg.fty0, pg.fty1, c->d_redo[0], pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
 	return FLUID_OK;
 }
 
@@ -464,10 +472,10 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 	if (pg.ftx1 > 0) {
 		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch;
 		*segments = ntasks_ll * pg.rc.segs;
-		FL_TRY(redo_reserve(c, ntasks_ll * pg.rc.segs + 1));
+		FL_TRY(redo_reserve(c, 0, ntasks_ll * pg.rc.segs + 1));
 		const int ntasks = (int) ntasks_ll;
-		CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
-		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo, b);
+		CU_TRY(cudaMemsetAsync(c->d_redo[0], 0, sizeof(int), c->stream));
+		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[0], b);
 	}
 	// nothing but listed rectangles to do: the narrowest window covers a strip (112 columns) and has the
 	// shortest colour passes -- a redo launch lasts as long as one tile does
@@ -724,13 +732,13 @@ static int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	if (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc) && stream_allowed(c, 1)) {
 		const int launches = 2 * ((limit - 1) / (2 * kBlurL));
 		const long long ntasks = (long long) rc.per_sim * c->batch;
-		FL_TRY(redo_reserve(c, ntasks * rc.segs + 1));
+		FL_TRY(redo_reserve(c, 1, ntasks * rc.segs + 1));
 		for (int l = 0; l < launches; l++) {
 			if (l > 0) std::swap(dst, src);
-			CU_TRY(cudaMemsetAsync(c->d_redo, 0, sizeof(int), c->stream));
-			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo, b);
+			CU_TRY(cudaMemsetAsync(c->d_redo[1], 0, sizeof(int), c->stream));
+			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
 			// few entries, each a chain of 2L barrier-separated phases over ~5000 cells: wide CTAs keep the chain short
-			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo, b);
+			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo[1], b);
 		}
 		done = launches * kBlurL;
 		FL_TRY(stream_report(c, 1, ntasks * rc.segs));
@@ -845,17 +853,26 @@ static int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, 
 }
 
 // DensStep1 (FluidSystem.cpp:289-299), one fluid.
-static int dev_dens_step(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float diff, float dt)
+// First half (sources and diffusion: no velocity involved; the blurred field ends in x0) and second half (advection).
+static int dev_dens_diffuse(fluid_ctx* c, float* x, float* x0, float diff, float dt)
 {
 	FL_TRY(dev_add_source(c, x, x0, dt));
-	std::swap(x, x0);
 	const float a = diffusion_a(c, diff, dt);
-	FL_TRY(dev_blur(c, 0, x, x0, a, 1 + 4 * a));
-	std::swap(x, x0);
+	return dev_blur(c, 0, x0, x, a, 1 + 4 * a); // after the reference's Swap: x0 is relaxed, x holds the sum
+}
+
+static int dev_dens_advect(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float dt)
+{
 	FL_TRY(halo_exchange(c, { x0 })); // 21 blur passes consumed 21 halo rows of the field advect samples
 	FL_TRY(dev_advect(c, 0, x, x0, u, v, dt));
 	FL_TRY(halo_exchange(c, { x }));
 	return FLUID_OK;
+}
+
+static int dev_dens_step(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float diff, float dt)
+{
+	FL_TRY(dev_dens_diffuse(c, x, x0, diff, dt));
+	return dev_dens_advect(c, x, x0, u, v, dt);
 }
 
 static int ensure_vort_scratch(fluid_ctx* c)
@@ -924,9 +941,13 @@ static inline float visc_avg(const fluid_ctx* c)
 }
 
 // FluidSystem::Update (FluidSystem.cpp:101-128) for FSType::ORIGINAL.
-// FluidSystem::Update (FluidSystem.cpp:101-128) in two halves: forcing + vorticity + VelStep, then DensStep +
-// damping.  fluid_update() slips bus transfers in between; everybody else calls dev_update.
-static int dev_update_velocity(fluid_ctx* c, float dt)
+// FluidSystem::Update (FluidSystem.cpp:101-128): forcing, [vorticity], VelStep, DensStep per fluid, [damping].
+// The densities' add_source + Blur touch neither velocity array, so on a single-GPU context they are enqueued on
+// a side stream (fork after the forcing, join before the advection) and share the GPU with VelStep.
+// `dens_ready`: an event (of another stream) after which the current density arrays are valid, or nullptr;
+// `after_velocity`: called once VelStep has been enqueued on c->stream, or empty.  fluid_update() uses both to
+// slip its bus transfers in; everybody else calls dev_update.
+static int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::function<int()>& after_velocity)
 {
 	{
 		ProfScope ps(c, FLUID_PROF_OTHER);
@@ -946,17 +967,42 @@ static int dev_update_velocity(fluid_ctx* c, float dt)
 			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 		}
 	}
+	const bool concurrent = c->overlap_density && c->slab_count <= 1;
+	auto diffuse_all = [&]() -> int {
+		for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
+			FL_TRY(dev_dens_diffuse(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], fluid_diff(c, fl), dt));
+		return FLUID_OK;
+	};
+	if (concurrent) {
+		if (!c->side_stream) {
+			CU_TRY(cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+		}
+		CU_TRY(cudaEventRecord(c->ev_fork, c->stream));
+		CU_TRY(cudaStreamWaitEvent(c->side_stream, c->ev_fork, 0));
+		if (dens_ready) CU_TRY(cudaStreamWaitEvent(c->side_stream, dens_ready, 0));
+		cudaStream_t main_stream = c->stream;
+		c->stream = c->side_stream; // every launch helper and profiling scope follows c->stream
+		const int rc = diffuse_all();
+		c->stream = main_stream;
+		FL_TRY(rc);
+		CU_TRY(cudaEventRecord(c->ev_join, c->side_stream));
+	}
 	if (c->vorticity != 0.0f) {
 		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
 		FL_TRY(halo_exchange(c, { c->f[FLUID_U], c->f[FLUID_V] })); // three stencil phases consumed 3 halo rows
 	}
-	return dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt);
-}
-
-static int dev_update_density(fluid_ctx* c, float dt)
-{
-	for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
-		FL_TRY(dev_dens_step(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], fluid_diff(c, fl), dt));
+	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt));
+	if (after_velocity) FL_TRY(after_velocity());
+	if (concurrent) {
+		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+	} else {
+		if (dens_ready) CU_TRY(cudaStreamWaitEvent(c->stream, dens_ready, 0));
+		FL_TRY(diffuse_all());
+	}
+	for (int fl = 0; fl < c->n_fluids; fl++)
+		FL_TRY(dev_dens_advect(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], dt));
 	if (c->damp != 0.0f) {
 		FL_TRY(dev_damp(c, c->f[FLUID_U], c->damp, dt));
 		FL_TRY(dev_damp(c, c->f[FLUID_V], c->damp, dt));
@@ -964,11 +1010,7 @@ static int dev_update_density(fluid_ctx* c, float dt)
 	return FLUID_OK;
 }
 
-static int dev_update(fluid_ctx* c, float dt)
-{
-	FL_TRY(dev_update_velocity(c, dt));
-	return dev_update_density(c, dt);
-}
+static int dev_update(fluid_ctx* c, float dt) { return dev_update_hooks(c, dt, nullptr, {}); }
 
 // ---------------------------------------------------------------------------
 // library-level entry points
@@ -1075,7 +1117,10 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->rb_scratch) cudaFree(c->rb_scratch);
 	if (c->d_oob) cudaFree(c->d_oob);
 	if (c->d_divbins) cudaFree(c->d_divbins);
-	if (c->d_redo) cudaFree(c->d_redo);
+	for (auto& p : c->d_redo) if (p) cudaFree(p);
+	if (c->side_stream) cudaStreamDestroy(c->side_stream);
+	if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+	if (c->ev_join) cudaEventDestroy(c->ev_join);
 	if (c->d_pixels) cudaFree(c->d_pixels);
 	if (c->d_lines) cudaFree(c->d_lines);
 	if (c->d_src) cudaFree(c->d_src);
@@ -1386,6 +1431,13 @@ extern "C" int fluid_ctx_set_stream_kernel(fluid_ctx* c, int on)
 {
 	CHECK_CTX(c);
 	c->rb_stream = on != 0;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_overlap(fluid_ctx* c, int on)
+{
+	CHECK_CTX(c);
+	c->overlap_density = on != 0;
 	return FLUID_OK;
 }
 
@@ -1884,13 +1936,14 @@ extern "C" int fluid_update(int N, float* u, float* v, float* dens, int nsrc, co
 		FL_TRY(up(c, FLUID_V, v));
 		CU_TRY(cudaMemcpy2DAsync(c->f[FLUID_DENS] + XO, dp, dens, w, w, c->g.NY + 2, cudaMemcpyHostToDevice, c->copy_stream));
 		CU_TRY(cudaEventRecord(c->ev_dens_up, c->copy_stream));
-		FL_TRY(dev_update_velocity(c, dt));
-		CU_TRY(cudaEventRecord(c->ev_vel_done, c->stream));
-		CU_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_vel_done, 0));
-		CU_TRY(cudaMemcpy2DAsync(u, w, c->f[FLUID_U] + XO, dp, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->copy_stream));
-		CU_TRY(cudaMemcpy2DAsync(v, w, c->f[FLUID_V] + XO, dp, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->copy_stream));
-		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_dens_up, 0));
-		FL_TRY(dev_update_density(c, dt));
+		auto velocity_home = [&]() -> int { // VelStep is enqueued: its results may leave while DensStep runs
+			CU_TRY(cudaEventRecord(c->ev_vel_done, c->stream));
+			CU_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_vel_done, 0));
+			CU_TRY(cudaMemcpy2DAsync(u, w, c->f[FLUID_U] + XO, dp, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->copy_stream));
+			CU_TRY(cudaMemcpy2DAsync(v, w, c->f[FLUID_V] + XO, dp, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->copy_stream));
+			return FLUID_OK;
+		};
+		FL_TRY(dev_update_hooks(c, dt, c->ev_dens_up, velocity_home));
 		return down_async(c, FLUID_DENS, dens);
 	};
 	const int rc = enqueue();

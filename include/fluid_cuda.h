@@ -213,10 +213,14 @@ int fluid_ctx_set_fluid(fluid_ctx *ctx, int k, float diff, float visc);
  * residency (2 = default, 1; 0 = one kernel launch per colour).  Results are
  * bit-identical for every setting; only the memory traffic differs. */
 int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
-/* FLUID_GS_REDBLACK on large grids: relax the interior with the register-resident streaming kernel
- * (4 sweeps per pass) and only the frame of tiles along the walls with the shared-memory tile kernel
- * (default on; 0 = tile kernel everywhere).  Results identical. */
+/* Large grids: the register-resident streaming kernels -- red-black relaxation, 4 sweeps per launch, and Blur,
+ * 5 passes per launch -- with the shared-memory tile kernel / the pass-per-launch kernel as their exact fallback
+ * (default on; 0 = tile and pass kernels everywhere).  Results identical. */
 int fluid_ctx_set_stream_kernel(fluid_ctx *ctx, int on);
+/* fluid_ctx_step / fluid_update: run the densities' add_source + Blur, which do not depend on the velocity, on a
+ * second stream beside VelStep (default on, single-GPU contexts only; 0 = one stream, kernels strictly in the
+ * reference's order -- what per-kernel profiling wants).  Results identical. */
+int fluid_ctx_set_overlap(fluid_ctx *ctx, int on);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
 int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur

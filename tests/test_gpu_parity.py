@@ -659,7 +659,8 @@ def test_whole_steps_agree_with_and_without_streaming(fl):
     """Whole frames (forcing, VelStep with both projections, DensStep) on random shapes and parameters, the
     large-grid kernels on and off: the pressure solve's exact power-of-two division with its unwritten zero
     guess, fields trading arrays with the scratch field after odd pass counts, Blur's multi-pass launches, the
-    redo lists and their feedback must all be invisible in the results."""
+    redo lists and their feedback, and the density diffusion running on a second stream beside VelStep, must all
+    be invisible in the results."""
     rng = np.random.default_rng(7)
     for case in range(10):
         batch = int(rng.choice([1, 1, 1, 2]))
@@ -684,6 +685,7 @@ def test_whole_steps_agree_with_and_without_streaming(fl):
         for stream in (True, False):
             fs = fl.FluidSystem().Setup(N, visc, diff, vorticity=vort, gs_order=fl.GS_REDBLACK, gs_iters=iters, batch=batch, slab=(0, 1, NY))
             fs.SetStreamKernel(stream)
+            fs.SetOverlap(stream)  # the reference run is strictly serial as well
             fs.SetFastDivision(2)
             for m in range(batch):
                 fs.SetSources(src, sim=m)
