@@ -132,7 +132,7 @@ struct fluid_ctx {
 	int* d_redo[2] = { nullptr, nullptr };
 	int redo_capacity[2] = { 0, 0 };
 	// Update(): add_source + Blur of the densities do not depend on the velocity, so they run on a second stream
-	// beside VelStep and fill the tails of its launches (single-GPU contexts; slabs keep one stream)
+	// beside VelStep and fill the tails of its launches
 	cudaStream_t side_stream = nullptr;
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_density = true;
@@ -967,7 +967,7 @@ static int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, cons
 			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 		}
 	}
-	const bool concurrent = c->overlap_density && c->slab_count <= 1;
+	const bool concurrent = c->overlap_density; // slabs too: the halo exchanges of the densities come after the join
 	auto diffuse_all = [&]() -> int {
 		for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
 			FL_TRY(dev_dens_diffuse(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], fluid_diff(c, fl), dt));

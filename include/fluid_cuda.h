@@ -218,7 +218,7 @@ int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
  * (default on; 0 = tile and pass kernels everywhere).  Results identical. */
 int fluid_ctx_set_stream_kernel(fluid_ctx *ctx, int on);
 /* fluid_ctx_step / fluid_update: run the densities' add_source + Blur, which do not depend on the velocity, on a
- * second stream beside VelStep (default on, single-GPU contexts only; 0 = one stream, kernels strictly in the
+ * second stream beside VelStep (default on; 0 = one stream, kernels strictly in the
  * reference's order -- what per-kernel profiling wants).  Results identical. */
 int fluid_ctx_set_overlap(fluid_ctx *ctx, int on);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
