@@ -330,7 +330,7 @@ def run_b200(args):
     step_gbs = B_CELL_UPDATE * float(N) * rows_per_gpu * args.steps / (ms * 1e-3) / 1e9
     ms_unit = gs_ms / units
     roofline = {
-        "bound": "hbm", "kernel": "%s; %d launches in the timed region" % (unit_name, gs_launches),
+        "bound": "hbm", "kernel": "%s; %d launches in the profiled pass" % (unit_name, gs_launches),
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
         "traffic": traffic, "traffic_kernel": tkernel,
         "algorithmic_bytes_per_launch": gs_bytes / units,
