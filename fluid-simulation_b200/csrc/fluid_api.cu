@@ -129,8 +129,15 @@ struct fluid_ctx {
 	} feedback[2];
 	// redo lists of the two streaming kernels: [0] = count, [1..] = (task, segment) entries.  One per kernel
 	// family (0 relaxation, 1 blur): the density diffusion may run on the side stream while VelStep runs
-	int* d_redo[2] = { nullptr, nullptr };
-	int redo_capacity[2] = { 0, 0 };
+	// ([2]: the relaxation of the second lane, see `lane`)
+	int* d_redo[3] = { nullptr, nullptr, nullptr };
+	int redo_capacity[3] = { 0, 0, 0 };
+	// VelStep's two diffusion solves (u, v) are independent: the second runs on its own stream ("lane" 1) with its
+	// own ping-pong scratch field and redo list, so that each fills the ragged end of the other's launches
+	int lane = 0;
+	float* rb_scratch2 = nullptr;
+	cudaStream_t lane_stream = nullptr;
+	cudaEvent_t ev_fork2 = nullptr, ev_join2 = nullptr;
 	// Update(): add_source + Blur of the densities do not depend on the velocity, so they run on a second stream
 	// beside VelStep and fill the tails of its launches
 	cudaStream_t side_stream = nullptr;
@@ -332,15 +339,16 @@ static bool stream_allowed(fluid_ctx* c, int which)
 }
 
 // After the last streaming launch of a solve: send its redo count home (asynchronously).
-static int stream_report(fluid_ctx* c, int which, long long segments)
+static int stream_report(fluid_ctx* c, int which, long long segments, int buffer = -1)
 {
+	if (buffer < 0) buffer = which;
 	auto& fb = c->feedback[which];
 	if (fb.pending) return FLUID_OK; // an earlier count is still in flight; one at a time
 	if (!fb.h_count) {
 		CU_TRY(cudaMallocHost(&fb.h_count, sizeof(int)));
 		CU_TRY(cudaEventCreateWithFlags(&fb.arrived, cudaEventDisableTiming));
 	}
-	CU_TRY(cudaMemcpyAsync(fb.h_count, c->d_redo[which], sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaMemcpyAsync(fb.h_count, c->d_redo[buffer], sizeof(int), cudaMemcpyDeviceToHost, c->stream));
 	CU_TRY(cudaEventRecord(fb.arrived, c->stream));
 	fb.segments = segments;
 	fb.pending = true;
@@ -453,7 +461,7 @@ static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, con
 	// persistent: one CTA per SM; behind the streaming kernel the redo list adds tiles the host cannot count
 	const int grid = (pg.ftx1 > 0) ? c->num_sms : (int) std::min<long long>(ntiles, c->num_sms);
 	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, pg.ntx, pg.nty, (int) ntiles, pg.ftx0, pg.ftx1,
-	       pg.fty0, pg.fty1, c->d_redo[0], pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
+	       pg.fty0, pg.fty1, c->d_redo[c->lane ? 2 : 0], pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
 	return FLUID_OK;
 }
 
@@ -472,10 +480,11 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 	if (pg.ftx1 > 0) {
 		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch;
 		*segments = ntasks_ll * pg.rc.segs;
-		FL_TRY(redo_reserve(c, 0, ntasks_ll * pg.rc.segs + 1));
+		const int rbuf = c->lane ? 2 : 0;
+		FL_TRY(redo_reserve(c, rbuf, ntasks_ll * pg.rc.segs + 1));
 		const int ntasks = (int) ntasks_ll;
-		CU_TRY(cudaMemsetAsync(c->d_redo[0], 0, sizeof(int), c->stream));
-		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[0], b);
+		CU_TRY(cudaMemsetAsync(c->d_redo[rbuf], 0, sizeof(int), c->stream));
+		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
 	}
 	// nothing but listed rectangles to do: the narrowest window covers a strip (112 columns) and has the
 	// shortest colour passes -- a redo launch lasts as long as one tile does
@@ -551,9 +560,10 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 	int field = -1;
 	for (int f = 0; f < c->n_fields; f++)
 		if (c->f[f] == x) field = f;
-	if (!c->rb_scratch) {
-		CU_TRY(cudaMalloc(&c->rb_scratch, c->field_bytes));
-		CU_TRY(cudaMemsetAsync(c->rb_scratch, 0, c->field_bytes, c->stream));
+	float*& scratch = c->lane ? c->rb_scratch2 : c->rb_scratch; // each lane ping-pongs (and trades arrays) with its own
+	if (!scratch) {
+		CU_TRY(cudaMalloc(&scratch, c->field_bytes));
+		CU_TRY(cudaMemsetAsync(scratch, 0, c->field_bytes, c->stream));
 	}
 	DivC dv;
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
@@ -590,7 +600,7 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 		n1 = limit - 2 * n2;
 	}
 	const float* in = x;
-	float* out = c->rb_scratch;
+	float* out = scratch;
 	long long segments = 0;
 	for (int k = 0; k < p5 + p4; k++) {
 		FL_TRY(rb_stream_pass_pow2<4>(c, b, in, out, x0, a, dv, x_is_zero && k == 0));
@@ -606,10 +616,10 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 		in = out;
 		out = t;
 	}
-	if (segments > 0) FL_TRY(stream_report(c, 0, segments)); // how much of the last pass had to be redone
+	if (segments > 0) FL_TRY(stream_report(c, 0, segments, c->lane ? 2 : 0)); // how much of the last pass had to be redone
 	if (in != x) { // odd number of passes: the field's values are in the scratch array now
-		c->f[field] = c->rb_scratch;
-		c->rb_scratch = x;
+		c->f[field] = scratch;
+		scratch = x;
 		x = c->f[field];
 	}
 	return FLUID_OK;
@@ -837,9 +847,29 @@ static int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, 
 	FL_TRY(dev_add_source2(c, u, u0, v, v0, dt));
 	std::swap(u, u0);
 	const float a = diffusion_a(c, visc, dt);
-	FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
 	std::swap(v, v0);
-	FL_TRY(dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a));
+	if (c->overlap_density) { // the two diffusions are independent: v on a second lane beside u
+		if (!c->lane_stream) {
+			CU_TRY(cudaStreamCreateWithFlags(&c->lane_stream, cudaStreamNonBlocking));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_fork2, cudaEventDisableTiming));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming));
+		}
+		CU_TRY(cudaEventRecord(c->ev_fork2, c->stream));
+		CU_TRY(cudaStreamWaitEvent(c->lane_stream, c->ev_fork2, 0));
+		cudaStream_t main_stream = c->stream;
+		c->stream = c->lane_stream;
+		c->lane = 1;
+		const int rc = dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a);
+		c->lane = 0;
+		c->stream = main_stream;
+		FL_TRY(rc);
+		CU_TRY(cudaEventRecord(c->ev_join2, c->lane_stream));
+		FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
+		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join2, 0));
+	} else {
+		FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
+		FL_TRY(dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a));
+	}
 	FL_TRY(halo_exchange(c, { u, v }));
 	FL_TRY(dev_project(c, u, v, u0, v0));
 	FL_TRY(halo_exchange(c, { u, v }));
@@ -1115,6 +1145,10 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	for (auto& p : c->f) if (p) cudaFree(p);
 	for (auto& p : c->vscr) if (p) cudaFree(p);
 	if (c->rb_scratch) cudaFree(c->rb_scratch);
+	if (c->rb_scratch2) cudaFree(c->rb_scratch2);
+	if (c->lane_stream) cudaStreamDestroy(c->lane_stream);
+	if (c->ev_fork2) cudaEventDestroy(c->ev_fork2);
+	if (c->ev_join2) cudaEventDestroy(c->ev_join2);
 	if (c->d_oob) cudaFree(c->d_oob);
 	if (c->d_divbins) cudaFree(c->d_divbins);
 	for (auto& p : c->d_redo) if (p) cudaFree(p);
