@@ -217,8 +217,9 @@ int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
  * 5 passes per launch -- with the shared-memory tile kernel / the pass-per-launch kernel as their exact fallback
  * (default on; 0 = tile and pass kernels everywhere).  Results identical. */
 int fluid_ctx_set_stream_kernel(fluid_ctx *ctx, int on);
-/* fluid_ctx_step / fluid_update: run the densities' add_source + Blur, which do not depend on the velocity, on a
- * second stream beside VelStep (default on; 0 = one stream, kernels strictly in the
+/* fluid_ctx_step / fluid_update / fluid_ctx_vel_step: run independent parts side by side on extra streams -- the
+ * densities' add_source + Blur beside VelStep, and VelStep's v diffusion beside its u diffusion (which costs one
+ * more scratch field) -- (default on; 0 = one stream, kernels strictly in the
  * reference's order -- what per-kernel profiling wants).  Results identical. */
 int fluid_ctx_set_overlap(fluid_ctx *ctx, int on);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
