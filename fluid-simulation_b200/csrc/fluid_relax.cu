@@ -1,0 +1,532 @@
+// Relaxation: LinearSolve1 (FluidSystem.cpp:534-548) and Blur (FluidSystem.cpp:722-743) on resident
+// fields -- which kernel family runs a solve (small-grid, streaming, tile, one colour per launch,
+// reference-order wavefront), the pass schedule, the verified division and the redo lists.
+#include "ctx.h"
+#include "kernels_relax.cuh"
+#include "kernels_rb_stream.cuh"
+#include "kernels_rb_tile.cuh"
+#include "kernels_blur_stream.cuh"
+#include "kernels_small.cuh"
+
+// ---- red-black tile path ---------------------------------------------------
+constexpr int kRbRY = 64, kRbNT = 512;
+
+// cuTensorMapEncodeTiled is fetched through the runtime so that the library
+// has no link-time dependency on libcuda (it must load on a machine without a driver).
+int get_encode_fn(EncodeTiledFn* out)
+{
+	static EncodeTiledFn fn = nullptr;
+	if (!fn) {
+		void* p = nullptr;
+		cudaDriverEntryPointQueryResult qres;
+		CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+		if (qres != cudaDriverEntryPointSuccess || !p) return fail(FLUID_ERR_CUDA, "driver does not provide cuTensorMapEncodeTiled");
+		fn = (EncodeTiledFn) p;
+	}
+	*out = fn;
+	return FLUID_OK;
+}
+
+// TMA descriptor of one field: 3-D tensor (pitch, NY+2, batch) of floats, box = one tile window.
+static int field_tmap(fluid_ctx* c, const float* base, int rx, const CUtensorMap** out)
+{
+	auto it = c->tmaps.find({ base, rx });
+	if (it == c->tmaps.end()) {
+		EncodeTiledFn enc = nullptr;
+		FL_TRY(get_encode_fn(&enc));
+		CUtensorMap m;
+		const cuuint64_t dims[3] = { (cuuint64_t) c->g.pitch, (cuuint64_t) (c->g.NY + 2), (cuuint64_t) c->batch };
+		const cuuint64_t strides[2] = { (cuuint64_t) c->g.pitch * sizeof(float), (cuuint64_t) c->g.plane * sizeof(float) };
+		const cuuint32_t box[3] = { (cuuint32_t) rx, (cuuint32_t) kRbRY, 1 };
+		const cuuint32_t estr[3] = { 1, 1, 1 };
+		CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*) base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+				 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+		if (r != CUDA_SUCCESS) return fail(FLUID_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int) r);
+		it = c->tmaps.emplace(std::make_pair(base, rx), m).first;
+	}
+	*out = &it->second;
+	return FLUID_OK;
+}
+
+// DivC for divisor cc: verified window if known / worth establishing, else range = 0 (callers use div.rn).
+int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
+{
+	out->c = cc;
+	out->y = 1.0f / cc;
+	out->lo = 0;
+	out->range = 0;
+	if (!(cc > 0.0f) || !isfinite(cc) || !isfinite(out->y) || c->fast_div_mode == 0) return FLUID_OK;
+	uint32_t key;
+	memcpy(&key, &cc, sizeof key);
+	auto it = c->divs.find(key);
+	if (it != c->divs.end()) {
+		*out = it->second;
+		return FLUID_OK;
+	}
+	// 2^31 trial divisions cost about as much as 2.5e8 cell updates: run the proof once that much work
+	// has been (or is about to be) done with this divisor -- at once for a large grid, after a few
+	// steps for a medium one, never for a divisor that changes every frame on a small grid
+	if (c->fast_div_mode == 1) {
+		double& seen = c->div_work[key];
+		seen += cell_updates;
+		if (seen < 2.5e8) return FLUID_OK;
+	}
+	if (!c->d_divbins) CU_TRY(cudaMalloc(&c->d_divbins, 256 * sizeof(unsigned int)));
+	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), c->stream));
+	LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins);
+	unsigned int bins[256];
+	CU_TRY(cudaMemcpyAsync(bins, c->d_divbins, sizeof bins, cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	if (bins[127] == 0) {
+		int elo = 127, ehi = 127;
+		while (elo > 1 && bins[elo - 1] == 0) elo--;
+		while (ehi < 254 && bins[ehi + 1] == 0) ehi++;
+		out->lo = (uint32_t) elo << 23;
+		out->range = (uint32_t) (ehi - elo + 1) << 23;
+	}
+	c->divs[key] = *out;
+	return FLUID_OK;
+}
+
+constexpr int kStreamHoldoff = 64;
+
+// May this solve use the streaming kernel?  Consumes the count of an earlier launch if it has arrived.
+static bool stream_allowed(fluid_ctx* c, int which)
+{
+	auto& fb = c->feedback[which];
+	if (fb.pending && cudaEventQuery(fb.arrived) == cudaSuccess) {
+		fb.pending = false;
+		if (getenv("FLUID_DEBUG_FEEDBACK")) fprintf(stderr, "feedback[%d]: %d of %lld segments redone\n", which, *fb.h_count, fb.segments);
+		if (fb.segments > 0 && (long long) *fb.h_count * 12 > fb.segments) fb.holdoff = kStreamHoldoff;
+	}
+	if (fb.holdoff > 0) {
+		fb.holdoff--;
+		return false;
+	}
+	return c->rb_stream;
+}
+
+// After the last streaming launch of a solve: send its redo count home (asynchronously).
+static int stream_report(fluid_ctx* c, int which, long long segments, int buffer = -1)
+{
+	if (buffer < 0) buffer = which;
+	auto& fb = c->feedback[which];
+	if (fb.pending) return FLUID_OK; // an earlier count is still in flight; one at a time
+	if (!fb.h_count) {
+		CU_TRY(cudaMallocHost(&fb.h_count, sizeof(int)));
+		CU_TRY(cudaEventCreateWithFlags(&fb.arrived, cudaEventDisableTiming));
+	}
+	CU_TRY(cudaMemcpyAsync(fb.h_count, c->d_redo[buffer], sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaEventRecord(fb.arrived, c->stream));
+	fb.segments = segments;
+	fb.pending = true;
+	return FLUID_OK;
+}
+
+// The list of rectangles a streaming kernel hands to its exact fallback: [0] = count, [1..] = entries.
+static int redo_reserve(fluid_ctx* c, int which, long long entries)
+{
+	if (entries > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many streaming tasks");
+	if (entries > c->redo_capacity[which]) {
+		if (c->d_redo[which]) CU_TRY(cudaFree(c->d_redo[which]));
+		c->d_redo[which] = nullptr;
+		CU_TRY(cudaMalloc(&c->d_redo[which], sizeof(int) * (size_t) entries));
+		c->redo_capacity[which] = (int) entries;
+	}
+	return FLUID_OK;
+}
+
+// Geometry of one pass of S sweeps: the tile grid, which tiles are left to the tile kernel (the frame)
+// and the rectangle the streaming kernel produces.
+struct PassGeom {
+	int TX, TY, ntx, nty;
+	int ftx0, ftx1, fty0, fty1; // streamed tiles: ftx0 <= tx < ftx1, fty0 <= ty < fty1; ftx1 = 0: none, the tile kernel does everything
+	StreamRect rc;
+};
+
+template <int S>
+static PassGeom pass_geometry(const fluid_ctx* c, bool stream_ok) // stream_ok: verified division at hand and streaming allowed
+{
+	PassGeom pg{};
+	pg.TY = kRbRY - 4 * S;
+	pg.TX = c->rb_rx - 2 * (((2 * S + 3) / 4) * 4);
+	pg.ntx = cdiv(c->g.N, pg.TX);
+	pg.nty = cdiv(c->g.NY, pg.TY);
+	pg.ftx0 = pg.ftx1 = pg.fty0 = pg.fty1 = 0;
+	if (!stream_ok) return pg; // the streaming kernel only knows the verified division
+	constexpr int L = StreamGeom<S>::L, HALO = StreamGeom<S>::HALO;
+	if (StreamGeom<S>::OUT > pg.TX) return pg;             // a redo tile must cover a strip's width
+	// Rows: all of them; the streaming kernel does the bottom and top walls' set_bnd (or, for a slab that
+	// ends in a neighbour's rows, treats the row beyond as fixed, like the tile kernel).
+	if (c->g.NY < 8 * L) return pg;
+	const int fy = pg.nty;
+	// Columns: the streaming kernel handles the left and right walls itself when a row is a whole number of
+	// float4 groups; otherwise it keeps one tile column away from them as well.
+	int fx0, fx1;
+	if (c->g.N % 4 == 0 && c->g.N >= 2 * StreamGeom<S>::OUT) {
+		fx0 = 0;
+		fx1 = pg.ntx;
+	} else {
+		fx0 = 1;
+		fx1 = pg.ntx - 1;
+		while (fx1 > 1 && pg.TX * fx1 + HALO > c->g.N + 1) fx1--;
+		if (fx1 <= 1) return pg;
+	}
+	const long long width = (fx0 == 0) ? c->g.N : (long long) (fx1 - 1) * pg.TX;
+	if (width * c->g.NY * c->batch < (1LL << 21)) return pg; // too little to bother
+	pg.ftx0 = fx0;
+	pg.ftx1 = fx1;
+	pg.fty1 = fy;
+	pg.rc.col0 = (fx0 == 0) ? XO + 1 : XO + 1 + pg.TX;
+	pg.rc.col1 = (fx0 == 0) ? XO + 1 + c->g.N : XO + 1 + pg.TX * fx1;
+	pg.rc.row0 = 1;
+	pg.rc.row1 = c->g.NY + 1;
+	pg.rc.nstrips = cdiv(pg.rc.col1 - pg.rc.col0, StreamGeom<S>::OUT);
+	const int rows = pg.rc.row1 - pg.rc.row0;
+	// chunks of about 256 rows, nudged so that the warp tasks fill whole waves of resident warps
+	int nchunks = std::max(1, cdiv(rows, 256));
+	// resident warps per SM of k_rb_stream<S> (register bound: 167 / 115 / 89 registers per thread)
+	const long long slots = (long long) c->num_sms * (S >= 4 ? 12 : (S == 2 ? 16 : 20));
+	constexpr int kWallSplit = 2; // wall strips: tasks of half the rows
+	const bool walls = (fx0 == 0);
+	const long long per_chunk = (long long) (pg.rc.nstrips + (walls ? 2 * (kWallSplit - 1) : 0)) * c->batch;
+	if (per_chunk * nchunks > slots / 2) {
+		const long long waves = std::max(1LL, (per_chunk * nchunks + slots / 2) / slots);
+		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
+	}
+	const int unit = 2 * kWallSplit; // chunk and wall task both an even number of rows: one colour phase per launch
+	// the bottom and top chunks run ~3S slower row steps next to their wall: make them that much shorter
+	const int shift = (nchunks > 2) ? 12 * S : 0;
+	pg.rc.row_shift = shift;
+	pg.rc.chunk_rows = (cdiv(rows + 2 * shift, nchunks) + unit - 1) / unit * unit;
+	pg.rc.nchunks = cdiv(rows + shift, pg.rc.chunk_rows);
+	pg.rc.wall_rows = walls ? pg.rc.chunk_rows / kWallSplit : 0;
+	pg.rc.wall_chunks = walls ? cdiv(rows + shift, pg.rc.wall_rows) : 0;
+	pg.rc.seg_rows = pg.TY;
+	pg.rc.segs = cdiv(pg.rc.chunk_rows, pg.TY);
+	pg.rc.per_sim = 2 * pg.rc.wall_chunks + (pg.rc.nstrips - (walls ? 2 : 0)) * pg.rc.nchunks;
+	return pg;
+}
+
+template <int S, int RX>
+static int rb_tile_pass_rx(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv,
+			   const PassGeom& pg)
+{
+	static bool configured[64] = {}; // per template instance and per device: function attributes are per device
+	constexpr size_t smem = (2 * (size_t) (kRbRY + 2) + kRbRY) * RX * sizeof(float); // two x windows + x0 staging
+	auto kern = k_rb_tile<S, kRbRY, RX, kRbNT>;
+	if (c->device >= 64 || !configured[c->device]) {
+		CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		if (c->device < 64) configured[c->device] = true;
+	}
+	const CUtensorMap *tm, *tm0;
+	FL_TRY(field_tmap(c, in, RX, &tm));
+	FL_TRY(field_tmap(c, x0, RX, &tm0));
+	long long ntiles = (long long) pg.ntx * pg.nty;
+	if (pg.ftx1 > 0) ntiles -= (long long) (pg.ftx1 - pg.ftx0) * (pg.fty1 - pg.fty0); // the frame only, possibly nothing
+	ntiles *= c->batch;
+	if (ntiles > 0x7fffffffLL) return fail(FLUID_ERR_UNSUPPORTED, "too many tiles");
+	// persistent: one CTA per SM; behind the streaming kernel the redo list adds tiles the host cannot count
+	const int grid = (pg.ftx1 > 0) ? c->num_sms : (int) std::min<long long>(ntiles, c->num_sms);
+	LAUNCH(kern, grid, kRbNT, smem, c->stream, *tm, *tm0, c->g, b, out, a, dv, pg.ntx, pg.nty, (int) ntiles, pg.ftx0, pg.ftx1,
+	       pg.fty0, pg.fty1, c->d_redo[c->lane ? 2 : 0], pg.rc, StreamGeom<S>::OUT, StreamGeom<S>::HALO);
+	return FLUID_OK;
+}
+
+// One pass of S red-black sweeps, in -> out: the streaming kernel on the interior rectangle (if the grid
+// is large enough to have one) and the tile kernel on the frame of tiles around it, or on everything.
+// The window width of the tile kernel is chosen per context so that ceil(N / (RX-8)) windows waste the
+// fewest columns (N=512: 3 x 192 instead of 3 x 256; N <= 120: one 128-wide window instead of 256).
+template <int S>
+static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv, bool streaming,
+			bool pow2, long long* segments)
+{
+	const PassGeom pg = pass_geometry<S>(c, streaming);
+	*segments = 0;
+	const bool whole = pg.ftx1 > 0 && pg.ftx0 == 0 && pg.ftx1 == pg.ntx && pg.fty0 == 0 && pg.fty1 == pg.nty; // the streaming kernel covers the grid
+	(void) pow2;
+	if (pg.ftx1 > 0) {
+		const long long ntasks_ll = (long long) pg.rc.per_sim * c->batch;
+		*segments = ntasks_ll * pg.rc.segs;
+		const int rbuf = c->lane ? 2 : 0;
+		FL_TRY(redo_reserve(c, rbuf, ntasks_ll * pg.rc.segs + 1));
+		const int ntasks = (int) ntasks_ll;
+		CU_TRY(cudaMemsetAsync(c->d_redo[rbuf], 0, sizeof(int), c->stream));
+		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
+	}
+	// nothing but listed rectangles to do: the narrowest window covers a strip (112 columns) and has the
+	// shortest colour passes -- a redo launch lasts as long as one tile does
+	if (whole && StreamGeom<S>::OUT <= 128 - 2 * StreamGeom<S>::HALO) {
+		PassGeom narrow = pg;
+		narrow.TX = 128 - 2 * StreamGeom<S>::HALO;
+		narrow.ntx = narrow.ftx1 = cdiv(c->g.N, narrow.TX);
+		return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv, narrow);
+	}
+	switch (c->rb_rx) {
+	case 128: return rb_tile_pass_rx<S, 128>(c, b, in, out, x0, a, dv, pg);
+	case 192: return rb_tile_pass_rx<S, 192>(c, b, in, out, x0, a, dv, pg);
+	default: return rb_tile_pass_rx<S, 256>(c, b, in, out, x0, a, dv, pg);
+	}
+}
+
+int choose_rb_rx(int N)
+{
+	int best = 256;
+	long long best_cost = -1;
+	for (int rx : { 256, 192, 128 }) {
+		const long long cost = (long long) cdiv(N, rx - 8) * rx;
+		if (best_cost < 0 || cost < best_cost) { best = rx; best_cost = cost; }
+	}
+	return best;
+}
+
+// The streaming kernel covers the whole grid (rows are float4 groups, the grid is large): no tile kernel involved.
+template <int S>
+static bool stream_covers(const fluid_ctx* c, StreamRect* rc)
+{
+	const PassGeom pg = pass_geometry<S>(c, c->rb_stream);
+	*rc = pg.rc;
+	return pg.ftx1 > 0 && pg.ftx0 == 0 && pg.ftx1 == pg.ntx && pg.fty0 == 0 && pg.fty1 == pg.nty;
+}
+
+// a == 1 and c a power of two (Project's pressure solve, c = 4): the division is a multiplication, exact for
+// every operand -- no verified window, no redo list, and five instead of twelve instructions per update, which
+// makes the pass HBM-bound.
+static bool is_pow2_solve(float a, float cc)
+{
+	int e = 0;
+	return a == 1.0f && cc > 0.0f && isfinite(cc) && frexpf(cc, &e) == 0.5f && (1.0f / cc) >= 1.17549435e-38f;
+}
+
+template <int S>
+static int rb_stream_pass_pow2(fluid_ctx* c, int b, const float* in, float* out, const float* x0, float a, const DivC& dv, bool x_is_zero)
+{
+	StreamRect rc;
+	if (!stream_covers<S>(c, &rc)) return fail(FLUID_ERR_CUDA, "internal: streaming pass on a grid it does not cover");
+	const int ntasks = (int) ((long long) rc.per_sim * c->batch);
+	if (x_is_zero) LAUNCH((k_rb_stream<S, true, true>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
+	else LAUNCH((k_rb_stream<S, true, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
+	return FLUID_OK;
+}
+
+// Will a solve with these coefficients start with a pass that can be told "x is zero"?  (dev_project asks before
+// it decides not to write p = 0.)
+bool solve_accepts_zero_x(const fluid_ctx* c, float a, float cc, int limit)
+{
+	StreamRect rc;
+	if (!(c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps >= 2 && limit >= 4 && is_pow2_solve(a, cc))) return false;
+	return stream_covers<4>(c, &rc);
+}
+
+// `limit` red-black sweeps as passes of 4, 2 or 1 sweeps, ping-ponging between x and the scratch field.
+// After an odd number of passes the result sits in the scratch array: if x is the storage of a context
+// field, that field and the scratch simply trade arrays (c->f is the only place that maps field ids to
+// storage, and x is updated for the caller) -- 20 sweeps are then five 4-sweep passes instead of four and
+// two 2-sweep passes.  For any other array the number of passes is made even.
+static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, int limit, bool x_is_zero)
+{
+	int field = -1;
+	for (int f = 0; f < c->n_fields; f++)
+		if (c->f[f] == x) field = f;
+	float*& scratch = c->lane ? c->rb_scratch2 : c->rb_scratch; // each lane ping-pongs (and trades arrays) with its own
+	if (!scratch) {
+		CU_TRY(cudaMalloc(&scratch, c->field_bytes));
+		CU_TRY(cudaMemsetAsync(scratch, 0, c->field_bytes, c->stream));
+	}
+	DivC dv;
+	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
+	const bool pow2 = is_pow2_solve(a, cc);
+	// otherwise the streaming kernel relies on the proven window reaching the largest finite float
+	const bool streaming = dv.range != 0 && (dv.lo + dv.range) == (255u << 23) && stream_allowed(c, 0);
+	// power-of-two solves first take as many whole-grid streaming passes of 5 and 4 sweeps as fit
+	int p5 = 0, p4 = 0;
+	StreamRect rc_unused;
+	if (pow2 && c->rb_tile_sweeps >= 2) {
+		// (5 sweeps per pass were tried: 260 us per pass against 148 us for 4 -- ten dependent levels per row step
+		// leave three warps per scheduler too little to overlap, and the strips shrink to 104 columns)
+		if (limit >= 4 && stream_covers<4>(c, &rc_unused)) p4 = limit / 4;
+	}
+	if (x_is_zero && p5 + p4 == 0) return fail(FLUID_ERR_CUDA, "internal: zero-x hint given to a solve that cannot use it");
+	limit -= 5 * p5 + 4 * p4;
+	int n4 = 0, n2 = 0, n1 = 0; // passes of 4, 2 and 1 sweeps; the total number of passes must be even
+	if (limit == 0) {
+		if (field < 0 && (p5 + p4) % 2) return fail(FLUID_ERR_CUDA, "internal: odd pass count on an array that is not a field");
+	} else if (c->rb_tile_sweeps >= 2) {
+		int rest = limit;
+		if (pass_geometry<4>(c, streaming).ftx1 > 0) { // 4 sweeps per pass pay off where the streaming kernel runs
+			n4 = rest / 4;
+			rest -= 4 * n4;
+		}
+		n2 = rest / 2;
+		n1 = rest % 2;
+		if (field < 0 && (p5 + p4 + n4 + n2 + n1) % 2) {
+			if (n4 > 0) { n4 -= 1; n2 += 2; }
+			else { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
+		}
+	} else {
+		n2 = (field < 0) ? (limit + p5 + p4) % 2 : 0; // an odd count needs one 2-sweep pass to make the number of passes even
+		n1 = limit - 2 * n2;
+	}
+	const float* in = x;
+	float* out = scratch;
+	long long segments = 0;
+	for (int k = 0; k < p5 + p4; k++) {
+		FL_TRY(rb_stream_pass_pow2<4>(c, b, in, out, x0, a, dv, x_is_zero && k == 0));
+		float* t = const_cast<float*>(in);
+		in = out;
+		out = t;
+	}
+	for (int k = 0; k < n4 + n2 + n1; k++) {
+		if (k < n4) FL_TRY(rb_tile_pass<4>(c, b, in, out, x0, a, dv, streaming, pow2, &segments));
+		else if (k < n4 + n2) FL_TRY(rb_tile_pass<2>(c, b, in, out, x0, a, dv, streaming, pow2, &segments));
+		else FL_TRY(rb_tile_pass<1>(c, b, in, out, x0, a, dv, streaming, pow2, &segments));
+		float* t = const_cast<float*>(in);
+		in = out;
+		out = t;
+	}
+	if (segments > 0) FL_TRY(stream_report(c, 0, segments, c->lane ? 2 : 0)); // how much of the last pass had to be redone
+	if (in != x) { // odd number of passes: the field's values are in the scratch array now
+		c->f[field] = scratch;
+		scratch = x;
+		x = c->f[field];
+	}
+	return FLUID_OK;
+}
+
+bool use_small_kernels(const fluid_ctx* c)
+{
+	return c->small_kernels && c->slab_count == 1 && c->g.N <= kSmallMaxN && c->g.NY == c->g.N;
+}
+
+static int small_configure(fluid_ctx* c)
+{
+	static bool configured[64] = {};
+	if (c->device >= 64 || !configured[c->device]) {
+		const int bytes = (int) small_smem_bytes(kSmallMaxN);
+		CU_TRY(cudaFuncSetAttribute(k_small_lin_solve<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+		CU_TRY(cudaFuncSetAttribute(k_small_lin_solve<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+		CU_TRY(cudaFuncSetAttribute(k_small_blur, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+		if (c->device < 64) configured[c->device] = true;
+	}
+	return FLUID_OK;
+}
+
+// LinearSolve1 (FluidSystem.cpp:534-548) in the context's relaxation order.
+// x may come back pointing at another array (rb_tile_solve); callers keep using x, not a copy made before.
+int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, bool x_is_zero)
+{
+	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
+	const int limit = a > 0 ? c->gs_iters : 1;
+	if (use_small_kernels(c)) {
+		FL_TRY(small_configure(c));
+		if (c->gs_order == FLUID_GS_REDBLACK)
+			LAUNCH(k_small_lin_solve<true>, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
+		else
+			LAUNCH(k_small_lin_solve<false>, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
+	} else if (c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 && b >= 0 && b <= 2) {
+		FL_TRY(rb_tile_solve(c, b, x, x0, a, cc, limit, x_is_zero));
+	} else if (c->gs_order == FLUID_GS_REDBLACK) {
+		for (int k = 0; k < limit; k++) {
+			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 0);
+			LAUNCH(k_rb_half, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, x, x0, a, cc, 1);
+		}
+	} else {
+		if (c->slab_count > 1)
+			return fail(FLUID_ERR_UNSUPPORTED, "the wavefront (reference-order) relaxation is a pipeline across slabs and is offered on one GPU only; use FLUID_GS_REDBLACK for row slabs");
+		// small tiles: a launch is bound by the latency of one tile (2T-1 dependent steps), not by throughput.
+		// Measured ms/step (T=16/32/64): N=1024 8.6/10.0/13.8, N=2048 14.5/14.0/17.4, N=8192 77/57/68.
+		const int T = (c->wavefront_tile > 0) ? c->wavefront_tile : (c->g.N < 2048 ? 16 : 32);
+		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
+		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
+		for (int s = 0; s <= last; s++) {
+			if (T == 16) LAUNCH(k_gs_wavefront<16>, dim3(ntx, limit, c->batch), 16, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
+			else if (T == 32) LAUNCH(k_gs_wavefront<32>, dim3(ntx, limit, c->batch), 32, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
+			else LAUNCH(k_gs_wavefront<64>, dim3(ntx, limit, c->batch), 64, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
+		}
+	}
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+// Blur (FluidSystem.cpp:722-743).  x and x0 are the caller's two buffers; on
+// return the result is in x and the penultimate iterate in x0.
+// Blur, L passes per launch (kernels_blur_stream.cuh): the task geometry, or false when the grid does not
+// qualify (rows must be whole float4 groups and at least two strips wide; small grids have their own kernel).
+constexpr int kBlurL = 5, kBlurSeg = 32;
+
+static bool blur_stream_geometry(const fluid_ctx* c, StreamRect* rc)
+{
+	constexpr int OUT = BlurGeom<kBlurL>::OUT;
+	const GridDesc& g = c->g;
+	if (!c->rb_stream || g.N % 4 != 0 || g.N < 2 * OUT || g.NY < 8 * kBlurL) return false;
+	if ((long long) g.N * g.NY * c->batch < (1LL << 21)) return false;
+	*rc = StreamRect{};
+	rc->col0 = XO + 1;
+	rc->col1 = XO + 1 + g.N;
+	rc->row0 = 1;
+	rc->row1 = g.NY + 1;
+	rc->nstrips = cdiv(g.N, OUT);
+	const int rows = g.NY;
+	int nchunks = std::max(1, cdiv(rows, 256));
+	const long long slots = (long long) c->num_sms * 16; // 4 CTAs of 4 warps per SM
+	constexpr int kWallSplit = 2;
+	const long long per_chunk = (long long) (rc->nstrips + 2 * (kWallSplit - 1)) * c->batch;
+	if (per_chunk * nchunks > slots / 2) {
+		const long long waves = std::max(1LL, (per_chunk * nchunks + slots / 2) / slots);
+		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
+	}
+	const int shift = (nchunks > 2) ? 6 * kBlurL : 0;
+	rc->row_shift = shift;
+	rc->chunk_rows = (cdiv(rows + 2 * shift, nchunks) + kWallSplit - 1) / kWallSplit * kWallSplit;
+	rc->nchunks = cdiv(rows + shift, rc->chunk_rows);
+	rc->wall_rows = rc->chunk_rows / kWallSplit;
+	rc->wall_chunks = cdiv(rows + shift, rc->wall_rows);
+	rc->seg_rows = kBlurSeg;
+	rc->segs = cdiv(rc->chunk_rows, kBlurSeg);
+	rc->per_sim = 2 * rc->wall_chunks + (rc->nstrips - 2) * rc->nchunks;
+	return true;
+}
+
+int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
+{
+	ProfScope ps(c, FLUID_PROF_BLUR);
+	int limit = a > 0 ? c->gs_iters : 1;
+	if (limit % 2 == 0) limit += 1;
+	if (use_small_kernels(c)) {
+		FL_TRY(small_configure(c));
+		LAUNCH(k_small_blur, c->batch, kSmallThreads, small_smem_bytes(c->g.N), c->stream, c->g, b, x, x0, a, cc, limit);
+		CU_TRY(cudaGetLastError());
+		return FLUID_OK;
+	}
+	float *dst = x, *src = x0;
+	DivC dv;
+	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
+	FL_TRY(dev_set_bnd(c, b, src));
+	// kBlurL passes per launch while an even number of such launches fits (the result must land in x with the
+	// penultimate iterate in x0, as the pass-per-launch sequence leaves them); single passes for the rest
+	int done = 0;
+	StreamRect rc;
+	const bool window_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
+	if (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc) && stream_allowed(c, 1)) {
+		const int launches = 2 * ((limit - 1) / (2 * kBlurL));
+		const long long ntasks = (long long) rc.per_sim * c->batch;
+		FL_TRY(redo_reserve(c, 1, ntasks * rc.segs + 1));
+		for (int l = 0; l < launches; l++) {
+			if (l > 0) std::swap(dst, src);
+			CU_TRY(cudaMemsetAsync(c->d_redo[1], 0, sizeof(int), c->stream));
+			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
+			// few entries, each a chain of 2L barrier-separated phases over ~5000 cells: wide CTAs keep the chain short
+			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo[1], b);
+		}
+		done = launches * kBlurL;
+		FL_TRY(stream_report(c, 1, ntasks * rc.segs));
+	}
+	for (int k = done; k < limit; k++) {
+		if (k > 0) std::swap(dst, src);
+		LAUNCH(k_blur_pass, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, b, dst, src, a, dv,
+		       k + 1 < limit ? 1 : 0);
+	}
+	FL_TRY(dev_zero_bnd(c, dst));
+	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}

@@ -1,0 +1,314 @@
+// The streaming and gather kernels of the Stable-Fluids step and their composition:
+// VelStep1 (FluidSystem.cpp:354-376), DensStep1 (:289-299), Update (:101-128), the headless render.
+#include "ctx.h"
+#include "kernels_basic.cuh"
+
+int dev_add_source(fluid_ctx* c, float* x, const float* s, float dt)
+{
+	ProfScope ps(c, FLUID_PROF_ADD_SOURCE);
+	LAUNCH(k_add_source, flat_blocks(c), 256, 0, c->stream, (float4*) x, (const float4*) s, dt, n4_of(c));
+	return FLUID_OK;
+}
+
+int dev_add_source2(fluid_ctx* c, float* x, const float* s, float* y, const float* t, float dt)
+{
+	ProfScope ps(c, FLUID_PROF_ADD_SOURCE);
+	LAUNCH(k_add_source2, flat_blocks(c), 256, 0, c->stream, (float4*) x, (const float4*) s, (float4*) y,
+	       (const float4*) t, dt, n4_of(c));
+	return FLUID_OK;
+}
+
+int dev_set_bnd(fluid_ctx* c, int b, float* x)
+{
+	const int n = std::max(c->g.N, c->g.NY);
+	LAUNCH(k_set_bnd, dim3(cdiv(n, 256), 1, c->batch), 256, 0, c->stream, c->g, b, x);
+	return FLUID_OK;
+}
+
+int dev_zero_bnd(fluid_ctx* c, float* x)
+{
+	const int n = std::max(c->g.N, c->g.NY) + 2;
+	LAUNCH(k_zero_bnd, dim3(cdiv(n, 256), 1, c->batch), 256, 0, c->stream, c->g, x);
+	return FLUID_OK;
+}
+int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, const float* v, float dt)
+{
+	ProfScope ps(c, FLUID_PROF_ADVECT);
+	const float dtN = dt * c->g.N;
+	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	if (c->slab_count > 1) {
+		if (euler) LAUNCH((k_advect<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+		else LAUNCH((k_advect<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	} else {
+		if (euler) LAUNCH((k_advect<false, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, 1, 0);
+		else LAUNCH((k_advect<false, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, 1, 0);
+	}
+	return FLUID_OK;
+}
+
+int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const float* v0, float dt)
+{
+	ProfScope ps(c, FLUID_PROF_ADVECT);
+	const float dtN = dt * c->g.N;
+	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	if (c->slab_count > 1) {
+		if (euler) LAUNCH((k_advect_velocity<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+		else LAUNCH((k_advect_velocity<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+	} else {
+		if (euler) LAUNCH((k_advect_velocity<false, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0);
+		else LAUNCH((k_advect_velocity<false, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0);
+	}
+	return FLUID_OK;
+}
+
+// Project (FluidSystem.cpp:982-1007).
+int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
+{
+	// p = 0 is the solve's starting guess.  Where the first pass of the solve can simply be told so, the zeros
+	// are neither written here nor read there (2 x 268 MB at N = 8192).
+	const int limit = c->gs_iters; // a = 1 > 0
+	const bool skip_zero = !use_small_kernels(c) && c->gs_order == FLUID_GS_REDBLACK && c->rb_tile_sweeps > 0 && limit >= 2 &&
+			       solve_accepts_zero_x(c, 1.0f, 4.0f, limit);
+	{
+		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
+		LAUNCH(k_divergence, rowgroup_grid(c, c->g.NY + 2), kBlk2D, 0, c->stream, c->g, u, v, div, skip_zero ? (float*) nullptr : p);
+	}
+	FL_TRY(dev_lin_solve(c, 0, p, div, 1.0f, 4.0f, skip_zero));
+	{
+		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
+		LAUNCH(k_subtract_gradient, rowgroup_grid(c, c->g.NY), kBlk2D, 0, c->stream, c->g, u, v, p);
+	}
+	return FLUID_OK;
+}
+// Halo exchange between row slabs.  The slabs overlap by slab_halo (+1) rows and every
+// kernel computes on all stored rows, so stale values creep in from the outer
+// halo edge by one row per stencil application; the fields named here are made
+// valid again over the full halo depth by asking the host's transport (NCCL
+// send/recv, peer copies ...) to refill the halo rows from the neighbours' owned
+// rows.  With a 48-row halo that is needed once per 20-sweep solve instead of
+// once per colour pass: 9 exchanges of ~3 MB per step instead of ~200 of 64 KB.
+static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> arrays)
+{
+	if (c->slab_count <= 1) return FLUID_OK;
+	if (!c->exchange) return fail(FLUID_ERR_INVALID, "this context is a row slab but no exchange callback is set (fluid_ctx_set_exchange)");
+	int ids[fluid_ctx::kMaxFields], n = 0;
+	for (const float* a : arrays)
+		for (int f = 0; f < c->n_fields; f++)
+			if (c->f[f] == a) ids[n++] = f;
+	ProfScope ps(c, FLUID_PROF_EXCHANGE);
+	if (!c->exchange_stream_ordered) CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
+	const int rc = c->exchange(c->exchange_user, n, ids);
+	if (rc != 0) return fail(FLUID_ERR_CUDA, "halo exchange callback failed with code %d", rc);
+	return FLUID_OK;
+}
+
+// VelStep1 (FluidSystem.cpp:354-376).  The four pointers are locals: the
+// reference's two Swap() calls per FlipFlopArr become local pointer swaps, so
+// the result lands in the arrays passed as u and v.
+int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt)
+{
+	// slabs: u, v (and the source arrays, which every slab fills itself) are valid over the whole halo on entry
+	FL_TRY(dev_add_source2(c, u, u0, v, v0, dt));
+	std::swap(u, u0);
+	const float a = diffusion_a(c, visc, dt);
+	std::swap(v, v0);
+	if (c->overlap_density) { // the two diffusions are independent: v on a second lane beside u
+		if (!c->lane_stream) {
+			CU_TRY(cudaStreamCreateWithFlags(&c->lane_stream, cudaStreamNonBlocking));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_fork2, cudaEventDisableTiming));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming));
+		}
+		CU_TRY(cudaEventRecord(c->ev_fork2, c->stream));
+		CU_TRY(cudaStreamWaitEvent(c->lane_stream, c->ev_fork2, 0));
+		cudaStream_t main_stream = c->stream;
+		c->stream = c->lane_stream;
+		c->lane = 1;
+		const int rc = dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a);
+		c->lane = 0;
+		c->stream = main_stream;
+		FL_TRY(rc);
+		CU_TRY(cudaEventRecord(c->ev_join2, c->lane_stream));
+		FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
+		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join2, 0));
+	} else {
+		FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
+		FL_TRY(dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a));
+	}
+	FL_TRY(halo_exchange(c, { u, v }));
+	FL_TRY(dev_project(c, u, v, u0, v0));
+	FL_TRY(halo_exchange(c, { u, v }));
+	std::swap(u, u0);
+	std::swap(v, v0);
+	FL_TRY(dev_advect_velocity(c, u, v, u0, v0, dt));
+	FL_TRY(halo_exchange(c, { u, v }));
+	FL_TRY(dev_project(c, u, v, u0, v0));
+	FL_TRY(halo_exchange(c, { u, v }));
+	return FLUID_OK;
+}
+
+// DensStep1 (FluidSystem.cpp:289-299), one fluid.
+// First half (sources and diffusion: no velocity involved; the blurred field ends in x0) and second half (advection).
+static int dev_dens_diffuse(fluid_ctx* c, float* x, float* x0, float diff, float dt)
+{
+	FL_TRY(dev_add_source(c, x, x0, dt));
+	const float a = diffusion_a(c, diff, dt);
+	return dev_blur(c, 0, x0, x, a, 1 + 4 * a); // after the reference's Swap: x0 is relaxed, x holds the sum
+}
+
+static int dev_dens_advect(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float dt)
+{
+	FL_TRY(halo_exchange(c, { x0 })); // 21 blur passes consumed 21 halo rows of the field advect samples
+	FL_TRY(dev_advect(c, 0, x, x0, u, v, dt));
+	FL_TRY(halo_exchange(c, { x }));
+	return FLUID_OK;
+}
+
+int dev_dens_step(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float diff, float dt)
+{
+	FL_TRY(dev_dens_diffuse(c, x, x0, diff, dt));
+	return dev_dens_advect(c, x, x0, u, v, dt);
+}
+
+static int ensure_vort_scratch(fluid_ctx* c)
+{
+	for (int k = 0; k < 4; k++) {
+		if (!c->vscr[k]) {
+			CU_TRY(cudaMalloc(&c->vscr[k], c->field_bytes));
+			CU_TRY(cudaMemsetAsync(c->vscr[k], 0, c->field_bytes, c->stream));
+		}
+	}
+	return FLUID_OK;
+}
+
+// VortConfinement (FluidSystem.cpp:1124-1175).
+int dev_vort_confinement(fluid_ctx* c, float* u, float* v, float vorticity)
+{
+	FL_TRY(ensure_vort_scratch(c));
+	ProfScope ps(c, FLUID_PROF_OTHER);
+	LAUNCH(k_vort_curl, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, c->vscr[0], c->vscr[1]);
+	LAUNCH(k_vort_dir, cell_grid(c), kBlk2D, 0, c->stream, c->g, c->vscr[1], c->vscr[2], c->vscr[3]);
+	LAUNCH(k_vort_apply, cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, c->vscr[0], c->vscr[2], c->vscr[3], vorticity);
+	return FLUID_OK;
+}
+
+int dev_damp(fluid_ctx* c, float* vel, float amount, float dt)
+{
+	const float f = powf(1 - amount, dt); // host libm, as the reference (FluidSystem.cpp:1181)
+	ProfScope ps(c, FLUID_PROF_OTHER);
+	LAUNCH(k_scale, flat_blocks(c), 256, 0, c->stream, (float4*) vel, f, n4_of(c));
+	return FLUID_OK;
+}
+
+int sync_sources(fluid_ctx* c)
+{
+	if (!c->src_dirty) return FLUID_OK;
+	std::vector<SourceDev> flat;
+	std::vector<int> first(c->batch + 1, 0);
+	for (int s = 0; s < c->batch; s++) {
+		first[s] = (int) flat.size();
+		flat.insert(flat.end(), c->src[s].begin(), c->src[s].end());
+	}
+	first[c->batch] = (int) flat.size();
+	if (c->d_src) CU_TRY(cudaFree(c->d_src));
+	c->d_src = nullptr;
+	if (!c->d_first) CU_TRY(cudaMalloc(&c->d_first, sizeof(int) * (c->batch + 1)));
+	if (!flat.empty()) {
+		CU_TRY(cudaMalloc(&c->d_src, sizeof(SourceDev) * flat.size()));
+		CU_TRY(cudaMemcpy(c->d_src, flat.data(), sizeof(SourceDev) * flat.size(), cudaMemcpyHostToDevice));
+	}
+	CU_TRY(cudaMemcpy(c->d_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice));
+	c->n_src = (int) flat.size();
+	c->src_dirty = false;
+	return FLUID_OK;
+}
+// FluidSystem::Update (FluidSystem.cpp:101-128) for FSType::ORIGINAL.
+// FluidSystem::Update (FluidSystem.cpp:101-128): forcing, [vorticity], VelStep, DensStep per fluid, [damping].
+// The densities' add_source + Blur touch neither velocity array, so on a single-GPU context they are enqueued on
+// a side stream (fork after the forcing, join before the advection) and share the GPU with VelStep.
+// `dens_ready`: an event (of another stream) after which the current density arrays are valid, or nullptr;
+// `after_velocity`: called once VelStep has been enqueued on c->stream, or empty.  fluid_update() uses both to
+// slip its bus transfers in; everybody else calls dev_update.
+int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::function<int()>& after_velocity)
+{
+	{
+		ProfScope ps(c, FLUID_PROF_OTHER);
+		CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));
+		CU_TRY(cudaMemsetAsync(c->f[FLUID_V_PREV], 0, c->field_bytes, c->stream));
+		for (int fl = 0; fl < c->n_fluids; fl++) CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV_OF(fl)], 0, c->field_bytes, c->stream));
+		if (c->n_src > 0) {
+			FieldPtrs fp = {};
+			fp.cur[0] = c->f[FLUID_U];
+			fp.prev[0] = c->f[FLUID_U_PREV];
+			fp.cur[1] = c->f[FLUID_V];
+			fp.prev[1] = c->f[FLUID_V_PREV];
+			for (int fl = 0; fl < c->n_fluids; fl++) {
+				fp.cur[2 + fl] = c->f[FLUID_DENS_OF(fl)];
+				fp.prev[2 + fl] = c->f[FLUID_DENS_PREV_OF(fl)];
+			}
+			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
+		}
+	}
+	const bool concurrent = c->overlap_density; // slabs too: the halo exchanges of the densities come after the join
+	auto diffuse_all = [&]() -> int {
+		for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
+			FL_TRY(dev_dens_diffuse(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], fluid_diff(c, fl), dt));
+		return FLUID_OK;
+	};
+	if (concurrent) {
+		if (!c->side_stream) {
+			CU_TRY(cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+			CU_TRY(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+		}
+		CU_TRY(cudaEventRecord(c->ev_fork, c->stream));
+		CU_TRY(cudaStreamWaitEvent(c->side_stream, c->ev_fork, 0));
+		if (dens_ready) CU_TRY(cudaStreamWaitEvent(c->side_stream, dens_ready, 0));
+		cudaStream_t main_stream = c->stream;
+		c->stream = c->side_stream; // every launch helper and profiling scope follows c->stream
+		const int rc = diffuse_all();
+		c->stream = main_stream;
+		FL_TRY(rc);
+		CU_TRY(cudaEventRecord(c->ev_join, c->side_stream));
+	}
+	if (c->vorticity != 0.0f) {
+		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
+		FL_TRY(halo_exchange(c, { c->f[FLUID_U], c->f[FLUID_V] })); // three stencil phases consumed 3 halo rows
+	}
+	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt));
+	if (after_velocity) FL_TRY(after_velocity());
+	if (concurrent) {
+		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+	} else {
+		if (dens_ready) CU_TRY(cudaStreamWaitEvent(c->stream, dens_ready, 0));
+		FL_TRY(diffuse_all());
+	}
+	for (int fl = 0; fl < c->n_fluids; fl++)
+		FL_TRY(dev_dens_advect(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], dt));
+	if (c->damp != 0.0f) {
+		FL_TRY(dev_damp(c, c->f[FLUID_U], c->damp, dt));
+		FL_TRY(dev_damp(c, c->f[FLUID_V], c->damp, dt));
+	}
+	return FLUID_OK;
+}
+
+int dev_update(fluid_ctx* c, float dt) { return dev_update_hooks(c, dt, nullptr, {}); }
+
+// FluidRenderer::DoBuffer without a window: colourise + velocity lines of ensemble member `sim` into
+// device buffers, then (optionally) to dense host arrays.
+int dev_render(fluid_ctx* c, int sim, const float* color_rgb, float* host_pixels, float* host_lines)
+{
+	if (!color_rgb || !host_pixels) return fail(FLUID_ERR_INVALID, "null pointer");
+	if (sim < 0 || sim >= c->batch) return fail(FLUID_ERR_INVALID, "sim %d out of range [0,%d)", sim, c->batch);
+	if (c->slab_count > 1) return fail(FLUID_ERR_UNSUPPORTED, "render a slab by downloading it; the display buffer is per whole grid");
+	const size_t cells = (size_t) (c->g.N + 2) * (c->g.NY + 2);
+	if (!c->d_pixels) CU_TRY(cudaMalloc(&c->d_pixels, cells * 3 * sizeof(float)));
+	if (host_lines && !c->d_lines) CU_TRY(cudaMalloc(&c->d_lines, cells * 4 * sizeof(float)));
+	const long long off = (long long) sim * c->g.plane;
+	LAUNCH(k_colourise, dim3(cdiv(c->g.N + 2, 32), cdiv(c->g.NY + 2, 8), 1), kBlk2D, 0, c->stream, c->g, c->f[FLUID_DENS] + off,
+	       c->f[FLUID_U] + off, c->f[FLUID_V] + off, color_rgb[0], color_rgb[1], color_rgb[2], c->d_pixels,
+	       host_lines ? c->d_lines : nullptr);
+	CU_TRY(cudaMemcpyAsync(host_pixels, c->d_pixels, cells * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	if (host_lines) CU_TRY(cudaMemcpyAsync(host_lines, c->d_lines, cells * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	return FLUID_OK;
+}

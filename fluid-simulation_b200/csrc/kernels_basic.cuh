@@ -368,17 +368,6 @@ __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __re
 // ensemble member are applied in list order by one thread (as the CPU loop
 // does), members in parallel.
 // ---------------------------------------------------------------------------
-struct SourceDev {
-	int field, i, j, mode;
-	float value;
-};
-
-// index 0 = u, 1 = v, 2 + k = density of fluid k
-struct FieldPtrs {
-	float* cur[2 + 8];
-	float* prev[2 + 8];
-};
-
 __global__ void k_apply_sources(GridDesc g, FieldPtrs f, const SourceDev* __restrict__ src,
 				const int* __restrict__ first, int batch)
 {

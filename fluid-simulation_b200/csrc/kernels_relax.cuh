@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 // the full sweep because nothing else reads them in between.
 // Algorithmic bytes per full sweep (both colours): 12 B per cell.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_rb_half(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
+static __global__ void __launch_bounds__(256) k_rb_half(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
 						  float a, float c, int colour)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(256) k_rb_half(GridDesc g, int b, float* __res
 // next pass's source), 2 = ZeroBorder (last pass, FluidSystem.cpp:742).
 // Algorithmic bytes: 8 B per cell per pass.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_blur_pass(GridDesc g, int b, float* __restrict__ dstb,
+static __global__ void __launch_bounds__(256) k_blur_pass(GridDesc g, int b, float* __restrict__ dstb,
 						    const float* __restrict__ srcb, float a, DivC dv, int out_border)
 {
 	const float c = dv.c;
