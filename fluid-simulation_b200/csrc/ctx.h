@@ -136,10 +136,25 @@ struct fluid_ctx {
 	bool overlap_density = true;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
-	int fast_div_mode = 1; // 0 never, 1 when the solve is large enough to repay the 1.5 ms check, 2 always
-	std::map<uint32_t, DivC> divs;
-	std::map<uint32_t, double> div_work; // cell updates seen per not-yet-verified divisor
+	// 0 never; 1 automatic: a divisor that comes back in a later frame / call, and has enough work behind it to
+	// repay the 1.8 ms proof, is verified in the background (no host wait) and used from the frame after it lands;
+	// 2 always, at once, waiting for the proof (tests, one-off solves)
+	int fast_div_mode = 1;
+	struct DivEntry { DivC dv; unsigned long long last_use; };
+	struct DivSeen { double work; unsigned long long first_epoch; };
+	std::map<uint32_t, DivEntry> divs;   // proven divisors (bounded: least recently used leaves)
+	std::map<uint32_t, DivSeen> div_seen; // not yet proven: cell updates and the epoch of the first sight (bounded)
+	unsigned long long epoch = 0;         // advances with every API call on the context and every frame
 	unsigned int* d_divbins = nullptr;
+	// the one proof that may be in flight: its divisor, pinned result bins, completion event, side stream
+	struct DivPending {
+		bool active = false;
+		uint32_t key = 0;
+		DivC dv{};
+		unsigned int* h_bins = nullptr; // pinned, 256 counters
+		cudaEvent_t done = nullptr;
+		cudaStream_t stream = nullptr;
+	} div_pending;
 	float* rb_scratch = nullptr;
 	std::map<std::pair<const float*, int>, CUtensorMap> tmaps; // (array, window width) -> descriptor
 	// optional per-kernel-class device timing (CUDA event pairs on c->stream)
@@ -178,6 +193,7 @@ struct ProfScope {
 
 static inline int ctx_bind(fluid_ctx* c)
 {
+	c->epoch++;
 	CU_TRY(cudaSetDevice(c->device));
 	return FLUID_OK;
 }

@@ -67,6 +67,12 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->ev_fork2) cudaEventDestroy(c->ev_fork2);
 	if (c->ev_join2) cudaEventDestroy(c->ev_join2);
 	if (c->d_oob) cudaFree(c->d_oob);
+	if (c->div_pending.stream) {
+		cudaStreamSynchronize(c->div_pending.stream);
+		cudaStreamDestroy(c->div_pending.stream);
+		cudaEventDestroy(c->div_pending.done);
+		cudaFreeHost(c->div_pending.h_bins);
+	}
 	if (c->d_divbins) cudaFree(c->d_divbins);
 	for (auto& p : c->d_redo) if (p) cudaFree(p);
 	if (c->side_stream) cudaStreamDestroy(c->side_stream);
@@ -92,6 +98,17 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	return FLUID_OK;
 }
 
+// Row slabs: every kernel computes on all stored rows and stale values creep in from the outer halo edge by
+// one row per stencil application.  Between two halo refreshes the longest chain is a projection: divergence
+// (1 row), gs_iters red-black sweeps (2 rows each), gradient (1 row) -- and Blur's gs_iters + 1 passes.
+static int check_slab_iters(int gs_iters, int halo)
+{
+	if (2 * gs_iters + 2 > halo)
+		return fail(FLUID_ERR_UNSUPPORTED, "row slabs: gs_iters=%d needs a halo of at least %d rows (2 per red-black sweep + 2), slab_halo is %d",
+			    gs_iters, 2 * gs_iters + 2, halo);
+	return FLUID_OK;
+}
+
 extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 {
 	if (!p || !out) return fail(FLUID_ERR_INVALID, "null argument");
@@ -108,11 +125,10 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 		return fail(FLUID_ERR_INVALID, "slab_index=%d / slab_count=%d is not a valid slab", p->slab_index, p->slab_count);
 	if (p->slab_count > 1) {
 		const int halo = p->slab_halo > 0 ? p->slab_halo : 48;
-		if (halo < 44) return fail(FLUID_ERR_INVALID, "slab_halo=%d is too small: a projection consumes 42 halo rows (20 red-black sweeps + 2)", halo);
 		if (p->slab_rows < halo + 1) return fail(FLUID_ERR_INVALID, "slab_rows=%d must exceed the halo depth %d", p->slab_rows, halo);
 		if (p->batch != 1) return fail(FLUID_ERR_UNSUPPORTED, "row slabs and ensembles cannot be combined");
 		if (p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_UNSUPPORTED, "row slabs need FLUID_GS_REDBLACK (the reference order is a pipeline across slabs)");
-		if (p->gs_iters > 20) return fail(FLUID_ERR_UNSUPPORTED, "row slabs support gs_iters <= 20 (the halo is consumed at 2 rows per sweep)");
+		FL_TRY(check_slab_iters(p->gs_iters, halo));
 	}
 
 	int ndev = 0;
@@ -336,6 +352,10 @@ extern "C" int fluid_ctx_set_modes(fluid_ctx* c, int gs_order, int gs_iters, int
 	if (gs_order != FLUID_GS_WAVEFRONT && gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", gs_order);
 	if (gs_iters < 1) return fail(FLUID_ERR_INVALID, "gs_iters=%d must be >= 1", gs_iters);
 	if (advect_mode != FLUID_ADVECT_MIDPOINT && advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", advect_mode);
+	if (c->slab_count > 1) {
+		if (gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_UNSUPPORTED, "row slabs need FLUID_GS_REDBLACK (the reference order is a pipeline across slabs)");
+		FL_TRY(check_slab_iters(gs_iters, c->slab_halo));
+	}
 	c->gs_order = gs_order;
 	c->gs_iters = gs_iters;
 	c->advect_mode = advect_mode;

@@ -48,7 +48,42 @@ static int field_tmap(fluid_ctx* c, const float* base, int rx, const CUtensorMap
 	return FLUID_OK;
 }
 
-// DivC for divisor cc: verified window if known / worth establishing, else range = 0 (callers use div.rn).
+// The mismatch-free exponent window around 1.0 from the 256 per-exponent mismatch counts of k_verify_division.
+static void window_from_bins(const unsigned int* bins, DivC* dv)
+{
+	dv->lo = dv->range = 0;
+	if (bins[127] != 0) return;
+	int elo = 127, ehi = 127;
+	while (elo > 1 && bins[elo - 1] == 0) elo--;
+	while (ehi < 254 && bins[ehi + 1] == 0) ehi++;
+	dv->lo = (uint32_t) elo << 23;
+	dv->range = (uint32_t) (ehi - elo + 1) << 23;
+}
+
+constexpr size_t kMaxProvenDivisors = 64, kMaxSeenDivisors = 256;
+
+static void remember_division(fluid_ctx* c, uint32_t key, const DivC& dv)
+{
+	if (c->divs.size() >= kMaxProvenDivisors) { // the least recently used entry leaves
+		auto oldest = c->divs.begin();
+		for (auto it = c->divs.begin(); it != c->divs.end(); ++it)
+			if (it->second.last_use < oldest->second.last_use) oldest = it;
+		c->divs.erase(oldest);
+	}
+	c->divs[key] = { dv, c->epoch };
+	c->div_seen.erase(key);
+}
+
+// DivC for divisor cc: verified window if known, else range = 0 (callers use the exact division).
+//
+// The proof costs 2^31 trial divisions (1.8 ms of the whole GPU).  The reference's main loop feeds the solver
+// the measured frame time (SystemManager.cpp:49-52), so an integration may see a new c = 1 + 4*dt*coef*N*N every
+// frame: a proof per frame would cost more than it saves, and waiting for it would stall the host in the middle
+// of the enqueue loop.  Automatic mode therefore (a) proves only a divisor that has COME BACK -- seen in an
+// earlier frame or API call -- and has at least 2.5e8 cell updates behind it (about what the proof costs),
+// (b) runs the proof on a side stream and picks the result up when it has landed, without waiting: until
+// then, and for divisors that never recur, solves use the exact division (tile / pass kernels), (c) keeps both
+// tables bounded.  Mode 2 proves at once and waits (tests, one-off solves).
 int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 {
 	out->c = cc;
@@ -58,33 +93,45 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	if (!(cc > 0.0f) || !isfinite(cc) || !isfinite(out->y) || c->fast_div_mode == 0) return FLUID_OK;
 	uint32_t key;
 	memcpy(&key, &cc, sizeof key);
+	auto& pd = c->div_pending;
+	if (pd.active && (c->fast_div_mode == 2 ? cudaEventSynchronize(pd.done) : cudaEventQuery(pd.done)) == cudaSuccess) {
+		window_from_bins(pd.h_bins, &pd.dv); // a background proof has landed
+		remember_division(c, pd.key, pd.dv);
+		pd.active = false;
+	}
 	auto it = c->divs.find(key);
 	if (it != c->divs.end()) {
-		*out = it->second;
+		it->second.last_use = c->epoch;
+		*out = it->second.dv;
 		return FLUID_OK;
 	}
-	// 2^31 trial divisions cost about as much as 2.5e8 cell updates: run the proof once that much work
-	// has been (or is about to be) done with this divisor -- at once for a large grid, after a few
-	// steps for a medium one, never for a divisor that changes every frame on a small grid
-	if (c->fast_div_mode == 1) {
-		double& seen = c->div_work[key];
-		seen += cell_updates;
-		if (seen < 2.5e8) return FLUID_OK;
-	}
 	if (!c->d_divbins) CU_TRY(cudaMalloc(&c->d_divbins, 256 * sizeof(unsigned int)));
-	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), c->stream));
-	LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins);
-	unsigned int bins[256];
-	CU_TRY(cudaMemcpyAsync(bins, c->d_divbins, sizeof bins, cudaMemcpyDeviceToHost, c->stream));
-	CU_TRY(cudaStreamSynchronize(c->stream));
-	if (bins[127] == 0) {
-		int elo = 127, ehi = 127;
-		while (elo > 1 && bins[elo - 1] == 0) elo--;
-		while (ehi < 254 && bins[ehi + 1] == 0) ehi++;
-		out->lo = (uint32_t) elo << 23;
-		out->range = (uint32_t) (ehi - elo + 1) << 23;
+	if (c->fast_div_mode == 2) {
+		CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), c->stream));
+		LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins);
+		unsigned int bins[256];
+		CU_TRY(cudaMemcpyAsync(bins, c->d_divbins, sizeof bins, cudaMemcpyDeviceToHost, c->stream));
+		CU_TRY(cudaStreamSynchronize(c->stream));
+		window_from_bins(bins, out);
+		remember_division(c, key, *out);
+		return FLUID_OK;
 	}
-	c->divs[key] = *out;
+	if (c->div_seen.size() >= kMaxSeenDivisors && !c->div_seen.count(key)) c->div_seen.clear(); // divisors that never came back
+	auto seen = c->div_seen.emplace(key, fluid_ctx::DivSeen{ 0.0, c->epoch }).first;
+	seen->second.work += cell_updates;
+	if (seen->second.first_epoch == c->epoch || seen->second.work < 2.5e8 || pd.active) return FLUID_OK;
+	if (!pd.stream) {
+		CU_TRY(cudaStreamCreateWithFlags(&pd.stream, cudaStreamNonBlocking));
+		CU_TRY(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
+		CU_TRY(cudaMallocHost(&pd.h_bins, 256 * sizeof(unsigned int)));
+	}
+	pd.key = key;
+	pd.dv = *out;
+	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), pd.stream));
+	LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, pd.stream, *out, c->d_divbins);
+	CU_TRY(cudaMemcpyAsync(pd.h_bins, c->d_divbins, 256 * sizeof(unsigned int), cudaMemcpyDeviceToHost, pd.stream));
+	CU_TRY(cudaEventRecord(pd.done, pd.stream));
+	pd.active = true;
 	return FLUID_OK;
 }
 
@@ -360,8 +407,12 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 		n2 = rest / 2;
 		n1 = rest % 2;
 		if (field < 0 && (p5 + p4 + n4 + n2 + n1) % 2) {
+			// one pass more: split a 4-sweep pass into 2 + 2, else a 2-sweep pass into 1 + 1; with neither (one
+			// single sweep left over after the power-of-two passes) a power-of-two pass gives way to 2 + 2
 			if (n4 > 0) { n4 -= 1; n2 += 2; }
-			else { n2 -= 1; n1 += 2; } // limit >= 2, so n2 >= 1 here
+			else if (n2 > 0) { n2 -= 1; n1 += 2; }
+			else if (p4 > 0) { p4 -= 1; n2 += 2; }
+			else return fail(FLUID_ERR_CUDA, "internal: cannot make the number of passes even");
 		}
 	} else {
 		n2 = (field < 0) ? (limit + p5 + p4) % 2 : 0; // an odd count needs one 2-sweep pass to make the number of passes even

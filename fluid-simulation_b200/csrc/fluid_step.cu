@@ -230,6 +230,7 @@ int sync_sources(fluid_ctx* c)
 // slip its bus transfers in; everybody else calls dev_update.
 int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::function<int()>& after_velocity)
 {
+	c->epoch++; // a frame (the divisor bookkeeping of division_for counts in frames and API calls)
 	{
 		ProfScope ps(c, FLUID_PROF_OTHER);
 		CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));

@@ -357,7 +357,9 @@ int fluid_ctx_time_kernel(fluid_ctx *ctx, int which, int reps, float *ms);
  *                                                                            *
  * - The first call on each device looks up the array's device address and    *
  *   raises the kernels' shared-memory limit; make that first call before any *
- *   stream capture begins.                                                   *
+ *   stream capture begins, and from ONE host thread: the per-device set-up   *
+ *   record is written without a lock, so two first calls racing on the same  *
+ *   device from different threads are not supported.                         *
  * - All calls share the one array, and it keeps the previous call's data     *
  *   (this function clears the part it is about to use).  Two calls whose GPU *
  *   work can overlap -- different streams, different host threads -- race on *

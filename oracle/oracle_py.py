@@ -93,6 +93,11 @@ class Oracle:
         L.oracle_render.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, _f32p, _f32p]
         L.oracle_total_inner_mass.argtypes = [c_int, _f32p]
         L.oracle_total_inner_mass.restype = c_float
+        L.oracle_set_threads.argtypes = [c_int]
+
+    def set_threads(self, n):
+        """Threads for the order-independent loops (bit-identical results; 1 = the serial restatement)."""
+        self.L.oracle_set_threads(n)
 
     def add_source(self, N, x, s, dt):
         self.L.oracle_add_source(N, x, s, dt)

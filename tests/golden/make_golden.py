@@ -40,6 +40,7 @@ def frames():
         (37, 25, 1e-3, 1e-4, 0.0, 0.0, "stam"),
         (256, 5, 1e-4, 1e-4, 0.0, 0.0, "stam"),
         (1024, 1, 1e-4, 1e-4, 0.0, 0.0, "stam"),     # BASELINE config 2, first step
+        (1024, 100, 1e-4, 1e-4, 0.0, 0.0, "stam"),   # BASELINE config 2 as written: after 100 steps (~4.5 min of one core)
     ]
     for N, steps, visc, diff, vort, damp, srcname in cases:
         sim = R.sim(N, visc, diff, vort, 20, damp)

@@ -7,6 +7,8 @@ Bar: BIT-EXACT (the float bit patterns are compared as integers) for
 and a relative-L2 tolerance of 1e-4 (north_star) for red-black vs the reference
 run to convergence.  Nothing here reads /root/reference.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -228,7 +230,7 @@ def _sources(name, N):
 def test_golden_frames_wavefront_bitwise(fl, golden_hashes):
     """Whole frames (FluidSystem::Update) on the resident context vs the hashes of
     the unmodified reference: N=64 x 100 and x 1000 steps (BASELINE config 1),
-    vorticity+damp, the Blower forcing, and the first step of config 2 (N=1024)."""
+    vorticity+damp, the Blower forcing, and config 2 (N=1024) after its first and after its 100th step."""
     import oracle_py as op
     for fr in golden_hashes:
         fs = fl.FluidSystem().Setup(fr["N"], fr["visc"], fr["diff"], fr["vorticity"], fr["damp"])
@@ -283,6 +285,39 @@ def test_redblack_tolerance_vs_reference_order_converged(fl, oracle):
             rel = np.linalg.norm(got - want) / np.linalg.norm(want)
             assert rel <= 1e-4, (name, steps, rel)
         fs.close()
+
+
+@pytest.mark.parametrize("N,iters", [(64, 4000), (128, 16000)])
+def test_redblack_tolerance_after_100_steps(fl, oracle, N, iters):
+    """the red-black criterion at N=64 AND 128, after 1 AND 100 steps.  A hundred
+    converged frames cost the CPU minutes (the reference order is a dependency chain), so the reference
+    side is the GPU's reference-order path -- first pinned, at this very sweep count, to the CPU
+    restatement over one frame, bit for bit -- and the red-black run is compared with it after frames
+    1 and 100.  The sweep count grows with N^2 (N=128: rho = 1 - (pi/129)^2, 16000 sweeps)."""
+    import oracle_py as op
+    src = op.stam_sources(N)
+    f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+    oracle.update(N, f, src, 1e-4, 1e-4, 0.1, 1, iters=iters, order=op.GS_LEX)
+    ref = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_WAVEFRONT, gs_iters=iters)
+    rb = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, gs_iters=iters)
+    for fs in (ref, rb):
+        fs.SetSources(src)
+    worst = 0.0
+    for frames_so_far, advance in ((1, 1), (100, 99)):
+        ref.Update(0.1, advance)
+        rb.Update(0.1, advance)
+        if frames_so_far == 1:
+            for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+                assert_bits(ref.download(fid), f[name], "reference order at %d sweeps vs the CPU: %s" % (iters, name))
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            want = ref.download(fid).astype(np.float64)
+            got = rb.download(fid)
+            rel = np.linalg.norm(got - want) / np.linalg.norm(want)
+            worst = max(worst, rel)
+            assert rel <= 1e-4, (N, name, frames_so_far, rel)
+    print("red-black vs reference order, N=%d, %d sweeps: worst rel-L2 over 1 and 100 frames %.3g" % (N, iters, worst))
+    ref.close()
+    rb.close()
 
 
 def test_ensemble_members_are_independent(fl, oracle):
@@ -373,18 +408,52 @@ def test_full_size_primitives_n8192(fl, oracle):
     assert_bits(z, z2, "set_bnd idempotent")
 
 
-def test_full_step_n2048_bitwise(fl, oracle):
+@pytest.mark.parametrize("order", [0, 1])
+def test_full_step_n2048_bitwise(fl, oracle, order):
+    """One whole frame at N=2048 in both relaxation orders (red-black: the streaming kernels, both lanes)."""
     import oracle_py as op
     N = 2048
     src = op.stam_sources(N)
     f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
-    oracle.update(N, f, src, 1e-4, 1e-4, 0.1, 1)
-    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4)
+    oracle.set_threads(os.cpu_count() if order == 1 else 1)
+    try:
+        oracle.update(N, f, src, 1e-4, 1e-4, 0.1, 1, order=order)
+    finally:
+        oracle.set_threads(1)
+    fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=order)
+    fs.SetFastDivision(2)
     fs.SetSources(src)
     fs.Update(0.1, 1)
     assert_bits(fs.GetVelX(), f["u"], "u")
+    assert_bits(fs.GetVelY(), f["v"], "v")
     assert_bits(fs.GetDensities(), f["d"], "dens")
     fs.close()
+
+
+def test_benchmarked_configuration_n8192_redblack_bitwise(fl, oracle):
+    """BASELINE config 3 exactly as bench.py times it -- N=8192, red-black, 20 sweeps, dt=0.1,
+    visc=diff=1e-4, source S1, density diffusion and the v-lane overlapped -- against the CPU red-black
+    statement, bit for bit, over two whole frames (the second starts from non-trivial fields and has
+    the proven division in place from the start: 4-sweep streaming passes, the power-of-two pressure
+    passes with the zero guess, redo launches, array trades).  The oracle's independent loops run on
+    all host cores (bit-identical to one core, tests/test_oracle.py)."""
+    import oracle_py as op
+    N, steps = 8192, 2
+    src = op.stam_sources(N)
+    f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+    oracle.set_threads(os.cpu_count())
+    try:
+        oracle.update(N, f, src, 1e-4, 1e-4, 0.1, steps, order=op.GS_RB)
+    finally:
+        oracle.set_threads(1)
+    for mode in (2, 1):  # proof at once / the automatic background proof (first frame on the exact kernels)
+        fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, gs_iters=20)
+        fs.SetFastDivision(mode)
+        fs.SetSources(src)
+        fs.Update(0.1, steps)
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            assert_bits(fs.download(fid), f[name], "N=8192 red-black frame, division mode %d: %s" % (mode, name))
+        fs.close()
 
 
 def test_mass_is_reported_like_the_reference(fl, golden_hashes, oracle):

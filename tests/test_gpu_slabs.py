@@ -93,7 +93,17 @@ def test_slab_argument_checks(fl):
     assert "exchange" in str(e.value)
     sd, rd, su, ru, n = fs.HaloRegions(fl.U)
     assert su is None and ru is None and sd and rd and n == 49 * (((128 + 2 + 31 + 31) // 32) * 32)
+    # the halo bounds the sweep count (2 rows per red-black sweep + 2), at creation and afterwards alike
+    with pytest.raises(fl.FluidError) as e:
+        fs.SetModes(fl.GS_REDBLACK, 30)
+    assert "halo" in str(e.value)
+    with pytest.raises(fl.FluidError):
+        fs.SetModes(fl.GS_WAVEFRONT, 20)
+    fs.SetModes(fl.GS_REDBLACK, 23)  # 2*23 + 2 = 48 rows: just fits
     fs.close()
+    with pytest.raises(fl.FluidError):
+        fl.FluidSystem().Setup(128, gs_order=fl.GS_REDBLACK, gs_iters=30, slab=(0, 2, 64))  # 62 rows needed, 48 there
+    fl.FluidSystem().Setup(128, gs_order=fl.GS_REDBLACK, gs_iters=30, slab=(0, 2, 64), slab_halo=62).close()
 
 
 @pytest.mark.parametrize("order,N,rows,count", [(0, 150, 60, 3), (1, 150, 60, 3), (1, 2048, 512, 2)])

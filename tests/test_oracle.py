@@ -96,6 +96,26 @@ def test_oracle_matches_live_reference(oracle, ref):
     sim.close()
 
 
+def test_threaded_oracle_is_bit_identical_to_the_serial_one(oracle):
+    """The oracle's order-independent loops (red-black colours, Blur passes, advect, divergence, gradient,
+    add_source) may run on several threads so that whole frames at the benchmark size can be checked in
+    seconds; every cell is the same expression of the same inputs, so nothing may change."""
+    import oracle_py as op
+    for N, steps in ((37, 6), (200, 3), (256, 2)):
+        src = op.stam_sources(N) + [(0, 3, N - 2, 0, -4.0), (2, N // 3, 5, 1, 0.7)]
+        runs = []
+        for threads in (1, 7):
+            oracle.set_threads(threads)
+            try:
+                f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+                oracle.update(N, f, src, 1e-4, 1e-4, 0.1, steps, order=op.GS_RB)
+            finally:
+                oracle.set_threads(1)
+            runs.append(f)
+        for k in runs[0]:
+            assert runs[0][k].tobytes() == runs[1][k].tobytes(), (N, k)
+
+
 def test_set_bnd_sign_table(oracle):
     """SetBorder sign table and corners (FluidSystem.cpp:465-500)."""
     N = 5
