@@ -79,6 +79,8 @@ struct fluid_ctx {
 	bool fl_set[FLUID_MAX_FLUIDS] = {}; // fluid k has its own coefficients (else it follows fluid 0)
 	float* vscr[4] = {};      // vorticity scratch, allocated on first use
 	SourceDev* d_src = nullptr;
+	float* d_src_saved = nullptr; // one float per entry (k_apply_sources / k_add_source_cells)
+	bool sparse_sources = true;  // Update(): add_source over the listed cells only, when the kernels that follow allow it
 	int* d_first = nullptr;
 	int n_src = 0;
 	std::vector<std::vector<SourceDev>> src; // per ensemble member
@@ -135,6 +137,7 @@ struct fluid_ctx {
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_density = true;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
+	int advect_kernel = 0; // 0 automatic, 1 one thread per cell (gathers), 2 row window (kernels_advect.cuh)
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
 	// 0 never; 1 automatic: a divisor that comes back in a later frame / call, and has enough work behind it to
 	// repay the 1.8 ms proof, is verified in the background (no host wait) and used from the frame after it lands;
@@ -227,7 +230,7 @@ int dev_zero_bnd(fluid_ctx* c, float* x);
 int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, const float* v, float dt);
 int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const float* v0, float dt);
 int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div);
-int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt);
+int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt, bool sources_added = false);
 int dev_dens_step(fluid_ctx* c, float* x, float* x0, const float* u, const float* v, float diff, float dt);
 int dev_vort_confinement(fluid_ctx* c, float* u, float* v, float vorticity);
 int dev_damp(fluid_ctx* c, float* vel, float amount, float dt);

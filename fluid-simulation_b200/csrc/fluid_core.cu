@@ -81,6 +81,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->d_pixels) cudaFree(c->d_pixels);
 	if (c->d_lines) cudaFree(c->d_lines);
 	if (c->d_src) cudaFree(c->d_src);
+	if (c->d_src_saved) cudaFree(c->d_src_saved);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);
@@ -327,7 +328,7 @@ extern "C" int fluid_ctx_set_sources(fluid_ctx* c, int sim, int n, const fluid_s
 		if (slot < 0) return fail(FLUID_ERR_INVALID, "source %d: field %d is not U, V or a density field of this context", k, s.field);
 		if (s.i < 0 || s.i > c->g.N + 1 || s.j < 0 || s.j > c->g.NYG + 1) return fail(FLUID_ERR_INVALID, "source %d: cell (%d,%d) outside the grid", k, s.i, s.j);
 		if (s.mode < FLUID_SRC_PREV_SET || s.mode > FLUID_SRC_CURR_SET) return fail(FLUID_ERR_INVALID, "source %d: unknown mode %d", k, s.mode);
-		v.push_back({ slot, s.i, s.j, s.mode, s.value });
+		v.push_back({ slot, s.i, s.j, s.mode, s.value, 0 });
 	}
 	auto same = [](const std::vector<SourceDev>& a, const std::vector<SourceDev>& b) {
 		return a.size() == b.size() && (a.empty() || memcmp(a.data(), b.data(), a.size() * sizeof(SourceDev)) == 0);
@@ -380,6 +381,21 @@ extern "C" int fluid_ctx_set_stream_kernel(fluid_ctx* c, int on)
 {
 	CHECK_CTX(c);
 	c->rb_stream = on != 0;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_advect_kernel(fluid_ctx* c, int which)
+{
+	CHECK_CTX(c);
+	if (which < 0 || which > 2) return fail(FLUID_ERR_INVALID, "advect kernel %d must be 0 (automatic), 1 (gather per cell) or 2 (row window)", which);
+	c->advect_kernel = which;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_sparse_sources(fluid_ctx* c, int on)
+{
+	CHECK_CTX(c);
+	c->sparse_sources = on != 0;
 	return FLUID_OK;
 }
 

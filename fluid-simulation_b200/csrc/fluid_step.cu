@@ -2,6 +2,9 @@
 // VelStep1 (FluidSystem.cpp:354-376), DensStep1 (:289-299), Update (:101-128), the headless render.
 #include "ctx.h"
 #include "kernels_basic.cuh"
+#include "kernels_advect.cuh"
+
+#include <tuple>
 
 int dev_add_source(fluid_ctx* c, float* x, const float* s, float dt)
 {
@@ -31,11 +34,48 @@ int dev_zero_bnd(fluid_ctx* c, float* x)
 	LAUNCH(k_zero_bnd, dim3(cdiv(n, 256), 1, c->batch), 256, 0, c->stream, c->g, x);
 	return FLUID_OK;
 }
+// Which advect kernel: the row-window kernel (kernels_advect.cuh) once the grid is large enough to give every
+// SM several warp tasks, the one-thread-per-cell gather kernel below that.  Bit-identical either way.
+static bool advect_rows_geometry(const fluid_ctx* c, AdvectTasks* tk)
+{
+	if (c->advect_kernel == 1) return false;
+	if (c->advect_kernel == 0 && (long long) c->g.N * c->g.NY * c->batch < (1LL << 20)) return false;
+	tk->nstrips = cdiv(c->g.N, 128);
+	const long long slots = (long long) c->num_sms * 16;
+	int rows = 32;
+	while (rows > 8 && (long long) tk->nstrips * cdiv(c->g.NY, rows) * c->batch < 2 * slots) rows /= 2;
+	tk->chunk_rows = rows;
+	tk->nchunks = cdiv(c->g.NY, rows);
+	return true;
+}
+
+template <bool VEL>
+static void launch_advect_rows(fluid_ctx* c, const AdvectTasks& tk, int b, float* oa, float* ob, const float* d0, const float* u, const float* v,
+			       float dtN)
+{
+	const dim3 grid(cdiv((long long) tk.nstrips * tk.nchunks, kAdvectWarps), c->batch);
+	const int nt = 32 * kAdvectWarps;
+	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	const int lo = c->own_lo, hi = c->own_lo + c->slab_rows - 1;
+	if (c->slab_count > 1) {
+		if (euler) LAUNCH((k_advect_rows<true, 1, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, lo, hi);
+		else LAUNCH((k_advect_rows<true, 0, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, lo, hi);
+	} else {
+		if (euler) LAUNCH((k_advect_rows<false, 1, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, 1, 0);
+		else LAUNCH((k_advect_rows<false, 0, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, 1, 0);
+	}
+}
+
 int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, const float* v, float dt)
 {
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
 	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	AdvectTasks tk;
+	if (advect_rows_geometry(c, &tk)) {
+		launch_advect_rows<false>(c, tk, b, d, nullptr, d0, u, v, dtN);
+		return FLUID_OK;
+	}
 	if (c->slab_count > 1) {
 		if (euler) LAUNCH((k_advect<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
 		else LAUNCH((k_advect<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, b, d, d0, u, v, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
@@ -51,6 +91,11 @@ int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
 	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	AdvectTasks tk;
+	if (advect_rows_geometry(c, &tk)) {
+		launch_advect_rows<true>(c, tk, 0, u, v, nullptr, u0, v0, dtN);
+		return FLUID_OK;
+	}
 	if (c->slab_count > 1) {
 		if (euler) LAUNCH((k_advect_velocity<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
 		else LAUNCH((k_advect_velocity<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
@@ -105,10 +150,10 @@ static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> array
 // VelStep1 (FluidSystem.cpp:354-376).  The four pointers are locals: the
 // reference's two Swap() calls per FlipFlopArr become local pointer swaps, so
 // the result lands in the arrays passed as u and v.
-int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt)
+int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt, bool sources_added)
 {
 	// slabs: u, v (and the source arrays, which every slab fills itself) are valid over the whole halo on entry
-	FL_TRY(dev_add_source2(c, u, u0, v, v0, dt));
+	if (!sources_added) FL_TRY(dev_add_source2(c, u, u0, v, v0, dt)); // (Update() may already have added its sparse forcing)
 	std::swap(u, u0);
 	const float a = diffusion_a(c, visc, dt);
 	std::swap(v, v0);
@@ -148,9 +193,9 @@ int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float v
 
 // DensStep1 (FluidSystem.cpp:289-299), one fluid.
 // First half (sources and diffusion: no velocity involved; the blurred field ends in x0) and second half (advection).
-static int dev_dens_diffuse(fluid_ctx* c, float* x, float* x0, float diff, float dt)
+static int dev_dens_diffuse(fluid_ctx* c, float* x, float* x0, float diff, float dt, bool sources_added = false)
 {
-	FL_TRY(dev_add_source(c, x, x0, dt));
+	if (!sources_added) FL_TRY(dev_add_source(c, x, x0, dt));
 	const float a = diffusion_a(c, diff, dt);
 	return dev_blur(c, 0, x0, x, a, 1 + 4 * a); // after the reference's Swap: x0 is relaxed, x holds the sum
 }
@@ -209,12 +254,23 @@ int sync_sources(fluid_ctx* c)
 		flat.insert(flat.end(), c->src[s].begin(), c->src[s].end());
 	}
 	first[c->batch] = (int) flat.size();
+	// PREV_SET entries: a later entry on the same cell overwrites an earlier one; the survivor is marked
+	for (int s = 0; s < c->batch; s++) {
+		std::map<std::tuple<int, int, int>, int> seen;
+		for (int k = first[s + 1] - 1; k >= first[s]; k--) {
+			SourceDev& e = flat[k];
+			e.last = (e.mode == 0 && seen.emplace(std::make_tuple(e.field, e.i, e.j), k).second) ? 1 : 0;
+		}
+	}
 	if (c->d_src) CU_TRY(cudaFree(c->d_src));
 	c->d_src = nullptr;
+	if (c->d_src_saved) CU_TRY(cudaFree(c->d_src_saved));
+	c->d_src_saved = nullptr;
 	if (!c->d_first) CU_TRY(cudaMalloc(&c->d_first, sizeof(int) * (c->batch + 1)));
 	if (!flat.empty()) {
 		CU_TRY(cudaMalloc(&c->d_src, sizeof(SourceDev) * flat.size()));
 		CU_TRY(cudaMemcpy(c->d_src, flat.data(), sizeof(SourceDev) * flat.size(), cudaMemcpyHostToDevice));
+		CU_TRY(cudaMalloc(&c->d_src_saved, sizeof(float) * flat.size()));
 	}
 	CU_TRY(cudaMemcpy(c->d_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice));
 	c->n_src = (int) flat.size();
@@ -231,28 +287,48 @@ int sync_sources(fluid_ctx* c)
 int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::function<int()>& after_velocity)
 {
 	c->epoch++; // a frame (the divisor bookkeeping of division_for counts in frames and API calls)
+	// The source arrays of a frame are zero except for the listed PREV_SET cells, so AddArrDt over them is known
+	// in advance (k_canon_zero, kernels_basic.cuh): the three dense x += dt*s passes and the zero fill of the
+	// densities' source arrays (which nothing else reads: Blur overwrites them) are left out.  Small grids keep
+	// the plain sequence (they are bound by launches, not bytes); so does a dt whose product with zero is NaN.
+	const bool sparse = c->sparse_sources && !use_small_kernels(c) && isfinite(dt);
+	FieldPtrs fp = {};
+	fp.cur[0] = c->f[FLUID_U];
+	fp.prev[0] = c->f[FLUID_U_PREV];
+	fp.cur[1] = c->f[FLUID_V];
+	fp.prev[1] = c->f[FLUID_V_PREV];
+	for (int fl = 0; fl < c->n_fluids; fl++) {
+		fp.cur[2 + fl] = c->f[FLUID_DENS_OF(fl)];
+		fp.prev[2 + fl] = c->f[FLUID_DENS_PREV_OF(fl)];
+	}
 	{
 		ProfScope ps(c, FLUID_PROF_OTHER);
-		CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream));
+		CU_TRY(cudaMemsetAsync(c->f[FLUID_U_PREV], 0, c->field_bytes, c->stream)); // the diffusion solves start from these
 		CU_TRY(cudaMemsetAsync(c->f[FLUID_V_PREV], 0, c->field_bytes, c->stream));
-		for (int fl = 0; fl < c->n_fluids; fl++) CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV_OF(fl)], 0, c->field_bytes, c->stream));
-		if (c->n_src > 0) {
-			FieldPtrs fp = {};
-			fp.cur[0] = c->f[FLUID_U];
-			fp.prev[0] = c->f[FLUID_U_PREV];
-			fp.cur[1] = c->f[FLUID_V];
-			fp.prev[1] = c->f[FLUID_V_PREV];
-			for (int fl = 0; fl < c->n_fluids; fl++) {
-				fp.cur[2 + fl] = c->f[FLUID_DENS_OF(fl)];
-				fp.prev[2 + fl] = c->f[FLUID_DENS_PREV_OF(fl)];
-			}
-			LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
-		}
+		if (!sparse)
+			for (int fl = 0; fl < c->n_fluids; fl++) CU_TRY(cudaMemsetAsync(c->f[FLUID_DENS_PREV_OF(fl)], 0, c->field_bytes, c->stream));
+		if (c->n_src > 0) LAUNCH(k_apply_sources, cdiv(c->batch, 64), 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch);
 	}
+	// x += dt*s for one group of fields, sparse form, on the current stream
+	auto add_sparse = [&](float* x, float* y, int slot_lo, int slot_hi) -> int {
+		ProfScope ps(c, FLUID_PROF_ADD_SOURCE);
+		const dim3 grid(cdiv(c->batch, 64));
+		if (c->n_src > 0)
+			LAUNCH(k_add_source_cells, grid, 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch, c->d_src_saved, dt, slot_lo, slot_hi, 0);
+		if (dt >= 0.0f) {
+			LAUNCH(k_canon_zero, flat_blocks(c), 256, 0, c->stream, (float4*) x, (float4*) y, n4_of(c));
+			if (c->n_src > 0)
+				LAUNCH(k_add_source_cells, grid, 64, 0, c->stream, c->g, fp, c->d_src, c->d_first, c->batch, c->d_src_saved, dt, slot_lo, slot_hi, 1);
+		}
+		return FLUID_OK;
+	};
 	const bool concurrent = c->overlap_density; // slabs too: the halo exchanges of the densities come after the join
 	auto diffuse_all = [&]() -> int {
 		for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
-			FL_TRY(dev_dens_diffuse(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], fluid_diff(c, fl), dt));
+		{
+			if (sparse) FL_TRY(add_sparse(c->f[FLUID_DENS_OF(fl)], nullptr, 2 + fl, 3 + fl));
+			FL_TRY(dev_dens_diffuse(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], fluid_diff(c, fl), dt, sparse));
+		}
 		return FLUID_OK;
 	};
 	if (concurrent) {
@@ -275,7 +351,8 @@ int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::
 		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
 		FL_TRY(halo_exchange(c, { c->f[FLUID_U], c->f[FLUID_V] })); // three stencil phases consumed 3 halo rows
 	}
-	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt));
+	if (sparse) FL_TRY(add_sparse(c->f[FLUID_U], c->f[FLUID_V], 0, 2));
+	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt, sparse));
 	if (after_velocity) FL_TRY(after_velocity());
 	if (concurrent) {
 		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));

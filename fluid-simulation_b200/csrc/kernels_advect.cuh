@@ -1,0 +1,283 @@
+// Advect1 (FluidSystem.cpp:850-862) for large grids: a register-resident row window instead of gathers.
+//
+// The one-thread-per-cell kernels (kernels_basic.cuh: k_advect, k_advect_velocity) spend 170-190
+// instructions and 12-16 scalar gathers per cell; ncu showed them bound by instruction issue with the
+// load/store unit close behind (one LDG costs the SM 1.8 cycles whatever it fetches), at 36-40 % of HBM
+// bandwidth.  Half of those instructions are addressing, bounds tests and conversions, not the
+// reference's arithmetic.
+//
+// Here a WARP owns a strip of 128 storage columns (4 adjacent cells per lane, one aligned float4) and
+// walks up through the rows of its chunk.  For every field it samples it keeps rows j-1, j, j+1 (and the
+// prefetched row j+2) in registers: the lane's float4 plus the one value left and right of it, fetched
+// from the neighbouring lanes by shuffle.  A backtrace that moves less than one cell -- |dt*N*v| < 1,
+// the normal case of a stable-fluids step away from a jet -- lands with its 2x2 interpolation stencil
+// inside that window, at an integer offset (dx, dy) in {-1,0} x {-1,0} from the cell.  When ALL cells
+// of the warp's row agree on (dx, dy) (one vote), the four stencil values of every cell are registers
+// picked at compile time: no addresses, no loads, only the reference's arithmetic.  The mid-point
+// sample (MidpointBackward, FluidSystem.h:185-206) and the final sample vote independently.  A row
+// whose cells disagree, or that reaches further, takes the gather path for that sample -- same
+// expressions, so results are bit-identical whichever path runs -- and reach stays unbounded.
+//
+// Per row of 128 cells: one LDG.128 + two shuffles per sampled field, two STG.128.
+#pragma once
+#include "grid.cuh"
+#include "kernels_basic.cuh"
+
+namespace fluid {
+
+constexpr int kAdvectWarps = 4; // warps (tasks) per CTA
+
+// One row of one field as the window keeps it: w[0] = storage column 4q-1, w[1..4] = the lane's own
+// float4 (columns 4q .. 4q+3), w[5] = column 4q+4.
+struct RowWin {
+	float w[6];
+};
+
+// pf points at storage column 4q (clamped into the row) of row 0 of the field; col_l / col_r are the
+// offsets of the values only lane 0 / lane 31 must fetch themselves (their neighbours are other warps').
+__device__ __forceinline__ RowWin advect_load_row(const float* __restrict__ pf, int y, int pitch, int lane, int off_l, int off_r)
+{
+	RowWin r;
+	const float* p = pf + y * pitch;
+	const float4 c = __ldg(reinterpret_cast<const float4*>(p));
+	r.w[1] = c.x;
+	r.w[2] = c.y;
+	r.w[3] = c.z;
+	r.w[4] = c.w;
+	r.w[0] = __shfl_up_sync(0xffffffffu, c.w, 1);
+	r.w[5] = __shfl_down_sync(0xffffffffu, c.x, 1);
+	if (lane == 0) r.w[0] = __ldg(p + off_l);
+	if (lane == 31) r.w[5] = __ldg(p + off_r);
+	return r;
+}
+
+// BilinearCoeffs::calc (FluidCode.h:91-112) for one sample: clamped position -> cell (i0, local row jl)
+// and weights.  Same arithmetic as bilin_calc (kernels_basic.cuh), kept apart so that the window path
+// never forms an address.
+struct BilinW {
+	int i0, jl;
+	float s0, s1, t0, t1;
+};
+
+template <bool SLAB>
+__device__ __forceinline__ BilinW advect_calc(const GridDesc& g, float px, float py, int* oob)
+{
+	BilinW r;
+	px = fminf(fmaxf(px, 0.5f), g.N + 0.5f);
+	py = fminf(fmaxf(py, 0.5f), g.NYG + 0.5f);
+	r.i0 = (int) px;
+	const int j0 = (int) py;
+	r.s1 = px - r.i0;
+	r.s0 = 1 - r.s1;
+	r.t1 = py - j0;
+	r.t0 = 1 - r.t1;
+	r.jl = j0;
+	if (SLAB) {
+		r.jl = j0 - g.j0;
+		if (r.jl < 0 || r.jl > g.NY) {
+			if (oob) *oob = 1;
+			r.jl = min(max(r.jl, 0), g.NY);
+		}
+	}
+	return r;
+}
+
+// BilinearCoeffs::Eval (FluidCode.h:88) from memory: the general path.
+__device__ __forceinline__ float advect_gather(const BilinW& c, const float* __restrict__ f, int pitch)
+{
+	const float* r0 = f + (c.jl * pitch + XO + c.i0);
+	const float* r1 = r0 + pitch;
+	const float d00 = __ldg(r0), d10 = __ldg(r0 + 1);
+	const float d01 = __ldg(r1), d11 = __ldg(r1 + 1);
+	return c.s0 * (c.t0 * d00 + c.t1 * d01) + c.s1 * (c.t0 * d10 + c.t1 * d11);
+}
+
+// ... and from the window: cell k of the lane, stencil offset (DX, DY) in {-1,0}^2, all compile time.
+template <int DX, int DY>
+__device__ __forceinline__ float advect_window(const BilinW& c, const RowWin (&win)[3], int k)
+{
+	const float d00 = win[DY + 1].w[k + DX + 1], d10 = win[DY + 1].w[k + DX + 2];
+	const float d01 = win[DY + 2].w[k + DX + 1], d11 = win[DY + 2].w[k + DX + 2];
+	return c.s0 * (c.t0 * d00 + c.t1 * d01) + c.s1 * (c.t0 * d10 + c.t1 * d11);
+}
+
+// The warp's vote: code (dx+1) | (dy+1) << 1 when every valid cell of every lane has the same stencil
+// offset inside the window, else -1.
+__device__ __forceinline__ int advect_vote(const BilinW (&c)[4], int i_first, int j, uint32_t valid)
+{
+	int code = -2; // this lane has no opinion yet
+	bool ok = true;
+#pragma unroll
+	for (int k = 0; k < 4; k++) {
+		const int dx = c[k].i0 - (i_first + k), dy = c[k].jl - j;
+		const int ck = (dx + 1) | ((dy + 1) << 1);
+		const bool in = ((unsigned) (dx + 1) <= 1u) && ((unsigned) (dy + 1) <= 1u);
+		if ((valid >> k) & 1) {
+			ok = ok && in && (code == -2 || code == ck);
+			code = ck;
+		}
+	}
+	const int c0 = __shfl_sync(0xffffffffu, code, 0); // lane 0 always holds the strip's first cell, which exists
+	return __all_sync(0xffffffffu, ok && (code == -2 || code == c0)) ? c0 : -1;
+}
+
+template <int NF>
+__device__ __forceinline__ void advect_sample(int code, const BilinW (&c)[4], const RowWin (&w0)[3], const RowWin (&w1)[3],
+					       const float* __restrict__ f0, const float* __restrict__ f1, int pitch, uint32_t valid,
+					       float (&o0)[4], float (&o1)[4])
+{
+	switch (code) {
+#define ADVECT_CASE(CODE, DX, DY)                                                                                 \
+	case CODE:                                                                                                \
+		_Pragma("unroll") for (int k = 0; k < 4; k++) {                                                   \
+			o0[k] = advect_window<DX, DY>(c[k], w0, k);                                               \
+			if (NF > 1) o1[k] = advect_window<DX, DY>(c[k], w1, k);                                   \
+		}                                                                                                 \
+		break;
+		ADVECT_CASE(0, -1, -1)
+		ADVECT_CASE(1, 0, -1)
+		ADVECT_CASE(2, -1, 0)
+		ADVECT_CASE(3, 0, 0)
+#undef ADVECT_CASE
+	default:
+#pragma unroll
+		for (int k = 0; k < 4; k++) {
+			if (!((valid >> k) & 1)) { // cells past the row's end: nothing to fetch, nothing is stored
+				o0[k] = 0.0f;
+				if (NF > 1) o1[k] = 0.0f;
+				continue;
+			}
+			o0[k] = advect_gather(c[k], f0, pitch);
+			if (NF > 1) o1[k] = advect_gather(c[k], f1, pitch);
+		}
+	}
+}
+
+struct AdvectTasks {
+	int nstrips, nchunks, chunk_rows;
+};
+
+// VEL: VelStep1's self-advection (FluidSystem.cpp:372-373), Advect1(1,u,u0,u0,v0) and Advect1(2,v,v0,u0,v0) in one
+// pass (outa = u, outb = v, b ignored).  Otherwise Advect1(b, outa, d0, u0, v0) for one scalar field.
+// MODE 0 = MidpointBackward, 1 = EulerBack (FluidSystem.h:185-219).
+template <bool SLAB, int MODE, bool VEL>
+__global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, AdvectTasks tk, int b, float* __restrict__ outab,
+									   float* __restrict__ outbb, const float* __restrict__ d0b,
+									   const float* __restrict__ u0b, const float* __restrict__ v0b,
+									   float dtN, int* oob_flag, int own_lo, int own_hi)
+{
+	const int task = blockIdx.x * kAdvectWarps + (threadIdx.x >> 5);
+	if (task >= tk.nstrips * tk.nchunks) return;
+	const int lane = threadIdx.x & 31;
+	const int chunk = task / tk.nstrips, strip = task - chunk * tk.nstrips;
+	const long long off = (long long) blockIdx.y * g.plane;
+	const float* u0 = u0b + off;
+	const float* v0 = v0b + off;
+	const float* d0 = VEL ? nullptr : d0b + off;
+	float* outa = outab + off;
+	float* outb = VEL ? outbb + off : nullptr;
+
+	const int pitch = g.pitch;
+	const int col = 32 + 128 * strip + 4 * lane; // storage column of the lane's first cell
+	const int colc = min(col, pitch - 4);         // lanes past the row's end read its last group (and store nothing)
+	const int i_first = col - XO;
+	uint32_t valid = 0;
+#pragma unroll
+	for (int k = 0; k < 4; k++)
+		if (i_first + k <= g.N) valid |= 1u << k;
+	const int off_l = -1, off_r = min(4, pitch - 1 - colc);
+	const float* pu = u0 + colc;
+	const float* pv = v0 + colc;
+	const float* pd = VEL ? nullptr : d0 + colc;
+	const float fi = (float) i_first;
+
+	const int j_lo = 1 + chunk * tk.chunk_rows, j_hi = min(g.NY, j_lo + tk.chunk_rows - 1);
+	RowWin wu[3], wv[3], wd[3], nu, nv, nd;
+	wu[1] = advect_load_row(pu, j_lo - 1, pitch, lane, off_l, off_r);
+	wv[1] = advect_load_row(pv, j_lo - 1, pitch, lane, off_l, off_r);
+	wu[2] = advect_load_row(pu, j_lo, pitch, lane, off_l, off_r);
+	wv[2] = advect_load_row(pv, j_lo, pitch, lane, off_l, off_r);
+	nu = advect_load_row(pu, j_lo + 1, pitch, lane, off_l, off_r);
+	nv = advect_load_row(pv, j_lo + 1, pitch, lane, off_l, off_r);
+	if (!VEL) {
+		wd[1] = advect_load_row(pd, j_lo - 1, pitch, lane, off_l, off_r);
+		wd[2] = advect_load_row(pd, j_lo, pitch, lane, off_l, off_r);
+		nd = advect_load_row(pd, j_lo + 1, pitch, lane, off_l, off_r);
+	}
+	const bool edge_lane = (i_first == 1) || (i_first + 3 >= g.N && i_first <= g.N);
+
+#pragma unroll 1
+	for (int j = j_lo; j <= j_hi; j++) {
+		// slide: rows j-1, j, j+1 <- j, j+1 and the prefetched one; fetch row j+2 for the next step now
+		wu[0] = wu[1]; wu[1] = wu[2]; wu[2] = nu;
+		wv[0] = wv[1]; wv[1] = wv[2]; wv[2] = nv;
+		if (!VEL) { wd[0] = wd[1]; wd[1] = wd[2]; wd[2] = nd; }
+		const int jn = min(j + 2, g.NY + 1);
+		nu = advect_load_row(pu, jn, pitch, lane, off_l, off_r);
+		nv = advect_load_row(pv, jn, pitch, lane, off_l, off_r);
+		if (!VEL) nd = advect_load_row(pd, jn, pitch, lane, off_l, off_r);
+
+		int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
+		const float fj = (float) (SLAB ? j + g.j0 : j);
+		float px[4], py[4];
+		if (MODE == 1) {
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				px[k] = (fi + k) - dtN * wu[1].w[1 + k];
+				py[k] = fj - dtN * wv[1].w[1 + k];
+			}
+		} else {
+			BilinW m[4];
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				const float dirx = -dtN * wu[1].w[1 + k];
+				const float diry = -dtN * wv[1].w[1 + k];
+				const float mx = (fi + k) + 0.5f * dirx;
+				const float my = fj + 0.5f * diry;
+				m[k] = advect_calc<SLAB>(g, mx, my, ((valid >> k) & 1) ? oob : nullptr);
+			}
+			float vx[4], vy[4];
+			advect_sample<2>(advect_vote(m, i_first, j, valid), m, wu, wv, u0, v0, pitch, valid, vx, vy);
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				px[k] = (fi + k) - dtN * vx[k];
+				py[k] = fj - dtN * vy[k];
+			}
+		}
+		BilinW c[4];
+#pragma unroll
+		for (int k = 0; k < 4; k++) c[k] = advect_calc<SLAB>(g, px[k], py[k], ((valid >> k) & 1) ? oob : nullptr);
+		const int code = advect_vote(c, i_first, j, valid);
+		float ra[4], rb[4];
+		if (VEL) advect_sample<2>(code, c, wu, wv, u0, v0, pitch, valid, ra, rb);
+		else advect_sample<1>(code, c, wd, wd, d0, d0, pitch, valid, ra, rb);
+
+		float* pa = outa + (j * pitch + col);
+		if (valid == 0xfu) {
+			*reinterpret_cast<float4*>(pa) = make_float4(ra[0], ra[1], ra[2], ra[3]);
+			if (VEL) *reinterpret_cast<float4*>(outb + (j * pitch + col)) = make_float4(rb[0], rb[1], rb[2], rb[3]);
+		} else {
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				if (!((valid >> k) & 1)) continue;
+				pa[k] = ra[k];
+				if (VEL) outb[j * pitch + col + k] = rb[k];
+			}
+		}
+		// SetBorder (FluidSystem.cpp:861): only the groups along a wall have border cells to write
+		if (edge_lane || ((j == 1) && (g.walls & 1)) || ((j == g.NY) && (g.walls & 2))) {
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				if (!((valid >> k) & 1)) continue;
+				if (VEL) {
+					mirror_border(g, outa, 1, i_first + k, j, ra[k]);
+					mirror_border(g, outb, 2, i_first + k, j, rb[k]);
+				} else {
+					mirror_border(g, outa, b, i_first + k, j, ra[k]);
+				}
+			}
+		}
+	}
+}
+
+} // namespace fluid

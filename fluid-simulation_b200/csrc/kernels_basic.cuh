@@ -386,6 +386,55 @@ __global__ void k_apply_sources(GridDesc g, FieldPtrs f, const SourceDev* __rest
 }
 
 // ---------------------------------------------------------------------------
+// AddArrDt (FluidSystem.cpp:449-453) when the source array is zero except for a short list of cells -- the
+// arrays Update has just zero-filled plus what the updaters wrote (FluidSystem.cpp:104-118).  x += dt*0 leaves
+// every value as it is except -0, which becomes +0 (for dt >= 0; for dt < 0 the addend is -0 and nothing
+// changes at all): k_canon_zero reads the field once and writes only the float4 groups that hold a -0 -- 4
+// instead of 12 bytes per cell, and the zero-filled array is not read.  The listed cells are different: they
+// get x + dt*source, the reference's expression on the reference's operands, from k_add_source_cells BEFORE
+// the sweep (which might turn a sum of -0 into +0) and are put back after it by k_restore_source_cells.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_canon_zero(float4* __restrict__ x, float4* __restrict__ y, long long n4)
+{
+	long long k = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+	const long long stride = (long long) gridDim.x * blockDim.x;
+	auto fix = [](float4* p) {
+		float4 a = *p;
+		const uint32_t nz = 0x80000000u;
+		if (__float_as_uint(a.x) == nz || __float_as_uint(a.y) == nz || __float_as_uint(a.z) == nz || __float_as_uint(a.w) == nz) {
+			a.x += 0.0f; a.y += 0.0f; a.z += 0.0f; a.w += 0.0f; // every other value is unchanged by + 0
+			*p = a;
+		}
+	};
+	for (; k < n4; k += stride) {
+		fix(x + k);
+		if (y) fix(y + k);
+	}
+}
+
+// slots [slot_lo, slot_hi) of the field table: 0 = u, 1 = v, 2 + k = density of fluid k
+__global__ void k_add_source_cells(GridDesc g, FieldPtrs f, const SourceDev* __restrict__ src, const int* __restrict__ first,
+				   int batch, float* __restrict__ saved, float dt, int slot_lo, int slot_hi, int restore)
+{
+	const int sim = blockIdx.x * blockDim.x + threadIdx.x;
+	if (sim >= batch) return;
+	const long long off = (long long) sim * g.plane;
+	for (int k = first[sim]; k < first[sim + 1]; k++) {
+		const SourceDev e = src[k];
+		const int jl = e.j - g.j0;
+		if (e.mode != 0 || !e.last || e.field < slot_lo || e.field >= slot_hi || jl < 0 || jl > g.NY + 1) continue;
+		float* p = f.cur[e.field] + (off + cell(g, e.i, jl));
+		if (restore) {
+			*p = saved[k];
+		} else {
+			const float y = *p + dt * e.value;
+			*p = y;
+			saved[k] = y;
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
 // VortConfinement (FluidSystem.cpp:1124-1175) in three order-independent
 // phases; SetBorder(0) of the intermediate fields fused via mirror_border.
 // ---------------------------------------------------------------------------

@@ -35,7 +35,7 @@ EXPORTS = [
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs", "fluid_ctx_set_fluid",
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_set_fast_division", "fluid_ctx_division_window", "fluid_ctx_set_small_grid_kernels",
-    "fluid_ctx_set_wavefront_tile", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap",
+    "fluid_ctx_set_wavefront_tile", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap", "fluid_ctx_set_advect_kernel", "fluid_ctx_set_sparse_sources",
     "fluid_ctx_set_exchange", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
     "fluid_ctx_local_rows",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
@@ -122,6 +122,8 @@ def lib():
     L.fluid_ctx_set_wavefront_tile.argtypes = [_vp, _ci]
     L.fluid_ctx_set_stream_kernel.argtypes = [_vp, _ci]
     L.fluid_ctx_set_overlap.argtypes = [_vp, _ci]
+    L.fluid_ctx_set_advect_kernel.argtypes = [_vp, _ci]
+    L.fluid_ctx_set_sparse_sources.argtypes = [_vp, _ci]
     L.fluid_ctx_render.argtypes = [_vp, _ci, _f32, _f32, _vp]
     L.fluid_ctx_division_window.argtypes = [_vp, _cf, ctypes.POINTER(_ci), ctypes.POINTER(_ci)]
     L.fluid_ctx_upload_local.argtypes = [_vp, _ci, _f32]
@@ -331,6 +333,8 @@ class FluidSystem:
 
     def SetStreamKernel(self, on): check(lib().fluid_ctx_set_stream_kernel(self.h, 1 if on else 0))
     def SetOverlap(self, on): check(lib().fluid_ctx_set_overlap(self.h, 1 if on else 0))
+    def SetAdvectKernel(self, which): check(lib().fluid_ctx_set_advect_kernel(self.h, which))
+    def SetSparseSources(self, on): check(lib().fluid_ctx_set_sparse_sources(self.h, 1 if on else 0))
 
     def SetWavefrontTile(self, tile): check(lib().fluid_ctx_set_wavefront_tile(self.h, tile))
 

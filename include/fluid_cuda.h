@@ -222,6 +222,17 @@ int fluid_ctx_set_stream_kernel(fluid_ctx *ctx, int on);
  * more scratch field) -- (default on; 0 = one stream, kernels strictly in the
  * reference's order -- what per-kernel profiling wants).  Results identical. */
 int fluid_ctx_set_overlap(fluid_ctx *ctx, int on);
+/* Advect1 (FluidSystem.cpp:850-862) kernel choice: 0 = automatic (row-window kernel on grids of 2^20 cells or
+ * more), 1 = one thread per cell with global gathers, 2 = row window (a warp keeps rows j-1..j+1 of the sampled
+ * fields in registers; backtraces shorter than one cell interpolate from registers, longer ones gather).
+ * Results identical. */
+int fluid_ctx_set_advect_kernel(fluid_ctx *ctx, int which);
+/* fluid_ctx_step / fluid_update: the source arrays of a frame are zero except for the listed PREV_SET cells
+ * (Update zero-fills them, FluidSystem.cpp:104-109), so AddArrDt (:449-453) over them is known in advance: every
+ * value stays, a -0 becomes +0, the listed cells get x + dt*source.  1 (default) = do exactly that (one read of
+ * the field, almost no writes) on grids larger than 128^2; 0 = zero-fill and add densely, as the reference does.
+ * Results identical. */
+int fluid_ctx_set_sparse_sources(fluid_ctx *ctx, int on);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
 int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur

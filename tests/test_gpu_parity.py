@@ -141,6 +141,88 @@ def test_advect(fl, oracle, N, mode):
     assert_bits(d, e, "advect with d0 aliasing u")
 
 
+def _smooth_velocity(N, rng, amp_cells, dt=0.1):
+    """A velocity field whose backtraces move up to `amp_cells` cells (dt*N*|v|), smooth over tens of
+    cells -- long runs of cells that agree on the integer part of their displacement, seams where it
+    changes sign or steps, plus a patch of noise and a patch of exact zeros."""
+    i = np.arange(N + 2, dtype=np.float64)
+    X, Y = np.meshgrid(i, i)  # [j, i]
+    kx, ky = 2 * np.pi / (N / 3.3), 2 * np.pi / (N / 2.1)
+    scale = amp_cells / (dt * N)
+    u = scale * np.sin(kx * X + 0.3) * np.cos(ky * Y)
+    v = scale * np.cos(kx * X) * np.sin(ky * Y + 1.1)
+    u[N // 5:N // 5 + 9, 40:170] += scale * rng.uniform(-3, 3, (9, 130))
+    v[N // 2:N // 2 + 40, :] = 0.0
+    u[N // 2:N // 2 + 40, :] = 0.0
+    v[3 * N // 4:3 * N // 4 + 20, N // 3:] = -0.0
+    return u.astype(np.float32).ravel(), v.astype(np.float32).ravel()
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("N,amp", [(130, 0.7), (513, 0.9), (1030, 0.6), (1030, 2.5), (2048, 0.95)])
+def test_advect_row_window_kernel_bitwise(fl, oracle, N, amp, mode):
+    """The row-window advect kernel (kernels_advect.cuh): register-window interpolation where a whole row
+    of a warp agrees on a sub-cell displacement, gathers elsewhere -- scalar and velocity forms, all
+    border modes, widths that are not a multiple of 4 or 128, against the oracle; and the gather kernel
+    on the same inputs."""
+    rng = np.random.default_rng(7000 + N + mode)
+    u, v = _smooth_velocity(N, rng, amp)
+    d0 = rand_field(rng, N)
+    d0.reshape(N + 2, N + 2)[5:9, :] = 0.0
+    for kernel in (2, 1):
+        fs = fl.FluidSystem().Setup(N, advect_mode=mode)
+        fs.SetAdvectKernel(kernel)
+        fs.upload(fl.U_PREV, u)
+        fs.upload(fl.V_PREV, v)
+        fs.upload(fl.DENS_PREV, d0)
+        for b in (0, 1, 2, 3):
+            d = rand_field(rng, N)
+            fs.upload(fl.DENS, d)
+            fs.advect(b, fl.DENS, fl.DENS_PREV, fl.U_PREV, fl.V_PREV, 0.1)
+            oracle.advect(N, b, d, d0, u, v, 0.1, mode)
+            assert_bits(fs.download(fl.DENS), d, "advect kernel %d N=%d b=%d amp=%g mode=%d" % (kernel, N, b, amp, mode))
+        # VelStep1's pair: Advect1(1,u,u0,u0,v0), Advect1(2,v,v0,u0,v0)
+        un, vn = rand_field(rng, N), rand_field(rng, N)
+        fs.upload(fl.U, un)
+        fs.upload(fl.V, vn)
+        fs.advect_velocity(fl.U, fl.V, fl.U_PREV, fl.V_PREV, 0.1)
+        oracle.advect(N, 1, un, u, u, v, 0.1, mode)
+        oracle.advect(N, 2, vn, v, u, v, 0.1, mode)
+        assert_bits(fs.download(fl.U), un, "advect_velocity u, kernel %d N=%d amp=%g mode=%d" % (kernel, N, amp, mode))
+        assert_bits(fs.download(fl.V), vn, "advect_velocity v, kernel %d N=%d amp=%g mode=%d" % (kernel, N, amp, mode))
+        fs.close()
+
+
+def test_advect_row_window_kernel_random_fields_and_clamps(fl, oracle):
+    """Rough fields: every row disagrees (gather path throughout), backtraces leave the domain (clamp), an
+    ensemble.  (No NaN inputs: the reference indexes out of bounds for a NaN coordinate, FluidCode.h:95-103.)"""
+    rng = np.random.default_rng(99)
+    N = 260
+    fs = fl.FluidSystem().Setup(N, batch=3)
+    fs.SetAdvectKernel(2)
+    for scale in (0.05, 1.0, 40.0):
+        ins = []
+        for sim in range(3):
+            u, v, d0, d = (rand_field(rng, N, scale), rand_field(rng, N, scale), rand_field(rng, N), rand_field(rng, N))
+            ins.append((u, v, d0, d))
+            for fid, a in ((fl.U_PREV, u), (fl.V_PREV, v), (fl.DENS_PREV, d0), (fl.DENS, d)):
+                fs.upload(fid, a, sim)
+        fs.advect(0, fl.DENS, fl.DENS_PREV, fl.U_PREV, fl.V_PREV, 0.1)
+        fs.advect_velocity(fl.U, fl.V, fl.U_PREV, fl.V_PREV, 0.1)
+        for sim, (u, v, d0, d) in enumerate(ins):
+            un, vn = np.zeros_like(u), np.zeros_like(u)
+            with np.errstate(all="ignore"):
+                oracle.advect(N, 0, d, d0, u, v, 0.1)
+                oracle.advect(N, 1, un, u, u, v, 0.1)
+                oracle.advect(N, 2, vn, v, u, v, 0.1)
+            assert_bits(fs.download(fl.DENS, sim), d, "dens, member %d scale %g" % (sim, scale))
+            got_u, got_v = fs.download(fl.U, sim), fs.download(fl.V, sim)
+            # the border cells of u/v start as zeros here and in the oracle alike
+            assert_bits(got_u, un, "u, member %d scale %g" % (sim, scale))
+            assert_bits(got_v, vn, "v, member %d scale %g" % (sim, scale))
+    fs.close()
+
+
 @pytest.mark.parametrize("order", [0, 1])
 @pytest.mark.parametrize("N", SIZES)
 def test_project(fl, oracle, N, order):
@@ -318,6 +400,42 @@ def test_redblack_tolerance_after_100_steps(fl, oracle, N, iters):
     print("red-black vs reference order, N=%d, %d sweeps: worst rel-L2 over 1 and 100 frames %.3g" % (N, iters, worst))
     ref.close()
     rb.close()
+
+
+@pytest.mark.parametrize("order", [0, 1])
+@pytest.mark.parametrize("dt", [0.1, -0.05, 0.0])
+def test_sparse_add_source_keeps_signed_zeros(fl, oracle, order, dt):
+    """Update() adds a frame's forcing over the listed cells only and sweeps the rest for -0 (x + dt*0).
+    Fields full of signed zeros, sources whose product with dt is -0, +0 or underflows, several entries
+    on one cell, a source in a border cell, negative and zero dt: frames must equal the oracle's dense
+    AddArrDt bit for bit, with the sparse path on and off."""
+    import oracle_py as op
+    N, steps = 150, 2
+    rng = np.random.default_rng(1234)
+    init = {}
+    for k in "uvd":
+        a = rand_field(rng, N, 0.3).reshape(N + 2, N + 2)
+        a[10:40, :] = -0.0
+        a[40:60, :] = 0.0
+        a[70:75, 20:90] = -0.0
+        init[k] = a.ravel().copy()
+    tiny = float(np.float32(-1e-45))
+    src = [(2, 30, 20, 0, 100.0), (0, 31, 20, 0, -0.0), (1, 32, 20, 0, tiny), (2, 33, 20, 0, 0.0), (0, 34, 50, 0, 5.0),
+           (0, 34, 50, 0, -7.0), (1, 0, 12, 0, 3.0), (2, 77, 72, 0, -0.0), (1, 77, 72, 1, 0.25), (1, 77, 72, 0, tiny),
+           (0, 100, 100, 2, -0.0), (0, 100, 100, 0, -0.0)]
+    f = {k: init[k].copy() for k in "uvd"}
+    f.update({k + "0": np.zeros((N + 2) ** 2, np.float32) for k in "uvd"})
+    oracle.update(N, f, src, 1e-4, 2e-4, dt, steps, order=order)
+    for sparse in (True, False):
+        fs = fl.FluidSystem().Setup(N, 1e-4, 2e-4, gs_order=order)
+        fs.SetSparseSources(sparse)
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            fs.upload(fid, init[name])
+        fs.SetSources(src)
+        fs.Update(dt, steps)
+        for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
+            assert_bits(fs.download(fid), f[name], "sparse=%s order=%d dt=%g: %s" % (sparse, order, dt, name))
+        fs.close()
 
 
 def test_ensemble_members_are_independent(fl, oracle):
