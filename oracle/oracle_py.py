@@ -94,6 +94,19 @@ class Oracle:
         L.oracle_total_inner_mass.argtypes = [c_int, _f32p]
         L.oracle_total_inner_mass.restype = c_float
         L.oracle_set_threads.argtypes = [c_int]
+        _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+        L.oracle_make_cell_info.argtypes = [c_int, c_int, _u8p]
+        L.oracle_calc_border.argtypes = [c_int, _u8p]
+        L.oracle_lin_solve_b.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.oracle_lin_solve_b_rb.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.oracle_blur_b.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.oracle_diffuse_blur_b.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.oracle_project_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int, c_int, _u8p]
+        L.oracle_advect_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_int]
+        L.oracle_vel_step_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_float, c_int, c_int, c_int, _u8p]
+        L.oracle_dens_step_bs.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_float, c_int, c_int, _u8p]
+        L.oracle_update_b.argtypes = [c_int] + [_f32p] * 6 + [_u8p, c_int, c_void_p, c_float, c_float, c_float, c_int, c_int,
+                                                              c_int, c_float, c_float, c_int]
 
     def set_threads(self, n):
         """Threads for the order-independent loops (bit-identical results; 1 = the serial restatement)."""
@@ -148,6 +161,44 @@ class Oracle:
     def total_inner_mass(self, N, d):
         return float(self.L.oracle_total_inner_mass(N, d))
 
+    # ---- FSType::ORIGINAL_BORDERED (cellInfo-masked variants) ----
+    def make_cell_info(self, N, square_border=False):
+        """cellInfo as Update rebuilds it each frame: ResetCellInfo, CalcBorderFromContent[, SquareBorder]."""
+        info = np.empty((N + 2) ** 2, np.uint8)
+        self.L.oracle_make_cell_info(N, 1 if square_border else 0, info)
+        return info
+
+    def calc_border(self, N, info):
+        self.L.oracle_calc_border(N, info)
+
+    def lin_solve_b(self, N, b, x, x0, a, c, info, iters=20, order=GS_LEX):
+        (self.L.oracle_lin_solve_b_rb if order == GS_RB else self.L.oracle_lin_solve_b)(N, b, x, x0, a, c, iters, info)
+
+    def blur_b(self, N, b, x, x0, a, c, info, iters=20):
+        self.L.oracle_blur_b(N, b, x, x0, a, c, iters, info)
+
+    def diffuse_blur_b(self, N, b, x, x0, diff, dt, info, iters=20):
+        self.L.oracle_diffuse_blur_b(N, b, x, x0, diff, dt, iters, info)
+
+    def project_b(self, N, u, v, p, div, info, iters=20, order=GS_LEX):
+        self.L.oracle_project_b(N, u, v, p, div, iters, order, info)
+
+    def advect_b(self, N, d, d0, u, v, dt, mode=ADV_MIDPOINT):
+        self.L.oracle_advect_b(N, d, d0, u, v, dt, mode)
+
+    def vel_step_b(self, N, u, v, u0, v0, visc, dt, info, iters=20, order=GS_LEX, mode=ADV_MIDPOINT):
+        self.L.oracle_vel_step_b(N, u, v, u0, v0, visc, dt, iters, order, mode, info)
+
+    def dens_step_bs(self, N, x, x0, u, v, diff, dt, info, iters=20, mode=ADV_MIDPOINT):
+        self.L.oracle_dens_step_bs(N, x, x0, u, v, diff, dt, iters, mode, info)
+
+    def update_b(self, N, fields, info, sources, visc, diff, dt, nsteps=1, iters=20, order=GS_LEX, mode=ADV_MIDPOINT,
+                 vorticity=0.0, damp=0.0):
+        arr = (SourceEntry * max(1, len(sources)))(*[SourceEntry(*s) for s in sources])
+        self.L.oracle_update_b(N, fields["u"], fields["v"], fields["d"], fields["u0"], fields["v0"], fields["d0"], info,
+                               len(sources), ctypes.cast(arr, c_void_p), visc, diff, dt, iters, order, mode, vorticity,
+                               damp, nsteps)
+
     def render(self, N, dens, u, v, color):
         n = (N + 2) ** 2
         px, ln = np.empty(n * 3, np.float32), np.empty(n * 4, np.float32)
@@ -185,12 +236,30 @@ class Ref:
         L.ref_advect.argtypes = [c_int, c_int, _f32p, _f32p, _f32p, _f32p, c_float]
         L.ref_advect_euler.argtypes = [c_int, c_int, _f32p, _f32p, _f32p, _f32p, c_float]
         L.ref_project.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int]
+        _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+        L.ref_create_typed.restype = c_void_p
+        L.ref_create_typed.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_int, c_int, c_float, c_int, c_int]
+        L.ref_cell_info.restype = ctypes.POINTER(ctypes.c_ubyte)
+        L.ref_cell_info.argtypes = [c_void_p]
+        L.ref_make_cell_info.argtypes = [c_int, c_int, _u8p]
+        L.ref_calc_border.argtypes = [c_int, _u8p]
+        L.ref_lin_solve_b.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.ref_diffuse_blur_b.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.ref_advect_b.argtypes = [c_int, c_int, _f32p, _f32p, _f32p, _f32p, c_float]
+        L.ref_project_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int, _u8p]
 
     class Sim:
-        def __init__(self, ref, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None):
-            """fluids: optional list of (diff, visc) per fluid (source field ids 2+k address fluid k)."""
+        def __init__(self, ref, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None, fstype=0, square_border=False):
+            """fluids: optional list of (diff, visc) per fluid (source field ids 2+k address fluid k).
+            fstype: 0 ORIGINAL, 1 ORIGINAL_BORDERED, 2 ORIGINAL_BORDERED_MF (FluidSystem.h:10-17)."""
             self.ref, self.N = ref, N
-            if fluids:
+            if fstype or square_border:
+                fl = fluids or [(diff, visc)]
+                d = np.array([f[0] for f in fl], np.float32)
+                v = np.array([f[1] for f in fl], np.float32)
+                self.h = ref.L.ref_create_typed(N, len(fl), d, v, vorticity, iters, 1 if vorticity != 0.0 else 0, damp, fstype,
+                                                1 if square_border else 0)
+            elif fluids:
                 d = np.array([f[0] for f in fluids], np.float32)
                 v = np.array([f[1] for f in fluids], np.float32)
                 self.h = ref.L.ref_create_multi(N, len(fluids), d, v, vorticity, iters, 1 if vorticity != 0.0 else 0, damp)
@@ -223,10 +292,13 @@ class Ref:
         def total_inner_mass(self):
             return float(self.ref.L.ref_total_inner_mass(self.h))
 
+        def cell_info(self):
+            return np.ctypeslib.as_array(self.ref.L.ref_cell_info(self.h), ((self.N + 2) ** 2,))
+
         def close(self):
             if self.h:
                 self.ref.L.ref_destroy(self.h)
                 self.h = None
 
-    def sim(self, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None):
-        return Ref.Sim(self, N, visc, diff, vorticity, iters, damp, fluids)
+    def sim(self, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None, fstype=0, square_border=False):
+        return Ref.Sim(self, N, visc, diff, vorticity, iters, damp, fluids, fstype, square_border)

@@ -23,6 +23,7 @@
 #define protected public
 #include "FluidSystem.h"
 #include "FluidCollider.h"
+#include "FluidBorder.h"
 #undef private
 #undef protected
 
@@ -118,6 +119,29 @@ void* ref_create_multi(int N, int nfluids, const float* diffs, const float* visc
 	s->fs.AddUpdater(s->src);
 	return s;
 }
+
+// Any solver type (FluidSystem.h:10-17: 0 ORIGINAL, 1 ORIGINAL_BORDERED, 2 ORIGINAL_BORDERED_MF) with
+// per-fluid properties and, optionally, the shipped scene's internal wall (SquareBorder, FluidBorder.cpp:4-19).
+void* ref_create_typed(int N, int nfluids, const float* diffs, const float* viscs, float vorticity, int steps, int use_vort,
+		       float damp, int fstype, int square_border)
+{
+	RefSim* s = new RefSim();
+	std::vector<FluidProps> props;
+	for (int k = 0; k < nfluids; k++) props.push_back({ { diffs[k], viscs[k] }, { 1.0f, 1.0f, 1.0f } });
+	s->fs.Setup(N, vorticity, props, (FluidSystem::FSType) fstype);
+	s->fs.steps = steps;
+	s->fs.useVort = use_vort != 0;
+	s->fs.damp = damp;
+	s->fs.Clear();
+	std::fill(s->fs.p.begin(), s->fs.p.end(), 0.0f);
+	s->src = new SourceUpdater();
+	s->fs.AddUpdater(s->src);
+	if (square_border) s->fs.AddBorder(new SquareBorder()); // (leaked with the simulation: FluidSystem has no border removal)
+	return s;
+}
+
+// cellInfo as the last Update (or Setup) left it (FluidSystem.h: GetInfo)
+unsigned char* ref_cell_info(void* h) { return ((RefSim*) h)->fs.cellInfo.data(); }
 
 float* ref_density(void* h, int fluid, int prev)
 {
@@ -245,6 +269,77 @@ void ref_advect_euler(int N, int b, float* d, const float* d0, const float* u, c
 			fs->EulerBack(N, i, j, dtN, vu, vv, vd, vd0);
 	fs->SetBorder(N, b, vd);
 	store(d, vd);
+	delete fs;
+}
+
+// ---- bordered variants (FluidSystem.cpp:550-578, 745-777, 864-874, 1009-1059, 1185-1232, 1388-1408) on caller buffers ----
+
+static FluidSystem* scratch_system_info(int N, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system(N, steps);
+	fs->cellInfo.assign(info, info + (size_t) (N + 2) * (N + 2));
+	return fs;
+}
+
+// ResetCellInfo + CalcBorderFromContent [+ SquareBorder::WriteBorder], i.e. what Update does to cellInfo
+// each frame when no collider is registered (FluidSystem.cpp:112-115).
+void ref_make_cell_info(int N, int square_border, unsigned char* info)
+{
+	FluidSystem* fs = scratch_system(N, 20);
+	fs->cellInfo.resize((size_t) (N + 2) * (N + 2));
+	fs->ResetCellInfo();
+	fs->CalcBorderFromContent();
+	if (square_border) {
+		SquareBorder sb;
+		sb.WriteBorder(N, fs, fs->cellInfo);
+	}
+	std::memcpy(info, fs->cellInfo.data(), fs->cellInfo.size());
+	delete fs;
+}
+
+// CalcBorderFromContent alone on a caller-made map (FLUID / OBJECT bits chosen by the caller)
+void ref_calc_border(int N, unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, 20, info);
+	fs->CalcBorderFromContent();
+	std::memcpy(info, fs->cellInfo.data(), fs->cellInfo.size());
+	delete fs;
+}
+
+void ref_lin_solve_b(int N, int b, float* x, const float* x0, float a, float c, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, steps, info);
+	vec vx = load(x, N), v0 = load(x0, N);
+	fs->LinearSolve1B(N, b, vx, v0, a, c);
+	store(x, vx);
+	delete fs;
+}
+
+void ref_diffuse_blur_b(int N, int b, float* x, float* x0, float diff, float dt, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, steps, info);
+	vec vx = load(x, N), v0 = load(x0, N);
+	fs->Diffuse_blurB(N, b, vx, v0, diff, dt);
+	store(x, vx);
+	store(x0, v0);
+	delete fs;
+}
+
+void ref_advect_b(int N, int b, float* d, const float* d0, const float* u, const float* v, float dt)
+{
+	FluidSystem* fs = scratch_system(N, 20);
+	vec vd = load(d, N), vd0 = load(d0, N), vu = load(u, N), vv = load(v, N);
+	fs->Advect1B(N, b, vd, vd0, vu, vv, dt);
+	store(d, vd);
+	delete fs;
+}
+
+void ref_project_b(int N, float* u, float* v, float* p, float* div, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, steps, info);
+	vec vu = load(u, N), vv = load(v, N), vp = load(p, N), vd = load(div, N);
+	fs->ProjectB(N, vu, vv, vp, vd);
+	store(u, vu); store(v, vv); store(p, vp); store(div, vd);
 	delete fs;
 }
 

@@ -221,3 +221,80 @@ def test_multifluid_golden_from_the_reference(oracle):
     want = multifluid_expected(oracle, N, steps, fluids, G["sources"])
     for k in ("u", "v", "d0", "d1"):
         assert_bits(want[k], G[k], "two fluids, " + k)
+
+
+# ---- FSType::ORIGINAL_BORDERED: the cellInfo-masked pipeline ------------------------------
+
+def _cell_map_with_objects(oracle, N, rng):
+    """A cell map with the shipped scene's internal wall plus blocks of non-FLUID (OBJECT) cells, direction
+    bits recomputed the way CalcBorderFromContent does after a collider has marked its cells."""
+    info = oracle.make_cell_info(N, square_border=False)
+    m = info.reshape(N + 2, N + 2)
+    for _ in range(3):
+        i0, j0 = rng.integers(2, N - 6, 2)
+        m[j0:j0 + 4, i0:i0 + 5] = (m[j0:j0 + 4, i0:i0 + 5] & ~np.uint8(16)) | np.uint8(32)
+    oracle.calc_border(N, info)
+    return info
+
+
+def test_bordered_cell_map_and_primitives_match_live_reference(oracle, ref):
+    rng = np.random.default_rng(77)
+    for N in (5, 16, 41):
+        for square in (False, True):
+            want = np.empty((N + 2) ** 2, np.uint8)
+            ref.L.ref_make_cell_info(N, 1 if square else 0, want)
+            assert oracle.make_cell_info(N, square).tobytes() == want.tobytes(), (N, square)
+        if N > 10:
+            info = _cell_map_with_objects(oracle, N, rng)
+            chk = info.copy()
+            ref.L.ref_calc_border(N, chk)  # idempotent on a map it has produced itself
+            assert chk.tobytes() == info.tobytes()
+            oracle.L.oracle_square_border(N, info.ctypes.data_as(__import__("ctypes").c_void_p))  # plus the internal wall
+        else:
+            info = oracle.make_cell_info(N, True)
+        r = lambda s=1.0: (rng.uniform(-1, 1, (N + 2) ** 2) * s).astype(np.float32)
+        for b in (0, 1, 2):
+            for a, c in ((np.float32(0.0), np.float32(1.0)), (np.float32(1.0), np.float32(4.0)), (np.float32(0.37), np.float32(2.48))):
+                x, x0 = r(), r()
+                y = x.copy()
+                oracle.lin_solve_b(N, b, x, x0, a, c, info)
+                ref.L.ref_lin_solve_b(N, b, y, x0, a, c, 20, info)
+                assert x.tobytes() == y.tobytes(), ("lin_solve_b", N, b, a)
+            for diff in (0.0, 2e-3):
+                x, x0 = r(), r()
+                y, y0 = x.copy(), x0.copy()
+                oracle.diffuse_blur_b(N, b, x, x0, diff, 0.1, info)
+                ref.L.ref_diffuse_blur_b(N, b, y, y0, diff, 0.1, 20, info)
+                assert x.tobytes() == y.tobytes() and x0.tobytes() == y0.tobytes(), ("blur_b", N, b, diff)
+        u, v, p, dv = r(), r(), r(), r()
+        U, V, P, D = u.copy(), v.copy(), p.copy(), dv.copy()
+        oracle.project_b(N, u, v, p, dv, info)
+        ref.L.ref_project_b(N, U, V, P, D, 20, info)
+        for got, wantf, name in ((u, U, "u"), (v, V, "v"), (p, P, "p"), (dv, D, "div")):
+            assert got.tobytes() == wantf.tobytes(), ("project_b", N, name)
+        d, d0, uu, vv = r(), r(), r(3.0), r(3.0)
+        e = d.copy()
+        oracle.advect_b(N, d, d0, uu, vv, 0.1)
+        ref.L.ref_advect_b(N, 0, e, d0, uu, vv, 0.1)
+        assert d.tobytes() == e.tobytes(), ("advect_b", N)
+
+
+def test_bordered_frames_match_live_reference(oracle, ref):
+    """Whole frames of FluidSystem::Update with FSType::ORIGINAL_BORDERED (VelStep1B + DensStep1BS), with and
+    without the scene's SquareBorder, vorticity and damping: the restatement against the unmodified reference,
+    including the reference's own quirk that the x velocity receives the y source (FluidSystem.cpp:380)."""
+    import oracle_py as op
+    for N, steps, square, vort, damp in ((16, 6, True, 0.0, 0.0), (64, 12, True, 0.0, 0.0), (50, 8, False, 0.55, 0.1), (64, 5, True, 0.3, 0.0)):
+        c = N // 2
+        src = op.stam_sources(N) + [(0, c + 3, c - 2, 0, 4.0), (1, 3, 3, 0, -6.0), (2, c - N // 4, c, 1, 0.8), (0, 5, N - 3, 2, 0.7)]
+        sim = ref.sim(N, 1e-4, 2e-4, vort, 20, damp, fstype=1, square_border=square)
+        sim.set_sources(src)
+        sim.update(0.1, steps)
+        info = oracle.make_cell_info(N, square)
+        assert info.tobytes() == sim.cell_info().tobytes()
+        f = {k: np.zeros((N + 2) ** 2, np.float32) for k in "u v d u0 v0 d0".split()}
+        oracle.update_b(N, f, info, src, 1e-4, 2e-4, 0.1, steps, vorticity=vort, damp=damp)
+        for name, w in (("u", 0), ("v", 1), ("d", 2), ("u0", 3), ("v0", 4), ("d0", 5)):
+            assert f[name].tobytes() == sim.field(w).tobytes(), (N, square, name)
+        assert np.abs(f["u"]).max() > 0 and np.abs(f["d"]).max() > 0
+        sim.close()
