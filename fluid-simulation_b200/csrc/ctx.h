@@ -137,6 +137,8 @@ struct fluid_ctx {
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_density = true;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
+	int fs_type = FLUID_TYPE_ORIGINAL; // which of the reference's step function pairs this context runs (SetType, FluidSystem.cpp:69-99)
+	unsigned char* d_info = nullptr;    // cellInfo, one byte per cell in the fields' pitched layout (bordered types)
 	int advect_kernel = 0; // 0 automatic, 1 one thread per cell (gathers), 2 row window (kernels_advect.cuh)
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
 	// 0 never; 1 automatic: a divisor that comes back in a later frame / call, and has enough work behind it to
@@ -261,6 +263,15 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 				  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
 				  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 int get_encode_fn(EncodeTiledFn* out);
+// fluid_bordered.cu (FSType::ORIGINAL_BORDERED: cellInfo-masked primitives)
+int bordered_alloc(fluid_ctx* c);
+int bordered_reset(fluid_ctx* c);
+int bordered_calc(fluid_ctx* c);
+int bordered_disable_edges(fluid_ctx* c, int n, const int* edges);
+int dev_lin_solve_b(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc);
+int dev_blur_b(fluid_ctx* c, int b, float* x, float* x0, float a, float cc);
+int dev_project_b(fluid_ctx* c, float* u, float* v, float* p, float* div);
+constexpr int kBndNone = -2; // advect: no SetBorder at all (Advect1B, FluidSystem.cpp:864-874)
 // fluid_core.cu
 int check_field_n(int f, int n);
 int check_distinct_n(int n_fields, std::initializer_list<int> ids);

@@ -82,6 +82,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->d_lines) cudaFree(c->d_lines);
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_src_saved) cudaFree(c->d_src_saved);
+	if (c->d_info) cudaFree(c->d_info);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);
@@ -119,7 +120,9 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	if (p->gs_iters < 1) return fail(FLUID_ERR_INVALID, "gs_iters=%d must be >= 1", p->gs_iters);
 	if (p->gs_order != FLUID_GS_WAVEFRONT && p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", p->gs_order);
 	if (p->advect_mode != FLUID_ADVECT_MIDPOINT && p->advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", p->advect_mode);
-	for (int r : p->reserved) if (r != 0) return fail(FLUID_ERR_INVALID, "reserved fields must be 0");
+	if (p->fs_type != FLUID_TYPE_ORIGINAL && p->fs_type != FLUID_TYPE_ORIGINAL_BORDERED) return fail(FLUID_ERR_INVALID, "unknown fs_type %d", p->fs_type);
+	if (p->fs_type != FLUID_TYPE_ORIGINAL && (p->slab_count > 1 || p->slab_rows > 0))
+		return fail(FLUID_ERR_UNSUPPORTED, "the bordered solver types run on whole square grids only (no row slabs)");
 	if (p->n_fluids < 0 || p->n_fluids > FLUID_MAX_FLUIDS) return fail(FLUID_ERR_INVALID, "n_fluids=%d out of range [1,%d]", p->n_fluids, FLUID_MAX_FLUIDS);
 	if (p->slab_rows < 0 || p->slab_rows > 1048576) return fail(FLUID_ERR_INVALID, "slab_rows=%d out of range", p->slab_rows);
 	if (p->slab_count < 0 || (p->slab_count > 1 && (p->slab_index < 0 || p->slab_index >= p->slab_count)))
@@ -213,6 +216,11 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 		c->src_dirty = true;
 		rc = sync_sources(c);
 		if (rc != FLUID_OK) break;
+		c->fs_type = p->fs_type;
+		if (c->fs_type != FLUID_TYPE_ORIGINAL) {
+			rc = bordered_alloc(c);
+			if (rc != FLUID_OK) break;
+		}
 		if (cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = fail(FLUID_ERR_CUDA, "stream sync failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
 	} while (0);
 	if (rc != FLUID_OK) {
@@ -389,6 +397,70 @@ extern "C" int fluid_ctx_set_advect_kernel(fluid_ctx* c, int which)
 	CHECK_CTX(c);
 	if (which < 0 || which > 2) return fail(FLUID_ERR_INVALID, "advect kernel %d must be 0 (automatic), 1 (gather per cell) or 2 (row window)", which);
 	c->advect_kernel = which;
+	return FLUID_OK;
+}
+
+#define CHECK_BORDERED(c)                                                                                         \
+	do {                                                                                                      \
+		CHECK_CTX(c);                                                                                     \
+		if ((c)->fs_type == FLUID_TYPE_ORIGINAL)                                                          \
+			return fail(FLUID_ERR_INVALID, "this context is FLUID_TYPE_ORIGINAL: it has no cell map (create it with fs_type = FLUID_TYPE_ORIGINAL_BORDERED)"); \
+	} while (0)
+
+extern "C" int fluid_ctx_reset_cell_info(fluid_ctx* c)
+{
+	CHECK_BORDERED(c);
+	return bordered_reset(c);
+}
+
+extern "C" int fluid_ctx_disable_edges(fluid_ctx* c, int n, const int* edges)
+{
+	CHECK_BORDERED(c);
+	if (n < 0 || (n > 0 && !edges)) return fail(FLUID_ERR_INVALID, "bad edge list");
+	for (int k = 0; k < n; k++) {
+		const int* e = edges + 4 * k;
+		const int dx = e[2] - e[0], dy = e[3] - e[1];
+		if (e[0] < 0 || e[0] > c->g.N + 1 || e[2] < 0 || e[2] > c->g.N + 1 || e[1] < 0 || e[1] > c->g.NY + 1 || e[3] < 0 || e[3] > c->g.NY + 1 ||
+		    abs(dx) + abs(dy) != 1)
+			return fail(FLUID_ERR_INVALID, "edge %d: (%d,%d)-(%d,%d) does not join two adjacent cells of the grid", k, e[0], e[1], e[2], e[3]);
+	}
+	return bordered_disable_edges(c, n, edges);
+}
+
+// SquareBorder::WriteBorder (FluidBorder.cpp:4-19): bounds in float, truncated, exactly as the scene computes them.
+extern "C" int fluid_ctx_add_square_border(fluid_ctx* c)
+{
+	CHECK_BORDERED(c);
+	const int N = c->g.N;
+	const float size = 0.3;
+	const int low = 1 + N / 2 - size * N / 2;
+	const int high = 1 + N / 2 + size * N / 2;
+	std::vector<int> e;
+	for (int i = low; i <= high; i++) {
+		const int four[4][4] = { { i, low, i, low - 1 }, { i, high, i, high + 1 }, { low, i, low - 1, i }, { high, i, high + 1, i } };
+		for (auto& q : four) e.insert(e.end(), q, q + 4);
+	}
+	return fluid_ctx_disable_edges(c, (int) e.size() / 4, e.data());
+}
+
+extern "C" int fluid_ctx_set_cell_info(fluid_ctx* c, const unsigned char* host_info, int recalc)
+{
+	CHECK_BORDERED(c);
+	if (!host_info) return fail(FLUID_ERR_INVALID, "null pointer");
+	const size_t w = (size_t) c->g.N + 2;
+	CU_TRY(cudaMemcpy2DAsync(c->d_info + XO, (size_t) c->g.pitch, host_info, w, w, c->g.NY + 2, cudaMemcpyHostToDevice, c->stream));
+	if (recalc) FL_TRY(bordered_calc(c));
+	CU_TRY(cudaStreamSynchronize(c->stream));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_get_cell_info(fluid_ctx* c, unsigned char* host_info)
+{
+	CHECK_BORDERED(c);
+	if (!host_info) return fail(FLUID_ERR_INVALID, "null pointer");
+	const size_t w = (size_t) c->g.N + 2;
+	CU_TRY(cudaMemcpy2DAsync(host_info, w, c->d_info + XO, (size_t) c->g.pitch, w, c->g.NY + 2, cudaMemcpyDeviceToHost, c->stream));
+	CU_TRY(cudaStreamSynchronize(c->stream));
 	return FLUID_OK;
 }
 

@@ -466,6 +466,7 @@ static int small_configure(fluid_ctx* c)
 // x may come back pointing at another array (rb_tile_solve); callers keep using x, not a copy made before.
 int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, float cc, bool x_is_zero)
 {
+	if (c->fs_type != FLUID_TYPE_ORIGINAL) return dev_lin_solve_b(c, b, x, x0, a, cc); // LinearSolve1B: cellInfo-masked
 	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
 	const int limit = a > 0 ? c->gs_iters : 1;
 	if (use_small_kernels(c)) {
@@ -540,6 +541,7 @@ static bool blur_stream_geometry(const fluid_ctx* c, StreamRect* rc)
 
 int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 {
+	if (c->fs_type != FLUID_TYPE_ORIGINAL) return dev_blur_b(c, b, x, x0, a, cc); // BlurB
 	ProfScope ps(c, FLUID_PROF_BLUR);
 	int limit = a > 0 ? c->gs_iters : 1;
 	if (limit % 2 == 0) limit += 1;

@@ -71,6 +71,7 @@ int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, c
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
 	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	if (c->fs_type != FLUID_TYPE_ORIGINAL) b = kBndNone; // Advect1B (FluidSystem.cpp:864-874): no SetBorder
 	AdvectTasks tk;
 	if (advect_rows_geometry(c, &tk)) {
 		launch_advect_rows<false>(c, tk, b, d, nullptr, d0, u, v, dtN);
@@ -91,17 +92,19 @@ int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const
 	ProfScope ps(c, FLUID_PROF_ADVECT);
 	const float dtN = dt * c->g.N;
 	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
+	const bool nobnd = c->fs_type != FLUID_TYPE_ORIGINAL;
+	const int bu = nobnd ? kBndNone : 1, bv = nobnd ? kBndNone : 2;
 	AdvectTasks tk;
 	if (advect_rows_geometry(c, &tk)) {
-		launch_advect_rows<true>(c, tk, 0, u, v, nullptr, u0, v0, dtN);
+		launch_advect_rows<true>(c, tk, nobnd ? kBndNone : 0, u, v, nullptr, u0, v0, dtN);
 		return FLUID_OK;
 	}
 	if (c->slab_count > 1) {
-		if (euler) LAUNCH((k_advect_velocity<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
-		else LAUNCH((k_advect_velocity<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1);
+		if (euler) LAUNCH((k_advect_velocity<true, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1, bu, bv);
+		else LAUNCH((k_advect_velocity<true, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, c->own_lo, c->own_lo + c->slab_rows - 1, bu, bv);
 	} else {
-		if (euler) LAUNCH((k_advect_velocity<false, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0);
-		else LAUNCH((k_advect_velocity<false, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0);
+		if (euler) LAUNCH((k_advect_velocity<false, 1>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0, bu, bv);
+		else LAUNCH((k_advect_velocity<false, 0>), cell_grid(c), kBlk2D, 0, c->stream, c->g, u, v, u0, v0, dtN, c->d_oob, 1, 0, bu, bv);
 	}
 	return FLUID_OK;
 }
@@ -109,6 +112,7 @@ int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const
 // Project (FluidSystem.cpp:982-1007).
 int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
 {
+	if (c->fs_type != FLUID_TYPE_ORIGINAL) return dev_project_b(c, u, v, p, div);
 	// p = 0 is the solve's starting guess.  Where the first pass of the solve can simply be told so, the zeros
 	// are neither written here nor read there (2 x 268 MB at N = 8192).
 	const int limit = c->gs_iters; // a = 1 > 0
@@ -153,7 +157,13 @@ static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> array
 int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt, bool sources_added)
 {
 	// slabs: u, v (and the source arrays, which every slab fills itself) are valid over the whole halo on entry
-	if (!sources_added) FL_TRY(dev_add_source2(c, u, u0, v, v0, dt)); // (Update() may already have added its sparse forcing)
+	if (c->fs_type != FLUID_TYPE_ORIGINAL) {
+		// VelStep1B (FluidSystem.cpp:378-398) is VelStep1 over the masked primitives, except that its first AddArrDt
+		// adds the Y source to vX (:380, AddArrDt(N, vX.Curr(), vY.Prev(), dt)): reproduced as the reference has it
+		FL_TRY(dev_add_source2(c, u, v0, v, v0, dt));
+	} else if (!sources_added) {
+		FL_TRY(dev_add_source2(c, u, u0, v, v0, dt)); // (Update() may already have added its sparse forcing)
+	}
 	std::swap(u, u0);
 	const float a = diffusion_a(c, visc, dt);
 	std::swap(v, v0);
@@ -291,7 +301,7 @@ int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::
 	// in advance (k_canon_zero, kernels_basic.cuh): the three dense x += dt*s passes and the zero fill of the
 	// densities' source arrays (which nothing else reads: Blur overwrites them) are left out.  Small grids keep
 	// the plain sequence (they are bound by launches, not bytes); so does a dt whose product with zero is NaN.
-	const bool sparse = c->sparse_sources && !use_small_kernels(c) && isfinite(dt);
+	const bool sparse = c->sparse_sources && !use_small_kernels(c) && isfinite(dt) && c->fs_type == FLUID_TYPE_ORIGINAL;
 	FieldPtrs fp = {};
 	fp.cur[0] = c->f[FLUID_U];
 	fp.prev[0] = c->f[FLUID_U_PREV];

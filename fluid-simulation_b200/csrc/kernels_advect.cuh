@@ -158,7 +158,7 @@ struct AdvectTasks {
 };
 
 // VEL: VelStep1's self-advection (FluidSystem.cpp:372-373), Advect1(1,u,u0,u0,v0) and Advect1(2,v,v0,u0,v0) in one
-// pass (outa = u, outb = v, b ignored).  Otherwise Advect1(b, outa, d0, u0, v0) for one scalar field.
+// pass (outa = u, outb = v; b = -2 leaves the border alone, as Advect1B does, anything else means SetBorder 1 / 2).  Otherwise Advect1(b, outa, d0, u0, v0) for one scalar field.
 // MODE 0 = MidpointBackward, 1 = EulerBack (FluidSystem.h:185-219).
 template <bool SLAB, int MODE, bool VEL>
 __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, AdvectTasks tk, int b, float* __restrict__ outab,
@@ -269,9 +269,9 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 #pragma unroll
 			for (int k = 0; k < 4; k++) {
 				if (!((valid >> k) & 1)) continue;
-				if (VEL) {
-					mirror_border(g, outa, 1, i_first + k, j, ra[k]);
-					mirror_border(g, outb, 2, i_first + k, j, rb[k]);
+				if (VEL) { // b = -2: VelStep1B's pair (no SetBorder); anything else: VelStep1's (SetBorder 1 and 2)
+					mirror_border(g, outa, b == -2 ? -2 : 1, i_first + k, j, ra[k]);
+					mirror_border(g, outb, b == -2 ? -2 : 2, i_first + k, j, rb[k]);
 				} else {
 					mirror_border(g, outa, b, i_first + k, j, ra[k]);
 				}

@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(256) k_advect(GridDesc g, int b, float* __rest
 template <bool SLAB, int MODE>
 __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __restrict__ ub, float* __restrict__ vb,
 							  const float* __restrict__ u0b, const float* __restrict__ v0b,
-							  float dtN, int* oob_flag, int own_lo, int own_hi)
+							  float dtN, int* oob_flag, int own_lo, int own_hi, int bu, int bv)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
 	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
@@ -358,8 +358,8 @@ __global__ void __launch_bounds__(256) k_advect_velocity(GridDesc g, float* __re
 	float* v = vb + off;
 	ub[mine] = un;
 	vb[mine] = vn;
-	mirror_border(g, u, 1, i, j, un);
-	mirror_border(g, v, 2, i, j, vn);
+	mirror_border(g, u, bu, i, j, un); // (1, 2) for VelStep1; no SetBorder (-2, -2) for VelStep1B
+	mirror_border(g, v, bv, i, j, vn);
 }
 
 // ---------------------------------------------------------------------------

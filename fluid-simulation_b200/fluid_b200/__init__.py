@@ -21,6 +21,7 @@ GS_WAVEFRONT, GS_REDBLACK = 0, 1
 ADVECT_MIDPOINT, ADVECT_EULER = 0, 1
 U, V, DENS, U_PREV, V_PREV, DENS_PREV = range(6)
 SRC_PREV_SET, SRC_CURR_ADD, SRC_CURR_SET = 0, 1, 2
+TYPE_ORIGINAL, TYPE_ORIGINAL_BORDERED = 0, 1
 K_LIN_SOLVE, K_BLUR, K_ADVECT, K_ADVECT_VEL, K_PROJECT, K_ADD_SOURCE = range(6)
 
 # every symbol include/fluid_cuda.h declares (tests check the .so exports them all)
@@ -36,6 +37,8 @@ EXPORTS = [
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_set_fast_division", "fluid_ctx_division_window", "fluid_ctx_set_small_grid_kernels",
     "fluid_ctx_set_wavefront_tile", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap", "fluid_ctx_set_advect_kernel", "fluid_ctx_set_sparse_sources",
+    "fluid_ctx_reset_cell_info", "fluid_ctx_disable_edges", "fluid_ctx_add_square_border", "fluid_ctx_set_cell_info",
+    "fluid_ctx_get_cell_info",
     "fluid_ctx_set_exchange", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
     "fluid_ctx_local_rows",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
@@ -57,7 +60,7 @@ class Params(ctypes.Structure):
                 ("advect_mode", ctypes.c_int), ("device", ctypes.c_int), ("visc", ctypes.c_float),
                 ("diff", ctypes.c_float), ("vorticity", ctypes.c_float), ("damp", ctypes.c_float),
                 ("slab_index", ctypes.c_int), ("slab_count", ctypes.c_int), ("slab_rows", ctypes.c_int),
-                ("slab_halo", ctypes.c_int), ("n_fluids", ctypes.c_int), ("reserved", ctypes.c_int * 1)]
+                ("slab_halo", ctypes.c_int), ("n_fluids", ctypes.c_int), ("fs_type", ctypes.c_int)]
 
 
 class Source(ctypes.Structure):
@@ -124,6 +127,12 @@ def lib():
     L.fluid_ctx_set_overlap.argtypes = [_vp, _ci]
     L.fluid_ctx_set_advect_kernel.argtypes = [_vp, _ci]
     L.fluid_ctx_set_sparse_sources.argtypes = [_vp, _ci]
+    _u8 = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+    L.fluid_ctx_reset_cell_info.argtypes = [_vp]
+    L.fluid_ctx_disable_edges.argtypes = [_vp, _ci, ctypes.POINTER(_ci)]
+    L.fluid_ctx_add_square_border.argtypes = [_vp]
+    L.fluid_ctx_set_cell_info.argtypes = [_vp, _u8, _ci]
+    L.fluid_ctx_get_cell_info.argtypes = [_vp, _u8]
     L.fluid_ctx_render.argtypes = [_vp, _ci, _f32, _f32, _vp]
     L.fluid_ctx_division_window.argtypes = [_vp, _cf, ctypes.POINTER(_ci), ctypes.POINTER(_ci)]
     L.fluid_ctx_upload_local.argtypes = [_vp, _ci, _f32]
@@ -218,7 +227,7 @@ class FluidSystem:
         self.batch = 1
 
     def Setup(self, N, visc=0.0, diff=0.0, vorticity=0.0, damp=0.0, gs_order=GS_WAVEFRONT, gs_iters=20,
-              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1, slab=None, slab_halo=0, n_fluids=1):
+              advect_mode=ADVECT_MIDPOINT, batch=1, device=-1, slab=None, slab_halo=0, n_fluids=1, fs_type=TYPE_ORIGINAL):
         """slab = (index, count, rows): this context is one row slab of a global N x (rows*count) grid;
         slab = (0, 1, rows): a whole non-square grid of N x rows."""
         self.close()
@@ -227,6 +236,7 @@ class FluidSystem:
         p.N, p.batch, p.gs_iters, p.gs_order, p.advect_mode, p.device = N, batch, gs_iters, gs_order, advect_mode, device
         p.visc, p.diff, p.vorticity, p.damp = visc, diff, vorticity, damp
         p.n_fluids = n_fluids
+        p.fs_type = fs_type
         self.NYG = N
         if slab is not None:
             p.slab_index, p.slab_count, p.slab_rows = slab
@@ -335,6 +345,23 @@ class FluidSystem:
     def SetOverlap(self, on): check(lib().fluid_ctx_set_overlap(self.h, 1 if on else 0))
     def SetAdvectKernel(self, which): check(lib().fluid_ctx_set_advect_kernel(self.h, which))
     def SetSparseSources(self, on): check(lib().fluid_ctx_set_sparse_sources(self.h, 1 if on else 0))
+
+    # cell map of a TYPE_ORIGINAL_BORDERED context (FluidSystem::GetInfo / DisableEdge / AddBorder(SquareBorder))
+    def ResetCellInfo(self): check(lib().fluid_ctx_reset_cell_info(self.h))
+    def AddSquareBorder(self): check(lib().fluid_ctx_add_square_border(self.h))
+
+    def DisableEdges(self, edges):
+        flat = [int(v) for e in edges for v in e]
+        arr = (ctypes.c_int * max(1, len(flat)))(*flat)
+        check(lib().fluid_ctx_disable_edges(self.h, len(flat) // 4, arr))
+
+    def SetCellInfo(self, info, recalc=False):
+        check(lib().fluid_ctx_set_cell_info(self.h, np.ascontiguousarray(info, np.uint8).ravel(), 1 if recalc else 0))
+
+    def GetInfo(self):
+        out = np.empty((self.N + 2) ** 2, np.uint8)
+        check(lib().fluid_ctx_get_cell_info(self.h, out))
+        return out
 
     def SetWavefrontTile(self, tile): check(lib().fluid_ctx_set_wavefront_tile(self.h, tile))
 

@@ -54,6 +54,26 @@ typedef enum fluid_advect_mode {
 	FLUID_ADVECT_EULER = 1     /* EulerBack, FluidSystem.h:208-219 (Stam's original, uncalled) */
 } fluid_advect_mode;
 
+/* Solver type (FluidSystem::FSType, FluidSystem.h:10-17; SetType, FluidSystem.cpp:69-99).
+ * ORIGINAL          = VelStep1  + DensStep1   (the path north_star names; every fast kernel serves it)
+ * ORIGINAL_BORDERED = VelStep1B + DensStep1BS (FluidSystem.cpp:378-398, 301-311): the same stencils masked per cell by
+ *                     cellInfo (FluidCode.h:61-73) -- internal walls, object cells -- with no SetBorder in solve,
+ *                     projection and advection.  Its first AddArrDt adds the Y source to vX, as the reference does
+ *                     (FluidSystem.cpp:380).  Every primitive of such a context (lin_solve, blur, project, advect,
+ *                     vel_step, dens_step, step) is the B variant; whole grids only (no row slabs). */
+typedef enum fluid_fs_type {
+	FLUID_TYPE_ORIGINAL = 0,
+	FLUID_TYPE_ORIGINAL_BORDERED = 1
+} fluid_fs_type;
+
+/* cellInfo bits (enum CellInfo, FluidCode.h:61-73) */
+#define FLUID_CELL_LEFT 1
+#define FLUID_CELL_RIGHT 2
+#define FLUID_CELL_TOP 4
+#define FLUID_CELL_BOTTOM 8
+#define FLUID_CELL_FLUID 16
+#define FLUID_CELL_OBJECT 32
+
 /* Field ids of a context: the Curr/Prev halves of the reference's FlipFlopArr
  * members vX, vY, densList[0] (FluidSystem.h:157-160, FluidCode.h:15-44). */
 typedef enum fluid_field {
@@ -104,7 +124,7 @@ typedef struct fluid_params {
 	int slab_index, slab_count, slab_rows;
 	int slab_halo;    /* 0 = default 48 rows; >= 44 */
 	int n_fluids;     /* density fields advanced by dens_step (fluid_count, FluidSystem.cpp:21); 0 = 1 */
-	int reserved[1];  /* must be 0 */
+	int fs_type;      /* fluid_fs_type: which pair of step functions SetType would pick (FluidSystem.cpp:69-99); 0 = ORIGINAL */
 } fluid_params;
 
 typedef struct fluid_ctx fluid_ctx;
@@ -233,6 +253,21 @@ int fluid_ctx_set_advect_kernel(fluid_ctx *ctx, int which);
  * the field, almost no writes) on grids larger than 128^2; 0 = zero-fill and add densely, as the reference does.
  * Results identical. */
 int fluid_ctx_set_sparse_sources(fluid_ctx *ctx, int on);
+/* ---- cell map of a FLUID_TYPE_ORIGINAL_BORDERED context ------------------ *
+ * The reference rebuilds cellInfo at the top of every Update: ResetCellInfo, colliders, CalcBorderFromContent,
+ * borders (FluidSystem.cpp:112-115).  Without moving objects that yields the same map every frame, so a context
+ * keeps ONE map and uses it until the host changes it.  A new context holds ResetCellInfo + CalcBorderFromContent
+ * (all interior cells FLUID, walls along the outer ring).  Dense host maps are (N+2)^2 bytes, ID(i,j) order. */
+/* ResetCellInfo + CalcBorderFromContent (FluidSystem.cpp:1215-1232, 1185-1213). */
+int fluid_ctx_reset_cell_info(fluid_ctx *ctx);
+/* DisableEdge (FluidSystem.cpp:1388-1408) for n edges, 4 ints each: x0, y0, x1, y1 (adjacent cells). */
+int fluid_ctx_disable_edges(fluid_ctx *ctx, int n, const int *edges);
+/* SquareBorder::WriteBorder (FluidBorder.cpp:4-19): the shipped scene's closed square wall around the centre. */
+int fluid_ctx_add_square_border(fluid_ctx *ctx);
+/* Replace / read the whole map (what a collider or a custom FluidBorder would have produced, FluidSystem.h GetInfo).
+ * recalc != 0: run CalcBorderFromContent on the uploaded FLUID / OBJECT bits afterwards. */
+int fluid_ctx_set_cell_info(fluid_ctx *ctx, const unsigned char *host_info, int recalc);
+int fluid_ctx_get_cell_info(fluid_ctx *ctx, unsigned char *host_info);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
 int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur

@@ -39,6 +39,12 @@ def golden_hashes():
 
 
 @pytest.fixture(scope="session")
+def golden_bordered():
+    """FSType::ORIGINAL_BORDERED frames of the unmodified reference (make_golden.py: bordered_frames)."""
+    return json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["bordered_frames"]
+
+
+@pytest.fixture(scope="session")
 def golden_fields():
     return np.load(os.path.join(GOLDEN, "golden_fields.npz"))
 

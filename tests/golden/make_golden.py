@@ -55,6 +55,26 @@ def frames():
     return out
 
 
+def bordered_sources(N):
+    c = N // 2
+    return op.stam_sources(N) + [(0, c + 3, c - 2, 0, 4.0), (1, 3, 3, 0, -6.0), (2, c - N // 4, c, 1, 0.8), (0, 5, N - 3, 2, 0.7)]
+
+
+def bordered_frames():
+    """FSType::ORIGINAL_BORDERED (VelStep1B + DensStep1BS), with the shipped scene's SquareBorder and its fluid
+    coefficients (SystemManager.cpp:103-108: diff 1e-6, visc 1e-4; N=192, vorticity 0.55, damp 0.1)."""
+    out = []
+    for N, steps, square, vort, damp in ((64, 100, True, 0.0, 0.0), (192, 10, True, 0.55, 0.1), (100, 25, False, 0.0, 0.0)):
+        sim = R.sim(N, 1e-4, 1e-6, vort, 20, damp, fstype=1, square_border=square)
+        sim.set_sources(bordered_sources(N))
+        sim.update(0.1, steps)
+        out.append(dict(N=N, steps=steps, visc=1e-4, diff=1e-6, vorticity=vort, damp=damp, square_border=square, dt=0.1, fstype=1,
+                        dens=op.fnv1a64(sim.field(2)), u=op.fnv1a64(sim.field(0)), v=op.fnv1a64(sim.field(1))))
+        sim.close()
+        print(out[-1])
+    return out
+
+
 def fields():
     z = {}
     for N in (12, 16):
@@ -128,7 +148,7 @@ def multifluid():
 if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "golden_multifluid.npz"), **multifluid())
     json.dump(dict(generator="tests/golden/make_golden.py", reference="surajiyer/Fluid-Simulation FluidSystem.cpp (unmodified)",
-                   compiler="g++ -std=c++20 -O2 -ffp-contract=off", frames=frames()),
+                   compiler="g++ -std=c++20 -O2 -ffp-contract=off", frames=frames(), bordered_frames=bordered_frames()),
               open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1)
     np.savez_compressed(os.path.join(HERE, "golden_fields.npz"), **fields())
     print("wrote", os.listdir(HERE))
