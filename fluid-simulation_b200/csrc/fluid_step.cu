@@ -381,7 +381,7 @@ int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::
 
 int dev_update(fluid_ctx* c, float dt) { return dev_update_hooks(c, dt, nullptr, {}); }
 
-// FluidRenderer::DoBuffer without a window: colourise + velocity lines of ensemble member `sim` into
+// FluidRenderer::DoBuffer without a window (color_rgb: 3 floats per fluid): colourise + velocity lines of ensemble member `sim` into
 // device buffers, then (optionally) to dense host arrays.
 int dev_render(fluid_ctx* c, int sim, const float* color_rgb, float* host_pixels, float* host_lines)
 {
@@ -392,9 +392,14 @@ int dev_render(fluid_ctx* c, int sim, const float* color_rgb, float* host_pixels
 	if (!c->d_pixels) CU_TRY(cudaMalloc(&c->d_pixels, cells * 3 * sizeof(float)));
 	if (host_lines && !c->d_lines) CU_TRY(cudaMalloc(&c->d_lines, cells * 4 * sizeof(float)));
 	const long long off = (long long) sim * c->g.plane;
-	LAUNCH(k_colourise, dim3(cdiv(c->g.N + 2, 32), cdiv(c->g.NY + 2, 8), 1), kBlk2D, 0, c->stream, c->g, c->f[FLUID_DENS] + off,
-	       c->f[FLUID_U] + off, c->f[FLUID_V] + off, color_rgb[0], color_rgb[1], color_rgb[2], c->d_pixels,
-	       host_lines ? c->d_lines : nullptr);
+	RenderFluids rf = {};
+	rf.n = c->n_fluids;
+	for (int fl = 0; fl < c->n_fluids; fl++) {
+		rf.dens[fl] = c->f[FLUID_DENS_OF(fl)] + off;
+		for (int k = 0; k < 3; k++) rf.col[fl][k] = color_rgb[3 * fl + k];
+	}
+	LAUNCH(k_colourise, dim3(cdiv(c->g.N + 2, 32), cdiv(c->g.NY + 2, 8), 1), kBlk2D, 0, c->stream, c->g, rf, c->d_info, c->f[FLUID_U] + off,
+	       c->f[FLUID_V] + off, c->d_pixels, host_lines ? c->d_lines : nullptr);
 	CU_TRY(cudaMemcpyAsync(host_pixels, c->d_pixels, cells * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
 	if (host_lines) CU_TRY(cudaMemcpyAsync(host_lines, c->d_lines, cells * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
 	CU_TRY(cudaStreamSynchronize(c->stream));

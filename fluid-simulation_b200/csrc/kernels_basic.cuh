@@ -501,14 +501,21 @@ __global__ void __launch_bounds__(256) k_vort_apply(GridDesc g, float* __restric
 
 // ---------------------------------------------------------------------------
 // Headless stand-in for the display path: the per-cell colourise loop and the
-// velocity line list of FluidRenderer::DoBuffer (FluidRenderer.cpp:56-84, 97-132) for one fluid,
-// written to dense device buffers instead of a GL texture / vertex buffer (graphics APIs are
-// unavailable on this box).  Cells of the grid's outer ring are not FLUID after ResetCellInfo
-// (FluidSystem.cpp:1215-1232) and come out green; there are no OBJECT cells on the ORIGINAL path.
+// velocity line list of FluidRenderer::DoBuffer (FluidRenderer.cpp:56-84, 97-132), written to dense device
+// buffers instead of a GL texture / vertex buffer (graphics APIs are unavailable on this box).
+// FLUID cells: every fluid's colour weighted by its density, normalised where the summed density exceeds 1
+// (:106-119); OBJECT cells magenta (:121-123); anything else green.  info == nullptr: the map ResetCellInfo
+// leaves (FluidSystem.cpp:1215-1232: outer ring not FLUID, no OBJECT cells), which the ORIGINAL path never changes.
 // pixels: (N+2)^2 x 3 floats, lines: (N+2)^2 x 4 floats (x0, y0, x1, y1), both indexed by ID(i,j).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_colourise(GridDesc g, const float* __restrict__ db, const float* __restrict__ ub,
-						    const float* __restrict__ vb, float cr, float cg, float cb,
+struct RenderFluids {
+	const float* dens[8];
+	float col[8][3];
+	int n;
+};
+
+__global__ void __launch_bounds__(256) k_colourise(GridDesc g, RenderFluids fl, const unsigned char* __restrict__ info,
+						    const float* __restrict__ ub, const float* __restrict__ vb,
 						    float* __restrict__ pixels, float* __restrict__ lines)
 {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -517,18 +524,23 @@ __global__ void __launch_bounds__(256) k_colourise(GridDesc g, const float* __re
 	const long long id = cell(g, i, j);
 	const long long out = (long long) i + (long long) (g.N + 2) * j;
 	float r = 0.f, gg = 0.f, b = 0.f;
-	if (i >= 1 && i <= g.N && j >= 1 && j <= g.NY) {
-		const float d = __ldg(db + id);
+	const unsigned char m = info ? info[id] : (unsigned char) ((i >= 1 && i <= g.N && j >= 1 && j <= g.NY) ? 31 : 15);
+	if (m & 16) {
 		float d_total = 0.f;
-		d_total += d;
-		r += cr * d;
-		gg += cg * d;
-		b += cb * d;
+		for (int n = 0; n < fl.n; n++) {
+			const float d = __ldg(fl.dens[n] + id);
+			d_total += d;
+			r += fl.col[n][0] * d;
+			gg += fl.col[n][1] * d;
+			b += fl.col[n][2] * d;
+		}
 		if (d_total > 1) {
 			r = div_exact(r, d_total);
 			gg = div_exact(gg, d_total);
 			b = div_exact(b, d_total);
 		}
+	} else if (m & 32) {
+		b = r = 1.f;
 	} else {
 		gg = 1.f;
 	}

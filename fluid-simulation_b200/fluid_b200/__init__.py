@@ -334,11 +334,13 @@ class FluidSystem:
     def SetTuning(self, rb_tile_sweeps): check(lib().fluid_ctx_set_tuning(self.h, rb_tile_sweeps))
 
     def Render(self, color=(1.0, 1.0, 1.0), sim=0, lines=True):
-        """FluidRenderer::DoBuffer headless: (pixels[(N+2)^2,3], lines[(N+2)^2,4] or None)."""
+        """FluidRenderer::DoBuffer headless: (pixels[(N+2)^2,3], lines[(N+2)^2,4] or None).
+        color: 3 floats per fluid of the context."""
         n = (self.N + 2) ** 2
         px = np.empty(n * 3, np.float32)
         ln = np.empty(n * 4, np.float32) if lines else None
-        check(lib().fluid_ctx_render(self.h, sim, np.asarray(color, np.float32), px, ln.ctypes.data if lines else None))
+        col = np.ascontiguousarray(np.asarray(color, np.float32).ravel())
+        check(lib().fluid_ctx_render(self.h, sim, col, px, ln.ctypes.data if lines else None))
         return px.reshape(n, 3), (ln.reshape(n, 4) if lines else None)
 
     def SetStreamKernel(self, on): check(lib().fluid_ctx_set_stream_kernel(self.h, 1 if on else 0))

@@ -338,10 +338,12 @@ int fluid_ctx_download_local(fluid_ctx *ctx, int field, float *host);
 int fluid_ctx_local_rows(fluid_ctx *ctx, int *rows_stored, int *first_global_row);
 
 /* Headless display path: the colourise loop and the velocity line list of
- * FluidRenderer::DoBuffer (FluidRenderer.cpp:56-84, 97-132) for one fluid of colour color_rgb,
- * computed on the device and copied to dense host arrays: host_pixels (N+2)^2 x 3 floats,
- * host_lines (N+2)^2 x 4 floats or NULL.  No window, texture upload or GL interop: graphics APIs
- * are unavailable on this box. */
+ * FluidRenderer::DoBuffer (FluidRenderer.cpp:56-84, 97-132) computed on the device and copied to dense host
+ * arrays: host_pixels (N+2)^2 x 3 floats, host_lines (N+2)^2 x 4 floats or NULL.  color_rgb holds 3 floats per
+ * fluid of the context (FluidProps::color, FluidCode.h:50): FLUID cells get every fluid's colour weighted by its
+ * density, normalised where the summed density exceeds 1; OBJECT cells (bordered contexts' cell map) are
+ * magenta, all other cells green.  No window, texture upload or GL interop: graphics APIs are unavailable on
+ * this box. */
 int fluid_ctx_render(fluid_ctx *ctx, int sim, const float *color_rgb, float *host_pixels, float *host_lines);
 
 /* Per-primitive device time inside fluid_ctx_step / vel_step / dens_step: when

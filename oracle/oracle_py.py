@@ -90,7 +90,7 @@ class Oracle:
         L.oracle_damp.argtypes = [c_int, _f32p, c_float, c_float]
         L.oracle_update.argtypes = [c_int] + [_f32p] * 6 + [c_int, c_void_p, c_float, c_float, c_float, c_int, c_int,
                                                            c_int, c_float, c_float, c_int]
-        L.oracle_render.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, _f32p, _f32p]
+        L.oracle_render.argtypes = [c_int, c_int, c_void_p, c_void_p, _f32p, _f32p, _f32p, _f32p, _f32p]
         L.oracle_total_inner_mass.argtypes = [c_int, _f32p]
         L.oracle_total_inner_mass.restype = c_float
         L.oracle_set_threads.argtypes = [c_int]
@@ -199,10 +199,17 @@ class Oracle:
                                len(sources), ctypes.cast(arr, c_void_p), visc, diff, dt, iters, order, mode, vorticity,
                                damp, nsteps)
 
-    def render(self, N, dens, u, v, color):
+    def render(self, N, dens, u, v, color, info=None):
+        """dens: one array or a list of arrays (one per fluid); color: 3 floats per fluid; info: cell map or None."""
         n = (N + 2) ** 2
+        if isinstance(dens, np.ndarray):
+            dens = [dens]
+        dens = [np.ascontiguousarray(d, np.float32) for d in dens]
+        ptrs = (c_void_p * len(dens))(*[d.ctypes.data for d in dens])
         px, ln = np.empty(n * 3, np.float32), np.empty(n * 4, np.float32)
-        self.L.oracle_render(N, dens, u, v, np.asarray(color, np.float32), px, ln)
+        inf = None if info is None else np.ascontiguousarray(info, np.uint8)
+        self.L.oracle_render(N, len(dens), ctypes.cast(ptrs, c_void_p), None if inf is None else inf.ctypes.data, u, v,
+                             np.ascontiguousarray(np.asarray(color, np.float32).ravel()), px, ln)
         return px.reshape(n, 3), ln.reshape(n, 4)
 
 

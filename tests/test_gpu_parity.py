@@ -701,6 +701,33 @@ def test_headless_render_matches_restated_renderer_loop(fl, oracle):
     g = px.reshape(N + 2, N + 2, 3)
     assert np.all(g[0, :, 1] == 1) and np.all(g[0, :, 0] == 0)  # outer ring is green
     fs.close()
+    # the shipped scene: two fluids with their own colours (SystemManager.cpp:103-108), summed and normalised per
+    # cell (FluidRenderer.cpp:106-119), and a cell map with OBJECT cells (magenta, :121-123)
+    colors = ((0.05, 0.05, 1.0), (1.0, 0.4, 0.05))
+    d2 = np.abs(rand_field(rng, N, 0.9))
+    d2[5 * (N + 2):9 * (N + 2)] = 0.0
+    fs = fl.FluidSystem().Setup(N, n_fluids=2)
+    for fid, a in ((fl.dens_of(0), d), (fl.dens_of(1), d2), (fl.U, u), (fl.V, v)):
+        fs.upload(fid, a)
+    px, ln = fs.Render(colors)
+    want_px, want_ln = oracle.render(N, [d, d2], u, v, colors)
+    assert_bits(px, want_px, "two fluids: pixels")
+    assert_bits(ln, want_ln, "two fluids: velocity lines")
+    fs.close()
+    info = oracle.make_cell_info(N, True)
+    m = info.reshape(N + 2, N + 2)
+    m[20:26, 30:41] = (m[20:26, 30:41] & ~np.uint8(16)) | np.uint8(32)
+    oracle.calc_border(N, info)
+    fs = fl.FluidSystem().Setup(N, n_fluids=2, fs_type=fl.TYPE_ORIGINAL_BORDERED)
+    fs.SetCellInfo(info)
+    for fid, a in ((fl.dens_of(0), d), (fl.dens_of(1), d2), (fl.U, u), (fl.V, v)):
+        fs.upload(fid, a)
+    px, _ = fs.Render(colors, lines=False)
+    want_px, _ = oracle.render(N, [d, d2], u, v, colors, info)
+    assert_bits(px, want_px, "cell map with objects: pixels")
+    g = px.reshape(N + 2, N + 2, 3)
+    assert np.all(g[20:26, 30:41] == np.array([1, 0, 1], np.float32))
+    fs.close()
 
 
 @pytest.mark.parametrize("order", [0, 1])
