@@ -43,6 +43,10 @@ def parse():
     ap.add_argument("--order", default="redblack", choices=["redblack", "wavefront"])
     ap.add_argument("--strong", action="store_true", help="N>1 GPUs: split ONE N x N grid into row slabs (strong scaling) "
                     "instead of N rows per GPU (weak scaling, the default)")
+    ap.add_argument("--ensemble", default="", metavar="MxN", help="BASELINE config 5: M independent N x N simulations with varied source "
+                    "positions, one launch per substep over all members; with several GPUs the members are dealt out as plain "
+                    "replicas (M/GPUs each, no communication).  Example: --ensemble 512x512")
+    ap.add_argument("--no-variable-dt", action="store_true", help="skip the extra pass that feeds a different dt every frame")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -222,19 +226,120 @@ def run_reference(args):
         one_step()
     dt = time.perf_counter() - t0
     value = cores * sample_n * sample_n * args.steps / dt
+    try:  # one core on a larger grid, beside the all-cores figure (reported, not the line's value)
+        single = cpu_baseline_single(2048, 1)["value"]
+    except Exception:
+        single = None
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "N=%d single-GPU throughput run (BASELINE config 3): dt=0.1 visc=diff=1e-4, 20 GS iterations, "
-                               "source S1; CPU arm: bounded sample, one N=%d simulation per host core per step" % (args.n, sample_n),
-                   "N": args.n, "sample_N": sample_n},
+        "config": {"workload": "BOUNDED SAMPLE of BASELINE config 3 (N=%d): one N=%d simulation per host core per step (%d cores), "
+                               "dt=0.1 visc=diff=1e-4, 20 GS iterations, source S1; the reference solver is single-threaded, one N=%d "
+                               "frame costs one core ~70 s" % (args.n, sample_n, cores, args.n),
+                   "N": args.n, "sample_N": sample_n, "single_core_N2048": single},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if have_ref else "port",
                          "sample": "%d independent N=%d simulations (one per core), %d steps" % (cores, sample_n, args.steps)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
+    return 0
+
+
+def slab_self_check(fl, np, torch, dist, rank, world, local):
+    """Driver-side evidence that the multi-rank path computes the right thing: before the timed region every rank
+    advances one slab of a small global grid (2048 columns x 1024 rows per rank: large enough for the streaming
+    relaxation, the streamed Blur and the row-window advect, i.e. the kernels the timed run uses) over the SAME
+    stream-ordered NCCL transport, the owned rows are assembled on rank 0 and compared, bit for bit, with one
+    non-square single-context run of the whole grid.  Returns "bitwise" or raises."""
+    from fluid_b200.slabs import NcclExchange
+    N, rows, steps = 2048, 1024, 2
+    NY = rows * world
+    src = [(fl.DENS, N // 2, NY // 2, fl.SRC_PREV_SET, 100.0), (fl.U, N // 2, NY // 2, fl.SRC_PREV_SET, 5.0),
+           (fl.V, N // 2, NY // 2, fl.SRC_PREV_SET, 5.0), (fl.U, 100, rows, fl.SRC_PREV_SET, -3.0), (fl.DENS, 1500, rows + 1, fl.SRC_PREV_SET, 40.0)]
+    fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=fl.GS_REDBLACK, gs_iters=ITERS, device=local, slab=(rank, world, rows))
+    fs.SetFastDivision(2)
+    tr = NcclExchange(fs, rank, world, local)
+    fs.SetSources(src)
+    fs.Update(DT, steps)
+    fs.Sync()
+    parts = []
+    for fid in (fl.U, fl.V, fl.DENS):
+        host = np.zeros((N + 2) * (NY + 2), np.float32)
+        fs.download(fid, out=host)  # writes the rows this rank owns (and the wall rows at the two ends)
+        t = torch.from_numpy(host.view(np.int32)).to("cuda:%d" % local)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)  # owned rows are disjoint: integer sum of bit patterns assembles the field
+        parts.append(t.cpu().numpy().view(np.float32))
+    del tr
+    fs.close()
+    verdict = "bitwise"
+    if rank == 0:
+        one = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=fl.GS_REDBLACK, gs_iters=ITERS, device=local, slab=(0, 1, NY))
+        one.SetFastDivision(2)
+        one.SetSources(src)
+        one.Update(DT, steps)
+        for fid, got, name in zip((fl.U, fl.V, fl.DENS), parts, "u v dens".split()):
+            want = one.download(fid)
+            if want.tobytes() != got.tobytes():
+                verdict = "MISMATCH in %s: %d of %d values differ" % (name, int((want.view(np.uint32) != got.view(np.uint32)).sum()), want.size)
+                break
+        one.close()
+    flag = torch.tensor([0 if verdict == "bitwise" else 1], device="cuda:%d" % local)
+    dist.broadcast(flag, 0)
+    if int(flag.item()) != 0:
+        raise SystemExit("bench.py: slab self-check failed: %s" % verdict)
+    return "bitwise (2048 x %d grid as %d NCCL slabs vs one context, %d frames, u v dens)" % (NY, world, steps)
+
+
+def measure_variable_dt(fs, steps):
+    """The reference's main loop feeds the solver its measured frame time (SystemManager.cpp:49-52), so c = 1 + 4*dt*coef*N^2
+    changes every frame and a proven short division never comes into play: the solves run with the exact division on the
+    tile kernels.  Device time of `steps` frames with a different dt each, CUDA events per frame."""
+    total = 0.0
+    for k in range(steps):
+        fs.Update(DT * (1.0 + 0.003 * (k + 1)), 1)
+        total += fs.LastStepMs()
+    return total / steps
+
+
+def run_ensemble(args, fl, np, torch, rank, world, local, dist):
+    """BASELINE config 5: M independent N x N simulations, one launch per substep over all members; replicas across GPUs."""
+    M, N = (int(v) for v in args.ensemble.lower().split("x"))
+    if M % world:
+        raise SystemExit("bench.py --ensemble: the number of members must be divisible by the number of GPUs")
+    mine = M // world
+    fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=fl.GS_REDBLACK, gs_iters=ITERS, batch=mine, device=local)
+    for b in range(mine):
+        g = rank * mine + b  # SURVEY 8(d): member b puts S1 at (1 + 37 b mod N, 1 + 101 b mod N)
+        cx, cy = 1 + (37 * g) % N, 1 + (101 * g) % N
+        fs.SetSources([(fl.DENS, cx, cy, fl.SRC_PREV_SET, 100.0), (fl.U, cx, cy, fl.SRC_PREV_SET, 5.0), (fl.V, cx, cy, fl.SRC_PREV_SET, 5.0)], sim=b)
+    sampler = ClockSampler(local)
+    sampler.start()
+    fs.Update(DT, max(args.warmup, 3))
+    fs.Sync()
+    barrier_sync(dist, local)
+    sampler.begin()
+    fl.lib().fluid_launch_count_reset()
+    fs.Update(DT, args.steps)
+    fs.Sync()
+    barrier_sync(dist, local)
+    sampler.end()
+    ms = max_over_ranks(dist, local, fs.LastStepMs())
+    launches = int(fl.lib().fluid_launch_count())
+    clocks = sampler.stop()
+    fs.close()
+    if rank == 0:
+        emit({"metric": METRIC, "value": float(M) * N * N * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+              "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+              "dtype": "f32", "data": "synthetic",
+              "config": {"workload": "ensemble (BASELINE config 5): %d independent N=%d simulations, source S1 at a different cell per member, "
+                                     "dt=0.1 visc=diff=1e-4, 20 GS iterations, red-black, one launch per substep over all members" % (M, N),
+                         "members": M, "N": N, "parallelism": "%d GPU(s), %d members each, replicas (no communication)" % (world, mine),
+                         "l2": "inputs larger than L2 (six %.0f MB fields per GPU vs 126 MB L2), no explicit flush" % (4e-6 * mine * (N + 2) ** 2)},
+              "clocks": clocks, "gpu_launches": launches, "e2e": None, "roofline": None, "cpu_baseline": None})
+    if dist is not None:
+        dist.destroy_process_group()
     return 0
 
 
@@ -248,9 +353,12 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device; this framework has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     fl.check(fl.lib().fluid_set_device(local))
+    if args.ensemble:
+        return run_ensemble(args, fl, np, torch, rank, world, local, dist)
     N = args.n
     order = fl.GS_REDBLACK if args.order == "redblack" else fl.GS_WAVEFRONT
     L = fl.lib()
+    slab_check = slab_self_check(fl, np, torch, dist, rank, world, local) if world > 1 else None
 
     # N GPUs: row slabs of a global N x (N*world) grid, one slab of N rows per GPU (weak scaling, h = 1/N),
     # halos over NCCL send/recv between neighbouring ranks (fluid_b200.slabs.NcclExchange)
@@ -303,6 +411,9 @@ def run_b200(args):
     prof = fs.Profile(reset=True)
     fs.SetProfiling(False)
     fs.SetOverlap(True)
+    var_ms = None
+    if not args.no_variable_dt and world == 1:
+        var_ms = measure_variable_dt(fs, max(3, min(args.steps, 8)))
     barrier_sync(dist, local)
     ms = max_over_ranks(dist, local, dev_ms)
     wall_ms = max_over_ranks(dist, local, wall_ms)
@@ -333,6 +444,8 @@ def run_b200(args):
         "bound": "hbm", "kernel": "%s; %d launches in the profiled pass" % (unit_name, gs_launches),
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
         "traffic": traffic, "traffic_kernel": tkernel,
+        "traffic_source": "profiles/roofline_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed "
+                          "`ncu --set full` capture of this kernel -- a constant read from that file, NOT measured in this run",
         "algorithmic_bytes_per_launch": gs_bytes / units,
         "ms_per_launch": ms_unit,
         "dram_gbs": (traffic / (ms_unit * 1e-3) / 1e9) if traffic else None,
@@ -373,6 +486,12 @@ def run_b200(args):
                        % (world, rows_per_gpu, N, rows_per_gpu * world, N, xcalls // args.steps, xbytes / args.steps / 1e6)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": roofline, "cpu_baseline": cpu,
+            "slab_check": slab_check,
+            "variable_dt": None if var_ms is None else {
+                "ms_per_step": var_ms, "value": cells / (var_ms * 1e-3), "unit": UNIT,
+                "note": "a different dt every frame, as the reference's main loop feeds it (SystemManager.cpp:49-52): no divisor "
+                        "recurs, so no short division is ever proven and the diffusion solves and Blur run with the exact division "
+                        "(tile / pass kernels); the headline `value` is measured with the fixed dt BASELINE.json's configs name"},
         }
         emit(line)
     if dist is not None:
