@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--ensemble", default="", metavar="MxN", help="BASELINE config 5: M independent N x N simulations with varied source "
                     "positions, one launch per substep over all members; with several GPUs the members are dealt out as plain "
                     "replicas (M/GPUs each, no communication).  Example: --ensemble 512x512")
+    ap.add_argument("--transport", default="peer", choices=["peer", "nccl"], help="halo transport of a multi-GPU run: the library's own "
+                    "pushes through peer memory (CUDA IPC mappings, two small kernels per refresh) or NCCL send/recv")
     ap.add_argument("--no-variable-dt", action="store_true", help="skip the extra pass that feeds a different dt every frame")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -247,20 +249,20 @@ def run_reference(args):
     return 0
 
 
-def slab_self_check(fl, np, torch, dist, rank, world, local):
+def slab_self_check(fl, np, torch, dist, rank, world, local, transport_name):
     """Driver-side evidence that the multi-rank path computes the right thing: before the timed region every rank
     advances one slab of a small global grid (2048 columns x 1024 rows per rank: large enough for the streaming
     relaxation, the streamed Blur and the row-window advect, i.e. the kernels the timed run uses) over the SAME
     stream-ordered NCCL transport, the owned rows are assembled on rank 0 and compared, bit for bit, with one
     non-square single-context run of the whole grid.  Returns "bitwise" or raises."""
-    from fluid_b200.slabs import NcclExchange
+    from fluid_b200.slabs import NcclExchange, PeerExchange
     N, rows, steps = 2048, 1024, 2
     NY = rows * world
     src = [(fl.DENS, N // 2, NY // 2, fl.SRC_PREV_SET, 100.0), (fl.U, N // 2, NY // 2, fl.SRC_PREV_SET, 5.0),
            (fl.V, N // 2, NY // 2, fl.SRC_PREV_SET, 5.0), (fl.U, 100, rows, fl.SRC_PREV_SET, -3.0), (fl.DENS, 1500, rows + 1, fl.SRC_PREV_SET, 40.0)]
     fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=fl.GS_REDBLACK, gs_iters=ITERS, device=local, slab=(rank, world, rows))
     fs.SetFastDivision(2)
-    tr = NcclExchange(fs, rank, world, local)
+    tr = PeerExchange(fs, rank, world, local) if transport_name == "peer" else NcclExchange(fs, rank, world, local)
     fs.SetSources(src)
     fs.Update(DT, steps)
     fs.Sync()
@@ -271,6 +273,8 @@ def slab_self_check(fl, np, torch, dist, rank, world, local):
         t = torch.from_numpy(host.view(np.int32)).to("cuda:%d" % local)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)  # owned rows are disjoint: integer sum of bit patterns assembles the field
         parts.append(t.cpu().numpy().view(np.float32))
+    if transport_name == "peer":
+        tr.close()
     del tr
     fs.close()
     verdict = "bitwise"
@@ -289,7 +293,7 @@ def slab_self_check(fl, np, torch, dist, rank, world, local):
     dist.broadcast(flag, 0)
     if int(flag.item()) != 0:
         raise SystemExit("bench.py: slab self-check failed: %s" % verdict)
-    return "bitwise (2048 x %d grid as %d NCCL slabs vs one context, %d frames, u v dens)" % (NY, world, steps)
+    return "bitwise (2048 x %d grid as %d slabs over the %s transport vs one context, %d frames, u v dens)" % (NY, world, transport_name, steps)
 
 
 def measure_variable_dt(fs, steps):
@@ -358,7 +362,7 @@ def run_b200(args):
     N = args.n
     order = fl.GS_REDBLACK if args.order == "redblack" else fl.GS_WAVEFRONT
     L = fl.lib()
-    slab_check = slab_self_check(fl, np, torch, dist, rank, world, local) if world > 1 else None
+    slab_check = slab_self_check(fl, np, torch, dist, rank, world, local, args.transport) if world > 1 else None
 
     # N GPUs: row slabs of a global N x (N*world) grid, one slab of N rows per GPU (weak scaling, h = 1/N),
     # halos over NCCL send/recv between neighbouring ranks (fluid_b200.slabs.NcclExchange)
@@ -366,12 +370,12 @@ def run_b200(args):
     if world > 1:
         if order != fl.GS_REDBLACK:
             raise SystemExit("bench.py: row slabs need --order redblack")
-        from fluid_b200.slabs import NcclExchange
+        from fluid_b200.slabs import NcclExchange, PeerExchange
         rows = N // world if args.strong else N
         if args.strong and N % world:
             raise SystemExit("bench.py --strong: N must be divisible by the number of GPUs")
         fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local, slab=(rank, world, rows))
-        transport = NcclExchange(fs, rank, world, local)
+        transport = PeerExchange(fs, rank, world, local) if args.transport == "peer" else NcclExchange(fs, rank, world, local)
     else:
         fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local)
     rows_per_gpu = (N // world) if (world > 1 and args.strong) else N
@@ -469,6 +473,8 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_single()
+    if transport is not None and args.transport == "peer":
+        transport.close()  # all ranks: nobody may still be pushing into a block that is about to be freed
     fs.close()
 
     if rank == 0:
@@ -481,9 +487,13 @@ def run_b200(args):
                        "N": N, "gs_order": args.order, "gs_iters": ITERS, "advect": "midpoint",
                        "l2": "inputs larger than L2 (six %.0f MB fields vs 126 MB L2), no explicit flush" % (4e-6 * (N + 2) ** 2),
                        "parallelism": "1 GPU" if world == 1 else
-                       "%d row slabs of %d rows (global grid %d x %d, h=1/%d), 48-row overlapped halos refreshed at 6 points per step "
-                       "over NCCL send/recv between neighbouring ranks (%d exchange calls, %.1f MB sent per rank per step, timed)"
-                       % (world, rows_per_gpu, N, rows_per_gpu * world, N, xcalls // args.steps, xbytes / args.steps / 1e6)},
+                       "%d row slabs of %d rows (global grid %d x %d, h=1/%d), 48-row overlapped halos refreshed at 6 points per step, "
+                       "timed; transport: %s"
+                       % (world, rows_per_gpu, N, rows_per_gpu * world, N,
+                          "pushes into the neighbours' memory over NVLink, ordered by flag words, two kernels per refresh on the "
+                          "context's stream (csrc/fluid_peer.cu; blocks mapped with CUDA IPC)" if args.transport == "peer" else
+                          "NCCL send/recv between neighbouring ranks (%d exchange calls, %.1f MB sent per rank per step)"
+                          % (xcalls // args.steps, xbytes / args.steps / 1e6))},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": roofline, "cpu_baseline": cpu,
             "slab_check": slab_check,

@@ -98,6 +98,12 @@ struct fluid_ctx {
 	// fluid_update overlaps its bus transfers with the step: second stream + the two events that order them
 	cudaStream_t copy_stream = nullptr;
 	cudaEvent_t ev_dens_up = nullptr, ev_vel_done = nullptr;
+	// native halo transport (fluid_peer.cu): my inboxes + flags, the neighbours' (peer pointers), refresh counter
+	void* peer_block = nullptr;
+	unsigned int* peer_counter = nullptr;
+	void *peer_lower = nullptr, *peer_upper = nullptr;
+	bool peer_connected = false;
+	unsigned int peer_seq = 0;
 	int* d_oob = nullptr;
 	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
@@ -272,6 +278,8 @@ int dev_lin_solve_b(fluid_ctx* c, int b, float* x, const float* x0, float a, flo
 int dev_blur_b(fluid_ctx* c, int b, float* x, float* x0, float a, float cc);
 int dev_project_b(fluid_ctx* c, float* u, float* v, float* p, float* div);
 constexpr int kBndNone = -2; // advect: no SetBorder at all (Advect1B, FluidSystem.cpp:864-874)
+// fluid_peer.cu
+int peer_halo_exchange(fluid_ctx* c, int n, const int* ids);
 // fluid_core.cu
 int check_field_n(int f, int n);
 int check_distinct_n(int n_fields, std::initializer_list<int> ids);

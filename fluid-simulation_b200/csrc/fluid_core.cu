@@ -67,6 +67,8 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->ev_fork2) cudaEventDestroy(c->ev_fork2);
 	if (c->ev_join2) cudaEventDestroy(c->ev_join2);
 	if (c->d_oob) cudaFree(c->d_oob);
+	if (c->peer_block) cudaFree(c->peer_block);
+	if (c->peer_counter) cudaFree(c->peer_counter);
 	if (c->div_pending.stream) {
 		cudaStreamSynchronize(c->div_pending.stream);
 		cudaStreamDestroy(c->div_pending.stream);

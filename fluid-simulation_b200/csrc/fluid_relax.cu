@@ -240,6 +240,10 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool stream_ok) // stream_ok: 
 	if (per_chunk * nchunks > slots / 2) {
 		const long long waves = std::max(1LL, (per_chunk * nchunks + slots / 2) / slots);
 		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
+	} else {
+		// a thin grid (a row slab of a strongly scaled run: 1100 rows gave 380 tasks for 1776 warp slots): shorter
+		// chunks, down to 64 rows (25 % more rows computed per task), until the tasks fill the resident warps
+		nchunks = (int) std::max<long long>(nchunks, std::min<long long>(rows / 64, slots / per_chunk));
 	}
 	const int unit = 2 * kWallSplit; // chunk and wall task both an even number of rows: one colour phase per launch
 	// the bottom and top chunks run ~3S slower row steps next to their wall: make them that much shorter
@@ -526,6 +530,8 @@ static bool blur_stream_geometry(const fluid_ctx* c, StreamRect* rc)
 	if (per_chunk * nchunks > slots / 2) {
 		const long long waves = std::max(1LL, (per_chunk * nchunks + slots / 2) / slots);
 		nchunks = (int) std::max(1LL, std::min<long long>(rows / 32, (waves * slots) / per_chunk));
+	} else {
+		nchunks = (int) std::max<long long>(nchunks, std::min<long long>(rows / 48, slots / per_chunk)); // thin grids, see pass_geometry
 	}
 	const int shift = (nchunks > 2) ? 6 * kBlurL : 0;
 	rc->row_shift = shift;

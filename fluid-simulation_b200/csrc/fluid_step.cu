@@ -139,12 +139,14 @@ int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
 static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> arrays)
 {
 	if (c->slab_count <= 1) return FLUID_OK;
-	if (!c->exchange) return fail(FLUID_ERR_INVALID, "this context is a row slab but no exchange callback is set (fluid_ctx_set_exchange)");
+	if (!c->exchange && !c->peer_connected)
+		return fail(FLUID_ERR_INVALID, "this context is a row slab but no halo transport is set (fluid_ctx_set_exchange or fluid_ctx_peer_halo_connect)");
 	int ids[fluid_ctx::kMaxFields], n = 0;
 	for (const float* a : arrays)
 		for (int f = 0; f < c->n_fields; f++)
 			if (c->f[f] == a) ids[n++] = f;
 	ProfScope ps(c, FLUID_PROF_EXCHANGE);
+	if (c->peer_connected) return peer_halo_exchange(c, n, ids); // pushes through peer memory, two kernels on this stream
 	if (!c->exchange_stream_ordered) CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
 	const int rc = c->exchange(c->exchange_user, n, ids);
 	if (rc != 0) return fail(FLUID_ERR_CUDA, "halo exchange callback failed with code %d", rc);

@@ -39,6 +39,7 @@ EXPORTS = [
     "fluid_ctx_set_wavefront_tile", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap", "fluid_ctx_set_advect_kernel", "fluid_ctx_set_sparse_sources",
     "fluid_ctx_reset_cell_info", "fluid_ctx_disable_edges", "fluid_ctx_add_square_border", "fluid_ctx_set_cell_info",
     "fluid_ctx_get_cell_info",
+    "fluid_ctx_peer_halo_local", "fluid_ctx_peer_halo_connect", "fluid_ipc_export", "fluid_ipc_import", "fluid_ipc_close",
     "fluid_ctx_set_exchange", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
     "fluid_ctx_local_rows",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
@@ -133,6 +134,11 @@ def lib():
     L.fluid_ctx_add_square_border.argtypes = [_vp]
     L.fluid_ctx_set_cell_info.argtypes = [_vp, _u8, _ci]
     L.fluid_ctx_get_cell_info.argtypes = [_vp, _u8]
+    L.fluid_ctx_peer_halo_local.argtypes = [_vp, ctypes.POINTER(_vp), ctypes.POINTER(ctypes.c_size_t)]
+    L.fluid_ctx_peer_halo_connect.argtypes = [_vp, _vp, _vp]
+    L.fluid_ipc_export.argtypes = [_vp, ctypes.c_char_p]
+    L.fluid_ipc_import.argtypes = [ctypes.c_char_p, ctypes.POINTER(_vp)]
+    L.fluid_ipc_close.argtypes = [_vp]
     L.fluid_ctx_render.argtypes = [_vp, _ci, _f32, _f32, _vp]
     L.fluid_ctx_division_window.argtypes = [_vp, _cf, ctypes.POINTER(_ci), ctypes.POINTER(_ci)]
     L.fluid_ctx_upload_local.argtypes = [_vp, _ci, _f32]
@@ -209,6 +215,23 @@ def vort_confinement(N, u, v, vorticity): check(lib().fluid_vort_confinement(N, 
 def damp(N, vel, amount, dt): check(lib().fluid_damp(N, vel, amount, dt))
 
 
+def ipc_export(device_ptr):
+    """64-byte CUDA IPC handle of a device allocation of this process."""
+    buf = ctypes.create_string_buffer(64)
+    check(lib().fluid_ipc_export(device_ptr, buf))
+    return buf.raw
+
+
+def ipc_import(handle):
+    """Device address, in this process, of an allocation another process exported."""
+    p = _vp()
+    check(lib().fluid_ipc_import(handle, ctypes.byref(p)))
+    return p.value
+
+
+def ipc_close(device_ptr): check(lib().fluid_ipc_close(device_ptr))
+
+
 def pinned_empty(n_floats):
     """float32 numpy array backed by pinned host memory from fluid_host_alloc."""
     p = _vp()
@@ -269,6 +292,15 @@ class FluidSystem:
 
     def upload_local(self, field, host): check(lib().fluid_ctx_upload_local(self.h, field, host))
     def download_local(self, field, host): check(lib().fluid_ctx_download_local(self.h, field, host))
+
+    def PeerHaloLocal(self):
+        """(device address, bytes) of this slab's inbox/flag block (allocated on first call)."""
+        p, n = _vp(), ctypes.c_size_t()
+        check(lib().fluid_ctx_peer_halo_local(self.h, ctypes.byref(p), ctypes.byref(n)))
+        return p.value, n.value
+
+    def PeerHaloConnect(self, lower_block, upper_block):
+        check(lib().fluid_ctx_peer_halo_connect(self.h, lower_block, upper_block))
 
     def SetStream(self, stream_handle, exchange_stream_ordered=False):
         check(lib().fluid_ctx_set_stream(self.h, stream_handle, 1 if exchange_stream_ordered else 0))

@@ -92,6 +92,36 @@ class NcclExchange:
         self.bytes += sum(b.numel() * 4 for blk in blocks for b in (blk[0], blk[2]) if b is not None)
 
 
+class PeerExchange:
+    """Halo transport for one slab per process WITHOUT a per-refresh callback: the library pushes halo rows straight
+    into the neighbours' memory over NVLink (csrc/fluid_peer.cu).  This class only does the one-time set-up: every
+    rank exports its inbox block as a CUDA IPC handle, the handles travel over torch.distributed, neighbours map
+    each other's blocks.  torch is plumbing for the handshake only."""
+
+    def __init__(self, fs, rank, world, device):
+        import torch.distributed as dist
+        from . import ipc_export, ipc_import
+        self.fs, self.rank, self.world, self.dist = fs, rank, world, dist
+        self.calls = self.bytes = 0  # (refreshes are counted by the library's profile, not here)
+        block, nbytes = fs.PeerHaloLocal()
+        handles = [None] * world
+        dist.all_gather_object(handles, ipc_export(block))
+        self.lower = ipc_import(handles[rank - 1]) if rank > 0 else None
+        self.upper = ipc_import(handles[rank + 1]) if rank + 1 < world else None
+        fs.PeerHaloConnect(self.lower, self.upper)
+        dist.barrier()  # everybody connected before anybody steps
+
+    def close(self):
+        """Call on every rank BEFORE the contexts are destroyed: nobody may still be pushing into a block that goes away."""
+        from . import ipc_close
+        self.fs.Sync()
+        self.dist.barrier()
+        for p in (self.lower, self.upper):
+            if p:
+                ipc_close(p)
+        self.lower = self.upper = None
+
+
 class LocalSlabGroup:
     """`count` slabs of `rows` rows each in one process on one device: the multi-GPU
     code path on a single GPU.  Every slab steps in its own host thread (the

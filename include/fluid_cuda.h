@@ -298,6 +298,23 @@ int fluid_ctx_division_window(fluid_ctx *ctx, float divisor, int *lo_exp, int *h
  * Forcing entries use global rows.  FLUID_GS_REDBLACK only.                     */
 typedef int (*fluid_exchange_fn)(void *user, int nfields, const int *fields);
 int fluid_ctx_set_exchange(fluid_ctx *ctx, fluid_exchange_fn fn, void *user);
+/* Native transport: halo rows pushed straight into the neighbour's memory over NVLink and ordered by flag words,
+ * two small kernels per refresh on the context's stream (csrc/fluid_peer.cu) -- no callback, no host round trip,
+ * no collective.  Each slab owns one block (inboxes + flags):
+ *   fluid_ctx_peer_halo_local    allocates it (once) and returns its device address and size;
+ *   fluid_ctx_peer_halo_connect  takes the addresses of the lower / upper neighbour's blocks AS THIS PROCESS SEES
+ *                                THEM (NULL at the two ends): directly when all slabs live in one process with peer
+ *                                access enabled, else a mapping made with fluid_ipc_import from the handle the
+ *                                neighbour's process obtained with fluid_ipc_export (CUDA IPC, 64 bytes, to be sent
+ *                                over whatever channel the host has -- MPI, torch.distributed, a pipe).
+ * Every slab must be connected before any of them steps, all slabs must run the same sequence of calls, and the
+ * slabs must sit on DIFFERENT GPUs (a slab's pull kernel waits for its neighbours' push kernels).  A block must
+ * outlive every neighbour's last step. */
+int fluid_ctx_peer_halo_local(fluid_ctx *ctx, void **block, size_t *bytes);
+int fluid_ctx_peer_halo_connect(fluid_ctx *ctx, void *lower_block, void *upper_block);
+int fluid_ipc_export(void *device_ptr, unsigned char handle[64]);
+int fluid_ipc_import(const unsigned char handle[64], void **device_ptr);
+int fluid_ipc_close(void *device_ptr);
 /* Run the context on the caller's stream (a cudaStream_t; NULL = back to the
  * context's own).  With exchange_stream_ordered != 0 the library does not wait for
  * the stream before calling the exchange callback: the transport must then enqueue

@@ -1,4 +1,5 @@
-"""Run under torchrun (one rank per GPU): the row-slab path over real NCCL send/recv,
+"""Run under torchrun (one rank per GPU): the row-slab path over real NCCL send/recv (stream-ordered and
+host-synchronous) and over the library's own peer-memory transport (pushes through CUDA IPC mappings),
 checked bit for bit against the CPU red-black statement on rank 0.  Used by
 tests/test_gpu_nccl_slabs.py; exits non-zero on any mismatch."""
 import os
@@ -12,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, os.path.join(ROOT, "fluid-simulation_b200"))
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import fluid_b200 as fl  # noqa: E402
-from fluid_b200.slabs import NcclExchange  # noqa: E402
+from fluid_b200.slabs import NcclExchange, PeerExchange  # noqa: E402
 
 
 def main():
@@ -27,9 +28,13 @@ def main():
     c = N // 2
     src = [(2, c, c, 0, 100.0), (0, c, c, 0, 5.0), (1, c, c, 0, 5.0), (1, 9, rows, 0, 3.0), (0, 11, rows + 1, 0, -2.0)]
     ok = True
-    for stream_ordered in (True, False):
+    for stream_ordered in (True, False, "peer"):
         fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, device=local, slab=(rank, world, rows))
-        NcclExchange(fs, rank, world, local, stream_ordered=stream_ordered)
+        peer = None
+        if stream_ordered == "peer":
+            peer = PeerExchange(fs, rank, world, local)
+        else:
+            NcclExchange(fs, rank, world, local, stream_ordered=stream_ordered)
         fs.SetSources(src)
         for name, fid in (("u", fl.U), ("v", fl.V), ("d", fl.DENS)):
             fs.upload(fid, init[name])
@@ -53,6 +58,8 @@ def main():
                 same = got.tobytes() == want[name].tobytes()
                 print("stream_ordered=%s field %s: %s" % (stream_ordered, name, "bitwise equal" if same else "MISMATCH"))
                 ok &= same
+        if peer is not None:
+            peer.close()
         fs.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)

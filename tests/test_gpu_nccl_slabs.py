@@ -1,6 +1,7 @@
 """GPU suite, needs >= 2 GPUs (skipped on a single-GPU box): the row-slab decomposition over
 real NCCL send/recv, one process per GPU under torchrun, bit-compared with the CPU red-black
-statement; both the stream-ordered and the host-synchronous exchange are exercised."""
+statement; the stream-ordered and the host-synchronous NCCL exchange and the library's own peer-memory
+transport (csrc/fluid_peer.cu, CUDA IPC) are exercised."""
 import os
 import subprocess
 import sys
@@ -21,4 +22,4 @@ def test_two_rank_nccl_slabs_bitwise():
            "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tests", "helpers", "nccl_slab_check.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
-    assert out.stdout.count("bitwise equal") == 6, out.stdout
+    assert out.stdout.count("bitwise equal") == 9, out.stdout
