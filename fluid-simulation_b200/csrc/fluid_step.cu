@@ -49,21 +49,29 @@ static bool advect_rows_geometry(const fluid_ctx* c, AdvectTasks* tk)
 	return true;
 }
 
-template <bool VEL>
-static void launch_advect_rows(fluid_ctx* c, const AdvectTasks& tk, int b, float* oa, float* ob, const float* d0, const float* u, const float* v,
-			       float dtN)
+template <bool VEL, bool PARTIAL>
+static void launch_advect_rows_p(fluid_ctx* c, const AdvectTasks& tk, int b, float* oa, float* ob, const float* d0, const float* u, const float* v,
+				 float dtN)
 {
 	const dim3 grid(cdiv((long long) tk.nstrips * tk.nchunks, kAdvectWarps), c->batch);
 	const int nt = 32 * kAdvectWarps;
 	const bool euler = (c->advect_mode == FLUID_ADVECT_EULER);
 	const int lo = c->own_lo, hi = c->own_lo + c->slab_rows - 1;
 	if (c->slab_count > 1) {
-		if (euler) LAUNCH((k_advect_rows<true, 1, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, lo, hi);
-		else LAUNCH((k_advect_rows<true, 0, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, lo, hi);
+		if (euler) LAUNCH((k_advect_rows<true, 1, VEL, PARTIAL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, lo, hi);
+		else LAUNCH((k_advect_rows<true, 0, VEL, PARTIAL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, lo, hi);
 	} else {
-		if (euler) LAUNCH((k_advect_rows<false, 1, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, 1, 0);
-		else LAUNCH((k_advect_rows<false, 0, VEL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, 1, 0);
+		if (euler) LAUNCH((k_advect_rows<false, 1, VEL, PARTIAL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, 1, 0);
+		else LAUNCH((k_advect_rows<false, 0, VEL, PARTIAL>), grid, nt, 0, c->stream, c->g, tk, b, oa, ob, d0, u, v, dtN, c->d_oob, 1, 0);
 	}
+}
+
+template <bool VEL>
+static void launch_advect_rows(fluid_ctx* c, const AdvectTasks& tk, int b, float* oa, float* ob, const float* d0, const float* u, const float* v,
+			       float dtN)
+{
+	if (c->g.N % 128 == 0) launch_advect_rows_p<VEL, false>(c, tk, b, oa, ob, d0, u, v, dtN); // whole strips: no masking of cells
+	else launch_advect_rows_p<VEL, true>(c, tk, b, oa, ob, d0, u, v, dtN);
 }
 
 int dev_advect(fluid_ctx* c, int b, float* d, const float* d0, const float* u, const float* v, float dt)

@@ -33,29 +33,47 @@ struct RowWin {
 	float w[6];
 };
 
-// pf points at storage column 4q (clamped into the row) of row 0 of the field; col_l / col_r are the
-// offsets of the values only lane 0 / lane 31 must fetch themselves (their neighbours are other warps').
-__device__ __forceinline__ RowWin advect_load_row(const float* __restrict__ pf, int y, int pitch, int lane, int off_l, int off_r)
+// A row as it is FETCHED: the lane's float4 and, for lanes 0 and 31 only, the value beyond the warp's strip.
+// The neighbours' values are shuffled in one row step later (advect_finish_row), when the loads have long
+// landed: shuffling right behind the load made every warp wait out the memory latency at the top of each
+// row step (ncu: 42 % of all stall samples on that first shuffle, issue slots 48 % busy).
+struct RowRaw {
+	float4 c;
+	float l, r;
+};
+
+// pf points at storage column 4q (clamped into the row) of row 0 of the field; off_l / off_r are the offsets
+// of the values only lane 0 / lane 31 must fetch themselves (their neighbours are other warps').
+__device__ __forceinline__ RowRaw advect_fetch_row(const float* __restrict__ pf, int y, int pitch, int lane, int off_l, int off_r)
 {
-	RowWin r;
+	RowRaw r;
 	const float* p = pf + y * pitch;
-	const float4 c = __ldg(reinterpret_cast<const float4*>(p));
-	r.w[1] = c.x;
-	r.w[2] = c.y;
-	r.w[3] = c.z;
-	r.w[4] = c.w;
-	r.w[0] = __shfl_up_sync(0xffffffffu, c.w, 1);
-	r.w[5] = __shfl_down_sync(0xffffffffu, c.x, 1);
-	if (lane == 0) r.w[0] = __ldg(p + off_l);
-	if (lane == 31) r.w[5] = __ldg(p + off_r);
+	r.c = __ldg(reinterpret_cast<const float4*>(p));
+	r.l = r.r = 0.0f;
+	if (lane == 0) r.l = __ldg(p + off_l);
+	if (lane == 31) r.r = __ldg(p + off_r);
 	return r;
 }
 
-// BilinearCoeffs::calc (FluidCode.h:91-112) for one sample: clamped position -> cell (i0, local row jl)
-// and weights.  Same arithmetic as bilin_calc (kernels_basic.cuh), kept apart so that the window path
-// never forms an address.
+__device__ __forceinline__ RowWin advect_finish_row(const RowRaw& q, int lane)
+{
+	RowWin r;
+	r.w[1] = q.c.x;
+	r.w[2] = q.c.y;
+	r.w[3] = q.c.z;
+	r.w[4] = q.c.w;
+	const float l = __shfl_up_sync(0xffffffffu, q.c.w, 1);
+	const float rr = __shfl_down_sync(0xffffffffu, q.c.x, 1);
+	r.w[0] = (lane == 0) ? q.l : l;
+	r.w[5] = (lane == 31) ? q.r : rr;
+	return r;
+}
+
+// BilinearCoeffs::calc (FluidCode.h:91-112) for one sample: clamped position -> cell and weights.  The cell is
+// kept as floats (fi0 = trunc(px), exactly what (float)(int)px is for 0.5 <= px < 2^24; fjl = the LOCAL row):
+// the window path never needs them as integers, only their distance from the thread's own cell.
 struct BilinW {
-	int i0, jl;
+	float fi0, fjl;
 	float s0, s1, t0, t1;
 };
 
@@ -65,18 +83,18 @@ __device__ __forceinline__ BilinW advect_calc(const GridDesc& g, float px, float
 	BilinW r;
 	px = fminf(fmaxf(px, 0.5f), g.N + 0.5f);
 	py = fminf(fmaxf(py, 0.5f), g.NYG + 0.5f);
-	r.i0 = (int) px;
-	const int j0 = (int) py;
-	r.s1 = px - r.i0;
+	r.fi0 = truncf(px);
+	const float fj0 = truncf(py);
+	r.s1 = px - r.fi0;
 	r.s0 = 1 - r.s1;
-	r.t1 = py - j0;
+	r.t1 = py - fj0;
 	r.t0 = 1 - r.t1;
-	r.jl = j0;
+	r.fjl = fj0;
 	if (SLAB) {
-		r.jl = j0 - g.j0;
-		if (r.jl < 0 || r.jl > g.NY) {
+		r.fjl = fj0 - (float) g.j0; // small integers: exact
+		if (r.fjl < 0.0f || r.fjl > (float) g.NY) {
 			if (oob) *oob = 1;
-			r.jl = min(max(r.jl, 0), g.NY);
+			r.fjl = fminf(fmaxf(r.fjl, 0.0f), (float) g.NY);
 		}
 	}
 	return r;
@@ -85,7 +103,7 @@ __device__ __forceinline__ BilinW advect_calc(const GridDesc& g, float px, float
 // BilinearCoeffs::Eval (FluidCode.h:88) from memory: the general path.
 __device__ __forceinline__ float advect_gather(const BilinW& c, const float* __restrict__ f, int pitch)
 {
-	const float* r0 = f + (c.jl * pitch + XO + c.i0);
+	const float* r0 = f + ((int) c.fjl * pitch + XO + (int) c.fi0);
 	const float* r1 = r0 + pitch;
 	const float d00 = __ldg(r0), d10 = __ldg(r0 + 1);
 	const float d01 = __ldg(r1), d11 = __ldg(r1 + 1);
@@ -102,26 +120,31 @@ __device__ __forceinline__ float advect_window(const BilinW& c, const RowWin (&w
 }
 
 // The warp's vote: code (dx+1) | (dy+1) << 1 when every valid cell of every lane has the same stencil
-// offset inside the window, else -1.
-__device__ __forceinline__ int advect_vote(const BilinW (&c)[4], int i_first, int j, uint32_t valid)
+// offset inside the window, else -1.  The offsets are differences of small integer-valued floats, so they
+// are exactly 0.0f or -1.0f when in range, and "all equal" is an OR of XORs of their bit patterns.
+template <bool PARTIAL>
+__device__ __forceinline__ int advect_vote(const BilinW (&c)[4], float fi, float fj, uint32_t valid)
 {
-	int code = -2; // this lane has no opinion yet
-	bool ok = true;
+	uint32_t dx[4], dy[4];
 #pragma unroll
 	for (int k = 0; k < 4; k++) {
-		const int dx = c[k].i0 - (i_first + k), dy = c[k].jl - j;
-		const int ck = (dx + 1) | ((dy + 1) << 1);
-		const bool in = ((unsigned) (dx + 1) <= 1u) && ((unsigned) (dy + 1) <= 1u);
-		if ((valid >> k) & 1) {
-			ok = ok && in && (code == -2 || code == ck);
-			code = ck;
-		}
+		dx[k] = __float_as_uint(c[k].fi0 - (fi + k));
+		dy[k] = __float_as_uint(c[k].fjl - fj);
 	}
+	uint32_t diff = 0;
+#pragma unroll
+	for (int k = 1; k < 4; k++)
+		if (!PARTIAL || ((valid >> k) & 1)) diff |= (dx[k] ^ dx[0]) | (dy[k] ^ dy[0]);
+	const uint32_t m1 = 0xbf800000u; // -1.0f
+	const bool inx = (dx[0] == 0u) || (dx[0] == m1), iny = (dy[0] == 0u) || (dy[0] == m1);
+	const int code = ((dx[0] == 0u) ? 1 : 0) | ((dy[0] == 0u) ? 2 : 0);
+	const bool mine = (diff == 0u) && inx && iny;
 	const int c0 = __shfl_sync(0xffffffffu, code, 0); // lane 0 always holds the strip's first cell, which exists
-	return __all_sync(0xffffffffu, ok && (code == -2 || code == c0)) ? c0 : -1;
+	const bool agree = PARTIAL ? ((valid == 0u) || (mine && code == c0)) : (mine && code == c0);
+	return __all_sync(0xffffffffu, agree) ? c0 : -1;
 }
 
-template <int NF>
+template <int NF, bool PARTIAL>
 __device__ __forceinline__ void advect_sample(int code, const BilinW (&c)[4], const RowWin (&w0)[3], const RowWin (&w1)[3],
 					       const float* __restrict__ f0, const float* __restrict__ f1, int pitch, uint32_t valid,
 					       float (&o0)[4], float (&o1)[4])
@@ -142,7 +165,7 @@ __device__ __forceinline__ void advect_sample(int code, const BilinW (&c)[4], co
 	default:
 #pragma unroll
 		for (int k = 0; k < 4; k++) {
-			if (!((valid >> k) & 1)) { // cells past the row's end: nothing to fetch, nothing is stored
+			if (PARTIAL && !((valid >> k) & 1)) { // cells past the row's end: nothing to fetch, nothing is stored
 				o0[k] = 0.0f;
 				if (NF > 1) o1[k] = 0.0f;
 				continue;
@@ -158,9 +181,11 @@ struct AdvectTasks {
 };
 
 // VEL: VelStep1's self-advection (FluidSystem.cpp:372-373), Advect1(1,u,u0,u0,v0) and Advect1(2,v,v0,u0,v0) in one
-// pass (outa = u, outb = v; b = -2 leaves the border alone, as Advect1B does, anything else means SetBorder 1 / 2).  Otherwise Advect1(b, outa, d0, u0, v0) for one scalar field.
+// pass (outa = u, outb = v; b = -2 leaves the border alone, as Advect1B does, anything else means SetBorder 1 / 2).
+// Otherwise Advect1(b, outa, d0, u0, v0) for one scalar field.
 // MODE 0 = MidpointBackward, 1 = EulerBack (FluidSystem.h:185-219).
-template <bool SLAB, int MODE, bool VEL>
+// PARTIAL: the row is not a whole number of 128-cell strips (N % 128 != 0): cells past its end are masked.
+template <bool SLAB, int MODE, bool VEL, bool PARTIAL>
 __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, AdvectTasks tk, int b, float* __restrict__ outab,
 									   float* __restrict__ outbb, const float* __restrict__ d0b,
 									   const float* __restrict__ u0b, const float* __restrict__ v0b,
@@ -178,13 +203,16 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 	float* outb = VEL ? outbb + off : nullptr;
 
 	const int pitch = g.pitch;
-	const int col = 32 + 128 * strip + 4 * lane; // storage column of the lane's first cell
-	const int colc = min(col, pitch - 4);         // lanes past the row's end read its last group (and store nothing)
+	const int col = 32 + 128 * strip + 4 * lane;        // storage column of the lane's first cell
+	const int colc = PARTIAL ? min(col, pitch - 4) : col; // lanes past the row's end read its last group (and store nothing)
 	const int i_first = col - XO;
-	uint32_t valid = 0;
+	uint32_t valid = 0xfu;
+	if (PARTIAL) {
+		valid = 0;
 #pragma unroll
-	for (int k = 0; k < 4; k++)
-		if (i_first + k <= g.N) valid |= 1u << k;
+		for (int k = 0; k < 4; k++)
+			if (i_first + k <= g.N) valid |= 1u << k;
+	}
 	const int off_l = -1, off_r = min(4, pitch - 1 - colc);
 	const float* pu = u0 + colc;
 	const float* pv = v0 + colc;
@@ -192,33 +220,36 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 	const float fi = (float) i_first;
 
 	const int j_lo = 1 + chunk * tk.chunk_rows, j_hi = min(g.NY, j_lo + tk.chunk_rows - 1);
-	RowWin wu[3], wv[3], wd[3], nu, nv, nd;
-	wu[1] = advect_load_row(pu, j_lo - 1, pitch, lane, off_l, off_r);
-	wv[1] = advect_load_row(pv, j_lo - 1, pitch, lane, off_l, off_r);
-	wu[2] = advect_load_row(pu, j_lo, pitch, lane, off_l, off_r);
-	wv[2] = advect_load_row(pv, j_lo, pitch, lane, off_l, off_r);
-	nu = advect_load_row(pu, j_lo + 1, pitch, lane, off_l, off_r);
-	nv = advect_load_row(pv, j_lo + 1, pitch, lane, off_l, off_r);
+	RowWin wu[3], wv[3], wd[3];
+	RowRaw nu, nv, nd;
+	wu[1] = advect_finish_row(advect_fetch_row(pu, j_lo - 1, pitch, lane, off_l, off_r), lane);
+	wv[1] = advect_finish_row(advect_fetch_row(pv, j_lo - 1, pitch, lane, off_l, off_r), lane);
+	wu[2] = advect_finish_row(advect_fetch_row(pu, j_lo, pitch, lane, off_l, off_r), lane);
+	wv[2] = advect_finish_row(advect_fetch_row(pv, j_lo, pitch, lane, off_l, off_r), lane);
+	nu = advect_fetch_row(pu, j_lo + 1, pitch, lane, off_l, off_r);
+	nv = advect_fetch_row(pv, j_lo + 1, pitch, lane, off_l, off_r);
 	if (!VEL) {
-		wd[1] = advect_load_row(pd, j_lo - 1, pitch, lane, off_l, off_r);
-		wd[2] = advect_load_row(pd, j_lo, pitch, lane, off_l, off_r);
-		nd = advect_load_row(pd, j_lo + 1, pitch, lane, off_l, off_r);
+		wd[1] = advect_finish_row(advect_fetch_row(pd, j_lo - 1, pitch, lane, off_l, off_r), lane);
+		wd[2] = advect_finish_row(advect_fetch_row(pd, j_lo, pitch, lane, off_l, off_r), lane);
+		nd = advect_fetch_row(pd, j_lo + 1, pitch, lane, off_l, off_r);
 	}
 	const bool edge_lane = (i_first == 1) || (i_first + 3 >= g.N && i_first <= g.N);
 
 #pragma unroll 1
 	for (int j = j_lo; j <= j_hi; j++) {
-		// slide: rows j-1, j, j+1 <- j, j+1 and the prefetched one; fetch row j+2 for the next step now
-		wu[0] = wu[1]; wu[1] = wu[2]; wu[2] = nu;
-		wv[0] = wv[1]; wv[1] = wv[2]; wv[2] = nv;
-		if (!VEL) { wd[0] = wd[1]; wd[1] = wd[2]; wd[2] = nd; }
+		// slide: rows j-1, j, j+1 <- j, j+1 and the row fetched one step ago (its neighbours' values are shuffled in
+		// now); fetch row j+2 for the next step
+		wu[0] = wu[1]; wu[1] = wu[2]; wu[2] = advect_finish_row(nu, lane);
+		wv[0] = wv[1]; wv[1] = wv[2]; wv[2] = advect_finish_row(nv, lane);
+		if (!VEL) { wd[0] = wd[1]; wd[1] = wd[2]; wd[2] = advect_finish_row(nd, lane); }
 		const int jn = min(j + 2, g.NY + 1);
-		nu = advect_load_row(pu, jn, pitch, lane, off_l, off_r);
-		nv = advect_load_row(pv, jn, pitch, lane, off_l, off_r);
-		if (!VEL) nd = advect_load_row(pd, jn, pitch, lane, off_l, off_r);
+		nu = advect_fetch_row(pu, jn, pitch, lane, off_l, off_r);
+		nv = advect_fetch_row(pv, jn, pitch, lane, off_l, off_r);
+		if (!VEL) nd = advect_fetch_row(pd, jn, pitch, lane, off_l, off_r);
 
 		int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
-		const float fj = (float) (SLAB ? j + g.j0 : j);
+		const float fjl = (float) j;                            // local row, for the vote
+		const float fj = (float) (SLAB ? j + g.j0 : j);         // global row, for the positions
 		float px[4], py[4];
 		if (MODE == 1) {
 #pragma unroll
@@ -234,10 +265,10 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 				const float diry = -dtN * wv[1].w[1 + k];
 				const float mx = (fi + k) + 0.5f * dirx;
 				const float my = fj + 0.5f * diry;
-				m[k] = advect_calc<SLAB>(g, mx, my, ((valid >> k) & 1) ? oob : nullptr);
+				m[k] = advect_calc<SLAB>(g, mx, my, (!PARTIAL || ((valid >> k) & 1)) ? oob : nullptr);
 			}
 			float vx[4], vy[4];
-			advect_sample<2>(advect_vote(m, i_first, j, valid), m, wu, wv, u0, v0, pitch, valid, vx, vy);
+			advect_sample<2, PARTIAL>(advect_vote<PARTIAL>(m, fi, fjl, valid), m, wu, wv, u0, v0, pitch, valid, vx, vy);
 #pragma unroll
 			for (int k = 0; k < 4; k++) {
 				px[k] = (fi + k) - dtN * vx[k];
@@ -246,14 +277,14 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 		}
 		BilinW c[4];
 #pragma unroll
-		for (int k = 0; k < 4; k++) c[k] = advect_calc<SLAB>(g, px[k], py[k], ((valid >> k) & 1) ? oob : nullptr);
-		const int code = advect_vote(c, i_first, j, valid);
+		for (int k = 0; k < 4; k++) c[k] = advect_calc<SLAB>(g, px[k], py[k], (!PARTIAL || ((valid >> k) & 1)) ? oob : nullptr);
+		const int code = advect_vote<PARTIAL>(c, fi, fjl, valid);
 		float ra[4], rb[4];
-		if (VEL) advect_sample<2>(code, c, wu, wv, u0, v0, pitch, valid, ra, rb);
-		else advect_sample<1>(code, c, wd, wd, d0, d0, pitch, valid, ra, rb);
+		if (VEL) advect_sample<2, PARTIAL>(code, c, wu, wv, u0, v0, pitch, valid, ra, rb);
+		else advect_sample<1, PARTIAL>(code, c, wd, wd, d0, d0, pitch, valid, ra, rb);
 
 		float* pa = outa + (j * pitch + col);
-		if (valid == 0xfu) {
+		if (!PARTIAL || valid == 0xfu) {
 			*reinterpret_cast<float4*>(pa) = make_float4(ra[0], ra[1], ra[2], ra[3]);
 			if (VEL) *reinterpret_cast<float4*>(outb + (j * pitch + col)) = make_float4(rb[0], rb[1], rb[2], rb[3]);
 		} else {
@@ -268,7 +299,7 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 		if (edge_lane || ((j == 1) && (g.walls & 1)) || ((j == g.NY) && (g.walls & 2))) {
 #pragma unroll
 			for (int k = 0; k < 4; k++) {
-				if (!((valid >> k) & 1)) continue;
+				if (PARTIAL && !((valid >> k) & 1)) continue;
 				if (VEL) { // b = -2: VelStep1B's pair (no SetBorder); anything else: VelStep1's (SetBorder 1 and 2)
 					mirror_border(g, outa, b == -2 ? -2 : 1, i_first + k, j, ra[k]);
 					mirror_border(g, outb, b == -2 ? -2 : 2, i_first + k, j, rb[k]);

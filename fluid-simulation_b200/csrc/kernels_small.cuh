@@ -94,9 +94,13 @@ __global__ void __launch_bounds__(kSmallThreads, 1) k_small_lin_solve(GridDesc g
 	} else {
 		const int last = 2 * N + 2 * (limit - 1);
 		for (int t = 2; t <= last; t++) {
-			for (int idx = threadIdx.x; idx < limit * N; idx += blockDim.x) {
-				const int k = idx / N, j = idx - k * N + 1;
-				const int i = t - 2 * k - j;
+			// sweeps with a cell on this hyperplane: 2 <= t - 2k <= 2N, at most N of them whatever `limit` is
+			// (a solve run to convergence has thousands of sweeps but never more than N in flight)
+			const int kmin = max(0, (t - 2 * N + 1) / 2), kmax = min(limit - 1, (t - 2) / 2);
+			const int nk = kmax - kmin + 1;
+			for (int idx = threadIdx.x; idx < nk * N; idx += blockDim.x) {
+				const int kk = idx / N, j = idx - kk * N + 1;
+				const int i = t - 2 * (kmin + kk) - j;
 				if (i < 1 || i > N) continue;
 				const int o = j * P + i;
 				const float v = relax(x0[o], a, x[o - 1], x[o + 1], x[o - P], x[o + P], c);
