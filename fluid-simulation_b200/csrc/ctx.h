@@ -108,6 +108,9 @@ struct fluid_ctx {
 	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
+	bool wavefront_persistent = true; // reference-order solve as ONE launch (tickets + progress counters) instead of one per hyperplane
+	int* d_wf_sync = nullptr;  // its ticket counter and per-column progress counters
+	long long wf_sync_capacity = 0;
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
 	bool rb_stream = true;     // interior of large grids by the register-resident streaming kernel (k_rb_stream)

@@ -85,6 +85,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_src_saved) cudaFree(c->d_src_saved);
 	if (c->d_info) cudaFree(c->d_info);
+	if (c->d_wf_sync) cudaFree(c->d_wf_sync);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);
@@ -485,6 +486,13 @@ extern "C" int fluid_ctx_set_wavefront_tile(fluid_ctx* c, int tile)
 	CHECK_CTX(c);
 	if (tile != 0 && tile != 16 && tile != 32 && tile != 64) return fail(FLUID_ERR_INVALID, "wavefront tile %d must be 0 (automatic), 16, 32 or 64", tile);
 	c->wavefront_tile = tile;
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_wavefront_persistent(fluid_ctx* c, int on)
+{
+	CHECK_CTX(c);
+	c->wavefront_persistent = on != 0;
 	return FLUID_OK;
 }
 

@@ -494,6 +494,23 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		const int T = (c->wavefront_tile > 0) ? c->wavefront_tile : (c->g.N < 2048 ? 16 : 32);
 		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
 		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
+		const long long tickets = (long long) c->batch * limit * ntx;
+		if (c->wavefront_persistent && tickets < (1LL << 28)) {
+			// one launch per solve: CTAs take (sweep, tile column) tickets and order themselves by progress counters
+			if (tickets + 1 > c->wf_sync_capacity) {
+				if (c->d_wf_sync) CU_TRY(cudaFree(c->d_wf_sync));
+				c->d_wf_sync = nullptr;
+				CU_TRY(cudaMalloc(&c->d_wf_sync, sizeof(int) * (size_t) (tickets + 1)));
+				c->wf_sync_capacity = tickets + 1;
+			}
+			CU_TRY(cudaMemsetAsync(c->d_wf_sync, 0, sizeof(int) * (size_t) (tickets + 1), c->stream));
+			const int grid = (int) std::min<long long>(tickets, (long long) c->num_sms * 32);
+			if (T == 16) LAUNCH(k_gs_wavefront_persistent<16>, grid, 16, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, c->d_wf_sync);
+			else if (T == 32) LAUNCH(k_gs_wavefront_persistent<32>, grid, 32, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, c->d_wf_sync);
+			else LAUNCH(k_gs_wavefront_persistent<64>, grid, 64, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, c->d_wf_sync);
+			CU_TRY(cudaGetLastError());
+			return FLUID_OK;
+		}
 		for (int s = 0; s <= last; s++) {
 			if (T == 16) LAUNCH(k_gs_wavefront<16>, dim3(ntx, limit, c->batch), 16, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);
 			else if (T == 32) LAUNCH(k_gs_wavefront<32>, dim3(ntx, limit, c->batch), 32, 0, c->stream, c->g, b, x, x0, a, cc, s, ntx, nty);

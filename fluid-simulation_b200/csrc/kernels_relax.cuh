@@ -23,23 +23,15 @@ namespace fluid {
 // read by the interior cell it mirrors, so the thread that updates an edge
 // cell rewrites its border cells (mirror_border) and the next sweep sees them.
 // ---------------------------------------------------------------------------
+// One tile (I, J) of one sweep: load the tile of x with its one-cell halo and the tile of x0, walk the cell
+// anti-diagonals in shared memory, store the tile (and the border cells that mirror its wall cells).
+// x is read past L1 (ld.global.cg): in the persistent kernel below the halo was written moments ago by CTAs
+// on other SMs.
 template <int T>
-__global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __restrict__ xb,
-						     const float* __restrict__ x0b, float a, float c, int s, int ntx,
-						     int nty)
+__device__ __forceinline__ void gs_wavefront_tile(const GridDesc& g, int b, float* __restrict__ x, const float* __restrict__ x0,
+						  float a, float c, int I, int J, float* sx, float* s0)
 {
 	constexpr int PS = T + 2; // (PS-1) odd multiple pattern: thread r touches r*(PS-1)+const -> conflict free
-	__shared__ float sx[(T + 2) * PS];
-	__shared__ float s0[T * PS];
-
-	const int I = blockIdx.x;
-	const int k = blockIdx.y;
-	const int J = s - 2 * k - I;
-	if (J < 0 || J >= nty) return;
-
-	const long long off = (long long) blockIdx.z * g.plane;
-	float* x = xb + off;
-	const float* x0 = x0b + off;
 	const int i0 = I * T + 1, j0 = J * T + 1;
 	const int w = min(T, g.N - i0 + 1), h = min(T, g.NY - j0 + 1);
 	const int r = threadIdx.x;
@@ -58,7 +50,7 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 #pragma unroll
 		for (int it = 0; it < NX; it++) {
 			const int rr = rsub + RPS * it;
-			if (rr < h + 2) vx[it] = *reinterpret_cast<const float4*>(x + cell(g, i0 + 4 * q4, j0 - 1 + rr));
+			if (rr < h + 2) vx[it] = __ldcg(reinterpret_cast<const float4*>(x + cell(g, i0 + 4 * q4, j0 - 1 + rr)));
 		}
 #pragma unroll
 		for (int it = 0; it < N0; it++) {
@@ -69,8 +61,8 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 		for (int it = 0; it < (T + 2 + T - 1) / T; it++) {
 			const int rr = r + T * it;
 			if (rr < h + 2) {
-				hl[it] = x[cell(g, i0 - 1, j0 - 1 + rr)];
-				hr[it] = x[cell(g, i0 + T, j0 - 1 + rr)];
+				hl[it] = __ldcg(x + cell(g, i0 - 1, j0 - 1 + rr));
+				hr[it] = __ldcg(x + cell(g, i0 + T, j0 - 1 + rr));
 			}
 		}
 #pragma unroll
@@ -100,7 +92,7 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 	} else {
 		for (int rr = 0; rr < h + 2; rr++) {
 			const long long row = cell(g, i0 - 1, j0 - 1 + rr);
-			for (int cc = r; cc < w + 2; cc += T) sx[rr * PS + cc] = x[row + cc];
+			for (int cc = r; cc < w + 2; cc += T) sx[rr * PS + cc] = __ldcg(x + row + cc);
 		}
 		for (int rr = 0; rr < h; rr++) {
 			const long long row = cell(g, i0, j0 + rr);
@@ -137,6 +129,73 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 				x[row + cc] = v;
 				mirror_border(g, x, b, i0 + cc, j, v);
 			}
+		}
+	}
+}
+
+
+template <int T>
+__global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __restrict__ xb,
+						     const float* __restrict__ x0b, float a, float c, int s, int ntx,
+						     int nty)
+{
+	constexpr int PS = T + 2;
+	__shared__ float sx[(T + 2) * PS];
+	__shared__ float s0[T * PS];
+	const int I = blockIdx.x;
+	const int k = blockIdx.y;
+	const int J = s - 2 * k - I;
+	if (J < 0 || J >= nty) return;
+	const long long off = (long long) blockIdx.z * g.plane;
+	gs_wavefront_tile<T>(g, b, xb + off, x0b + off, a, c, I, J, sx, s0);
+}
+
+// The same schedule WITHOUT a launch per hyperplane: one launch per solve.  A CTA takes a ticket = one tile
+// column I of one sweep k of one member and walks it from J = 0 to nty-1; before tile (I, J, k) it waits until
+//   (I-1, J, k) is done      -- its new west halo,
+//   (I+1, J, k-1) is done    -- its old east halo,
+//   (I, J+1, k-1) is done    -- its old north halo (the last tile of a column waits for the whole column below:
+//                               it reads the border row the previous sweep mirrored),
+// which it reads off per-column progress counters (tiles done, published with release semantics after the
+// tile's stores).  Tickets are dealt in the order sweep-major, column-minor, and every wait is on a ticket with a
+// smaller number: whoever a CTA waits for has taken its ticket earlier, so it is running or finished -- CTAs that
+// have not started yet are never waited for, and the kernel cannot deadlock however few CTAs are resident.
+// Round 1 needed 549 launches of a few microseconds each per solve at N = 8192 (2 ntx + 2 sweeps - 3).
+// sync[0] = ticket counter, sync[1 + (sim*limit + k)*ntx + I] = progress of that column; zeroed by the host.
+template <int T>
+__global__ void __launch_bounds__(T) k_gs_wavefront_persistent(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
+								float a, float c, int limit, int ntx, int nty, int batch, int* __restrict__ sync)
+{
+	constexpr int PS = T + 2;
+	__shared__ float sx[(T + 2) * PS];
+	__shared__ float s0[T * PS];
+	__shared__ int s_ticket;
+	const int total = batch * limit * ntx;
+	volatile int* progress = sync + 1;
+	for (;;) {
+		__syncthreads();
+		if (threadIdx.x == 0) s_ticket = atomicAdd(&sync[0], 1);
+		__syncthreads();
+		const int ticket = s_ticket;
+		if (ticket >= total) return;
+		const int I = ticket % ntx, k = (ticket / ntx) % limit, sim = ticket / (ntx * limit);
+		const long long off = (long long) sim * g.plane;
+		volatile int* mine = progress + ticket;
+		volatile int* west = (I > 0) ? progress + ticket - 1 : nullptr;
+		volatile int* below = (k > 0) ? progress + ticket - ntx : nullptr;                    // (I, *, k-1)
+		volatile int* east = (k > 0 && I + 1 < ntx) ? progress + ticket - ntx + 1 : nullptr;  // (I+1, *, k-1)
+		for (int J = 0; J < nty; J++) {
+			if (threadIdx.x == 0) {
+				if (west) while (*west < J + 1) __nanosleep(64);
+				if (east) while (*east < J + 1) __nanosleep(64);
+				if (below) while (*below < min(J + 2, nty)) __nanosleep(64);
+				__threadfence();
+			}
+			__syncthreads();
+			gs_wavefront_tile<T>(g, b, xb + off, x0b + off, a, c, I, J, sx, s0);
+			__threadfence(); // this thread's stores before the counter
+			__syncthreads();
+			if (threadIdx.x == 0) *mine = J + 1;
 		}
 	}
 }

@@ -36,7 +36,7 @@ EXPORTS = [
     "fluid_ctx_sync", "fluid_ctx_last_step_ms", "fluid_ctx_set_modes", "fluid_ctx_set_coeffs", "fluid_ctx_set_fluid",
     "fluid_ctx_set_profiling", "fluid_ctx_profile", "fluid_ctx_set_tuning",
     "fluid_ctx_set_fast_division", "fluid_ctx_division_window", "fluid_ctx_set_small_grid_kernels",
-    "fluid_ctx_set_wavefront_tile", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap", "fluid_ctx_set_advect_kernel", "fluid_ctx_set_sparse_sources",
+    "fluid_ctx_set_wavefront_tile", "fluid_ctx_set_wavefront_persistent", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap", "fluid_ctx_set_advect_kernel", "fluid_ctx_set_sparse_sources",
     "fluid_ctx_reset_cell_info", "fluid_ctx_disable_edges", "fluid_ctx_add_square_border", "fluid_ctx_set_cell_info",
     "fluid_ctx_get_cell_info",
     "fluid_ctx_peer_halo_local", "fluid_ctx_peer_halo_connect", "fluid_ipc_export", "fluid_ipc_import", "fluid_ipc_close",
@@ -124,6 +124,7 @@ def lib():
     L.fluid_ctx_set_fast_division.argtypes = [_vp, _ci]
     L.fluid_ctx_set_small_grid_kernels.argtypes = [_vp, _ci]
     L.fluid_ctx_set_wavefront_tile.argtypes = [_vp, _ci]
+    L.fluid_ctx_set_wavefront_persistent.argtypes = [_vp, _ci]
     L.fluid_ctx_set_stream_kernel.argtypes = [_vp, _ci]
     L.fluid_ctx_set_overlap.argtypes = [_vp, _ci]
     L.fluid_ctx_set_advect_kernel.argtypes = [_vp, _ci]
@@ -398,6 +399,7 @@ class FluidSystem:
         return out
 
     def SetWavefrontTile(self, tile): check(lib().fluid_ctx_set_wavefront_tile(self.h, tile))
+    def SetWavefrontPersistent(self, on): check(lib().fluid_ctx_set_wavefront_persistent(self.h, 1 if on else 0))
 
     def SetSmallGridKernels(self, on): check(lib().fluid_ctx_set_small_grid_kernels(self.h, 1 if on else 0))
 

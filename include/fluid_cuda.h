@@ -270,6 +270,9 @@ int fluid_ctx_set_cell_info(fluid_ctx *ctx, const unsigned char *host_info, int 
 int fluid_ctx_get_cell_info(fluid_ctx *ctx, unsigned char *host_info);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
 int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
+/* Reference-order solve as ONE launch whose CTAs take (sweep, tile column) tickets and order themselves with
+ * progress counters (default), or 0 = one launch per hyperplane of the (tile, sweep) schedule.  Results identical. */
+int fluid_ctx_set_wavefront_persistent(fluid_ctx *ctx, int on);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur
  * (all passes) as ONE single-CTA launch per ensemble member, from shared memory.  on = 0
  * forces the large-grid kernels (identical results; used by the tests). */

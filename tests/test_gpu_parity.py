@@ -606,13 +606,16 @@ def test_errors_are_status_codes(fl):
     fs.close()
 
 
+@pytest.mark.parametrize("persistent", [True, False])
 @pytest.mark.parametrize("tile", [16, 32, 64])
-def test_wavefront_tile_sizes_bitwise(fl, oracle, tile):
+def test_wavefront_tile_sizes_bitwise(fl, oracle, tile, persistent):
+    """Reference-order relaxation: one launch per solve (tickets + progress counters) and one launch per hyperplane."""
     import oracle_py as op
     rng = np.random.default_rng(tile)
     for N in (130, 257, 320):
         fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=7)
         fs.SetWavefrontTile(tile)
+        fs.SetWavefrontPersistent(persistent)
         for b in (0, 1, 2, 3):
             x, x0 = rand_field(rng, N), rand_field(rng, N)
             a = np.float32(0.6)
@@ -620,8 +623,36 @@ def test_wavefront_tile_sizes_bitwise(fl, oracle, tile):
             fs.upload(fl.V, x0)
             fs.lin_solve(b, fl.U, fl.V, a, 1 + 4 * a)
             oracle.lin_solve(N, b, x, x0, a, 1 + 4 * a, 7, op.GS_LEX)
-            assert_bits(fs.download(fl.U), x, "wavefront tile %d N=%d b=%d" % (tile, N, b))
+            assert_bits(fs.download(fl.U), x, "wavefront tile %d N=%d b=%d persistent=%s" % (tile, N, b, persistent))
         fs.close()
+
+
+def test_wavefront_persistent_many_sweeps_and_members(fl, oracle):
+    """More sweeps in flight than tile columns, an ensemble (tickets of several members), a grid much larger than
+    the resident CTAs can cover at once (N=2048, 20 sweeps: 1280 tickets of 64 tiles), repeated solves."""
+    import oracle_py as op
+    rng = np.random.default_rng(5150)
+    N, B = 150, 3
+    fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=45, batch=B)
+    xs = [(rand_field(rng, N), rand_field(rng, N)) for _ in range(B)]
+    for sim, (x, x0) in enumerate(xs):
+        fs.upload(fl.U, x, sim)
+        fs.upload(fl.V, x0, sim)
+    fs.lin_solve(1, fl.U, fl.V, np.float32(1.0), np.float32(4.0))
+    for sim, (x, x0) in enumerate(xs):
+        oracle.lin_solve(N, 1, x, x0, 1.0, 4.0, 45, op.GS_LEX)
+        assert_bits(fs.download(fl.U, sim), x, "member %d" % sim)
+    fs.close()
+    N = 2048
+    fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=20)
+    for rep in range(2):
+        x, x0 = rand_field(rng, N), rand_field(rng, N)
+        fs.upload(fl.U, x)
+        fs.upload(fl.V, x0)
+        fs.lin_solve(2, fl.U, fl.V, np.float32(10.49), np.float32(42.96))
+        oracle.lin_solve(N, 2, x, x0, np.float32(10.49), np.float32(42.96), 20, op.GS_LEX)
+        assert_bits(fs.download(fl.U), x, "N=2048 solve %d" % rep)
+    fs.close()
 
 
 @pytest.mark.parametrize("small", [True, False])
