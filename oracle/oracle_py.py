@@ -105,6 +105,11 @@ class Oracle:
         L.oracle_advect_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_int]
         L.oracle_vel_step_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_float, c_int, c_int, c_int, _u8p]
         L.oracle_dens_step_bs.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_float, c_float, c_int, c_int, _u8p]
+        L.oracle_lin_solve_bso.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, c_void_p, _f32p, c_int, c_int, _u8p]
+        L.oracle_lin_solve_bo.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, c_int, _u8p]
+        L.oracle_project_bo.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int, c_int, _u8p]
+        L.oracle_update_mf.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, _f32p, c_int, c_void_p, c_void_p, _f32p, _f32p, c_float, _u8p,
+                                       c_int, c_void_p, c_float, c_int, c_int, c_int, c_float, c_float, c_int]
         L.oracle_update_b.argtypes = [c_int] + [_f32p] * 6 + [_u8p, c_int, c_void_p, c_float, c_float, c_float, c_int, c_int,
                                                               c_int, c_float, c_float, c_int]
 
@@ -192,6 +197,29 @@ class Oracle:
     def dens_step_bs(self, N, x, x0, u, v, diff, dt, info, iters=20, mode=ADV_MIDPOINT):
         self.L.oracle_dens_step_bs(N, x, x0, u, v, diff, dt, iters, mode, info)
 
+    # ---- FSType::ORIGINAL_BORDERED_MF ----
+    @staticmethod
+    def _ptrs(arrays):
+        return ctypes.cast((c_void_p * len(arrays))(*[a.ctypes.data for a in arrays]), c_void_p)
+
+    def lin_solve_bso(self, N, b, x, x0, aSc, a_fallback, dens, coef, info, iters=20, order=GS_LEX):
+        self.L.oracle_lin_solve_bso(N, b, x, x0, aSc, a_fallback, len(dens), self._ptrs(dens), np.asarray(coef, np.float32), iters, order, info)
+
+    def lin_solve_bo(self, N, b, x, x0, a, c, info, iters=20, order=GS_LEX):
+        self.L.oracle_lin_solve_bo(N, b, x, x0, a, c, iters, order, info)
+
+    def project_bo(self, N, u, v, p, div, info, iters=20, order=GS_LEX):
+        self.L.oracle_project_bo(N, u, v, p, div, iters, order, info)
+
+    def update_mf(self, N, f, info, sources, fluids, dt, nsteps=1, visc_air=0.001, iters=20, order=GS_LEX, mode=ADV_MIDPOINT,
+                  vorticity=0.0, damp=0.0):
+        """f: dict with u, v, u0, v0, p and lists d, d0 (one array per fluid); fluids: [(diff, visc), ...]."""
+        arr = (SourceEntry * max(1, len(sources)))(*[SourceEntry(*s) for s in sources])
+        diff = np.array([x[0] for x in fluids], np.float32)
+        visc = np.array([x[1] for x in fluids], np.float32)
+        self.L.oracle_update_mf(N, f["u"], f["v"], f["u0"], f["v0"], f["p"], len(fluids), self._ptrs(f["d"]), self._ptrs(f["d0"]), diff, visc,
+                                visc_air, info, len(sources), ctypes.cast(arr, c_void_p), dt, iters, order, mode, vorticity, damp, nsteps)
+
     def update_b(self, N, fields, info, sources, visc, diff, dt, nsteps=1, iters=20, order=GS_LEX, mode=ADV_MIDPOINT,
                  vorticity=0.0, damp=0.0):
         arr = (SourceEntry * max(1, len(sources)))(*[SourceEntry(*s) for s in sources])
@@ -254,6 +282,13 @@ class Ref:
         L.ref_diffuse_blur_b.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
         L.ref_advect_b.argtypes = [c_int, c_int, _f32p, _f32p, _f32p, _f32p, c_float]
         L.ref_project_b.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int, _u8p]
+        L.ref_lin_solve_bo.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, _u8p]
+        L.ref_project_bo.argtypes = [c_int, _f32p, _f32p, _f32p, _f32p, c_int, _u8p]
+        L.ref_lin_solve_bso.argtypes = [c_int, c_int, _f32p, _f32p, c_float, c_float, c_int, c_void_p, _f32p, c_int, _u8p]
+        L.ref_p.restype = ctypes.POINTER(c_float)
+        L.ref_p.argtypes = [c_void_p]
+        L.ref_visc_air.restype = c_float
+        L.ref_visc_air.argtypes = [c_void_p]
 
     class Sim:
         def __init__(self, ref, N, visc, diff, vorticity=0.0, iters=20, damp=0.0, fluids=None, fstype=0, square_border=False):
@@ -298,6 +333,9 @@ class Ref:
 
         def total_inner_mass(self):
             return float(self.ref.L.ref_total_inner_mass(self.h))
+
+        def p(self):
+            return np.ctypeslib.as_array(self.ref.L.ref_p(self.h), ((self.N + 2) ** 2,))
 
         def cell_info(self):
             return np.ctypeslib.as_array(self.ref.L.ref_cell_info(self.h), ((self.N + 2) ** 2,))

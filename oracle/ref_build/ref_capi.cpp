@@ -140,6 +140,10 @@ void* ref_create_typed(int N, int nfluids, const float* diffs, const float* visc
 	return s;
 }
 
+// the system's own pressure array (FluidSystem.h:162; ProjectBO solves into it, FluidSystem.cpp:1096-1098)
+float* ref_p(void* h) { return ((RefSim*) h)->fs.p.data(); }
+float ref_visc_air(void* h) { return ((RefSim*) h)->fs.visc_air; }
+
 // cellInfo as the last Update (or Setup) left it (FluidSystem.h: GetInfo)
 unsigned char* ref_cell_info(void* h) { return ((RefSim*) h)->fs.cellInfo.data(); }
 
@@ -340,6 +344,47 @@ void ref_project_b(int N, float* u, float* v, float* p, float* div, int steps, c
 	vec vu = load(u, N), vv = load(v, N), vp = load(p, N), vd = load(div, N);
 	fs->ProjectB(N, vu, vv, vp, vd);
 	store(u, vu); store(v, vv); store(p, vp); store(div, vd);
+	delete fs;
+}
+
+// LinearSolve1BO / ProjectBO (FluidSystem.cpp:580-615, 1061-1122) on caller buffers; `p` is loaded into and
+// read back from the member array the reference really uses.
+void ref_lin_solve_bo(int N, int b, float* x, const float* x0, float a, float c, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, steps, info);
+	vec vx = load(x, N), v0 = load(x0, N);
+	fs->LinearSolve1BO(N, b, vx, v0, a, c);
+	store(x, vx);
+	delete fs;
+}
+
+void ref_project_bo(int N, float* u, float* v, float* p, float* div, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, steps, info);
+	vec vu = load(u, N), vv = load(v, N), vd = load(div, N), unused = load(p, N);
+	fs->p = load(p, N);
+	fs->ProjectBO(N, vu, vv, unused, vd);
+	store(u, vu); store(v, vv); store(p, fs->p); store(div, vd);
+	delete fs;
+}
+
+// LinearSolve1BSO (FluidSystem.cpp:673-720) with nfluids density fields and their coefficients of one kind
+void ref_lin_solve_bso(int N, int b, float* x, const float* x0, float aSc, float a_fallback, int nfluids, const float* const* dens,
+		       const float* coef, int steps, const unsigned char* info)
+{
+	FluidSystem* fs = scratch_system_info(N, steps, info);
+	fs->fluid_count = nfluids;
+	fs->densList.resize(nfluids);
+	fs->fprops.resize(nfluids);
+	for (int k = 0; k < nfluids; k++) {
+		fs->densList[k].Resize((N + 2) * (N + 2));
+		fs->densList[k].Curr() = load(dens[k], N);
+		fs->fprops[k].coef[FluidProps::VISC] = coef[k];
+		fs->fprops[k].coef[FluidProps::DIFF] = 0;
+	}
+	vec vx = load(x, N), v0 = load(x0, N);
+	fs->LinearSolve1BSO(N, b, vx, v0, aSc, a_fallback, FluidProps::VISC);
+	store(x, vx);
 	delete fs;
 }
 

@@ -298,3 +298,57 @@ def test_bordered_frames_match_live_reference(oracle, ref):
             assert f[name].tobytes() == sim.field(w).tobytes(), (N, square, name)
         assert np.abs(f["u"]).max() > 0 and np.abs(f["d"]).max() > 0
         sim.close()
+
+
+def test_multifluid_bordered_primitives_and_frames_match_live_reference(oracle, ref):
+    """FSType::ORIGINAL_BORDERED_MF = VelStep1BSO + DensStep1BS, what the shipped scene runs (SystemManager.cpp:103-108):
+    LinearSolve1BSO, LinearSolve1BO, ProjectBO and whole frames with two fluids against the unmodified reference."""
+    import ctypes
+    import oracle_py as op
+    rng = np.random.default_rng(4040)
+    for N in (7, 24, 45):
+        info = _cell_map_with_objects(oracle, N, rng) if N > 10 else oracle.make_cell_info(N, True)
+        r = lambda s=1.0: (rng.uniform(-1, 1, (N + 2) ** 2) * s).astype(np.float32)
+        for b in (0, 1, 2):
+            x, x0 = r(), r()
+            y = x.copy()
+            oracle.lin_solve_bo(N, b, x, x0, np.float32(0.7), np.float32(3.8), info)
+            ref.L.ref_lin_solve_bo(N, b, y, x0, 0.7, 3.8, 20, info)
+            assert x.tobytes() == y.tobytes(), ("lin_solve_bo", N, b)
+            dens = [np.abs(r(0.6)), np.abs(r(0.9))]
+            dens[0].reshape(N + 2, N + 2)[3:5, :] = 0.0
+            dens[1].reshape(N + 2, N + 2)[3:6, :] = 0.0   # cells with no fluid at all: the air fallback
+            coef = np.array([1e-4, 3e-4], np.float32)
+            x, x0 = r(), r()
+            y = x.copy()
+            aSc = np.float32(0.1) * np.float32(N) * np.float32(N)
+            oracle.lin_solve_bso(N, b, x, x0, aSc, np.float32(0.001), dens, coef, info)
+            ptrs = (ctypes.c_void_p * 2)(*[d.ctypes.data for d in dens])
+            ref.L.ref_lin_solve_bso(N, b, y, x0, aSc, 0.001, 2, ctypes.cast(ptrs, ctypes.c_void_p), coef, 20, info)
+            assert x.tobytes() == y.tobytes(), ("lin_solve_bso", N, b)
+        u, v, p, dv = r(), r(), r(), r()
+        U, V, P, D = u.copy(), v.copy(), p.copy(), dv.copy()
+        oracle.project_bo(N, u, v, p, dv, info)
+        ref.L.ref_project_bo(N, U, V, P, D, 20, info)
+        for got, want, name in ((u, U, "u"), (v, V, "v"), (p, P, "p"), (dv, D, "div")):
+            assert got.tobytes() == want.tobytes(), ("project_bo", N, name)
+    fluids = [(0.000001, 0.0001), (0.0001, 0.0003)]  # (diff, visc) of the shipped scene
+    for N, steps, square, vort, damp in ((16, 5, True, 0.0, 0.0), (48, 10, True, 0.55, 0.1), (64, 6, False, 0.0, 0.0)):
+        c = N // 2
+        src = [(2, c, c, 0, 100.0), (3, c - 5, c + 4, 0, 60.0), (0, c, c, 0, 5.0), (1, c, c, 0, 5.0), (3, 4, 4, 1, 0.9), (1, 3, N - 2, 0, -4.0)]
+        sim = ref.sim(N, 0, 0, vort, 20, damp, fluids=fluids, fstype=2, square_border=square)
+        sim.set_sources(src)
+        sim.update(0.1, steps)
+        info = oracle.make_cell_info(N, square)
+        n = (N + 2) ** 2
+        f = {k: np.zeros(n, np.float32) for k in "u v u0 v0 p".split()}
+        f["d"] = [np.zeros(n, np.float32) for _ in fluids]
+        f["d0"] = [np.zeros(n, np.float32) for _ in fluids]
+        oracle.update_mf(N, f, info, src, fluids, 0.1, steps, visc_air=ref.L.ref_visc_air(sim.h), vorticity=vort, damp=damp)
+        assert f["u"].tobytes() == sim.field(0).tobytes() and f["v"].tobytes() == sim.field(1).tobytes(), (N, "velocity")
+        assert f["u0"].tobytes() == sim.field(3).tobytes() and f["v0"].tobytes() == sim.field(4).tobytes(), (N, "scratch")
+        assert f["p"].tobytes() == sim.p().tobytes(), (N, "p")
+        for k in range(len(fluids)):
+            assert f["d"][k].tobytes() == sim.density(k).tobytes(), (N, "density", k)
+        assert np.abs(f["u"]).max() > 0
+        sim.close()
