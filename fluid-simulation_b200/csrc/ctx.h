@@ -109,8 +109,8 @@ struct fluid_ctx {
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
 	bool wavefront_persistent = true; // reference-order solve as ONE launch (tickets + progress counters) instead of one per hyperplane
-	int* d_wf_sync = nullptr;  // its ticket counter and per-column progress counters
-	long long wf_sync_capacity = 0;
+	int* d_wf_sync[2] = { nullptr, nullptr }; // its ticket counter and per-column progress counters, one set per lane (u and v solve side by side)
+	long long wf_sync_capacity[2] = { 0, 0 };
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
 	bool rb_stream = true;     // interior of large grids by the register-resident streaming kernel (k_rb_stream)

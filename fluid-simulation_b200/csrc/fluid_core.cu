@@ -85,7 +85,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_src_saved) cudaFree(c->d_src_saved);
 	if (c->d_info) cudaFree(c->d_info);
-	if (c->d_wf_sync) cudaFree(c->d_wf_sync);
+	for (auto& p : c->d_wf_sync) if (p) cudaFree(p);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
 	for (auto& e : c->prof_pool) cudaEventDestroy(e);

@@ -497,17 +497,19 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		const long long tickets = (long long) c->batch * limit * ntx;
 		if (c->wavefront_persistent && tickets < (1LL << 28)) {
 			// one launch per solve: CTAs take (sweep, tile column) tickets and order themselves by progress counters
-			if (tickets + 1 > c->wf_sync_capacity) {
-				if (c->d_wf_sync) CU_TRY(cudaFree(c->d_wf_sync));
-				c->d_wf_sync = nullptr;
-				CU_TRY(cudaMalloc(&c->d_wf_sync, sizeof(int) * (size_t) (tickets + 1)));
-				c->wf_sync_capacity = tickets + 1;
+			int*& wsync = c->d_wf_sync[c->lane ? 1 : 0];
+			long long& wcap = c->wf_sync_capacity[c->lane ? 1 : 0];
+			if (tickets + 1 > wcap) {
+				if (wsync) CU_TRY(cudaFree(wsync));
+				wsync = nullptr;
+				CU_TRY(cudaMalloc(&wsync, sizeof(int) * (size_t) (tickets + 1)));
+				wcap = tickets + 1;
 			}
-			CU_TRY(cudaMemsetAsync(c->d_wf_sync, 0, sizeof(int) * (size_t) (tickets + 1), c->stream));
+			CU_TRY(cudaMemsetAsync(wsync, 0, sizeof(int) * (size_t) (tickets + 1), c->stream));
 			const int grid = (int) std::min<long long>(tickets, (long long) c->num_sms * 32);
-			if (T == 16) LAUNCH(k_gs_wavefront_persistent<16>, grid, 16, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, c->d_wf_sync);
-			else if (T == 32) LAUNCH(k_gs_wavefront_persistent<32>, grid, 32, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, c->d_wf_sync);
-			else LAUNCH(k_gs_wavefront_persistent<64>, grid, 64, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, c->d_wf_sync);
+			if (T == 16) LAUNCH(k_gs_wavefront_persistent<16>, grid, 16, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, wsync);
+			else if (T == 32) LAUNCH(k_gs_wavefront_persistent<32>, grid, 32, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, wsync);
+			else LAUNCH(k_gs_wavefront_persistent<64>, grid, 64, 0, c->stream, c->g, b, x, x0, a, cc, limit, ntx, nty, c->batch, wsync);
 			CU_TRY(cudaGetLastError());
 			return FLUID_OK;
 		}

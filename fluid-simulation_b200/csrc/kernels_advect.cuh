@@ -33,39 +33,33 @@ struct RowWin {
 	float w[6];
 };
 
-// A row as it is FETCHED: the lane's float4 and, for lanes 0 and 31 only, the value beyond the warp's strip.
-// The neighbours' values are shuffled in one row step later (advect_finish_row), when the loads have long
-// landed: shuffling right behind the load made every warp wait out the memory latency at the top of each
-// row step (ncu: 42 % of all stall samples on that first shuffle, issue slots 48 % busy).
-struct RowRaw {
-	float4 c;
-	float l, r;
-};
+// Rows are FETCHED one row step ahead with cp.async into a small per-warp ring in shared memory (two slots per
+// field) and read back into the window when their turn comes.  History: (1) plain loads followed at once by
+// the neighbour shuffles made every warp wait out the memory latency at the top of each row step (ncu: 42 % of
+// the stall samples on the first shuffle); (2) loads kept in registers for one row step fixed the velocity
+// kernel but not the scalar one -- with three fields the loads in flight share scoreboard slots with the ones
+// being consumed, and the first use of an OLD row waited for a load issued a moment ago (31 % of the samples
+// on one select).  cp.async has its own completion groups (wait_group), so consuming row j+1 never waits for
+// row j+2; and the neighbours' values are simply the adjacent floats of the ring slot: no shuffles, no
+// predicated scalar loads into registers, no selects.
+// Slot layout (floats): [3] = storage column 4q0-1, [4 .. 131] = the strip's 128 columns, [132] = column 4q0+128.
+constexpr int kAdvectSlot = 136;
 
-// pf points at storage column 4q (clamped into the row) of row 0 of the field; off_l / off_r are the offsets
-// of the values only lane 0 / lane 31 must fetch themselves (their neighbours are other warps').
-__device__ __forceinline__ RowRaw advect_fetch_row(const float* __restrict__ pf, int y, int pitch, int lane, int off_l, int off_r)
+__device__ __forceinline__ void advect_fetch_row(uint32_t slot, const float* __restrict__ pf, int y, int pitch, int lane, int off_l, int off_r)
 {
-	RowRaw r;
 	const float* p = pf + y * pitch;
-	r.c = __ldg(reinterpret_cast<const float4*>(p));
-	r.l = r.r = 0.0f;
-	if (lane == 0) r.l = __ldg(p + off_l);
-	if (lane == 31) r.r = __ldg(p + off_r);
-	return r;
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot + 16u + 16u * lane), "l"(p) : "memory");
+	if (lane == 0) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(slot + 12u), "l"(p + off_l) : "memory");
+	if (lane == 31) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(slot + 4u * 132u), "l"(p + off_r) : "memory");
 }
 
-__device__ __forceinline__ RowWin advect_finish_row(const RowRaw& q, int lane)
+__device__ __forceinline__ RowWin advect_finish_row(uint32_t slot, int lane)
 {
 	RowWin r;
-	r.w[1] = q.c.x;
-	r.w[2] = q.c.y;
-	r.w[3] = q.c.z;
-	r.w[4] = q.c.w;
-	const float l = __shfl_up_sync(0xffffffffu, q.c.w, 1);
-	const float rr = __shfl_down_sync(0xffffffffu, q.c.x, 1);
-	r.w[0] = (lane == 0) ? q.l : l;
-	r.w[5] = (lane == 31) ? q.r : rr;
+	const uint32_t a = slot + 16u + 16u * lane;
+	asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.w[1]), "=f"(r.w[2]), "=f"(r.w[3]), "=f"(r.w[4]) : "r"(a) : "memory");
+	asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r.w[0]) : "r"(a - 4u) : "memory");
+	asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r.w[5]) : "r"(a + 16u) : "memory");
 	return r;
 }
 
@@ -220,32 +214,47 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 	const float fi = (float) i_first;
 
 	const int j_lo = 1 + chunk * tk.chunk_rows, j_hi = min(g.NY, j_lo + tk.chunk_rows - 1);
+	constexpr int NF = VEL ? 2 : 3; // fields sampled: u, v (and d0)
+	__shared__ __align__(16) float ring_all[kAdvectWarps][2][NF][kAdvectSlot];
+	const uint32_t ring = (uint32_t) __cvta_generic_to_shared(&ring_all[threadIdx.x >> 5][0][0][0]);
+	auto slot_of = [&](int parity, int f) { return ring + 4u * (uint32_t) ((parity * NF + f) * kAdvectSlot); };
+	auto fetch_rows = [&](int y, int parity) { // one completion group per row
+		advect_fetch_row(slot_of(parity, 0), pu, y, pitch, lane, off_l, off_r);
+		advect_fetch_row(slot_of(parity, 1), pv, y, pitch, lane, off_l, off_r);
+		if (!VEL) advect_fetch_row(slot_of(parity, 2), pd, y, pitch, lane, off_l, off_r);
+		asm volatile("cp.async.commit_group;" ::: "memory");
+	};
+	auto arrived = [&]() { // every copy this warp has issued so far is in shared memory and visible to all its lanes
+		asm volatile("cp.async.wait_group 0;" ::: "memory");
+		__syncwarp();
+	};
 	RowWin wu[3], wv[3], wd[3];
-	RowRaw nu, nv, nd;
-	wu[1] = advect_finish_row(advect_fetch_row(pu, j_lo - 1, pitch, lane, off_l, off_r), lane);
-	wv[1] = advect_finish_row(advect_fetch_row(pv, j_lo - 1, pitch, lane, off_l, off_r), lane);
-	wu[2] = advect_finish_row(advect_fetch_row(pu, j_lo, pitch, lane, off_l, off_r), lane);
-	wv[2] = advect_finish_row(advect_fetch_row(pv, j_lo, pitch, lane, off_l, off_r), lane);
-	nu = advect_fetch_row(pu, j_lo + 1, pitch, lane, off_l, off_r);
-	nv = advect_fetch_row(pv, j_lo + 1, pitch, lane, off_l, off_r);
+	fetch_rows(j_lo - 1, 0);
+	fetch_rows(j_lo, 1);
+	arrived();
+	wu[1] = advect_finish_row(slot_of(0, 0), lane);
+	wv[1] = advect_finish_row(slot_of(0, 1), lane);
+	wu[2] = advect_finish_row(slot_of(1, 0), lane);
+	wv[2] = advect_finish_row(slot_of(1, 1), lane);
 	if (!VEL) {
-		wd[1] = advect_finish_row(advect_fetch_row(pd, j_lo - 1, pitch, lane, off_l, off_r), lane);
-		wd[2] = advect_finish_row(advect_fetch_row(pd, j_lo, pitch, lane, off_l, off_r), lane);
-		nd = advect_fetch_row(pd, j_lo + 1, pitch, lane, off_l, off_r);
+		wd[1] = advect_finish_row(slot_of(0, 2), lane);
+		wd[2] = advect_finish_row(slot_of(1, 2), lane);
 	}
+	__syncwarp(); // all lanes have read slot 0 before it is refilled
+	fetch_rows(j_lo + 1, 0);
 	const bool edge_lane = (i_first == 1) || (i_first + 3 >= g.N && i_first <= g.N);
 
 #pragma unroll 1
 	for (int j = j_lo; j <= j_hi; j++) {
-		// slide: rows j-1, j, j+1 <- j, j+1 and the row fetched one step ago (its neighbours' values are shuffled in
-		// now); fetch row j+2 for the next step
-		wu[0] = wu[1]; wu[1] = wu[2]; wu[2] = advect_finish_row(nu, lane);
-		wv[0] = wv[1]; wv[1] = wv[2]; wv[2] = advect_finish_row(nv, lane);
-		if (!VEL) { wd[0] = wd[1]; wd[1] = wd[2]; wd[2] = advect_finish_row(nd, lane); }
-		const int jn = min(j + 2, g.NY + 1);
-		nu = advect_fetch_row(pu, jn, pitch, lane, off_l, off_r);
-		nv = advect_fetch_row(pv, jn, pitch, lane, off_l, off_r);
-		if (!VEL) nd = advect_fetch_row(pd, jn, pitch, lane, off_l, off_r);
+		// slide: rows j-1, j, j+1 <- j, j+1 and the row fetched one step ago (ring slot (j - j_lo) & 1); then fetch
+		// row j+2 into the slot that held row j
+		const int par = (j - j_lo) & 1;
+		arrived();
+		wu[0] = wu[1]; wu[1] = wu[2]; wu[2] = advect_finish_row(slot_of(par, 0), lane);
+		wv[0] = wv[1]; wv[1] = wv[2]; wv[2] = advect_finish_row(slot_of(par, 1), lane);
+		if (!VEL) { wd[0] = wd[1]; wd[1] = wd[2]; wd[2] = advect_finish_row(slot_of(par, 2), lane); }
+		__syncwarp();
+		fetch_rows(min(j + 2, g.NY + 1), par ^ 1);
 
 		int* oob = (SLAB && j >= own_lo && j <= own_hi) ? oob_flag : nullptr; // halo rows may legitimately trace off the slab
 		const float fjl = (float) j;                            // local row, for the vote

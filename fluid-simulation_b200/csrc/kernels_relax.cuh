@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(T) k_gs_wavefront(GridDesc g, int b, float* __
 // Round 1 needed 549 launches of a few microseconds each per solve at N = 8192 (2 ntx + 2 sweeps - 3).
 // sync[0] = ticket counter, sync[1 + (sim*limit + k)*ntx + I] = progress of that column; zeroed by the host.
 template <int T>
-__global__ void __launch_bounds__(T) k_gs_wavefront_persistent(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
+__global__ void __launch_bounds__(T, (T <= 32) ? 24 : 12) k_gs_wavefront_persistent(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
 								float a, float c, int limit, int ntx, int nty, int batch, int* __restrict__ sync)
 {
 	constexpr int PS = T + 2;
