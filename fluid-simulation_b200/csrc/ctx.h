@@ -108,7 +108,7 @@ struct fluid_ctx {
 	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
-	bool wavefront_persistent = true; // reference-order solve as ONE launch (tickets + progress counters) instead of one per hyperplane
+	int wavefront_persistent = 1; // reference-order solve as ONE launch (tickets + progress counters) instead of one per hyperplane: 0 never, 1 automatic, 2 always
 	int* d_wf_sync[2] = { nullptr, nullptr }; // its ticket counter and per-column progress counters, one set per lane (u and v solve side by side)
 	long long wf_sync_capacity[2] = { 0, 0 };
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
@@ -147,6 +147,8 @@ struct fluid_ctx {
 	bool overlap_density = true;
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	int fs_type = FLUID_TYPE_ORIGINAL; // which of the reference's step function pairs this context runs (SetType, FluidSystem.cpp:69-99)
+	float *mf_a = nullptr, *mf_c = nullptr, *mf_p = nullptr; // ORIGINAL_BORDERED_MF: per-cell coefficients of LinearSolve1BSO, the system's own pressure array
+	float visc_air = 0.001f;            // FluidSystem.h:149, the viscosity of cells that hold no fluid
 	unsigned char* d_info = nullptr;    // cellInfo, one byte per cell in the fields' pitched layout (bordered types)
 	int advect_kernel = 0; // 0 automatic, 1 one thread per cell (gathers), 2 row window (kernels_advect.cuh)
 	// divisors whose short division sequence has been verified exhaustively (grid.cuh: DivC)
@@ -280,6 +282,9 @@ int bordered_disable_edges(fluid_ctx* c, int n, const int* edges);
 int dev_lin_solve_b(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc);
 int dev_blur_b(fluid_ctx* c, int b, float* x, float* x0, float a, float cc);
 int dev_project_b(fluid_ctx* c, float* u, float* v, float* p, float* div);
+int dev_mf_coeffs(fluid_ctx* c, float dt);
+int dev_lin_solve_bso(fluid_ctx* c, int b, float* x, const float* x0);
+int dev_project_bo(fluid_ctx* c, float* u, float* v, float* div);
 constexpr int kBndNone = -2; // advect: no SetBorder at all (Advect1B, FluidSystem.cpp:864-874)
 // fluid_peer.cu
 int peer_halo_exchange(fluid_ctx* c, int n, const int* ids);

@@ -46,28 +46,86 @@ int bordered_disable_edges(fluid_ctx* c, int n, const int* edges)
 	return FLUID_OK;
 }
 
-// LinearSolve1B (FluidSystem.cpp:550-578) in the context's relaxation order.
-int dev_lin_solve_b(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
+// The masked relaxations in the context's order: MODE_B LinearSolve1B (:550-578), MODE_BSO LinearSolve1BSO (:673-720, per-cell
+// coefficient arrays ab / cb, always gs_iters sweeps), MODE_BO LinearSolve1BO (:580-615).
+template <int MODE>
+static int lin_solve_masked(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc, const float* ab, const float* cb)
 {
 	ProfScope ps(c, FLUID_PROF_LIN_SOLVE);
-	const int limit = a > 0 ? c->gs_iters : 1;
+	const int limit = (MODE == MODE_BSO) ? c->gs_iters : (a > 0 ? c->gs_iters : 1);
 	if (c->gs_order == FLUID_GS_REDBLACK) {
 		const dim3 grid(cdiv((c->g.N + 1) / 2, 256), c->g.NY, c->batch);
 		for (int k = 0; k < limit; k++) {
-			LAUNCH(k_rb_half_b, grid, 256, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, 0);
-			LAUNCH(k_rb_half_b, grid, 256, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, 1);
+			LAUNCH(k_rb_half_b<MODE>, grid, 256, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, ab, cb, 0);
+			LAUNCH(k_rb_half_b<MODE>, grid, 256, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, ab, cb, 1);
 		}
 	} else {
-		const int T = (c->wavefront_tile > 0) ? c->wavefront_tile : (c->g.N < 2048 ? 16 : 32);
+		// tiles of 16 or 32 cells (the masked kernels stage up to five arrays per tile in static shared memory)
+		const int T = (c->wavefront_tile > 0) ? std::min(c->wavefront_tile, 32) : (c->g.N < 2048 ? 16 : 32);
 		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
 		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
 		for (int s = 0; s <= last; s++) {
-			if (T == 16) LAUNCH(k_gs_wavefront_b<16>, dim3(ntx, limit, c->batch), 16, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, s, ntx, nty);
-			else if (T == 32) LAUNCH(k_gs_wavefront_b<32>, dim3(ntx, limit, c->batch), 32, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, s, ntx, nty);
-			else LAUNCH(k_gs_wavefront_b<64>, dim3(ntx, limit, c->batch), 64, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, s, ntx, nty);
+			if (T == 16) LAUNCH((k_gs_wavefront_b<16, MODE>), dim3(ntx, limit, c->batch), 16, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, ab, cb, s, ntx, nty);
+			else LAUNCH((k_gs_wavefront_b<32, MODE>), dim3(ntx, limit, c->batch), 32, 0, c->stream, c->g, b, x, x0, c->d_info, a, cc, ab, cb, s, ntx, nty);
 		}
 	}
 	CU_TRY(cudaGetLastError());
+	return FLUID_OK;
+}
+
+int dev_lin_solve_b(fluid_ctx* c, int b, float* x, const float* x0, float a, float cc)
+{
+	return lin_solve_masked<MODE_B>(c, b, x, x0, a, cc, nullptr, nullptr);
+}
+
+// ---- FSType::ORIGINAL_BORDERED_MF (VelStep1BSO, FluidSystem.cpp:424-447) ----
+static int mf_scratch(fluid_ctx* c)
+{
+	for (float** p : { &c->mf_a, &c->mf_c, &c->mf_p }) {
+		if (!*p) {
+			CU_TRY(cudaMalloc(p, c->field_bytes));
+			CU_TRY(cudaMemsetAsync(*p, 0, c->field_bytes, c->stream));
+		}
+	}
+	return FLUID_OK;
+}
+
+// The per-cell (a, c) of LinearSolve1BSO for this velocity step: Diffuse1BSO (:828-831) passes aSc = dt*N*N, the
+// fallback visc_air and the fluids' viscosities; the densities are the CURRENT ones.
+int dev_mf_coeffs(fluid_ctx* c, float dt)
+{
+	FL_TRY(mf_scratch(c));
+	MfFluids fl = {};
+	fl.n = c->n_fluids;
+	for (int k = 0; k < c->n_fluids; k++) {
+		fl.dens[k] = c->f[FLUID_DENS_OF(k)];
+		fl.coef[k] = c->fl_set[k] ? c->fl_visc[k] : c->visc;
+	}
+	const float aSc = dt * c->g.N * c->g.N;
+	ProfScope ps(c, FLUID_PROF_OTHER);
+	LAUNCH(k_mf_coeffs, cells_grid(c, 0), kBlkRow, 0, c->stream, c->g, fl, aSc, c->visc_air, c->mf_a, c->mf_c);
+	return FLUID_OK;
+}
+
+int dev_lin_solve_bso(fluid_ctx* c, int b, float* x, const float* x0)
+{
+	return lin_solve_masked<MODE_BSO>(c, b, x, x0, 0.0f, 0.0f, c->mf_a, c->mf_c);
+}
+
+// ProjectBO (FluidSystem.cpp:1061-1122): the pressure lives in the context's own array (the reference solves into its
+// member p and ignores the array passed as p_old, :1096-1098), so the caller's p array is left untouched.
+int dev_project_bo(fluid_ctx* c, float* u, float* v, float* div)
+{
+	FL_TRY(mf_scratch(c));
+	{
+		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
+		LAUNCH(k_divergence_bo, cells_grid(c, 2), kBlkRow, 0, c->stream, c->g, u, v, div, c->mf_p, c->d_info);
+	}
+	FL_TRY((lin_solve_masked<MODE_BO>(c, 0, c->mf_p, div, 1.0f, 4.0f, nullptr, nullptr)));
+	{
+		ProfScope ps(c, FLUID_PROF_PROJECT_AUX);
+		LAUNCH(k_subtract_gradient_b, cells_grid(c, 0), kBlkRow, 0, c->stream, c->g, u, v, c->mf_p, c->d_info);
+	}
 	return FLUID_OK;
 }
 

@@ -85,6 +85,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->d_src) cudaFree(c->d_src);
 	if (c->d_src_saved) cudaFree(c->d_src_saved);
 	if (c->d_info) cudaFree(c->d_info);
+	for (float* p : { c->mf_a, c->mf_c, c->mf_p }) if (p) cudaFree(p);
 	for (auto& p : c->d_wf_sync) if (p) cudaFree(p);
 	if (c->d_first) cudaFree(c->d_first);
 	for (auto& sg : c->prof_segs) { cudaEventDestroy(sg.a); cudaEventDestroy(sg.b); }
@@ -123,7 +124,7 @@ extern "C" int fluid_ctx_create(const fluid_params* p, fluid_ctx** out)
 	if (p->gs_iters < 1) return fail(FLUID_ERR_INVALID, "gs_iters=%d must be >= 1", p->gs_iters);
 	if (p->gs_order != FLUID_GS_WAVEFRONT && p->gs_order != FLUID_GS_REDBLACK) return fail(FLUID_ERR_INVALID, "unknown gs_order %d", p->gs_order);
 	if (p->advect_mode != FLUID_ADVECT_MIDPOINT && p->advect_mode != FLUID_ADVECT_EULER) return fail(FLUID_ERR_INVALID, "unknown advect_mode %d", p->advect_mode);
-	if (p->fs_type != FLUID_TYPE_ORIGINAL && p->fs_type != FLUID_TYPE_ORIGINAL_BORDERED) return fail(FLUID_ERR_INVALID, "unknown fs_type %d", p->fs_type);
+	if (p->fs_type != FLUID_TYPE_ORIGINAL && p->fs_type != FLUID_TYPE_ORIGINAL_BORDERED && p->fs_type != FLUID_TYPE_ORIGINAL_BORDERED_MF) return fail(FLUID_ERR_INVALID, "unknown fs_type %d", p->fs_type);
 	if (p->fs_type != FLUID_TYPE_ORIGINAL && (p->slab_count > 1 || p->slab_rows > 0))
 		return fail(FLUID_ERR_UNSUPPORTED, "the bordered solver types run on whole square grids only (no row slabs)");
 	if (p->n_fluids < 0 || p->n_fluids > FLUID_MAX_FLUIDS) return fail(FLUID_ERR_INVALID, "n_fluids=%d out of range [1,%d]", p->n_fluids, FLUID_MAX_FLUIDS);
@@ -492,7 +493,8 @@ extern "C" int fluid_ctx_set_wavefront_tile(fluid_ctx* c, int tile)
 extern "C" int fluid_ctx_set_wavefront_persistent(fluid_ctx* c, int on)
 {
 	CHECK_CTX(c);
-	c->wavefront_persistent = on != 0;
+	if (on < 0 || on > 2) return fail(FLUID_ERR_INVALID, "wavefront_persistent=%d must be 0 (never), 1 (automatic) or 2 (always)", on);
+	c->wavefront_persistent = on;
 	return FLUID_OK;
 }
 
@@ -554,6 +556,13 @@ extern "C" int fluid_ctx_dens_step(fluid_ctx* c, float dt)
 	CHECK_CTX(c);
 	for (int fl = 0; fl < c->n_fluids; fl++)
 		FL_TRY(dev_dens_step(c, c->f[FLUID_DENS_OF(fl)], c->f[FLUID_DENS_PREV_OF(fl)], c->f[FLUID_U], c->f[FLUID_V], fluid_diff(c, fl), dt));
+	return FLUID_OK;
+}
+
+extern "C" int fluid_ctx_set_visc_air(fluid_ctx* c, float visc_air)
+{
+	CHECK_CTX(c);
+	c->visc_air = visc_air;
 	return FLUID_OK;
 }
 

@@ -495,8 +495,12 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		const int ntx = cdiv(c->g.N, T), nty = cdiv(c->g.NY, T);
 		const int last = (ntx - 1) + (nty - 1) + 2 * (limit - 1);
 		const long long tickets = (long long) c->batch * limit * ntx;
-		if (c->wavefront_persistent && tickets < (1LL << 28)) {
-			// one launch per solve: CTAs take (sweep, tile column) tickets and order themselves by progress counters
+		// One launch per solve (CTAs take (sweep, tile column) tickets and order themselves by progress counters) pays
+		// where launches dominate: measured ms/step, persistent vs per-hyperplane launches: N=1024 6.4 vs 7.0, N=2048 12.8 vs
+		// 11.4, N=8192 81 vs 47 -- a tile's waits, fences and L2-only loads cost more than the launch gaps they replace once
+		// every launch carries thousands of tiles.  Automatic choice: grids up to 1024 cells wide; mode 2 forces it.
+		const bool persistent = c->wavefront_persistent == 2 || (c->wavefront_persistent == 1 && c->g.N <= 1024);
+		if (persistent && tickets < (1LL << 28)) {
 			int*& wsync = c->d_wf_sync[c->lane ? 1 : 0];
 			long long& wcap = c->wf_sync_capacity[c->lane ? 1 : 0];
 			if (tickets + 1 > wcap) {

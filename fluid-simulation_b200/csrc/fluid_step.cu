@@ -120,6 +120,7 @@ int dev_advect_velocity(fluid_ctx* c, float* u, float* v, const float* u0, const
 // Project (FluidSystem.cpp:982-1007).
 int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
 {
+	if (c->fs_type == FLUID_TYPE_ORIGINAL_BORDERED_MF) return dev_project_bo(c, u, v, div); // (p_old is ignored, as in the reference)
 	if (c->fs_type != FLUID_TYPE_ORIGINAL) return dev_project_b(c, u, v, p, div);
 	// p = 0 is the solve's starting guess.  Where the first pass of the solve can simply be told so, the zeros
 	// are neither written here nor read there (2 x 268 MB at N = 8192).
@@ -177,6 +178,11 @@ int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float v
 	std::swap(u, u0);
 	const float a = diffusion_a(c, visc, dt);
 	std::swap(v, v0);
+	const bool mf = (c->fs_type == FLUID_TYPE_ORIGINAL_BORDERED_MF);
+	if (mf) FL_TRY(dev_mf_coeffs(c, dt)); // VelStep1BSO: the viscosity is mixed per cell from the densities (Diffuse1BSO, :828-831)
+	auto diffuse = [&](int b, float*& x, const float* x0) -> int {
+		return mf ? dev_lin_solve_bso(c, b, x, x0) : dev_lin_solve(c, b, x, x0, a, 1 + 4 * a);
+	};
 	if (c->overlap_density) { // the two diffusions are independent: v on a second lane beside u
 		if (!c->lane_stream) {
 			CU_TRY(cudaStreamCreateWithFlags(&c->lane_stream, cudaStreamNonBlocking));
@@ -188,16 +194,16 @@ int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float v
 		cudaStream_t main_stream = c->stream;
 		c->stream = c->lane_stream;
 		c->lane = 1;
-		const int rc = dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a);
+		const int rc = diffuse(2, v, v0);
 		c->lane = 0;
 		c->stream = main_stream;
 		FL_TRY(rc);
 		CU_TRY(cudaEventRecord(c->ev_join2, c->lane_stream));
-		FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
+		FL_TRY(diffuse(1, u, u0));
 		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join2, 0));
 	} else {
-		FL_TRY(dev_lin_solve(c, 1, u, u0, a, 1 + 4 * a));
-		FL_TRY(dev_lin_solve(c, 2, v, v0, a, 1 + 4 * a));
+		FL_TRY(diffuse(1, u, u0));
+		FL_TRY(diffuse(2, v, v0));
 	}
 	FL_TRY(halo_exchange(c, { u, v }));
 	FL_TRY(dev_project(c, u, v, u0, v0));

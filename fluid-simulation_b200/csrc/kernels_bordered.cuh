@@ -74,18 +74,66 @@ __device__ __forceinline__ float relax_b(unsigned char m, float x0, float a, flo
 	return div_exact(x0 + a * add, c);
 }
 
-// LinearSolve1B (FluidSystem.cpp:550-578) in the reference's lexicographic order: the tile hyperplane schedule of
-// k_gs_wavefront (kernels_relax.cuh) -- launch s runs every tile (I, J) of sweep k with I + J + 2k = s; inside a
-// tile thread r walks row r along the cell anti-diagonal.  A masked stencil reads a subset of the plain one's
-// neighbours (or the cell itself), so the same schedule respects every dependence.
-template <int T>
+// The three masked relaxations of the bordered solver types:
+//   MODE_B    LinearSolve1B   (FluidSystem.cpp:550-578)  scalar a, c
+//   MODE_BSO  LinearSolve1BSO (FluidSystem.cpp:673-720)  a, c per cell (viscosity mixed from the densities, k_mf_coeffs)
+//   MODE_BO   LinearSolve1BO  (FluidSystem.cpp:580-615)  neighbours in the order right, left, top, bottom; an
+//             unreachable neighbour is replaced by bScX * own value (bScX for all four sides, as the reference has
+//             it) plus the neighbour cell's own value when that cell is not FLUID (an object's velocity)
+enum { MODE_B = 0, MODE_BSO = 1, MODE_BO = 2 };
+
+__device__ __forceinline__ float relax_bo(unsigned char m, unsigned char me, unsigned char mw, unsigned char mn, unsigned char ms, float x0, float a,
+					  float mine, float w, float e, float s, float n, float c, float bScX)
+{
+	float add = (m & CI_RIGHT) ? e : (bScX * mine + ((me & CI_FLUID) ? 0.0f : e));
+	add += (m & CI_LEFT) ? w : (bScX * mine + ((mw & CI_FLUID) ? 0.0f : w));
+	add += (m & CI_TOP) ? n : (bScX * mine + ((mn & CI_FLUID) ? 0.0f : n));
+	add += (m & CI_BOTTOM) ? s : (bScX * mine + ((ms & CI_FLUID) ? 0.0f : s));
+	return div_exact(x0 + a * add, c);
+}
+
+// Per-cell coefficients of LinearSolve1BSO (FluidSystem.cpp:700-716): a = aSc * (sum_n d_n*coef_n) / sum_n d_n where the
+// summed density exceeds 1e-9, else aSc * a_fallback; c = 1 + 4a.  The densities do not change during VelStep, so the
+// pair is computed once per velocity step instead of once per cell and sweep.
+struct MfFluids {
+	const float* dens[8];
+	float coef[8];
+	int n;
+};
+
+__global__ void __launch_bounds__(256) k_mf_coeffs(GridDesc g, MfFluids fl, float aSc, float a_fallback, float* __restrict__ ab, float* __restrict__ cb)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x + 1, j = blockIdx.y + 1;
+	if (i > g.N || j > g.NY) return;
+	const long long id = off + cell(g, i, j);
+	float c = 1.0f, a = 0.0f, total = 0.0f;
+	for (int n = 0; n < fl.n; n++) {
+		const float d = __ldg(fl.dens[n] + id);
+		a += d * fl.coef[n];
+		total += d;
+	}
+	if (total > 0.000000001f) a = div_exact(aSc * a, total);
+	else a = aSc * a_fallback;
+	c += 4 * a;
+	ab[id] = a;
+	cb[id] = c;
+}
+
+// The masked relaxations in the reference's lexicographic order: the tile hyperplane schedule of k_gs_wavefront
+// (kernels_relax.cuh) -- launch s runs every tile (I, J) of sweep k with I + J + 2k = s; inside a tile thread r walks
+// row r along the cell anti-diagonal.  A masked stencil reads a subset of the plain one's neighbours (or the cell
+// itself, or a non-FLUID cell that no sweep writes), so the same schedule respects every dependence.
+template <int T, int MODE>
 __global__ void __launch_bounds__(T) k_gs_wavefront_b(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
-						       const unsigned char* __restrict__ info, float a, float c, int s, int ntx, int nty)
+						       const unsigned char* __restrict__ info, float a, float c, const float* __restrict__ ab,
+						       const float* __restrict__ cb, int s, int ntx, int nty)
 {
 	constexpr int PS = T + 2;
 	__shared__ float sx[(T + 2) * PS];
 	__shared__ float s0[T * PS];
-	__shared__ unsigned char sm[T * PS];
+	__shared__ float sa[(MODE == MODE_BSO) ? T * PS : 1], sc[(MODE == MODE_BSO) ? T * PS : 1];
+	__shared__ unsigned char sm[(T + 2) * PS]; // with halo (MODE_BO looks at the neighbours' FLUID bits)
 	const int I = blockIdx.x, k = blockIdx.y, J = s - 2 * k - I;
 	if (J < 0 || J >= nty) return;
 	const long long off = (long long) blockIdx.z * g.plane;
@@ -96,25 +144,38 @@ __global__ void __launch_bounds__(T) k_gs_wavefront_b(GridDesc g, int b, float* 
 	const int r = threadIdx.x;
 	for (int rr = 0; rr < h + 2; rr++) {
 		const long long row = cell(g, i0 - 1, j0 - 1 + rr);
-		for (int cc = r; cc < w + 2; cc += T) sx[rr * PS + cc] = x[row + cc];
+		for (int cc = r; cc < w + 2; cc += T) {
+			sx[rr * PS + cc] = x[row + cc];
+			sm[rr * PS + cc] = info[row + cc];
+		}
 	}
 	for (int rr = 0; rr < h; rr++) {
 		const long long row = cell(g, i0, j0 + rr);
 		for (int cc = r; cc < w; cc += T) {
 			s0[rr * PS + cc] = __ldg(x0 + row + cc);
-			sm[rr * PS + cc] = info[row + cc];
+			if (MODE == MODE_BSO) {
+				sa[rr * PS + cc] = __ldg(ab + off + row + cc);
+				sc[rr * PS + cc] = __ldg(cb + off + row + cc);
+			}
 		}
 	}
 	__syncthreads();
 	const float bScX = (b == 1) ? -1.0f : 1.0f, bScY = (b == 2) ? -1.0f : 1.0f;
 	float* me = &sx[(r + 1) * PS + 1];
+	const unsigned char* mm = &sm[(r + 1) * PS + 1];
 	const int nd = w + h - 1;
 	for (int d = 0; d < nd; d++) {
 		const int col = d - r;
 		if (r < h && col >= 0 && col < w) {
-			const unsigned char m = sm[r * PS + col];
-			if (m & CI_FLUID)
-				me[col] = relax_b(m, s0[r * PS + col], a, me[col], me[col - 1], me[col + 1], me[col - PS], me[col + PS], c, bScX, bScY);
+			const unsigned char m = mm[col];
+			if (m & CI_FLUID) {
+				const float ca = (MODE == MODE_BSO) ? sa[r * PS + col] : a, ccc = (MODE == MODE_BSO) ? sc[r * PS + col] : c;
+				if (MODE == MODE_BO)
+					me[col] = relax_bo(m, mm[col + 1], mm[col - 1], mm[col + PS], mm[col - PS], s0[r * PS + col], ca, me[col], me[col - 1],
+							   me[col + 1], me[col - PS], me[col + PS], ccc, bScX);
+				else
+					me[col] = relax_b(m, s0[r * PS + col], ca, me[col], me[col - 1], me[col + 1], me[col - PS], me[col + PS], ccc, bScX, bScY);
+			}
 		}
 		__syncthreads();
 	}
@@ -124,10 +185,12 @@ __global__ void __launch_bounds__(T) k_gs_wavefront_b(GridDesc g, int b, float* 
 	}
 }
 
-// Red-black ordering of LinearSolve1B, one colour per launch, one thread per cell of that colour
-// (colour 0 = i + j even).  No counterpart in the reference; bit-identical to oracle_lin_solve_b_rb.
+// Red-black ordering of the same relaxations, one colour per launch, one thread per cell of that colour
+// (colour 0 = i + j even).  No counterpart in the reference; bit-identical to the oracle's red-black statements.
+template <int MODE>
 __global__ void __launch_bounds__(256) k_rb_half_b(GridDesc g, int b, float* __restrict__ xb, const float* __restrict__ x0b,
-						    const unsigned char* __restrict__ info, float a, float c, int colour)
+						    const unsigned char* __restrict__ info, float a, float c, const float* __restrict__ ab,
+						    const float* __restrict__ cb, int colour)
 {
 	const long long off = (long long) blockIdx.z * g.plane;
 	float* x = xb + off;
@@ -139,7 +202,15 @@ __global__ void __launch_bounds__(256) k_rb_half_b(GridDesc g, int b, float* __r
 	const unsigned char m = info[id];
 	if (!(m & CI_FLUID)) return;
 	const float bScX = (b == 1) ? -1.0f : 1.0f, bScY = (b == 2) ? -1.0f : 1.0f;
-	x[id] = relax_b(m, __ldg(x0 + id), a, x[id], x[id - 1], x[id + 1], x[id - g.pitch], x[id + g.pitch], c, bScX, bScY);
+	if (MODE == MODE_BSO) {
+		a = __ldg(ab + off + id);
+		c = __ldg(cb + off + id);
+	}
+	if (MODE == MODE_BO)
+		x[id] = relax_bo(m, info[id + 1], info[id - 1], info[id + g.pitch], info[id - g.pitch], __ldg(x0 + id), a, x[id], x[id - 1], x[id + 1],
+				 x[id - g.pitch], x[id + g.pitch], c, bScX);
+	else
+		x[id] = relax_b(m, __ldg(x0 + id), a, x[id], x[id - 1], x[id + 1], x[id - g.pitch], x[id + g.pitch], c, bScX, bScY);
 }
 
 // One pass of BlurB (FluidSystem.cpp:758-772): dst = masked stencil of src on FLUID cells; the others keep
@@ -210,6 +281,31 @@ __global__ void __launch_bounds__(256) k_subtract_gradient_b(GridDesc g, float* 
 		u[id] = 0.0f;
 		v[id] = 0.0f;
 	}
+}
+
+// ProjectBO part 1 (FluidSystem.cpp:1066-1092) fused with the whole-array p = 0 (:1094): the divergence of EVERY interior
+// cell (the reference's FLUID test is commented out), an unreachable neighbour replaced by minus the own value plus the
+// neighbour cell's velocity when that cell is not FLUID.
+__global__ void __launch_bounds__(256) k_divergence_bo(GridDesc g, const float* __restrict__ ub, const float* __restrict__ vb,
+							float* __restrict__ divb, float* __restrict__ pb, const unsigned char* __restrict__ info)
+{
+	const long long off = (long long) blockIdx.z * g.plane;
+	const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+	if (i > g.N + 1 || j > g.NY + 1) return;
+	const long long id = cell(g, i, j);
+	(pb + off)[id] = 0.0f;
+	if (i < 1 || i > g.N || j < 1 || j > g.NY) return;
+	const float* u = ub + off;
+	const float* v = vb + off;
+	const unsigned char m = info[id];
+	const float uc = __ldg(u + id), vc = __ldg(v + id);
+	const float ue = __ldg(u + id + 1), uw = __ldg(u + id - 1), vn = __ldg(v + id + g.pitch), vs = __ldg(v + id - g.pitch);
+	float val = 0.0f;
+	val += (m & CI_RIGHT) ? ue : (-uc + ((info[id + 1] & CI_FLUID) ? 0.0f : ue));
+	val -= (m & CI_LEFT) ? uw : (-uc + ((info[id - 1] & CI_FLUID) ? 0.0f : uw));
+	val += (m & CI_TOP) ? vn : (-vc + ((info[id + g.pitch] & CI_FLUID) ? 0.0f : vn));
+	val -= (m & CI_BOTTOM) ? vs : (-vc + ((info[id - g.pitch] & CI_FLUID) ? 0.0f : vs));
+	(divb + off)[id] = div_exact(-0.5f * val, (float) g.N);
 }
 
 } // namespace fluid

@@ -21,7 +21,7 @@ GS_WAVEFRONT, GS_REDBLACK = 0, 1
 ADVECT_MIDPOINT, ADVECT_EULER = 0, 1
 U, V, DENS, U_PREV, V_PREV, DENS_PREV = range(6)
 SRC_PREV_SET, SRC_CURR_ADD, SRC_CURR_SET = 0, 1, 2
-TYPE_ORIGINAL, TYPE_ORIGINAL_BORDERED = 0, 1
+TYPE_ORIGINAL, TYPE_ORIGINAL_BORDERED, TYPE_ORIGINAL_BORDERED_MF = 0, 1, 2
 K_LIN_SOLVE, K_BLUR, K_ADVECT, K_ADVECT_VEL, K_PROJECT, K_ADD_SOURCE = range(6)
 
 # every symbol include/fluid_cuda.h declares (tests check the .so exports them all)
@@ -38,7 +38,7 @@ EXPORTS = [
     "fluid_ctx_set_fast_division", "fluid_ctx_division_window", "fluid_ctx_set_small_grid_kernels",
     "fluid_ctx_set_wavefront_tile", "fluid_ctx_set_wavefront_persistent", "fluid_ctx_render", "fluid_ctx_set_stream_kernel", "fluid_ctx_set_overlap", "fluid_ctx_set_advect_kernel", "fluid_ctx_set_sparse_sources",
     "fluid_ctx_reset_cell_info", "fluid_ctx_disable_edges", "fluid_ctx_add_square_border", "fluid_ctx_set_cell_info",
-    "fluid_ctx_get_cell_info",
+    "fluid_ctx_get_cell_info", "fluid_ctx_set_visc_air",
     "fluid_ctx_peer_halo_local", "fluid_ctx_peer_halo_connect", "fluid_ipc_export", "fluid_ipc_import", "fluid_ipc_close",
     "fluid_ctx_set_exchange", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
     "fluid_ctx_local_rows",
@@ -135,6 +135,7 @@ def lib():
     L.fluid_ctx_add_square_border.argtypes = [_vp]
     L.fluid_ctx_set_cell_info.argtypes = [_vp, _u8, _ci]
     L.fluid_ctx_get_cell_info.argtypes = [_vp, _u8]
+    L.fluid_ctx_set_visc_air.argtypes = [_vp, _cf]
     L.fluid_ctx_peer_halo_local.argtypes = [_vp, ctypes.POINTER(_vp), ctypes.POINTER(ctypes.c_size_t)]
     L.fluid_ctx_peer_halo_connect.argtypes = [_vp, _vp, _vp]
     L.fluid_ipc_export.argtypes = [_vp, ctypes.c_char_p]
@@ -382,6 +383,7 @@ class FluidSystem:
     def SetSparseSources(self, on): check(lib().fluid_ctx_set_sparse_sources(self.h, 1 if on else 0))
 
     # cell map of a TYPE_ORIGINAL_BORDERED context (FluidSystem::GetInfo / DisableEdge / AddBorder(SquareBorder))
+    def SetViscAir(self, v): check(lib().fluid_ctx_set_visc_air(self.h, v))
     def ResetCellInfo(self): check(lib().fluid_ctx_reset_cell_info(self.h))
     def AddSquareBorder(self): check(lib().fluid_ctx_add_square_border(self.h))
 
@@ -399,7 +401,9 @@ class FluidSystem:
         return out
 
     def SetWavefrontTile(self, tile): check(lib().fluid_ctx_set_wavefront_tile(self.h, tile))
-    def SetWavefrontPersistent(self, on): check(lib().fluid_ctx_set_wavefront_persistent(self.h, 1 if on else 0))
+    def SetWavefrontPersistent(self, on):
+        """True / 2 = always one launch per solve, False / 0 = never, 1 = automatic (the default)."""
+        check(lib().fluid_ctx_set_wavefront_persistent(self.h, (2 if on else 0) if isinstance(on, bool) else int(on)))
 
     def SetSmallGridKernels(self, on): check(lib().fluid_ctx_set_small_grid_kernels(self.h, 1 if on else 0))
 

@@ -63,7 +63,15 @@ typedef enum fluid_advect_mode {
  *                     vel_step, dens_step, step) is the B variant; whole grids only (no row slabs). */
 typedef enum fluid_fs_type {
 	FLUID_TYPE_ORIGINAL = 0,
-	FLUID_TYPE_ORIGINAL_BORDERED = 1
+	FLUID_TYPE_ORIGINAL_BORDERED = 1,
+	/* VelStep1BSO + DensStep1BS (FluidSystem.cpp:424-447, 301-311): what the shipped scene runs (SystemManager.cpp:108).
+	 * The velocity diffuses with a viscosity mixed per cell from the densities of all fluids (LinearSolve1BSO, :673-720;
+	 * cells without fluid take fluid_ctx_set_visc_air, default 0.001 as FluidSystem.h:149) and the projection is ProjectBO
+	 * (:1061-1122), which solves into the system's own pressure array and lets the velocity stored in non-FLUID neighbour
+	 * cells enter the divergence and the solve (LinearSolve1BO, :580-615).  The reference's quirks are reproduced: the
+	 * Y source added to vX (:426), bScX used for all four sides in LinearSolve1BO (:605-608), p_old ignored (:1096-1098).
+	 * Rigid colliders themselves are out of scope: the cell map is static until the host changes it. */
+	FLUID_TYPE_ORIGINAL_BORDERED_MF = 2
 } fluid_fs_type;
 
 /* cellInfo bits (enum CellInfo, FluidCode.h:61-73) */
@@ -268,10 +276,13 @@ int fluid_ctx_add_square_border(fluid_ctx *ctx);
  * recalc != 0: run CalcBorderFromContent on the uploaded FLUID / OBJECT bits afterwards. */
 int fluid_ctx_set_cell_info(fluid_ctx *ctx, const unsigned char *host_info, int recalc);
 int fluid_ctx_get_cell_info(fluid_ctx *ctx, unsigned char *host_info);
+/* FLUID_TYPE_ORIGINAL_BORDERED_MF: viscosity of cells that hold no fluid (visc_air, FluidSystem.h:149; default 0.001). */
+int fluid_ctx_set_visc_air(fluid_ctx *ctx, float visc_air);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
 int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
 /* Reference-order solve as ONE launch whose CTAs take (sweep, tile column) tickets and order themselves with
- * progress counters (default), or 0 = one launch per hyperplane of the (tile, sweep) schedule.  Results identical. */
+ * progress counters: 0 = never (one launch per hyperplane of the (tile, sweep) schedule), 1 = automatic (grids up
+ * to 1024 cells wide, where it is the faster of the two; default), 2 = always.  Results identical. */
 int fluid_ctx_set_wavefront_persistent(fluid_ctx *ctx, int on);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur
  * (all passes) as ONE single-CTA launch per ensemble member, from shared memory.  on = 0

@@ -20,7 +20,7 @@ if what in ("all", "wavefront"):
         for persistent in (True, False):
             for tile in ((16, 32) if persistent else (0,)):
                 fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_WAVEFRONT)
-                fs.SetWavefrontPersistent(persistent)
+                fs.SetWavefrontPersistent(2 if persistent else 0)
                 fs.SetWavefrontTile(tile)
                 fs.SetSources(src_of(N))
                 fs.Update(0.1, 2)

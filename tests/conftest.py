@@ -45,6 +45,12 @@ def golden_bordered():
 
 
 @pytest.fixture(scope="session")
+def golden_mf():
+    """FSType::ORIGINAL_BORDERED_MF frames of the unmodified reference, two fluids (make_golden.py: mf_frames)."""
+    return json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["mf_frames"]
+
+
+@pytest.fixture(scope="session")
 def golden_fields():
     return np.load(os.path.join(GOLDEN, "golden_fields.npz"))
 

@@ -75,6 +75,22 @@ def bordered_frames():
     return out
 
 
+def mf_frames():
+    """FSType::ORIGINAL_BORDERED_MF (VelStep1BSO + DensStep1BS) with the shipped scene's two fluids (SystemManager.cpp:99-108)."""
+    fluids = [(0.000001, 0.0001), (0.0001, 0.0003)]
+    out = []
+    for N, steps, square, vort, damp in ((192, 10, True, 0.55, 0.1), (64, 60, True, 0.0, 0.0)):
+        c = N // 2
+        src = [(2, c, c, 0, 100.0), (3, c - 5, c + 4, 0, 60.0), (0, c, c, 0, 5.0), (1, c, c, 0, 5.0), (3, 4, 4, 1, 0.9), (1, 3, N - 2, 0, -4.0)]
+        sim = R.sim(N, 0, 0, vort, 20, damp, fluids=fluids, fstype=2, square_border=square)
+        sim.set_sources(src)
+        sim.update(0.1, steps)
+        out.append(dict(N=N, steps=steps, vorticity=vort, damp=damp, square_border=square, dt=0.1, fstype=2, fluids=fluids,
+                        dens0=op.fnv1a64(sim.density(0)), dens1=op.fnv1a64(sim.density(1)), u=op.fnv1a64(sim.field(0)), v=op.fnv1a64(sim.field(1))))
+        sim.close()
+    return out
+
+
 def fields():
     z = {}
     for N in (12, 16):
@@ -148,7 +164,7 @@ def multifluid():
 if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "golden_multifluid.npz"), **multifluid())
     json.dump(dict(generator="tests/golden/make_golden.py", reference="surajiyer/Fluid-Simulation FluidSystem.cpp (unmodified)",
-                   compiler="g++ -std=c++20 -O2 -ffp-contract=off", frames=frames(), bordered_frames=bordered_frames()),
+                   compiler="g++ -std=c++20 -O2 -ffp-contract=off", frames=frames(), bordered_frames=bordered_frames(), mf_frames=mf_frames()),
               open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1)
     np.savez_compressed(os.path.join(HERE, "golden_fields.npz"), **fields())
     print("wrote", os.listdir(HERE))

@@ -203,3 +203,102 @@ def test_bordered_ensemble_and_host_calls(fl, oracle):
     fs.close()
     with pytest.raises(fl.FluidError):
         fl.FluidSystem().Setup(128, gs_order=fl.GS_REDBLACK, slab=(0, 2, 64), fs_type=fl.TYPE_ORIGINAL_BORDERED)
+
+
+# ---- FSType::ORIGINAL_BORDERED_MF: VelStep1BSO + DensStep1BS, what the shipped scene runs -----------------------------------
+
+SCENE_FLUIDS = [(0.000001, 0.0001), (0.0001, 0.0003)]  # (diff, visc), SystemManager.cpp:103-106
+
+
+def _mf_sources(N):
+    c = N // 2
+    return [(2, c, c, 0, 100.0), (3, c - 5, c + 4, 0, 60.0), (0, c, c, 0, 5.0), (1, c, c, 0, 5.0), (3, 4, 4, 1, 0.9), (1, 3, N - 2, 0, -4.0)]
+
+
+def _mf_context(fl, N, order, square, vort=0.0, damp=0.0, info=None):
+    fs = fl.FluidSystem().Setup(N, 0.0, 0.0, vort, damp, gs_order=order, n_fluids=len(SCENE_FLUIDS), fs_type=fl.TYPE_ORIGINAL_BORDERED_MF)
+    for k, (diff, visc) in enumerate(SCENE_FLUIDS):
+        fs.SetFluid(k, diff, visc)
+    if info is not None:
+        fs.SetCellInfo(info)
+    elif square:
+        fs.AddSquareBorder()
+    return fs
+
+
+@pytest.mark.parametrize("order", [0, 1])
+@pytest.mark.parametrize("N,steps,square,vort,damp", [(16, 5, True, 0.0, 0.0), (48, 10, True, 0.55, 0.1), (130, 4, False, 0.0, 0.0), (200, 3, True, 0.3, 0.0)])
+def test_multifluid_bordered_frames_vs_oracle_bitwise(fl, oracle, N, steps, square, vort, damp, order):
+    src = _mf_sources(N)
+    info = oracle.make_cell_info(N, square)
+    n = (N + 2) ** 2
+    f = {k: np.zeros(n, np.float32) for k in "u v u0 v0 p".split()}
+    f["d"] = [np.zeros(n, np.float32) for _ in SCENE_FLUIDS]
+    f["d0"] = [np.zeros(n, np.float32) for _ in SCENE_FLUIDS]
+    oracle.update_mf(N, f, info, src, SCENE_FLUIDS, 0.1, steps, order=order, vorticity=vort, damp=damp)
+    fs = _mf_context(fl, N, order, square, vort, damp)
+    fs.SetSources([(fl.dens_of(s[0] - 2) if s[0] >= 2 else s[0],) + tuple(s[1:]) for s in src])
+    fs.Update(0.1, steps)
+    assert_bits(fs.download(fl.U), f["u"], "MF frame N=%d order=%d: u" % (N, order))
+    assert_bits(fs.download(fl.V), f["v"], "MF frame N=%d order=%d: v" % (N, order))
+    assert_bits(fs.download(fl.U_PREV), f["u0"], "MF frame N=%d order=%d: u.Prev (untouched by ProjectBO)" % (N, order))
+    assert_bits(fs.download(fl.V_PREV), f["v0"], "MF frame N=%d order=%d: v.Prev (div)" % (N, order))
+    for k in range(len(SCENE_FLUIDS)):
+        assert_bits(fs.download(fl.dens_of(k)), f["d"][k], "MF frame N=%d order=%d: density %d" % (N, order, k))
+    fs.close()
+
+
+def test_multifluid_bordered_with_object_cells(fl, oracle):
+    """Non-FLUID cells inside the grid carrying a velocity (what a collider leaves): their velocity enters ProjectBO's
+    divergence and LinearSolve1BO."""
+    N, steps = 60, 3
+    rng = np.random.default_rng(8)
+    info = object_map(oracle, N, rng, True)
+    src = _mf_sources(N)
+    n = (N + 2) ** 2
+    init_u, init_v = rand_field(rng, N, 0.3), rand_field(rng, N, 0.3)
+    for order in (0, 1):
+        f = {"u": init_u.copy(), "v": init_v.copy(), "u0": np.zeros(n, np.float32), "v0": np.zeros(n, np.float32), "p": np.zeros(n, np.float32)}
+        f["d"] = [np.zeros(n, np.float32) for _ in SCENE_FLUIDS]
+        f["d0"] = [np.zeros(n, np.float32) for _ in SCENE_FLUIDS]
+        oracle.update_mf(N, f, info, src, SCENE_FLUIDS, 0.1, steps, order=order)
+        fs = _mf_context(fl, N, order, False, info=info)
+        fs.upload(fl.U, init_u)
+        fs.upload(fl.V, init_v)
+        fs.SetSources([(fl.dens_of(s[0] - 2) if s[0] >= 2 else s[0],) + tuple(s[1:]) for s in src])
+        fs.Update(0.1, steps)
+        assert_bits(fs.download(fl.U), f["u"], "objects, order %d: u" % order)
+        assert_bits(fs.download(fl.V), f["v"], "objects, order %d: v" % order)
+        assert_bits(fs.download(fl.dens_of(1)), f["d"][1], "objects, order %d: density 1" % order)
+        fs.close()
+
+
+@pytest.mark.parametrize("N,steps", [(16, 8), (64, 12), (192, 3)])
+def test_multifluid_bordered_frames_vs_live_reference(fl, ref, N, steps):
+    """The shipped scene's solver set-up (two fluids, ORIGINAL_BORDERED_MF, SquareBorder, vorticity 0.55, damp 0.1;
+    SystemManager.cpp:99-108) against the UNMODIFIED reference executed here."""
+    src = _mf_sources(N)
+    sim = ref.sim(N, 0, 0, 0.55, 20, 0.1, fluids=SCENE_FLUIDS, fstype=2, square_border=True)
+    sim.set_sources(src)
+    sim.update(0.1, steps)
+    fs = _mf_context(fl, N, 0, True, 0.55, 0.1)
+    fs.SetSources([(fl.dens_of(s[0] - 2) if s[0] >= 2 else s[0],) + tuple(s[1:]) for s in src])
+    fs.Update(0.1, steps)
+    assert_bits(fs.download(fl.U), sim.field(0), "vs live reference N=%d: u" % N)
+    assert_bits(fs.download(fl.V), sim.field(1), "vs live reference N=%d: v" % N)
+    for k in range(len(SCENE_FLUIDS)):
+        assert_bits(fs.download(fl.dens_of(k)), sim.density(k), "vs live reference N=%d: density %d" % (N, k))
+    fs.close()
+    sim.close()
+
+
+def test_multifluid_bordered_golden_frames(fl, golden_mf):
+    import oracle_py as op
+    for fr in golden_mf:
+        N = fr["N"]
+        fs = _mf_context(fl, N, 0, fr["square_border"], fr["vorticity"], fr["damp"])
+        fs.SetSources([(fl.dens_of(s[0] - 2) if s[0] >= 2 else s[0],) + tuple(s[1:]) for s in _mf_sources(N)])
+        fs.Update(fr["dt"], fr["steps"])
+        got = (op.fnv1a64(fs.download(fl.dens_of(0))), op.fnv1a64(fs.download(fl.dens_of(1))), op.fnv1a64(fs.GetVelX()), op.fnv1a64(fs.GetVelY()))
+        assert got == (fr["dens0"], fr["dens1"], fr["u"], fr["v"]), fr
+        fs.close()

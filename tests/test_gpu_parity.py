@@ -634,6 +634,7 @@ def test_wavefront_persistent_many_sweeps_and_members(fl, oracle):
     rng = np.random.default_rng(5150)
     N, B = 150, 3
     fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=45, batch=B)
+    fs.SetWavefrontPersistent(True)
     xs = [(rand_field(rng, N), rand_field(rng, N)) for _ in range(B)]
     for sim, (x, x0) in enumerate(xs):
         fs.upload(fl.U, x, sim)
@@ -645,6 +646,7 @@ def test_wavefront_persistent_many_sweeps_and_members(fl, oracle):
     fs.close()
     N = 2048
     fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=20)
+    fs.SetWavefrontPersistent(True)
     for rep in range(2):
         x, x0 = rand_field(rng, N), rand_field(rng, N)
         fs.upload(fl.U, x)
