@@ -145,9 +145,11 @@ struct fluid_ctx {
 	cudaStream_t side_stream = nullptr;
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_density = true;
+	bool side_join_pending = false; // the densities' side-stream work of this frame has not been joined yet (row slabs join it before the first halo refresh)
 	int rb_rx = 256; // tile window width, see choose_rb_rx
 	int fs_type = FLUID_TYPE_ORIGINAL; // which of the reference's step function pairs this context runs (SetType, FluidSystem.cpp:69-99)
 	float *mf_a = nullptr, *mf_c = nullptr, *mf_p = nullptr; // ORIGINAL_BORDERED_MF: per-cell coefficients of LinearSolve1BSO, the system's own pressure array
+	bool mf_coeffs_ready = false;       // Update() has computed mf_a / mf_c for the velocity step that follows
 	float visc_air = 0.001f;            // FluidSystem.h:149, the viscosity of cells that hold no fluid
 	unsigned char* d_info = nullptr;    // cellInfo, one byte per cell in the fields' pitched layout (bordered types)
 	int advect_kernel = 0; // 0 automatic, 1 one thread per cell (gathers), 2 row window (kernels_advect.cuh)

@@ -154,6 +154,13 @@ static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> array
 	for (const float* a : arrays)
 		for (int f = 0; f < c->n_fields; f++)
 			if (c->f[f] == a) ids[n++] = f;
+	// A refresh is short and its two ends wait for each other: nothing else may be queued on this GPU that could keep
+	// its kernels from starting at once.  The densities' diffusion shares the GPU with the velocity diffusion up to
+	// here (one-wave streaming launches that leave no room for anything else while they run) and is joined now.
+	if (c->side_join_pending) {
+		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+		c->side_join_pending = false;
+	}
 	ProfScope ps(c, FLUID_PROF_EXCHANGE);
 	if (c->peer_connected) return peer_halo_exchange(c, n, ids); // pushes through peer memory, two kernels on this stream
 	if (!c->exchange_stream_ordered) CU_TRY(cudaStreamSynchronize(c->stream)); // the transport reads the owned rows
@@ -179,7 +186,10 @@ int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float v
 	const float a = diffusion_a(c, visc, dt);
 	std::swap(v, v0);
 	const bool mf = (c->fs_type == FLUID_TYPE_ORIGINAL_BORDERED_MF);
-	if (mf) FL_TRY(dev_mf_coeffs(c, dt)); // VelStep1BSO: the viscosity is mixed per cell from the densities (Diffuse1BSO, :828-831)
+	// VelStep1BSO: the viscosity is mixed per cell from the densities as they are BEFORE this frame's DensStep (Diffuse1BSO,
+	// :828-831).  Update() has computed the coefficients already, before it let the densities' own step start on the side stream.
+	if (mf && !c->mf_coeffs_ready) FL_TRY(dev_mf_coeffs(c, dt));
+	c->mf_coeffs_ready = false;
 	auto diffuse = [&](int b, float*& x, const float* x0) -> int {
 		return mf ? dev_lin_solve_bso(c, b, x, x0) : dev_lin_solve(c, b, x, x0, a, 1 + 4 * a);
 	};
@@ -348,6 +358,10 @@ int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::
 		}
 		return FLUID_OK;
 	};
+	if (c->fs_type == FLUID_TYPE_ORIGINAL_BORDERED_MF) { // reads the densities: before their side-stream step may touch them
+		FL_TRY(dev_mf_coeffs(c, dt));
+		c->mf_coeffs_ready = true;
+	}
 	const bool concurrent = c->overlap_density; // slabs too: the halo exchanges of the densities come after the join
 	auto diffuse_all = [&]() -> int {
 		for (int fl = 0; fl < c->n_fluids; fl++) // DensStep1's loop over fluid_count (FluidSystem.cpp:291)
@@ -372,6 +386,7 @@ int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::
 		c->stream = main_stream;
 		FL_TRY(rc);
 		CU_TRY(cudaEventRecord(c->ev_join, c->side_stream));
+		c->side_join_pending = true;
 	}
 	if (c->vorticity != 0.0f) {
 		FL_TRY(dev_vort_confinement(c, c->f[FLUID_U], c->f[FLUID_V], c->vorticity));
@@ -381,7 +396,8 @@ int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::
 	FL_TRY(dev_vel_step(c, c->f[FLUID_U], c->f[FLUID_V], c->f[FLUID_U_PREV], c->f[FLUID_V_PREV], visc_avg(c), dt, sparse));
 	if (after_velocity) FL_TRY(after_velocity());
 	if (concurrent) {
-		CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+		if (c->side_join_pending) CU_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+		c->side_join_pending = false;
 	} else {
 		if (dens_ready) CU_TRY(cudaStreamWaitEvent(c->stream, dens_ready, 0));
 		FL_TRY(diffuse_all());

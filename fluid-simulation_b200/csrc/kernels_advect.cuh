@@ -72,7 +72,7 @@ struct BilinW {
 };
 
 template <bool SLAB>
-__device__ __forceinline__ BilinW advect_calc(const GridDesc& g, float px, float py, int* oob)
+__device__ __forceinline__ BilinW advect_calc(const GridDesc& g, float px, float py)
 {
 	BilinW r;
 	px = fminf(fmaxf(px, 0.5f), g.N + 0.5f);
@@ -83,15 +83,19 @@ __device__ __forceinline__ BilinW advect_calc(const GridDesc& g, float px, float
 	r.s0 = 1 - r.s1;
 	r.t1 = py - fj0;
 	r.t0 = 1 - r.t1;
-	r.fjl = fj0;
-	if (SLAB) {
-		r.fjl = fj0 - (float) g.j0; // small integers: exact
-		if (r.fjl < 0.0f || r.fjl > (float) g.NY) {
-			if (oob) *oob = 1;
-			r.fjl = fminf(fmaxf(r.fjl, 0.0f), (float) g.NY);
-		}
+	r.fjl = SLAB ? fj0 - (float) g.j0 : fj0; // small integers: exact.  (Rows off the slab are the gather path's business:
+	return r;                                // the window path only ever takes rows j-1 .. j+1.)
+}
+
+// A sample whose rows are not stored on this slab (backtrace longer than the halo) sets *oob and is clamped into the
+// slab so that the access stays legal; the host reports it after the step.
+template <bool SLAB>
+__device__ __forceinline__ void advect_slab_rows(const GridDesc& g, BilinW& c, int* oob)
+{
+	if (SLAB && (c.fjl < 0.0f || c.fjl > (float) g.NY)) {
+		if (oob) *oob = 1;
+		c.fjl = fminf(fmaxf(c.fjl, 0.0f), (float) g.NY);
 	}
-	return r;
 }
 
 // BilinearCoeffs::Eval (FluidCode.h:88) from memory: the general path.
@@ -138,10 +142,10 @@ __device__ __forceinline__ int advect_vote(const BilinW (&c)[4], float fi, float
 	return __all_sync(0xffffffffu, agree) ? c0 : -1;
 }
 
-template <int NF, bool PARTIAL>
-__device__ __forceinline__ void advect_sample(int code, const BilinW (&c)[4], const RowWin (&w0)[3], const RowWin (&w1)[3],
+template <int NF, bool PARTIAL, bool SLAB>
+__device__ __forceinline__ void advect_sample(int code, const GridDesc& g, BilinW (&c)[4], const RowWin (&w0)[3], const RowWin (&w1)[3],
 					       const float* __restrict__ f0, const float* __restrict__ f1, int pitch, uint32_t valid,
-					       float (&o0)[4], float (&o1)[4])
+					       int* oob, float (&o0)[4], float (&o1)[4])
 {
 	switch (code) {
 #define ADVECT_CASE(CODE, DX, DY)                                                                                 \
@@ -164,6 +168,7 @@ __device__ __forceinline__ void advect_sample(int code, const BilinW (&c)[4], co
 				if (NF > 1) o1[k] = 0.0f;
 				continue;
 			}
+			advect_slab_rows<SLAB>(g, c[k], oob);
 			o0[k] = advect_gather(c[k], f0, pitch);
 			if (NF > 1) o1[k] = advect_gather(c[k], f1, pitch);
 		}
@@ -274,10 +279,10 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 				const float diry = -dtN * wv[1].w[1 + k];
 				const float mx = (fi + k) + 0.5f * dirx;
 				const float my = fj + 0.5f * diry;
-				m[k] = advect_calc<SLAB>(g, mx, my, (!PARTIAL || ((valid >> k) & 1)) ? oob : nullptr);
+				m[k] = advect_calc<SLAB>(g, mx, my);
 			}
 			float vx[4], vy[4];
-			advect_sample<2, PARTIAL>(advect_vote<PARTIAL>(m, fi, fjl, valid), m, wu, wv, u0, v0, pitch, valid, vx, vy);
+			advect_sample<2, PARTIAL, SLAB>(advect_vote<PARTIAL>(m, fi, fjl, valid), g, m, wu, wv, u0, v0, pitch, valid, oob, vx, vy);
 #pragma unroll
 			for (int k = 0; k < 4; k++) {
 				px[k] = (fi + k) - dtN * vx[k];
@@ -286,11 +291,11 @@ __global__ void __launch_bounds__(32 * kAdvectWarps) k_advect_rows(GridDesc g, A
 		}
 		BilinW c[4];
 #pragma unroll
-		for (int k = 0; k < 4; k++) c[k] = advect_calc<SLAB>(g, px[k], py[k], (!PARTIAL || ((valid >> k) & 1)) ? oob : nullptr);
+		for (int k = 0; k < 4; k++) c[k] = advect_calc<SLAB>(g, px[k], py[k]);
 		const int code = advect_vote<PARTIAL>(c, fi, fjl, valid);
 		float ra[4], rb[4];
-		if (VEL) advect_sample<2, PARTIAL>(code, c, wu, wv, u0, v0, pitch, valid, ra, rb);
-		else advect_sample<1, PARTIAL>(code, c, wd, wd, d0, d0, pitch, valid, ra, rb);
+		if (VEL) advect_sample<2, PARTIAL, SLAB>(code, g, c, wu, wv, u0, v0, pitch, valid, oob, ra, rb);
+		else advect_sample<1, PARTIAL, SLAB>(code, g, c, wd, wd, d0, d0, pitch, valid, oob, ra, rb);
 
 		float* pa = outa + (j * pitch + col);
 		if (!PARTIAL || valid == 0xfu) {
