@@ -88,6 +88,7 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 {
 	out->c = cc;
 	out->y = 1.0f / cc;
+	out->rc = 1.0 / (double) cc;
 	out->lo = 0;
 	out->range = 0;
 	if (!(cc > 0.0f) || !isfinite(cc) || !isfinite(out->y) || c->fast_div_mode == 0) return FLUID_OK;

@@ -82,6 +82,7 @@ static void static_tile_pass(const StaticSetup* st, const GridDesc& g, int b, co
 	DivC dv; // plain IEEE division: establishing a verified window would need a device buffer
 	dv.c = cc;
 	dv.y = 0.0f;
+	dv.rc = 1.0 / (double) cc;
 	dv.lo = dv.range = 0;
 	LAUNCH((k_rb_tile<S, kRbRY, kRbRX, kRbNT>), std::min(ntiles, st->num_sms), kRbNT, kRbSmem, stream, tm_in, tm_x0, g, b, out, a,
 	       dv, ntx, nty, ntiles, 0, 0, 0, 0, nullptr, StreamRect{}, 0, 0);

@@ -99,7 +99,7 @@ __device__ __forceinline__ void rb_colour_pass(float* q, const float2 (&x0)[KB],
 			const int o = 2 * (k / CB) * RX + 32 * (k % CB);
 			// a verified divisor is positive and finite: the cells left over are the subnormal fringe, cheaper in double
 			const float t = (SECOND ? x0[k].y : x0[k].x) + a * (((q[o - 1] + q[o + 1]) + q[o - RX]) + q[o + RX]);
-			q[o] = (dv.range != 0) ? div_wide(t, c) : div_exact(t, c);
+			q[o] = (dv.range != 0) ? div_bracket(t, dv) : div_exact(t, c);
 		}
 	}
 	if (WALL) {

@@ -284,7 +284,13 @@ static __global__ void __launch_bounds__(256) k_blur_pass(GridDesc g, int b, flo
 		vals[2] = relax_fast(xc.z, a, xc.y, xc.w, xs.z, xn.z, dv, bad);
 		vals[3] = relax_fast(xc.w, a, xc.z, xe, xs.w, xn.w, dv, bad);
 	}
-	if (bad) {
+	if (bad && dv.range != 0) {
+		// a verified divisor is positive and finite; the group is on the subnormal fringe of the field: exact without a division
+		vals[0] = div_bracket(xc.x + a * (((xw + xc.y) + xs.x) + xn.x), dv);
+		vals[1] = div_bracket(xc.y + a * (((xc.x + xc.z) + xs.y) + xn.y), dv);
+		vals[2] = div_bracket(xc.z + a * (((xc.y + xc.w) + xs.z) + xn.z), dv);
+		vals[3] = div_bracket(xc.w + a * (((xc.z + xe) + xs.w) + xn.w), dv);
+	} else if (bad) {
 		vals[0] = relax(xc.x, a, xw, xc.y, xs.x, xn.x, c);
 		vals[1] = relax(xc.y, a, xc.x, xc.z, xs.y, xn.y, c);
 		vals[2] = relax(xc.z, a, xc.y, xc.w, xs.z, xn.z, c);

@@ -3,7 +3,7 @@
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/r02_run5_gpus.txt 2>&1
-timeout 900 python -m pytest tests -q -m gpu -p no:cacheprovider --timeout=400 -rf -k "multifluid or nccl or multi or wavefront" > gpurun_out/r02_run5_tests.log 2>&1
+timeout 900 python -m pytest tests -q -m gpu -p no:cacheprovider --timeout=400 -rf -k "multifluid or nccl or multi or slab or advect" > gpurun_out/r02_run5_tests.log 2>&1
 echo "pytest rc=$?" >> gpurun_out/r02_run5_tests.log
 for tr in peer nccl; do
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29611 bench.py --gpus 2 --steps 20 --warmup 3 --transport $tr > gpurun_out/r02_run5_bench_2gpu_$tr.json 2> gpurun_out/r02_run5_bench_2gpu_$tr.err

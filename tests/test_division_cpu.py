@@ -30,3 +30,23 @@ def test_division_by_a_power_of_two_is_a_multiplication():
                 assert np.array_equal((x / c).view(np.uint32), (x * y).view(np.uint32))
     one = np.float32(1.0)
     assert np.array_equal((one * t).view(np.uint32), t.view(np.uint32))  # a = 1: a * s is s
+
+
+def test_bracketed_reciprocal_product_decides_the_correctly_rounded_quotient():
+    """div_bracket (csrc/grid.cuh): q = RN64(t * RN64(1/c)) is within 2^-52 of t/c, so t/c lies strictly between
+    q*(1-2^-50) and q*(1+2^-50); rounding to single is monotone, so when both ends round to the same float that float
+    is RN32(t/c) -- for subnormal quotients too.  Checked here on the CPU over the operands it is used for (the
+    subnormal fringe of a field); undecided cases (a rounding boundary or an exact tie near q) fall back to division."""
+    rng = np.random.default_rng(0)
+    for c in (np.float32(42.94), np.float32(3.0), np.float32(1.6553601), np.float32(4.0), np.float32(1e-3), np.float32(1.0000001)):
+        t = rng.integers(0, 0x00ffffff * 4, 1_000_000, dtype=np.uint32).view(np.float32)
+        t = np.concatenate([t, -t, (rng.standard_normal(200_000) * 1e-30).astype(np.float32), (rng.standard_normal(200_000)).astype(np.float32),
+                            np.array([0.0, -0.0, 3 * 2.0 ** -149, 2.0 ** -149, 2.0 ** -126, np.inf, -np.inf], np.float32)])
+        with np.errstate(all="ignore"):
+            want = (t / c).astype(np.float32)
+            q = t.astype(np.float64) * (np.float64(1.0) / np.float64(c))
+            lo = (q * (1 - 2.0 ** -50)).astype(np.float32)
+            hi = (q * (1 + 2.0 ** -50)).astype(np.float32)
+        decided = lo.view(np.uint32) == hi.view(np.uint32)
+        assert decided.mean() > 0.8
+        assert np.array_equal(lo.view(np.uint32)[decided], want.view(np.uint32)[decided]), float(c)
