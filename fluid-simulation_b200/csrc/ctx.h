@@ -252,6 +252,7 @@ int dev_damp(fluid_ctx* c, float* vel, float amount, float dt);
 int sync_sources(fluid_ctx* c);
 int dev_update(fluid_ctx* c, float dt);
 int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::function<int()>& after_velocity);
+int dev_halo_refresh(fluid_ctx* c, int n, const int* fields);
 int dev_render(fluid_ctx* c, int sim, const float* color_rgb, float* host_pixels, float* host_lines);
 // Diffuse1 (FluidSystem.cpp:810-814): a = dt*diff*N*N left to right in float.
 static inline float diffusion_a(const fluid_ctx* c, float coef, float dt) { return dt * coef * c->g.N * c->g.N; }

@@ -605,6 +605,14 @@ extern "C" int fluid_ctx_sync(fluid_ctx* c)
 	return FLUID_OK;
 }
 
+extern "C" int fluid_ctx_halo_refresh(fluid_ctx* c, int nfields, const int* fields)
+{
+	CHECK_CTX(c);
+	if (!fields) return fail(FLUID_ERR_INVALID, "null pointer");
+	for (int k = 0; k < nfields; k++) FL_TRY(check_field(fields[k]));
+	return dev_halo_refresh(c, nfields, fields);
+}
+
 extern "C" int fluid_ctx_set_exchange(fluid_ctx* c, fluid_exchange_fn fn, void* user)
 {
 	CHECK_CTX(c);

@@ -17,6 +17,8 @@
 // GPUs, so nobody waits for a kernel that shares its device.  No counterpart in the reference.
 #include "ctx.h"
 
+#include <stdlib.h>
+
 namespace {
 
 struct PushArgs {
@@ -159,7 +161,9 @@ int peer_halo_exchange(fluid_ctx* c, int n, const int* ids)
 		pl.dst_low[q] = (float4*) rd;
 		pl.dst_high[q] = (float4*) ru;
 	}
-	const int blocks = (int) std::min<long long>((pa.n4 + 255) / 256, 2LL * c->num_sms);
+	static const int env_blocks = getenv("FLUID_PEER_BLOCKS") ? atoi(getenv("FLUID_PEER_BLOCKS")) : 0;
+	const int cap = env_blocks > 0 ? env_blocks : 2 * c->num_sms;
+	const int blocks = (int) std::min<long long>((pa.n4 + 255) / 256, (long long) cap);
 	LAUNCH(k_halo_push, blocks, 256, 0, c->stream, pa, c->peer_counter);
 	LAUNCH(k_halo_pull, blocks, 256, 0, c->stream, pl);
 	CU_TRY(cudaGetLastError());

@@ -145,6 +145,16 @@ int dev_project(fluid_ctx* c, float* u, float* v, float*& p, float* div)
 // send/recv, peer copies ...) to refill the halo rows from the neighbours' owned
 // rows.  With a 48-row halo that is needed once per 20-sweep solve instead of
 // once per colour pass: 9 exchanges of ~3 MB per step instead of ~200 of 64 KB.
+static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> arrays);
+
+// One halo refresh of the listed fields, on its own (tests and transport measurements).
+int dev_halo_refresh(fluid_ctx* c, int n, const int* fields)
+{
+	if (n == 1) return halo_exchange(c, { c->f[fields[0]] });
+	if (n == 2) return halo_exchange(c, { c->f[fields[0]], c->f[fields[1]] });
+	return fail(FLUID_ERR_INVALID, "a refresh carries 1 or 2 fields");
+}
+
 static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> arrays)
 {
 	if (c->slab_count <= 1) return FLUID_OK;

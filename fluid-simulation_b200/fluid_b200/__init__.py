@@ -40,7 +40,7 @@ EXPORTS = [
     "fluid_ctx_reset_cell_info", "fluid_ctx_disable_edges", "fluid_ctx_add_square_border", "fluid_ctx_set_cell_info",
     "fluid_ctx_get_cell_info", "fluid_ctx_set_visc_air",
     "fluid_ctx_peer_halo_local", "fluid_ctx_peer_halo_connect", "fluid_ipc_export", "fluid_ipc_import", "fluid_ipc_close",
-    "fluid_ctx_set_exchange", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
+    "fluid_ctx_set_exchange", "fluid_ctx_halo_refresh", "fluid_ctx_set_stream", "fluid_ctx_halo_regions", "fluid_ctx_upload_local", "fluid_ctx_download_local",
     "fluid_ctx_local_rows",
     "fluid_ctx_add_source", "fluid_ctx_set_bnd", "fluid_ctx_lin_solve", "fluid_ctx_blur", "fluid_ctx_advect",
     "fluid_ctx_advect_velocity", "fluid_ctx_project", "fluid_ctx_time_kernel",
@@ -147,6 +147,7 @@ def lib():
     L.fluid_ctx_download_local.argtypes = [_vp, _ci, _f32]
     L.fluid_ctx_local_rows.argtypes = [_vp, ctypes.POINTER(_ci), ctypes.POINTER(_ci)]
     L.fluid_ctx_set_exchange.argtypes = [_vp, EXCHANGE_FN, _vp]
+    L.fluid_ctx_halo_refresh.argtypes = [_vp, _ci, ctypes.POINTER(_ci)]
     L.fluid_ctx_set_stream.argtypes = [_vp, _vp, _ci]
     L.fluid_ctx_halo_regions.argtypes = [_vp, _ci] + [ctypes.POINTER(_vp)] * 4 + [ctypes.POINTER(ctypes.c_size_t)]
     L.fluid_ctx_set_profiling.argtypes = [_vp, _ci]
@@ -285,6 +286,10 @@ class FluidSystem:
                 return 1
         self._exchange_cb = EXCHANGE_FN(thunk)  # keep a reference alive
         check(lib().fluid_ctx_set_exchange(self.h, self._exchange_cb, None))
+
+    def HaloRefresh(self, fields):
+        arr = (ctypes.c_int * len(fields))(*fields)
+        check(lib().fluid_ctx_halo_refresh(self.h, len(fields), arr))
 
     def LocalRows(self):
         """(rows stored incl. halo and border rows, global row index of the first)."""

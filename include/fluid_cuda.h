@@ -311,6 +311,9 @@ int fluid_ctx_division_window(fluid_ctx *ctx, float divisor, int *lo_exp, int *h
  * idle when the callback runs.  upload/download take the GLOBAL dense array.    *
  * Forcing entries use global rows.  FLUID_GS_REDBLACK only.                     */
 typedef int (*fluid_exchange_fn)(void *user, int nfields, const int *fields);
+/* One halo refresh of 1 or 2 fields by themselves, through whichever transport the slab has (what the steps do at their
+ * six refresh points; for tests and for timing a transport).  Every slab must make the same call. */
+int fluid_ctx_halo_refresh(fluid_ctx *ctx, int nfields, const int *fields);
 int fluid_ctx_set_exchange(fluid_ctx *ctx, fluid_exchange_fn fn, void *user);
 /* Native transport: halo rows pushed straight into the neighbour's memory over NVLink and ordered by flag words,
  * two small kernels per refresh on the context's stream (csrc/fluid_peer.cu) -- no callback, no host round trip,
