@@ -78,9 +78,11 @@ class ClockSampler:
         self.t1 = time.perf_counter()
 
     def start(self):
+        if os.environ.get("FLUID_BENCH_NO_SAMPLER"):  # diagnostic only: does polling nvidia-smi disturb the run?
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "25"],
+                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("FLUID_BENCH_SAMPLE_MS", "25")],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()

@@ -113,6 +113,7 @@ struct fluid_ctx {
 	long long wf_sync_capacity[2] = { 0, 0 };
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
+	bool stream_inline = false; // this solve's streaming passes recompute out-of-window colour passes on the spot (no redo list)
 	bool rb_stream = true;     // interior of large grids by the register-resident streaming kernel (k_rb_stream)
 	// Feedback for the streaming kernels ([0] relaxation, [1] blur).  They hand every segment that met a
 	// dividend outside the verified window to an exact fallback; on fields that are mostly fringe (an ensemble

@@ -138,8 +138,12 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 
 constexpr int kStreamHoldoff = 64;
 
-// May this solve use the streaming kernel?  Consumes the count of an earlier launch if it has arrived.
-static bool stream_allowed(fluid_ctx* c, int which)
+// How may this solve use the streaming kernel?  0 = not at all, 1 = with the redo list (segments that met a dividend
+// outside the proven window are listed and recomputed exactly behind the launch), 2 = inline (every colour pass that met
+// one is recomputed exactly on the spot, no list).  Consumes the count of an earlier launch if it has arrived: when more
+// than a twelfth of the segments came back, the next kStreamHoldoff solves run inline -- the list pays off when the
+// fringe is a thin line through a large field, the inline variant when most of the field is fringe (ensembles).
+static int stream_allowed(fluid_ctx* c, int which)
 {
 	auto& fb = c->feedback[which];
 	if (fb.pending && cudaEventQuery(fb.arrived) == cudaSuccess) {
@@ -147,11 +151,12 @@ static bool stream_allowed(fluid_ctx* c, int which)
 		if (getenv("FLUID_DEBUG_FEEDBACK")) fprintf(stderr, "feedback[%d]: %d of %lld segments redone\n", which, *fb.h_count, fb.segments);
 		if (fb.segments > 0 && (long long) *fb.h_count * 12 > fb.segments) fb.holdoff = kStreamHoldoff;
 	}
+	if (!c->rb_stream) return 0;
 	if (fb.holdoff > 0) {
 		fb.holdoff--;
-		return false;
+		return 2;
 	}
-	return c->rb_stream;
+	return 1;
 }
 
 // After the last streaming launch of a solve: send its redo count home (asynchronously).
@@ -304,7 +309,13 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 		FL_TRY(redo_reserve(c, rbuf, ntasks_ll * pg.rc.segs + 1));
 		const int ntasks = (int) ntasks_ll;
 		CU_TRY(cudaMemsetAsync(c->d_redo[rbuf], 0, sizeof(int), c->stream));
-		LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
+		if (c->stream_inline) {
+			LAUNCH((k_rb_stream<S, false, false, true>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
+			*segments = 0;              // nothing is listed, nothing to report
+			if (whole) return FLUID_OK; // ... and no frame of tiles around the streamed rectangle either
+		} else {
+			LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
+		}
 	}
 	// nothing but listed rectangles to do: the narrowest window covers a strip (112 columns) and has the
 	// shortest colour passes -- a redo launch lasts as long as one tile does
@@ -389,7 +400,9 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
 	const bool pow2 = is_pow2_solve(a, cc);
 	// otherwise the streaming kernel relies on the proven window reaching the largest finite float
-	const bool streaming = dv.range != 0 && (dv.lo + dv.range) == (255u << 23) && stream_allowed(c, 0);
+	const int stream_mode = (dv.range != 0 && (dv.lo + dv.range) == (255u << 23)) ? stream_allowed(c, 0) : 0;
+	const bool streaming = stream_mode != 0;
+	c->stream_inline = (stream_mode == 2);
 	// power-of-two solves first take as many whole-grid streaming passes of 5 and 4 sweeps as fit
 	int p5 = 0, p4 = 0;
 	StreamRect rc_unused;
@@ -590,19 +603,24 @@ int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	int done = 0;
 	StreamRect rc;
 	const bool window_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
-	if (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc) && stream_allowed(c, 1)) {
+	const int blur_mode = (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc)) ? stream_allowed(c, 1) : 0;
+	if (blur_mode != 0) {
 		const int launches = 2 * ((limit - 1) / (2 * kBlurL));
 		const long long ntasks = (long long) rc.per_sim * c->batch;
 		FL_TRY(redo_reserve(c, 1, ntasks * rc.segs + 1));
 		for (int l = 0; l < launches; l++) {
 			if (l > 0) std::swap(dst, src);
+			if (blur_mode == 2) { // mostly fringe: exact on the spot, no list
+				LAUNCH((k_blur_stream<kBlurL, true>), cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
+				continue;
+			}
 			CU_TRY(cudaMemsetAsync(c->d_redo[1], 0, sizeof(int), c->stream));
 			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
 			// few entries, each a chain of 2L barrier-separated phases over ~5000 cells: wide CTAs keep the chain short
 			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo[1], b);
 		}
 		done = launches * kBlurL;
-		FL_TRY(stream_report(c, 1, ntasks * rc.segs));
+		if (blur_mode == 1) FL_TRY(stream_report(c, 1, ntasks * rc.segs));
 	}
 	for (int k = done; k < limit; k++) {
 		if (k > 0) std::swap(dst, src);

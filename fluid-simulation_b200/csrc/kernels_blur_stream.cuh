@@ -34,7 +34,9 @@ struct BlurGeom {
 
 // b is 0, 1 or 2 here (the host keeps other values on the pass-per-launch path: without mirroring the
 // two buffers' stored borders would alternate as the passes' inputs).
-template <int L, bool WALL>
+// INL: as in kernels_rb_stream.cuh -- no redo list; a level whose dividends left the proven window is recomputed at once
+// with div_bracket (its inputs, the previous iterate's rows, are still in the ring).
+template <int L, bool WALL, bool INL>
 __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float* __restrict__ xin, float* __restrict__ xout, float a,
 						 const DivC& dv, int lane0_col, int out_lo, int out_hi, int col_lo, int col_hi,
 						 int b, float* ring, int* __restrict__ redo, int redo_base, int seg_rows)
@@ -144,10 +146,17 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 				const float wl = __shfl_up_sync(0xffffffffu, c4.w, 1);
 				const float er = __shfl_down_sync(0xffffffffu, c4.x, 1);
 				float4 o;
-				o.x = stream_relax(c4.x, a, wl, c4.y, s4.x, n4.x, dv, low);
-				o.y = stream_relax(c4.y, a, c4.x, c4.z, s4.y, n4.y, dv, low);
-				o.z = stream_relax(c4.z, a, c4.y, c4.w, s4.z, n4.z, dv, low);
-				o.w = stream_relax(c4.w, a, c4.z, er, s4.w, n4.w, dv, low);
+				uint32_t lowp = 0xffffffffu;
+				o.x = stream_relax(c4.x, a, wl, c4.y, s4.x, n4.x, dv, INL ? lowp : low);
+				o.y = stream_relax(c4.y, a, c4.x, c4.z, s4.y, n4.y, dv, INL ? lowp : low);
+				o.z = stream_relax(c4.z, a, c4.y, c4.w, s4.z, n4.z, dv, INL ? lowp : low);
+				o.w = stream_relax(c4.w, a, c4.z, er, s4.w, n4.w, dv, INL ? lowp : low);
+				if (INL && __any_sync(0xffffffffu, lowp < 2u * dv.lo - 1u)) {
+					o.x = div_bracket(c4.x + a * (((wl + c4.y) + s4.x) + n4.x), dv);
+					o.y = div_bracket(c4.y + a * (((c4.x + c4.z) + s4.y) + n4.y), dv);
+					o.z = div_bracket(c4.z + a * (((c4.y + c4.w) + s4.z) + n4.z), dv);
+					o.w = div_bracket(c4.w + a * (((c4.z + er) + s4.w) + n4.w), dv);
+				}
 				if (WALL) side_walls(o);
 				if (h < L) {
 					lev[h < L ? h : 0][sy] = o;
@@ -155,10 +164,10 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 						if (has_bot && y == 1) lev[h < L ? h : 0][ss] = wallB ? mirror_y(o) : s4;
 					}
 				} else if (STEADY ? (y >= out_lo) : (y >= out_lo && y <= out_hi)) {
-					bad = bad || !(o.x == o.x) || !(o.y == o.y) || !(o.z == o.z) || !(o.w == o.w);
+					if (!INL) bad = bad || !(o.x == o.x) || !(o.y == o.y) || !(o.z == o.z) || !(o.w == o.w);
 					store_row(o, pout);
 					pout += g.pitch;
-					if (--seg_left == 0 || (!STEADY && y == out_hi)) close_segment();
+					if (!INL && (--seg_left == 0 || (!STEADY && y == out_hi))) close_segment();
 					if (!STEADY && wallB && y == 1) store_border_row(o, 0);
 					if (!STEADY && wallT && y == g.NY) store_border_row(o, g.NY + 1);
 				}
@@ -172,7 +181,7 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 	}
 }
 
-template <int L>
+template <int L, bool INL = false>
 __global__ void __launch_bounds__(128, 4) k_blur_stream(GridDesc g, StreamRect rc, const float* __restrict__ xinb, float* __restrict__ xoutb,
 							float a, DivC dv, int ntasks, int* __restrict__ redo, int b)
 {
@@ -184,8 +193,8 @@ __global__ void __launch_bounds__(128, 4) k_blur_stream(GridDesc g, StreamRect r
 	const long long off = (long long) k.sim * g.plane;
 	const int lane0_col = rc.col0 + k.strip * BlurGeom<L>::OUT - BlurGeom<L>::HALO;
 	const bool wall = k.wall || lane0_col <= XO || lane0_col + 128 > XO + g.N + 1; // lanes reach a border column
-	if (wall) blur_stream_task<L, true>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
-	else blur_stream_task<L, false>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	if (wall) blur_stream_task<L, true, INL>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	else blur_stream_task<L, false, INL>(g, xinb + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 }
 
 // The listed (task, segment) rectangles again, with exact division: one CTA per entry does the L passes on

@@ -116,7 +116,13 @@ __device__ __forceinline__ float stream_relax(float x0, float a, float w, float 
 // cell; in the other passes the border cell -- which the plain update has just treated like an interior
 // cell -- gets its previous value back.  The border column is stored with the rows.
 // XZERO: x is known to be zero everywhere (Project has just "set" p = 0 without writing it): it is not read.
-template <int S, bool WALL, bool POW2, bool XZERO>
+// INL: no redo list -- after every colour pass of a row (two updates per lane) the warp votes on whether any of its
+// dividends left the proven window and, if so, recomputes that pass with div_bracket (exact; the inputs of a red-black
+// update are the other colour and x0, both still in place).  Costs two instructions per pass when nothing is wrong and
+// keeps fields that are mostly fringe (ensembles of small grids: a point source decaying through the subnormals in every
+// member) on this kernel instead of the tile kernel, whose edge tiles dominate on small members.  (A dividend that is
+// infinite or NaN is not caught here -- the sequence turns it into NaN where IEEE division of an infinity would keep it.)
+template <int S, bool WALL, bool POW2, bool XZERO, bool INL>
 __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* __restrict__ xin, const float* __restrict__ x0g,
 					       float* __restrict__ xout, float a, const DivC& dv, int lane0_col, int out_lo,
 					       int out_hi, int col_lo, int col_hi, int b, float* ring, int* __restrict__ redo, int redo_base, int seg_rows)
@@ -253,8 +259,13 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 				if (ph) { // cells .x and .z of the row have the active colour
 					const float wl = __shfl_up_sync(0xffffffffu, x[sy].w, 1);
 					const float keep = x[sy].x;
-					x[sy].x = stream_relax<POW2>(r[sy].x, a, wl, x[sy].y, x[ss].x, x[sn].x, dv, low);
-					x[sy].z = stream_relax<POW2>(r[sy].z, a, x[sy].y, x[sy].w, x[ss].z, x[sn].z, dv, low);
+					uint32_t lowp = 0xffffffffu;
+					x[sy].x = stream_relax<POW2>(r[sy].x, a, wl, x[sy].y, x[ss].x, x[sn].x, dv, INL ? lowp : low);
+					x[sy].z = stream_relax<POW2>(r[sy].z, a, x[sy].y, x[sy].w, x[ss].z, x[sn].z, dv, INL ? lowp : low);
+					if (INL && !POW2 && __any_sync(0xffffffffu, lowp < 2u * dv.lo - 1u)) {
+						x[sy].x = div_bracket(r[sy].x + a * (((wl + x[sy].y) + x[ss].x) + x[sn].x), dv);
+						x[sy].z = div_bracket(r[sy].z + a * (((x[sy].y + x[sy].w) + x[ss].z) + x[sn].z), dv);
+					}
 					if (WALL) {
 						if (ghostR) x[sy].x = keep; // the right border cell is not an interior cell
 						const float v1 = __shfl_down_sync(0xffffffffu, x[sy].x, 1); // cell i = 1 was updated
@@ -273,8 +284,13 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 				} else {  // cells .y and .w
 					const float er = __shfl_down_sync(0xffffffffu, x[sy].x, 1);
 					const float keep = x[sy].w;
-					x[sy].y = stream_relax<POW2>(r[sy].y, a, x[sy].x, x[sy].z, x[ss].y, x[sn].y, dv, low);
-					x[sy].w = stream_relax<POW2>(r[sy].w, a, x[sy].z, er, x[ss].w, x[sn].w, dv, low);
+					uint32_t lowp = 0xffffffffu;
+					x[sy].y = stream_relax<POW2>(r[sy].y, a, x[sy].x, x[sy].z, x[ss].y, x[sn].y, dv, INL ? lowp : low);
+					x[sy].w = stream_relax<POW2>(r[sy].w, a, x[sy].z, er, x[ss].w, x[sn].w, dv, INL ? lowp : low);
+					if (INL && !POW2 && __any_sync(0xffffffffu, lowp < 2u * dv.lo - 1u)) {
+						x[sy].y = div_bracket(r[sy].y + a * (((x[sy].x + x[sy].z) + x[ss].y) + x[sn].y), dv);
+						x[sy].w = div_bracket(r[sy].w + a * (((x[sy].z + er) + x[ss].w) + x[sn].w), dv);
+					}
 					if (WALL) {
 						if (ghostL) x[sy].w = keep; // the left border cell is not an interior cell
 						const float vN = __shfl_up_sync(0xffffffffu, x[sy].w, 1);   // cell i = N was updated
@@ -294,12 +310,12 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 			}
 			if (STEADY ? (t - L >= out_lo) : (t - L >= out_lo && t - L <= out_hi)) { // this row has now received all L passes
 				const float4 v = x[(u - L + 4 * W) % W];
-				if (!POW2) bad = bad || !(v.x == v.x) || !(v.y == v.y) || !(v.z == v.z) || !(v.w == v.w);
+				if (!POW2 && !INL) bad = bad || !(v.x == v.x) || !(v.y == v.y) || !(v.z == v.z) || !(v.w == v.w);
 				if (store_lane) *reinterpret_cast<float4*>(pout) = v;
 				if (WALL && ghostL) pout[3] = v.w;
 				if (WALL && ghostR) pout[0] = v.x;
 				pout += g.pitch;
-				if (!POW2 && (--seg_left == 0 || (!STEADY && t - L == out_hi))) close_segment();
+				if (!POW2 && !INL && (--seg_left == 0 || (!STEADY && t - L == out_hi))) close_segment();
 				if (!STEADY && botw && t - L == 1) store_border_row(x[(u - L - 1 + 4 * W) % W], v, 0, wallB);
 				if (!STEADY && topw && t - L == g.NY) store_border_row(x[(u - L + 1 + 4 * W) % W], v, g.NY + 1, wallT);
 			}
@@ -331,7 +347,7 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 }
 
 // redo[0] counts, redo[1..] lists the (task, segment) rectangles the tile kernel must recompute exactly.
-template <int S, bool POW2, bool XZERO = false>
+template <int S, bool POW2, bool XZERO = false, bool INL = false>
 __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g, StreamRect rc, const float* __restrict__ xinb,
 							const float* __restrict__ x0b, float* __restrict__ xoutb, float a, DivC dv,
 							int ntasks, int* __restrict__ redo, int b)
@@ -346,8 +362,8 @@ __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g,
 	// the wall variant for every strip whose lanes reach a border column: the first and the last strip, and the
 	// last but one when the last is narrower than the halo
 	const bool wall = k.wall || lane0_col <= XO || lane0_col + 128 > XO + g.N + 1;
-	if (wall) rb_stream_task<S, true, POW2, XZERO>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
-	else rb_stream_task<S, false, POW2, XZERO>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	if (wall) rb_stream_task<S, true, POW2, XZERO, INL>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	else rb_stream_task<S, false, POW2, XZERO, INL>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 }
 
 } // namespace fluid
