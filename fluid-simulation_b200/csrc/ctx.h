@@ -104,6 +104,7 @@ struct fluid_ctx {
 	void *peer_lower = nullptr, *peer_upper = nullptr;
 	bool peer_connected = false;
 	unsigned int peer_seq = 0;
+	cudaEvent_t pace_ev[4] = {};
 	int* d_oob = nullptr;
 	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
@@ -114,6 +115,7 @@ struct fluid_ctx {
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member
 	int rb_tile_sweeps = 2;
 	bool stream_inline = false; // this solve's streaming passes recompute out-of-window colour passes on the spot (no redo list)
+	bool stream_force_inline = false; // tests: every streaming pass in the inline-exact variant
 	bool rb_stream = true;     // interior of large grids by the register-resident streaming kernel (k_rb_stream)
 	// Feedback for the streaming kernels ([0] relaxation, [1] blur).  They hand every segment that met a
 	// dividend outside the verified window to an exact fallback; on fields that are mostly fringe (an ensemble

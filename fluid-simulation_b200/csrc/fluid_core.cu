@@ -3,6 +3,8 @@
 // resident fields).  Without a CUDA device every entry point fails; there is no CPU fallback.
 #include "ctx.h"
 
+#include <stdlib.h>
+
 thread_local char t_err[512] = "";
 thread_local unsigned long long t_launches = 0;
 
@@ -68,6 +70,7 @@ extern "C" int fluid_ctx_destroy(fluid_ctx* c)
 	if (c->ev_join2) cudaEventDestroy(c->ev_join2);
 	if (c->d_oob) cudaFree(c->d_oob);
 	if (c->peer_block) cudaFree(c->peer_block);
+	for (auto& e : c->pace_ev) if (e) cudaEventDestroy(e);
 	if (c->peer_counter) cudaFree(c->peer_counter);
 	if (c->div_pending.stream) {
 		cudaStreamSynchronize(c->div_pending.stream);
@@ -392,7 +395,9 @@ extern "C" int fluid_ctx_render(fluid_ctx* c, int sim, const float* color_rgb, f
 extern "C" int fluid_ctx_set_stream_kernel(fluid_ctx* c, int on)
 {
 	CHECK_CTX(c);
+	if (on < 0 || on > 2) return fail(FLUID_ERR_INVALID, "stream kernel mode %d must be 0 (off), 1 (on) or 2 (on, always the inline-exact variant)", on);
 	c->rb_stream = on != 0;
+	c->stream_force_inline = on == 2;
 	return FLUID_OK;
 }
 
@@ -581,7 +586,19 @@ extern "C" int fluid_ctx_step(fluid_ctx* c, float dt, int nsteps)
 	CHECK_CTX(c);
 	if (nsteps < 0) return fail(FLUID_ERR_INVALID, "nsteps=%d must be >= 0", nsteps);
 	CU_TRY(cudaEventRecord(c->ev0, c->stream));
-	for (int s = 0; s < nsteps; s++) FL_TRY(dev_update(c, dt));
+	// Pacing (env FLUID_PACE_FRAMES = d > 0, diagnostic): the host enqueues frame k only when frame k - d has finished
+	static const int pace = getenv("FLUID_PACE_FRAMES") ? atoi(getenv("FLUID_PACE_FRAMES")) : 0;
+	for (int s = 0; s < nsteps; s++) {
+		if (pace > 0 && c->slab_count > 1) {
+			cudaEvent_t& e = c->pace_ev[s % 4];
+			if (!e) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+			if (s >= pace) CU_TRY(cudaEventSynchronize(c->pace_ev[(s - pace) % 4]));
+			FL_TRY(dev_update(c, dt));
+			CU_TRY(cudaEventRecord(e, c->stream));
+		} else {
+			FL_TRY(dev_update(c, dt));
+		}
+	}
 	CU_TRY(cudaEventRecord(c->ev1, c->stream));
 	c->timed = true;
 	CU_TRY(cudaGetLastError());

@@ -152,6 +152,7 @@ static int stream_allowed(fluid_ctx* c, int which)
 		if (fb.segments > 0 && (long long) *fb.h_count * 12 > fb.segments) fb.holdoff = kStreamHoldoff;
 	}
 	if (!c->rb_stream) return 0;
+	if (c->stream_force_inline) return 2;
 	if (fb.holdoff > 0) {
 		fb.holdoff--;
 		return 2;

@@ -382,7 +382,7 @@ class FluidSystem:
         check(lib().fluid_ctx_render(self.h, sim, col, px, ln.ctypes.data if lines else None))
         return px.reshape(n, 3), (ln.reshape(n, 4) if lines else None)
 
-    def SetStreamKernel(self, on): check(lib().fluid_ctx_set_stream_kernel(self.h, 1 if on else 0))
+    def SetStreamKernel(self, on): check(lib().fluid_ctx_set_stream_kernel(self.h, (1 if on else 0) if isinstance(on, bool) else int(on)))
     def SetOverlap(self, on): check(lib().fluid_ctx_set_overlap(self.h, 1 if on else 0))
     def SetAdvectKernel(self, which): check(lib().fluid_ctx_set_advect_kernel(self.h, which))
     def SetSparseSources(self, on): check(lib().fluid_ctx_set_sparse_sources(self.h, 1 if on else 0))

@@ -470,14 +470,18 @@ def test_ensemble_members_are_independent(fl, oracle):
         fs.close()
 
 
-def test_ensemble_on_the_streaming_kernels_bitwise(fl, oracle):
+@pytest.mark.parametrize("stream", [1, 2])
+def test_ensemble_on_the_streaming_kernels_bitwise(fl, oracle, stream):
     """Eight members of N=512 are enough cells for the register-resident streaming kernels, which then work on
     member planes (strips and chunks per member, wall strips in every member).  Three steps, so that the redo
-    feedback may also switch a solve back to the tile kernels on the way: every member equals its own CPU run."""
+    feedback may also switch a solve to the inline-exact variant on the way (stream = 2: that variant from the first
+    solve on -- point sources decaying through the subnormals make every member mostly fringe): every member equals
+    its own CPU run."""
     import oracle_py as op
     N, B, steps = 512, 8, 3
     fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, batch=B)
     fs.SetFastDivision(2)
+    fs.SetStreamKernel(stream)
     srcs = []
     for b in range(B):
         cx, cy = 1 + (37 * b) % N, 1 + (101 * b) % N
@@ -804,13 +808,15 @@ def test_two_fluids_resident_context(fl, oracle, order):
     fs.close()
 
 
-@pytest.mark.parametrize("N,stream", [(2500, True), (2500, False), (2502, True), (2524, True)])
+@pytest.mark.parametrize("N,stream", [(2500, True), (2500, False), (2502, True), (2524, True), (2500, 2), (2502, 2), (2524, 2)])
 def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
     """Large grids: the rows away from the bottom and top walls are relaxed by the register-resident
     streaming kernel (4, 2 or 1 sweeps per pass) -- including the left and right walls when N is a multiple
     of 4 (2500, 2524 = 28 mod 32, where lanes fold back onto the border column), one tile column away from
     them otherwise (2502) -- the rest by the tile kernel.  Mixed pass schedules (20 = 4x4+2x2,
-    7 = 4+2+1 -> 4+1+1+1, 6, 2) against the CPU red-black statement, and the tile-only path on the same inputs."""
+    7 = 4+2+1 -> 4+1+1+1, 6, 2) against the CPU red-black statement, and the tile-only path on the same inputs.
+    stream = 2: the inline-exact variant (dividends outside the proven window recomputed on the spot, no redo list);
+    a patch of the fields is scaled into the subnormal range so that both exact fallbacks really run."""
     import oracle_py as op
     rng = np.random.default_rng(N)
     for iters, b, a in ((20, 1, np.float32(10.49)), (7, 2, np.float32(1.0)), (6, 0, np.float32(0.3)), (2, 1, np.float32(0.3)),
@@ -820,6 +826,10 @@ def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
         fs.SetFastDivision(2)
         x, x0 = rand_field(rng, N), rand_field(rng, N)
         x0[rng.integers(0, x0.size, x0.size // 5)] = 0.0
+        for arr in (x, x0):
+            g = arr.reshape(N + 2, N + 2)
+            g[700:1000, 200:1300] *= np.float32(1e-38)
+            g[1:30, N - 50:] *= np.float32(1e-37)
         c = np.float32(4.0) if a == 1 else 1 + 4 * a
         fs.upload(fl.U, x)
         fs.upload(fl.V, x0)
@@ -829,7 +839,7 @@ def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
         fs.close()
 
 
-@pytest.mark.parametrize("N,stream", [(2048, True), (2500, True), (2048, False)])
+@pytest.mark.parametrize("N,stream", [(2048, True), (2500, True), (2048, False), (2048, 2), (2500, 2)])
 def test_streamed_blur_bitwise(fl, oracle, N, stream):
     """Blur on large grids runs five Jacobi passes per launch in a register-resident window (an even number
     of such launches, single passes for the rest: 21 = 4x5+1, 11 = 2x5+1, 31 = 6x5+1, 7 = single passes only),
