@@ -586,10 +586,15 @@ extern "C" int fluid_ctx_step(fluid_ctx* c, float dt, int nsteps)
 	CHECK_CTX(c);
 	if (nsteps < 0) return fail(FLUID_ERR_INVALID, "nsteps=%d must be >= 0", nsteps);
 	CU_TRY(cudaEventRecord(c->ev0, c->stream));
-	// Pacing (env FLUID_PACE_FRAMES = d > 0, diagnostic): the host enqueues frame k only when frame k - d has finished
-	static const int pace = getenv("FLUID_PACE_FRAMES") ? atoi(getenv("FLUID_PACE_FRAMES")) : 0;
+	// Row slabs on the peer-memory transport: the host enqueues frame k only when frame k-2 has finished.  With the host
+	// many frames ahead of the GPU a frame took 10.0 ms instead of 6.07 (2 GPUs, N=8192 rows each; bounded to 1, 2 or 3
+	// frames: 6.12 / 6.07 / 6.07): each refresh waits on the neighbour GPU, and the deeper the queue of launches behind
+	// such a wait, the later the refresh kernels of BOTH sides got to start.  Two frames of run-ahead still hide every
+	// launch latency.  (FLUID_PACE_FRAMES overrides: 0 = unbounded.)
+	static const int pace_env = getenv("FLUID_PACE_FRAMES") ? atoi(getenv("FLUID_PACE_FRAMES")) : -1;
+	const int pace = (c->slab_count > 1 && c->peer_connected) ? (pace_env >= 0 ? std::min(pace_env, 3) : 2) : 0;
 	for (int s = 0; s < nsteps; s++) {
-		if (pace > 0 && c->slab_count > 1) {
+		if (pace > 0) {
 			cudaEvent_t& e = c->pace_ev[s % 4];
 			if (!e) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 			if (s >= pace) CU_TRY(cudaEventSynchronize(c->pace_ev[(s - pace) % 4]));
