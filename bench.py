@@ -24,7 +24,7 @@ sys.path.insert(0, os.path.join(ROOT, "fluid-simulation_b200"))
 METRIC = "grid cell-updates/s per vel_step+dens_step (20 GS iters); HBM GB/s vs roofline"
 UNIT = "cell-updates/s"
 DT, VISC, DIFF, ITERS = 0.1, 1e-4, 1e-4, 20
-SETTLE = 20  # untimed frames on top of --warmup, see run_b200
+SETTLE = int(os.environ.get("FLUID_BENCH_SETTLE", "20"))  # untimed frames on top of --warmup, see run_b200 (0 for short profiler runs)
 
 # Algorithmic bytes per cell: fp32, every array read/written once per pass.
 B_GS_SWEEP = 12          # x0 R, x R, x W (a red-black sweep = both colours)

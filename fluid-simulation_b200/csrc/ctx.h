@@ -13,6 +13,7 @@
 
 #include <cuda.h> // CUtensorMap (types only; the encode function is fetched at run time)
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -185,14 +186,23 @@ struct fluid_ctx {
 	std::vector<cudaEvent_t> prof_pool;
 };
 
-// RAII segment: brackets the launches of one primitive with two events when
-// profiling is on; costs nothing otherwise.
+// RAII segment: an NVTX range named after the kernel class around the launches of one primitive (header-only NVTX 3:
+// a no-op of a few nanoseconds unless a tool such as ncu --nvtx or nsys is attached), and, when profiling is on, two
+// events that bracket them on the stream.
+static inline const char* prof_class_name(int cls)
+{
+	static const char* const names[] = { "fluid:lin_solve", "fluid:blur", "fluid:advect", "fluid:project_aux", "fluid:add_source", "fluid:other",
+					     "fluid:halo_exchange" };
+	return (cls >= 0 && cls < 7) ? names[cls] : "fluid:?";
+}
+
 struct ProfScope {
 	fluid_ctx* c;
 	int idx = -1;
 	unsigned long long l0 = 0;
 	ProfScope(fluid_ctx* ctx, int cls) : c(ctx)
 	{
+		nvtxRangePushA(prof_class_name(cls));
 		if (!c->prof_on) return;
 		cudaEvent_t ev[2];
 		for (auto& e : ev) {
@@ -206,6 +216,7 @@ struct ProfScope {
 	}
 	~ProfScope()
 	{
+		nvtxRangePop();
 		if (idx < 0) return;
 		cudaEventRecord(c->prof_segs[idx].b, c->stream);
 		c->prof_segs[idx].launches = t_launches - l0;

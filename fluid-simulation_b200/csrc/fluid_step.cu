@@ -189,6 +189,8 @@ static int halo_exchange(fluid_ctx* c, std::initializer_list<const float*> array
 // the result lands in the arrays passed as u and v.
 int dev_vel_step(fluid_ctx* c, float* u, float* v, float* u0, float* v0, float visc, float dt, bool sources_added)
 {
+	nvtxRangePushA("fluid:VelStep");
+	struct Pop { ~Pop() { nvtxRangePop(); } } pop_on_return;
 	// slabs: u, v (and the source arrays, which every slab fills itself) are valid over the whole halo on entry
 	if (c->fs_type != FLUID_TYPE_ORIGINAL) {
 		// VelStep1B (FluidSystem.cpp:378-398) is VelStep1 over the masked primitives, except that its first AddArrDt
@@ -335,8 +337,14 @@ int sync_sources(fluid_ctx* c)
 // `dens_ready`: an event (of another stream) after which the current density arrays are valid, or nullptr;
 // `after_velocity`: called once VelStep has been enqueued on c->stream, or empty.  fluid_update() uses both to
 // slip its bus transfers in; everybody else calls dev_update.
+struct NvtxRange {
+	explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+	~NvtxRange() { nvtxRangePop(); }
+};
+
 int dev_update_hooks(fluid_ctx* c, float dt, cudaEvent_t dens_ready, const std::function<int()>& after_velocity)
 {
+	NvtxRange frame("fluid:Update");
 	c->epoch++; // a frame (the divisor bookkeeping of division_for counts in frames and API calls)
 	// The source arrays of a frame are zero except for the listed PREV_SET cells, so AddArrDt over them is known
 	// in advance (k_canon_zero, kernels_basic.cuh): the three dense x += dt*s passes and the zero fill of the
