@@ -252,6 +252,19 @@ def run_reference(args):
     return 0
 
 
+def make_transport(name, fs, rank, world, local):
+    """(transport, name actually used): the peer-memory transport if every rank can map its neighbours' blocks
+    (CUDA IPC), else NCCL send/recv on all ranks."""
+    from fluid_b200.slabs import NcclExchange, PeerExchange
+    if name == "peer":
+        try:
+            return PeerExchange(fs, rank, world, local), "peer"
+        except RuntimeError as e:
+            if rank == 0:
+                print("bench.py: %s; falling back to the NCCL transport" % e, file=sys.stderr)
+    return NcclExchange(fs, rank, world, local), "nccl"
+
+
 def slab_self_check(fl, np, torch, dist, rank, world, local, transport_name):
     """Driver-side evidence that the multi-rank path computes the right thing: before the timed region every rank
     advances one slab of a small global grid (2048 columns x 1024 rows per rank: large enough for the streaming
@@ -265,7 +278,7 @@ def slab_self_check(fl, np, torch, dist, rank, world, local, transport_name):
            (fl.V, N // 2, NY // 2, fl.SRC_PREV_SET, 5.0), (fl.U, 100, rows, fl.SRC_PREV_SET, -3.0), (fl.DENS, 1500, rows + 1, fl.SRC_PREV_SET, 40.0)]
     fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=fl.GS_REDBLACK, gs_iters=ITERS, device=local, slab=(rank, world, rows))
     fs.SetFastDivision(2)
-    tr = PeerExchange(fs, rank, world, local) if transport_name == "peer" else NcclExchange(fs, rank, world, local)
+    tr, transport_name = make_transport(transport_name, fs, rank, world, local)
     fs.SetSources(src)
     fs.Update(DT, steps)
     fs.Sync()
@@ -276,7 +289,7 @@ def slab_self_check(fl, np, torch, dist, rank, world, local, transport_name):
         t = torch.from_numpy(host.view(np.int32)).to("cuda:%d" % local)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)  # owned rows are disjoint: integer sum of bit patterns assembles the field
         parts.append(t.cpu().numpy().view(np.float32))
-    if transport_name == "peer":
+    if isinstance(tr, PeerExchange):
         tr.close()
     del tr
     fs.close()
@@ -379,7 +392,7 @@ def run_b200(args):
         if args.strong and N % world:
             raise SystemExit("bench.py --strong: N must be divisible by the number of GPUs")
         fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local, slab=(rank, world, rows))
-        transport = PeerExchange(fs, rank, world, local) if args.transport == "peer" else NcclExchange(fs, rank, world, local)
+        transport, args.transport = make_transport(args.transport, fs, rank, world, local)
     else:
         fs = fl.FluidSystem().Setup(N, VISC, DIFF, gs_order=order, gs_iters=ITERS, device=local)
     rows_per_gpu = (N // world) if (world > 1 and args.strong) else N
@@ -481,7 +494,7 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_single()
-    if transport is not None and args.transport == "peer":
+    if transport is not None and hasattr(transport, "lower"):
         transport.close()  # all ranks: nobody may still be pushing into a block that is about to be freed
     fs.close()
 

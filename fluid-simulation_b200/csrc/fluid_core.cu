@@ -618,6 +618,11 @@ extern "C" int fluid_ctx_sync(fluid_ctx* c)
 	if (c->slab_count > 1) {
 		int oob = 0;
 		CU_TRY(cudaMemcpy(&oob, c->d_oob, sizeof(int), cudaMemcpyDeviceToHost));
+		if (oob & 2) {
+			CU_TRY(cudaMemset(c->d_oob, 0, sizeof(int)));
+			return fail(FLUID_ERR_CUDA, "halo refresh: a neighbouring slab did not deliver its rows within ~2 s (its process ended, or the slabs "
+						    "did not make the same sequence of calls); results are invalid");
+		}
 		if (oob) {
 			CU_TRY(cudaMemset(c->d_oob, 0, sizeof(int)));
 			return fail(FLUID_ERR_UNSUPPORTED, "advect: a backtrace reached rows that are not stored on this slab "

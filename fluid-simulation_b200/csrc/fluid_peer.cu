@@ -69,13 +69,26 @@ __global__ void __launch_bounds__(256) k_halo_push(PushArgs a, unsigned int* __r
 	}
 }
 
-__global__ void __launch_bounds__(256) k_halo_pull(PullArgs a)
+// A neighbour that never pushes (its process died, the slabs made different sequences of calls) must not hang this
+// GPU: after ~4e9 clock cycles (about two seconds) of waiting the kernel gives up, raises bit 1 of *fault and lets the
+// step run on with stale halo rows; fluid_ctx_sync reports it.
+__device__ __forceinline__ void wait_for_flag(const unsigned int* flag, unsigned int seq, int* fault)
 {
-	if (threadIdx.x == 0) { // sequence numbers only grow; signed difference survives the wrap
-		if (a.flag_below)
-			while ((int) (*(volatile const unsigned int*) a.flag_below - a.seq) < 0) __nanosleep(200);
-		if (a.flag_above)
-			while ((int) (*(volatile const unsigned int*) a.flag_above - a.seq) < 0) __nanosleep(200);
+	const long long t0 = clock64();
+	while ((int) (*(volatile const unsigned int*) flag - seq) < 0) { // sequence numbers only grow; signed difference survives the wrap
+		__nanosleep(200);
+		if (clock64() - t0 > 4000000000LL) {
+			atomicOr(fault, 2);
+			break;
+		}
+	}
+}
+
+__global__ void __launch_bounds__(256) k_halo_pull(PullArgs a, int* __restrict__ fault)
+{
+	if (threadIdx.x == 0) {
+		if (a.flag_below) wait_for_flag(a.flag_below, a.seq, fault);
+		if (a.flag_above) wait_for_flag(a.flag_above, a.seq, fault);
 		__threadfence_system();
 	}
 	__syncthreads();
@@ -165,7 +178,7 @@ int peer_halo_exchange(fluid_ctx* c, int n, const int* ids)
 	const int cap = env_blocks > 0 ? env_blocks : 2 * c->num_sms;
 	const int blocks = (int) std::min<long long>((pa.n4 + 255) / 256, (long long) cap);
 	LAUNCH(k_halo_push, blocks, 256, 0, c->stream, pa, c->peer_counter);
-	LAUNCH(k_halo_pull, blocks, 256, 0, c->stream, pl);
+	LAUNCH(k_halo_pull, blocks, 256, 0, c->stream, pl, c->d_oob);
 	CU_TRY(cudaGetLastError());
 	return FLUID_OK;
 }

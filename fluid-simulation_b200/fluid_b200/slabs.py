@@ -100,14 +100,36 @@ class PeerExchange:
 
     def __init__(self, fs, rank, world, device):
         import torch.distributed as dist
-        from . import ipc_export, ipc_import
+        from . import ipc_close, ipc_export, ipc_import
         self.fs, self.rank, self.world, self.dist = fs, rank, world, dist
         self.calls = self.bytes = 0  # (refreshes are counted by the library's profile, not here)
         block, nbytes = fs.PeerHaloLocal()
+        import torch
         handles = [None] * world
-        dist.all_gather_object(handles, ipc_export(block))
-        self.lower = ipc_import(handles[rank - 1]) if rank > 0 else None
-        self.upper = ipc_import(handles[rank + 1]) if rank + 1 < world else None
+        self.lower = self.upper = None
+        err = None
+        try:
+            mine = ipc_export(block)
+        except Exception as e:  # e.g. a platform without CUDA IPC
+            mine, err = None, e
+        dist.all_gather_object(handles, mine)
+        try:
+            if err is None and all(h is not None for h in handles):
+                self.lower = ipc_import(handles[rank - 1]) if rank > 0 else None
+                self.upper = ipc_import(handles[rank + 1]) if rank + 1 < world else None
+            elif err is None:
+                err = RuntimeError("a neighbour could not export its block")
+        except Exception as e:
+            err = e
+        # all ranks agree on success before anybody connects (a slab that waits for a neighbour that gave up would hang)
+        ok = torch.tensor([0 if err else 1], device=torch.device("cuda", device))
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            for p in (self.lower, self.upper):
+                if p:
+                    ipc_close(p)
+            self.lower = self.upper = None
+            raise RuntimeError("peer-memory halo transport unavailable on some rank (%s)" % (err or "see the other ranks"))
         fs.PeerHaloConnect(self.lower, self.upper)
         dist.barrier()  # everybody connected before anybody steps
 
