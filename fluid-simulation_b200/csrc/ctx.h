@@ -131,7 +131,8 @@ struct fluid_ctx {
 		cudaEvent_t arrived = nullptr;
 		bool pending = false;
 		long long segments = 0; // segments of the launch whose count is in flight
-		int holdoff = 0;
+		int holdoff = 0;      // solves left before the windowed sequence is tried again
+		int holdoff_len = 0;  // length of the next hold-off: doubles while the trials keep coming back mostly fringe
 	} feedback[2];
 	// redo lists of the two streaming kernels: [0] = count, [1..] = (task, segment) entries.  One per kernel
 	// family (0 relaxation, 1 blur): the density diffusion may run on the side stream while VelStep runs
@@ -173,7 +174,7 @@ struct fluid_ctx {
 		bool active = false;
 		uint32_t key = 0;
 		DivC dv{};
-		unsigned int* h_bins = nullptr; // pinned, 256 counters
+		unsigned int* h_bins = nullptr; // pinned, 512 counters (window, scaled sequence)
 		cudaEvent_t done = nullptr;
 		cudaStream_t stream = nullptr;
 	} div_pending;

@@ -52,6 +52,9 @@ static int field_tmap(fluid_ctx* c, const float* base, int rx, const CUtensorMap
 static void window_from_bins(const unsigned int* bins, DivC* dv)
 {
 	dv->lo = dv->range = 0;
+	dv->full = 1; // bins[256 ..]: k_verify_division_full
+	for (int e = 256; e < 512; e++)
+		if (bins[e] != 0) dv->full = 0;
 	if (bins[127] != 0) return;
 	int elo = 127, ehi = 127;
 	while (elo > 1 && bins[elo - 1] == 0) elo--;
@@ -76,7 +79,7 @@ static void remember_division(fluid_ctx* c, uint32_t key, const DivC& dv)
 
 // DivC for divisor cc: verified window if known, else range = 0 (callers use the exact division).
 //
-// The proof costs 2^31 trial divisions (1.8 ms of the whole GPU).  The reference's main loop feeds the solver
+// The proof costs 2^31 trial divisions for the window and 1.6e9 for the scaled sequence (about 3 ms of the whole GPU).  The reference's main loop feeds the solver
 // the measured frame time (SystemManager.cpp:49-52), so an integration may see a new c = 1 + 4*dt*coef*N*N every
 // frame: a proof per frame would cost more than it saves, and waiting for it would stall the host in the middle
 // of the enqueue loop.  Automatic mode therefore (a) proves only a divisor that has COME BACK -- seen in an
@@ -91,12 +94,16 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	out->rc = 1.0 / (double) cc;
 	out->lo = 0;
 	out->range = 0;
+	out->full = 0;
 	if (!(cc > 0.0f) || !isfinite(cc) || !isfinite(out->y) || c->fast_div_mode == 0) return FLUID_OK;
 	uint32_t key;
 	memcpy(&key, &cc, sizeof key);
 	auto& pd = c->div_pending;
 	if (pd.active && (c->fast_div_mode == 2 ? cudaEventSynchronize(pd.done) : cudaEventQuery(pd.done)) == cudaSuccess) {
 		window_from_bins(pd.h_bins, &pd.dv); // a background proof has landed
+		if (getenv("FLUID_DEBUG_FEEDBACK"))
+			fprintf(stderr, "division proof for c = %.9g: window exponents [%u, %u), scaled sequence %s\n", pd.dv.c, pd.dv.lo >> 23,
+				(pd.dv.lo + pd.dv.range) >> 23, pd.dv.full ? "proven" : "not proven");
 		remember_division(c, pd.key, pd.dv);
 		pd.active = false;
 	}
@@ -106,11 +113,12 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 		*out = it->second.dv;
 		return FLUID_OK;
 	}
-	if (!c->d_divbins) CU_TRY(cudaMalloc(&c->d_divbins, 256 * sizeof(unsigned int)));
+	if (!c->d_divbins) CU_TRY(cudaMalloc(&c->d_divbins, 512 * sizeof(unsigned int)));
 	if (c->fast_div_mode == 2) {
-		CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), c->stream));
+		CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 512 * sizeof(unsigned int), c->stream));
 		LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins);
-		unsigned int bins[256];
+		LAUNCH(k_verify_division_full, c->num_sms * 8, 256, 0, c->stream, *out, c->d_divbins + 256);
+		unsigned int bins[512];
 		CU_TRY(cudaMemcpyAsync(bins, c->d_divbins, sizeof bins, cudaMemcpyDeviceToHost, c->stream));
 		CU_TRY(cudaStreamSynchronize(c->stream));
 		window_from_bins(bins, out);
@@ -124,42 +132,50 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 	if (!pd.stream) {
 		CU_TRY(cudaStreamCreateWithFlags(&pd.stream, cudaStreamNonBlocking));
 		CU_TRY(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
-		CU_TRY(cudaMallocHost(&pd.h_bins, 256 * sizeof(unsigned int)));
+		CU_TRY(cudaMallocHost(&pd.h_bins, 512 * sizeof(unsigned int)));
 	}
 	pd.key = key;
 	pd.dv = *out;
-	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 256 * sizeof(unsigned int), pd.stream));
+	CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 512 * sizeof(unsigned int), pd.stream));
 	LAUNCH(k_verify_division, c->num_sms * 8, 256, 0, pd.stream, *out, c->d_divbins);
-	CU_TRY(cudaMemcpyAsync(pd.h_bins, c->d_divbins, 256 * sizeof(unsigned int), cudaMemcpyDeviceToHost, pd.stream));
+	LAUNCH(k_verify_division_full, c->num_sms * 8, 256, 0, pd.stream, *out, c->d_divbins + 256);
+	CU_TRY(cudaMemcpyAsync(pd.h_bins, c->d_divbins, 512 * sizeof(unsigned int), cudaMemcpyDeviceToHost, pd.stream));
 	CU_TRY(cudaEventRecord(pd.done, pd.stream));
 	pd.active = true;
 	return FLUID_OK;
 }
 
-constexpr int kStreamHoldoff = 64;
+constexpr int kStreamHoldoff = 64, kStreamHoldoffMax = 8192;
 
-// How may this solve use the streaming kernel?  0 = not at all (tile / pass kernels), 1 = with the redo list (segments
-// that met a dividend outside the proven window are listed and recomputed exactly behind the launch), 2 = inline (every
-// colour pass that met one is recomputed exactly on the spot, no list; only when forced, fluid_ctx_set_stream_kernel(2)).
+// How may this solve use the streaming kernel?  0 = not at all (tile / pass kernels), 1 = windowed sequence with the redo
+// list (segments that met a dividend outside the proven window are listed and recomputed exactly behind the launch),
+// 2 = scaled sequence (exact on the fringe as well, two instructions more per update, nothing listed but NaN rows).
 // Consumes the count of an earlier launch if it has arrived: when more than a twelfth of the segments came back (an
-// ensemble of small grids is mostly fringe) the next kStreamHoldoff solves use the tile / pass kernels.  Measured on
-// 512 members of N=512: relaxation 25 ms per frame on the tile kernel, 40 ms on the inline variant (nearly every pass
-// of every row has some lane on the fringe, and the exact recomputation runs on the FP64 and conversion pipes), which
-// is why the inline variant is not chosen automatically.
-static int stream_allowed(fluid_ctx* c, int which)
+// ensemble of small grids is mostly fringe) the next kStreamHoldoff solves (twice as many after every trial that comes
+// back the same way) use the scaled sequence if it is proven for this divisor (full_ok), else the tile / pass kernels.  Measured on 512 members of N=512, relaxation per frame: 25 ms
+// on the tile kernel, 40 ms with an exact FP64 recomputation per flagged colour pass (round 2's first inline variant:
+// nearly every pass of every row has some lane on the fringe, and the conversion pipe is narrow).
+static int stream_allowed(fluid_ctx* c, int which, bool full_ok)
 {
 	auto& fb = c->feedback[which];
 	if (fb.pending && cudaEventQuery(fb.arrived) == cudaSuccess) {
 		fb.pending = false;
 		if (getenv("FLUID_DEBUG_FEEDBACK")) fprintf(stderr, "feedback[%d]: %d of %lld segments redone\n", which, *fb.h_count, fb.segments);
-		if (fb.segments > 0 && (long long) *fb.h_count * 12 > fb.segments) fb.holdoff = kStreamHoldoff;
+		if (fb.segments > 0 && (long long) *fb.h_count * 12 > fb.segments) {
+			fb.holdoff_len = std::min(std::max(fb.holdoff_len * 2, kStreamHoldoff), kStreamHoldoffMax);
+			fb.holdoff = fb.holdoff_len;
+		} else {
+			fb.holdoff_len = fb.holdoff = 0; // the fringe has gone: back to the windowed sequence
+		}
 	}
 	if (!c->rb_stream) return 0;
-	if (c->stream_force_inline) return 2;
+	if (c->stream_force_inline) return full_ok ? 2 : 1;
 	if (fb.holdoff > 0) {
 		fb.holdoff--;
-		return 0;
+		return full_ok ? 2 : 0;
 	}
+	// a trial at the end of a hold-off is ONE solve: its count takes a few solves to come home, and those stay as they were
+	if (fb.holdoff_len > 0 && !fb.pending) fb.holdoff = 8;
 	return 1;
 }
 
@@ -266,6 +282,7 @@ static PassGeom pass_geometry(const fluid_ctx* c, bool stream_ok) // stream_ok: 
 	pg.rc.seg_rows = pg.TY;
 	pg.rc.segs = cdiv(pg.rc.chunk_rows, pg.TY);
 	pg.rc.per_sim = 2 * pg.rc.wall_chunks + (pg.rc.nstrips - (walls ? 2 : 0)) * pg.rc.nchunks;
+	pg.rc.nsims = c->batch;
 	return pg;
 }
 
@@ -315,8 +332,7 @@ static int rb_tile_pass(fluid_ctx* c, int b, const float* in, float* out, const 
 		CU_TRY(cudaMemsetAsync(c->d_redo[rbuf], 0, sizeof(int), c->stream));
 		if (c->stream_inline) {
 			LAUNCH((k_rb_stream<S, false, false, true>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
-			*segments = 0;              // nothing is listed, nothing to report
-			if (whole) return FLUID_OK; // ... and no frame of tiles around the streamed rectangle either
+			*segments = 0; // what is listed is not fringe: nothing to report
 		} else {
 			LAUNCH((k_rb_stream<S, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, pg.rc, in, x0, out, a, dv, ntasks, c->d_redo[rbuf], b);
 		}
@@ -371,6 +387,11 @@ static int rb_stream_pass_pow2(fluid_ctx* c, int b, const float* in, float* out,
 	StreamRect rc;
 	if (!stream_covers<S>(c, &rc)) return fail(FLUID_ERR_CUDA, "internal: streaming pass on a grid it does not cover");
 	const int ntasks = (int) ((long long) rc.per_sim * c->batch);
+	if (c->batch > 1 && S >= 4) { // ensembles: shorter unrolled blocks (see StreamRect::nsims)
+		if (x_is_zero) LAUNCH((k_rb_stream<S, true, true, false, 2>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
+		else LAUNCH((k_rb_stream<S, true, false, false, 2>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
+		return FLUID_OK;
+	}
 	if (x_is_zero) LAUNCH((k_rb_stream<S, true, true>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
 	else LAUNCH((k_rb_stream<S, true, false>), cdiv(ntasks, 4), 128, 0, c->stream, c->g, rc, in, x0, out, a, dv, ntasks, (int*) nullptr, b);
 	return FLUID_OK;
@@ -404,7 +425,7 @@ static int rb_tile_solve(fluid_ctx* c, int b, float*& x, const float* x0, float 
 	FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
 	const bool pow2 = is_pow2_solve(a, cc);
 	// otherwise the streaming kernel relies on the proven window reaching the largest finite float
-	const int stream_mode = (dv.range != 0 && (dv.lo + dv.range) == (255u << 23)) ? stream_allowed(c, 0) : 0;
+	const int stream_mode = (dv.range != 0 && (dv.lo + dv.range) == (255u << 23)) ? stream_allowed(c, 0, dv.full != 0) : 0;
 	const bool streaming = stream_mode != 0;
 	c->stream_inline = (stream_mode == 2);
 	// power-of-two solves first take as many whole-grid streaming passes of 5 and 4 sweeps as fit
@@ -583,6 +604,7 @@ static bool blur_stream_geometry(const fluid_ctx* c, StreamRect* rc)
 	rc->seg_rows = kBlurSeg;
 	rc->segs = cdiv(rc->chunk_rows, kBlurSeg);
 	rc->per_sim = 2 * rc->wall_chunks + (rc->nstrips - 2) * rc->nchunks;
+	rc->nsims = c->batch;
 	return true;
 }
 
@@ -607,19 +629,18 @@ int dev_blur(fluid_ctx* c, int b, float* x, float* x0, float a, float cc)
 	int done = 0;
 	StreamRect rc;
 	const bool window_ok = dv.range != 0 && (dv.lo + dv.range) == (255u << 23);
-	const int blur_mode = (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc)) ? stream_allowed(c, 1) : 0;
+	const int blur_mode = (window_ok && b >= 0 && b <= 2 && limit > 2 * kBlurL && blur_stream_geometry(c, &rc)) ? stream_allowed(c, 1, dv.full != 0) : 0;
 	if (blur_mode != 0) {
 		const int launches = 2 * ((limit - 1) / (2 * kBlurL));
 		const long long ntasks = (long long) rc.per_sim * c->batch;
 		FL_TRY(redo_reserve(c, 1, ntasks * rc.segs + 1));
 		for (int l = 0; l < launches; l++) {
 			if (l > 0) std::swap(dst, src);
-			if (blur_mode == 2) { // mostly fringe: exact on the spot, no list
-				LAUNCH((k_blur_stream<kBlurL, true>), cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
-				continue;
-			}
 			CU_TRY(cudaMemsetAsync(c->d_redo[1], 0, sizeof(int), c->stream));
-			LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
+			if (blur_mode == 2) // mostly fringe: the scaled sequence
+				LAUNCH((k_blur_stream<kBlurL, true>), cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
+			else
+				LAUNCH(k_blur_stream<kBlurL>, cdiv((int) ntasks, 4), 128, 0, c->stream, c->g, rc, src, dst, a, dv, (int) ntasks, c->d_redo[1], b);
 			// few entries, each a chain of 2L barrier-separated phases over ~5000 cells: wide CTAs keep the chain short
 			LAUNCH((k_blur_redo<kBlurL, kBlurSeg>), 2 * c->num_sms, 1024, 0, c->stream, c->g, rc, src, dst, a, cc, c->d_redo[1], b);
 		}

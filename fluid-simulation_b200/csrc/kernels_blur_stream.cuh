@@ -34,8 +34,7 @@ struct BlurGeom {
 
 // b is 0, 1 or 2 here (the host keeps other values on the pass-per-launch path: without mirroring the
 // two buffers' stored borders would alternate as the passes' inputs).
-// INL: as in kernels_rb_stream.cuh -- no redo list; a level whose dividends left the proven window is recomputed at once
-// with div_bracket (its inputs, the previous iterate's rows, are still in the ring).
+// INL: as in kernels_rb_stream.cuh -- the scaled sequence for every update; only NaN rows are listed.
 template <int L, bool WALL, bool INL>
 __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float* __restrict__ xin, float* __restrict__ xout, float a,
 						 const DivC& dv, int lane0_col, int out_lo, int out_hi, int col_lo, int col_hi,
@@ -146,16 +145,16 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 				const float wl = __shfl_up_sync(0xffffffffu, c4.w, 1);
 				const float er = __shfl_down_sync(0xffffffffu, c4.x, 1);
 				float4 o;
-				uint32_t lowp = 0xffffffffu;
-				o.x = stream_relax(c4.x, a, wl, c4.y, s4.x, n4.x, dv, INL ? lowp : low);
-				o.y = stream_relax(c4.y, a, c4.x, c4.z, s4.y, n4.y, dv, INL ? lowp : low);
-				o.z = stream_relax(c4.z, a, c4.y, c4.w, s4.z, n4.z, dv, INL ? lowp : low);
-				o.w = stream_relax(c4.w, a, c4.z, er, s4.w, n4.w, dv, INL ? lowp : low);
-				if (INL && __any_sync(0xffffffffu, lowp < 2u * dv.lo - 1u)) {
-					o.x = div_bracket(c4.x + a * (((wl + c4.y) + s4.x) + n4.x), dv);
-					o.y = div_bracket(c4.y + a * (((c4.x + c4.z) + s4.y) + n4.y), dv);
-					o.z = div_bracket(c4.z + a * (((c4.y + c4.w) + s4.z) + n4.z), dv);
-					o.w = div_bracket(c4.w + a * (((c4.z + er) + s4.w) + n4.w), dv);
+				if (INL) {
+					o.x = stream_relax_full(c4.x, a, wl, c4.y, s4.x, n4.x, dv);
+					o.y = stream_relax_full(c4.y, a, c4.x, c4.z, s4.y, n4.y, dv);
+					o.z = stream_relax_full(c4.z, a, c4.y, c4.w, s4.z, n4.z, dv);
+					o.w = stream_relax_full(c4.w, a, c4.z, er, s4.w, n4.w, dv);
+				} else {
+					o.x = stream_relax(c4.x, a, wl, c4.y, s4.x, n4.x, dv, low);
+					o.y = stream_relax(c4.y, a, c4.x, c4.z, s4.y, n4.y, dv, low);
+					o.z = stream_relax(c4.z, a, c4.y, c4.w, s4.z, n4.z, dv, low);
+					o.w = stream_relax(c4.w, a, c4.z, er, s4.w, n4.w, dv, low);
 				}
 				if (WALL) side_walls(o);
 				if (h < L) {
@@ -164,10 +163,10 @@ __device__ __forceinline__ void blur_stream_task(const GridDesc& g, const float*
 						if (has_bot && y == 1) lev[h < L ? h : 0][ss] = wallB ? mirror_y(o) : s4;
 					}
 				} else if (STEADY ? (y >= out_lo) : (y >= out_lo && y <= out_hi)) {
-					if (!INL) bad = bad || !(o.x == o.x) || !(o.y == o.y) || !(o.z == o.z) || !(o.w == o.w);
+					bad = bad || !(o.x == o.x) || !(o.y == o.y) || !(o.z == o.z) || !(o.w == o.w);
 					store_row(o, pout);
 					pout += g.pitch;
-					if (!INL && (--seg_left == 0 || (!STEADY && y == out_hi))) close_segment();
+					if ((--seg_left == 0 || (!STEADY && y == out_hi))) close_segment();
 					if (!STEADY && wallB && y == 1) store_border_row(o, 0);
 					if (!STEADY && wallT && y == g.NY) store_border_row(o, g.NY + 1);
 				}

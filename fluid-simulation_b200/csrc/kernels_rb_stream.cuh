@@ -29,6 +29,9 @@
 #ifndef STREAM_B4
 #define STREAM_B4 4
 #endif
+#ifndef STREAM_INL_B
+#define STREAM_INL_B 2
+#endif
 namespace fluid {
 
 constexpr int kStreamDepth = 4; // rows in flight per warp (cp.async ring)
@@ -45,6 +48,11 @@ struct StreamRect {
 	int row_shift;  // the first and last chunk are this much shorter: their wall handling costs extra row steps
 	int seg_rows;   // a task reports trouble per segment of this many rows (the tile kernel's tile height)
 	int segs;       // segments per task at most; a redo entry is task * segs + segment
+	// Ensembles (nsims > 1): all members' wall tasks first, then all members' inner tasks.  The two kinds run different
+	// instruction sequences of 15-30 KB each, and warps of both kinds on one SM at the same time miss the instruction cache
+	// on most fetches (ncu, 512 members of N=512, members' tasks interleaved: 7 warps waiting for instructions per issue,
+	// 22 % issue utilisation; two of a member's five strips are wall strips).
+	int nsims;
 };
 
 struct StreamTask { int sim, strip, out_lo, out_hi; bool wall; };
@@ -53,8 +61,21 @@ struct StreamTask { int sim, strip, out_lo, out_hi; bool wall; };
 __device__ __forceinline__ StreamTask stream_task(const StreamRect& rc, int task)
 {
 	StreamTask k;
-	k.sim = task / rc.per_sim;
-	int q = task - k.sim * rc.per_sim, rows;
+	int q, rows;
+	if (rc.nsims > 1) {
+		const int nwall = 2 * rc.wall_chunks, wall_total = nwall * rc.nsims;
+		if (task < wall_total) {
+			k.sim = task / nwall;
+			q = task - k.sim * nwall;
+		} else {
+			const int t2 = task - wall_total, ninner = rc.per_sim - nwall;
+			k.sim = t2 / ninner;
+			q = nwall + t2 - k.sim * ninner;
+		}
+	} else {
+		k.sim = task / rc.per_sim;
+		q = task - k.sim * rc.per_sim;
+	}
 	k.wall = q < 2 * rc.wall_chunks;
 	if (k.wall) {
 		const int side = q / rc.wall_chunks, sub = q - side * rc.wall_chunks;
@@ -103,6 +124,24 @@ __device__ __forceinline__ float stream_relax(float x0, float a, float w, float 
 	return __uint_as_float((__float_as_uint(q) & 0x7fffffffu) | (tb & 0x80000000u));
 }
 
+// The update with the scaled sequence (grid.cuh: div_scaled), exact for every dividend below 2^64: no window, no guard.
+__device__ __forceinline__ float stream_relax_full(float x0, float a, float w, float e, float s, float n, const DivC& dv)
+{
+	const float t = x0 + a * (((w + e) + s) + n);
+	return div_scaled(t * 0x1p64f, dv);
+}
+
+// ... with x0 already scaled by 2^64 (the right-hand side of a red-black solve is the same in every pass, so a row is
+// scaled once when it enters the window): RN(p * 2^64 + x0 * 2^64) = 2^64 * RN(p + x0) -- both sums round at the same
+// relative position, and where p + x0 is subnormal it is exact in both -- so one fused multiply-add forms the scaled
+// dividend from the rounded product p = a * sum.  (An x0 that overflows when scaled makes the dividend infinite or NaN:
+// listed.)
+__device__ __forceinline__ float stream_relax_full_pre(float x0s, float a, float w, float e, float s, float n, const DivC& dv)
+{
+	const float p = a * (((w + e) + s) + n);
+	return div_scaled(__fmaf_rn(p, 0x1p64f, x0s), dv);
+}
+
 // One warp task: rows [out_lo, out_hi] x storage columns [lane0_col + HALO, ... + OUT) of one member,
 // with the verified short division.  Segments of rows in which some dividend fell outside the proven
 // window (the subnormal fringe of a field, an overflow) may have been stored wrong: they go on the redo
@@ -116,13 +155,12 @@ __device__ __forceinline__ float stream_relax(float x0, float a, float w, float 
 // cell; in the other passes the border cell -- which the plain update has just treated like an interior
 // cell -- gets its previous value back.  The border column is stored with the rows.
 // XZERO: x is known to be zero everywhere (Project has just "set" p = 0 without writing it): it is not read.
-// INL: no redo list -- after every colour pass of a row (two updates per lane) the warp votes on whether any of its
-// dividends left the proven window and, if so, recomputes that pass with div_bracket (exact; the inputs of a red-black
-// update are the other colour and x0, both still in place).  Costs two instructions per pass when nothing is wrong and
-// keeps fields that are mostly fringe (ensembles of small grids: a point source decaying through the subnormals in every
-// member) on this kernel instead of the tile kernel, whose edge tiles dominate on small members.  (A dividend that is
-// infinite or NaN is not caught here -- the sequence turns it into NaN where IEEE division of an infinity would keep it.)
-template <int S, bool WALL, bool POW2, bool XZERO, bool INL>
+// INL: every update uses the scaled sequence (stream_relax_full_pre), which is exact on the subnormal fringe of a field
+// as well: nothing is listed for it.  Nine instructions more per update than the windowed sequence with its guard, so
+// it is the choice where the fringe is most of the field (ensembles of small grids: a point source decaying through the subnormals in every member; the host
+// switches over when the redo counts say so) and not elsewhere.  Only infinite, NaN or >= 2^64 dividends are still
+// listed (they reach the stored rows as NaN).
+template <int S, bool WALL, bool POW2, bool XZERO, bool INL, int BS>
 __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* __restrict__ xin, const float* __restrict__ x0g,
 					       float* __restrict__ xout, float a, const DivC& dv, int lane0_col, int out_lo,
 					       int out_hi, int col_lo, int col_hi, int b, float* ring, int* __restrict__ redo, int redo_base, int seg_rows)
@@ -182,7 +220,9 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 	// in registers left the warps waiting on the loads for a third of their time).  A lane reads back only
 	// the 2 x 16 bytes it copied itself, so no synchronisation between lanes is involved.
 	constexpr int kDepth = kStreamDepth;
-	constexpr int B = (S >= 4) ? STREAM_B4 : W; // row steps per unrolled block (POW2 too: all W steps unrolled measured 200 instead of 148 us per pass)
+	// (INL: two steps -- its passes are longer, and it runs where wall strips and inner strips share the SMs; BS: the
+	// host's choice, two steps for ensembles for the same reason)
+	constexpr int B = (S >= 4) ? (BS ? BS : (INL ? STREAM_INL_B : STREAM_B4)) : W; // row steps per unrolled block (POW2 too: all W steps unrolled measured 200 instead of 148 us per pass)
 	const uint32_t ring_base = (uint32_t) __cvta_generic_to_shared(ring) + 16u * lane;
 	auto fetch = [&](int slot, bool real) { // next row of x and x0 into ring slot `slot`
 		if (real) {
@@ -241,6 +281,12 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 				if (XZERO) x[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 				else asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x[u].x), "=f"(x[u].y), "=f"(x[u].z), "=f"(x[u].w) : "r"(sa) : "memory");
 				asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r[u].x), "=f"(r[u].y), "=f"(r[u].z), "=f"(r[u].w) : "r"(sa + 512u) : "memory");
+				if (INL && !POW2) { // stream_relax_full_pre wants the right-hand side scaled
+					r[u].x *= 0x1p64f;
+					r[u].y *= 0x1p64f;
+					r[u].z *= 0x1p64f;
+					r[u].w *= 0x1p64f;
+				}
 			}
 			if (STEADY || issued <= row_hi) { // refill the slot just read
 				fetch(slot, STEADY || (issued >= 0 && issued <= g.NY + 1));
@@ -259,12 +305,12 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 				if (ph) { // cells .x and .z of the row have the active colour
 					const float wl = __shfl_up_sync(0xffffffffu, x[sy].w, 1);
 					const float keep = x[sy].x;
-					uint32_t lowp = 0xffffffffu;
-					x[sy].x = stream_relax<POW2>(r[sy].x, a, wl, x[sy].y, x[ss].x, x[sn].x, dv, INL ? lowp : low);
-					x[sy].z = stream_relax<POW2>(r[sy].z, a, x[sy].y, x[sy].w, x[ss].z, x[sn].z, dv, INL ? lowp : low);
-					if (INL && !POW2 && __any_sync(0xffffffffu, lowp < 2u * dv.lo - 1u)) {
-						x[sy].x = div_bracket(r[sy].x + a * (((wl + x[sy].y) + x[ss].x) + x[sn].x), dv);
-						x[sy].z = div_bracket(r[sy].z + a * (((x[sy].y + x[sy].w) + x[ss].z) + x[sn].z), dv);
+					if (INL && !POW2) {
+						x[sy].x = stream_relax_full_pre(r[sy].x, a, wl, x[sy].y, x[ss].x, x[sn].x, dv);
+						x[sy].z = stream_relax_full_pre(r[sy].z, a, x[sy].y, x[sy].w, x[ss].z, x[sn].z, dv);
+					} else {
+						x[sy].x = stream_relax<POW2>(r[sy].x, a, wl, x[sy].y, x[ss].x, x[sn].x, dv, low);
+						x[sy].z = stream_relax<POW2>(r[sy].z, a, x[sy].y, x[sy].w, x[ss].z, x[sn].z, dv, low);
 					}
 					if (WALL) {
 						if (ghostR) x[sy].x = keep; // the right border cell is not an interior cell
@@ -284,12 +330,12 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 				} else {  // cells .y and .w
 					const float er = __shfl_down_sync(0xffffffffu, x[sy].x, 1);
 					const float keep = x[sy].w;
-					uint32_t lowp = 0xffffffffu;
-					x[sy].y = stream_relax<POW2>(r[sy].y, a, x[sy].x, x[sy].z, x[ss].y, x[sn].y, dv, INL ? lowp : low);
-					x[sy].w = stream_relax<POW2>(r[sy].w, a, x[sy].z, er, x[ss].w, x[sn].w, dv, INL ? lowp : low);
-					if (INL && !POW2 && __any_sync(0xffffffffu, lowp < 2u * dv.lo - 1u)) {
-						x[sy].y = div_bracket(r[sy].y + a * (((x[sy].x + x[sy].z) + x[ss].y) + x[sn].y), dv);
-						x[sy].w = div_bracket(r[sy].w + a * (((x[sy].z + er) + x[ss].w) + x[sn].w), dv);
+					if (INL && !POW2) {
+						x[sy].y = stream_relax_full_pre(r[sy].y, a, x[sy].x, x[sy].z, x[ss].y, x[sn].y, dv);
+						x[sy].w = stream_relax_full_pre(r[sy].w, a, x[sy].z, er, x[ss].w, x[sn].w, dv);
+					} else {
+						x[sy].y = stream_relax<POW2>(r[sy].y, a, x[sy].x, x[sy].z, x[ss].y, x[sn].y, dv, low);
+						x[sy].w = stream_relax<POW2>(r[sy].w, a, x[sy].z, er, x[ss].w, x[sn].w, dv, low);
 					}
 					if (WALL) {
 						if (ghostL) x[sy].w = keep; // the left border cell is not an interior cell
@@ -310,12 +356,12 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 			}
 			if (STEADY ? (t - L >= out_lo) : (t - L >= out_lo && t - L <= out_hi)) { // this row has now received all L passes
 				const float4 v = x[(u - L + 4 * W) % W];
-				if (!POW2 && !INL) bad = bad || !(v.x == v.x) || !(v.y == v.y) || !(v.z == v.z) || !(v.w == v.w);
+				if (!POW2) bad = bad || !(v.x == v.x) || !(v.y == v.y) || !(v.z == v.z) || !(v.w == v.w);
 				if (store_lane) *reinterpret_cast<float4*>(pout) = v;
 				if (WALL && ghostL) pout[3] = v.w;
 				if (WALL && ghostR) pout[0] = v.x;
 				pout += g.pitch;
-				if (!POW2 && !INL && (--seg_left == 0 || (!STEADY && t - L == out_hi))) close_segment();
+				if (!POW2 && (--seg_left == 0 || (!STEADY && t - L == out_hi))) close_segment();
 				if (!STEADY && botw && t - L == 1) store_border_row(x[(u - L - 1 + 4 * W) % W], v, 0, wallB);
 				if (!STEADY && topw && t - L == g.NY) store_border_row(x[(u - L + 1 + 4 * W) % W], v, g.NY + 1, wallT);
 			}
@@ -347,7 +393,7 @@ __device__ __forceinline__ void rb_stream_task(const GridDesc& g, const float* _
 }
 
 // redo[0] counts, redo[1..] lists the (task, segment) rectangles the tile kernel must recompute exactly.
-template <int S, bool POW2, bool XZERO = false, bool INL = false>
+template <int S, bool POW2, bool XZERO = false, bool INL = false, int BS = 0>
 __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g, StreamRect rc, const float* __restrict__ xinb,
 							const float* __restrict__ x0b, float* __restrict__ xoutb, float a, DivC dv,
 							int ntasks, int* __restrict__ redo, int b)
@@ -362,8 +408,8 @@ __global__ void __launch_bounds__(128, (S >= 4) ? 3 : 4) k_rb_stream(GridDesc g,
 	// the wall variant for every strip whose lanes reach a border column: the first and the last strip, and the
 	// last but one when the last is narrower than the halo
 	const bool wall = k.wall || lane0_col <= XO || lane0_col + 128 > XO + g.N + 1;
-	if (wall) rb_stream_task<S, true, POW2, XZERO, INL>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
-	else rb_stream_task<S, false, POW2, XZERO, INL>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	if (wall) rb_stream_task<S, true, POW2, XZERO, INL, BS>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
+	else rb_stream_task<S, false, POW2, XZERO, INL, BS>(g, xinb + off, x0b + off, xoutb + off, a, dv, lane0_col, k.out_lo, k.out_hi, rc.col0, rc.col1, b, ring, redo, task * rc.segs, rc.seg_rows);
 }
 
 } // namespace fluid

@@ -50,3 +50,24 @@ if what in ("all", "ensemble"):
         print(json.dumps({"case": "ensemble 512x512", "overlap": overlap, "ms_per_step": ms, "cell_updates_per_s": M * N * N / (ms * 1e-3),
                           "classes_ms_per_step": {k: v[0] / 5 for k, v in prof.items()}, "launches": {k: v[1] // 5 for k, v in prof.items()}}), flush=True)
     fs.close()
+if what in ("ensemble_modes",):
+    # the same ensemble with the streaming kernels on automatic (redo feedback picks the sequence), forced to the scaled
+    # division sequence, and off (tile / pass kernels only)
+    M, N = 512, 512
+    for mode in (1, 2, 0):
+        fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_REDBLACK, batch=M)
+        fs.SetStreamKernel(mode)
+        for b in range(M):
+            cx, cy = 1 + (37 * b) % N, 1 + (101 * b) % N
+            fs.SetSources([(fl.DENS, cx, cy, fl.SRC_PREV_SET, 100.0), (fl.U, cx, cy, fl.SRC_PREV_SET, 5.0), (fl.V, cx, cy, fl.SRC_PREV_SET, 5.0)], sim=b)
+        fs.Update(0.1, 10)
+        fs.Sync()
+        fs.SetProfiling(True)
+        fs.Profile(reset=True)
+        fs.Update(0.1, 5)
+        fs.Sync()
+        ms = fs.LastStepMs() / 5
+        prof = fs.Profile(reset=True)
+        print(json.dumps({"case": "ensemble 512x512", "stream_kernel": mode, "ms_per_step": ms, "cell_updates_per_s": M * N * N / (ms * 1e-3),
+                          "classes_ms_per_step": {k: v[0] / 5 for k, v in prof.items()}, "launches": {k: v[1] // 5 for k, v in prof.items()}}), flush=True)
+        fs.close()

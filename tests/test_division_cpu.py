@@ -50,3 +50,26 @@ def test_bracketed_reciprocal_product_decides_the_correctly_rounded_quotient():
         decided = lo.view(np.uint32) == hi.view(np.uint32)
         assert decided.mean() > 0.8
         assert np.array_equal(lo.view(np.uint32)[decided], want.view(np.uint32)[decided]), float(c)
+
+
+def test_scaled_short_division_is_exact_on_the_subnormal_fringe(tmp_path):
+    """div_scaled (csrc/grid.cuh), restated operation for operation in tests/helpers/div_scaled_check.c: the short
+    reciprocal sequence on the dividend scaled by 2^64, the quotient scaled back, ties of subnormal quotients settled
+    by the sign of the exact residual.  Every dividend whose quotient can be subnormal (all bit patterns below 2^-118,
+    both signs, zeros included) and a stride through the rest of [0, 2^64), against the machine's IEEE division.
+    (The GPU proves the same per divisor over all of [0, 2^64) before it uses the sequence: k_verify_division_full.)"""
+    import os
+    import subprocess
+    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "helpers", "div_scaled_check.c")
+    exe = str(tmp_path / "div_scaled_check")
+    flags = ["-mfma"] if "fma" in open("/proc/cpuinfo").read() else []
+    subprocess.check_call(["gcc", "-O2", "-std=c11", "-ffp-contract=off"] + flags + ["-o", exe, src, "-lm"])
+    divisors = ["3.0", "5.0", "11.4857597", "1.0004", "108.374184", "2685.3542", "1.0000001", "1000000"]
+    for first, last, stride in ((0, 0x04000000, 1), (0, 0x5F800000, 997)):
+        out = subprocess.check_output([exe, str(first), str(last), str(stride)] + (divisors if stride > 1 else divisors[:3]), text=True)
+        for line in out.strip().splitlines():
+            c, tried, bad, adjusted = line.split()
+            assert int(bad) == 0, line
+            assert int(tried) > 1_000_000
+            if stride == 1:
+                assert int(adjusted) > 0, "the tie rule was never exercised: " + line

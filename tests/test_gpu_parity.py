@@ -815,8 +815,8 @@ def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
     of 4 (2500, 2524 = 28 mod 32, where lanes fold back onto the border column), one tile column away from
     them otherwise (2502) -- the rest by the tile kernel.  Mixed pass schedules (20 = 4x4+2x2,
     7 = 4+2+1 -> 4+1+1+1, 6, 2) against the CPU red-black statement, and the tile-only path on the same inputs.
-    stream = 2: the inline-exact variant (dividends outside the proven window recomputed on the spot, no redo list);
-    a patch of the fields is scaled into the subnormal range so that both exact fallbacks really run."""
+    stream = 2: the scaled division sequence (exact on the subnormal fringe, nothing listed for it); patches of the
+    fields are scaled into the subnormal range and beyond 2^64 so that every exact fallback really runs."""
     import oracle_py as op
     rng = np.random.default_rng(N)
     for iters, b, a in ((20, 1, np.float32(10.49)), (7, 2, np.float32(1.0)), (6, 0, np.float32(0.3)), (2, 1, np.float32(0.3)),
@@ -830,6 +830,7 @@ def test_streaming_interior_kernel_bitwise(fl, oracle, N, stream):
             g = arr.reshape(N + 2, N + 2)
             g[700:1000, 200:1300] *= np.float32(1e-38)
             g[1:30, N - 50:] *= np.float32(1e-37)
+            g[1500:1560, 900:1000] *= np.float32(1e28)  # beyond 2^64: the scaled sequence (stream = 2) overflows to NaN there and lists the rows
         c = np.float32(4.0) if a == 1 else 1 + 4 * a
         fs.upload(fl.U, x)
         fs.upload(fl.V, x0)
@@ -857,6 +858,7 @@ def test_streamed_blur_bitwise(fl, oracle, N, stream):
         g0[300:420, 100:400] *= np.float32(1e-38)   # products and quotients in the subnormal range
         g0[900:1100, 1500:1900] = 0.0
         g0[1:40, 1:60] *= np.float32(1e-36)         # ... next to two walls
+        g0[1300:1340, 700:800] *= np.float32(1e28)  # beyond 2^64: NaN from the scaled sequence (stream = 2), listed and redone
         c = 1 + 4 * a
         fs.upload(fl.U, x)
         fs.upload(fl.V, x0)
