@@ -245,8 +245,9 @@ int fluid_ctx_set_tuning(fluid_ctx *ctx, int rb_tile_sweeps);
  * 5 passes per launch -- with the shared-memory tile kernel / the pass-per-launch kernel as their exact fallback
  * (1, default; 0 = tile and pass kernels everywhere).  Dividends outside the proven window of the short division
  * (the subnormal fringe of a field) are normally listed per segment and recomputed exactly behind the launch; when
- * most segments come back (ensembles of small grids) the library switches by itself to the inline-exact variant,
- * which recomputes such a colour pass on the spot; 2 forces that variant.  Results identical. */
+ * most segments come back (ensembles of small grids) the library switches by itself to the scaled division
+ * sequence, which is exact on the fringe as well (proven per divisor like the window; nine instructions more per
+ * update); 2 forces that sequence.  Results identical. */
 int fluid_ctx_set_stream_kernel(fluid_ctx *ctx, int on);
 /* fluid_ctx_step / fluid_update / fluid_ctx_vel_step: run independent parts side by side on extra streams -- the
  * densities' add_source + Blur beside VelStep, and VelStep's v diffusion beside its u diffusion (which costs one
