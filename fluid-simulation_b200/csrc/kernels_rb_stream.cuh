@@ -103,11 +103,10 @@ struct StreamGeom {
 	static constexpr int OUT = 128 - 2 * HALO;           // columns a strip produces
 };
 
-// The update with the verified short division and a 3-instruction guard instead of per-update
+// The update with the verified short division and a 2-instruction guard instead of per-update
 // predicates: `low` keeps the unsigned minimum of 2*bits(t)-1 over every dividend (the doubling drops
 // the sign, the -1 sends zero -- always exact -- to the top), compared once per task against the
-// lower end of the proven window; the sign of the quotient is copied from the dividend, which is a
-// no-op except that it turns the sequence's +0 for t = -0 into the correct -0.  The upper end of the
+// lower end of the proven window (zeros keep their sign inside div_seq).  The upper end of the
 // window is the largest finite float (the host checks), so only an infinite or NaN dividend can
 // exceed it, and those come out of the sequence as NaN and are caught when the rows are stored.
 // POW2: a == 1 and c is a power of two -- the pressure solve of Project (a = 1, c = 4).  1.0f * s is s and
@@ -118,10 +117,8 @@ __device__ __forceinline__ float stream_relax(float x0, float a, float w, float 
 {
 	if (POW2) return (x0 + (((w + e) + s) + n)) * dv.y;
 	const float t = x0 + a * (((w + e) + s) + n);
-	const float q = div_seq(t, dv);
-	const uint32_t tb = __float_as_uint(t);
-	low = min(low, 2u * tb - 1u);
-	return __uint_as_float((__float_as_uint(q) & 0x7fffffffu) | (tb & 0x80000000u));
+	low = min(low, 2u * __float_as_uint(t) - 1u);
+	return div_seq(t, dv);
 }
 
 // The update with the scaled sequence (grid.cuh: div_scaled), exact for every dividend below 2^64: no window, no guard.

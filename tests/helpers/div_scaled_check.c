@@ -14,8 +14,8 @@ static inline uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 static inline float div_seq(float t, float c, float y)
 {
 	const float q0 = t * y;
-	const float r = fmaf(-c, q0, t);
-	return fmaf(r, y, q0);
+	const float rn = fmaf(c, q0, -t); /* the residual with the opposite sign: zeros keep their sign */
+	return fmaf(rn, -y, q0);
 }
 
 static inline float div_scaled(float ts, float c, float y, unsigned long long* adjusted)
@@ -30,7 +30,7 @@ static inline float div_scaled(float ts, float c, float y, unsigned long long* a
 		q += u2f(dsign | 1u);
 		++*adjusted;
 	}
-	return u2f((f2u(q) & 0x7fffffffu) | (f2u(ts) & 0x80000000u));
+	return q;
 }
 
 int main(int argc, char** argv)
