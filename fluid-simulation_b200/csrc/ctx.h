@@ -110,7 +110,8 @@ struct fluid_ctx {
 	float* d_pixels = nullptr; // headless display buffers, allocated on first fluid_ctx_render
 	float* d_lines = nullptr;      // set by advect when a backtrace leaves the rows stored on this slab
 	int wavefront_tile = 0;    // 0 = automatic, else 32 or 64
-	int wavefront_persistent = 1; // reference-order solve as ONE launch (tickets + progress counters) instead of one per hyperplane: 0 never, 1 automatic, 2 always
+	int wavefront_persistent = 1; // reference-order solve as ONE launch instead of one per hyperplane of tiles: 0 never, 1 automatic (= 3), 2 tile tickets, 3 row pipeline
+	bool rowwave_used = false;    // a row-pipeline launch since the last fluid_ctx_sync (which then reads its watchdog flag)
 	int* d_wf_sync[2] = { nullptr, nullptr }; // its ticket counter and per-column progress counters, one set per lane (u and v solve side by side)
 	long long wf_sync_capacity[2] = { 0, 0 };
 	bool small_kernels = true; // N <= kSmallMaxN: whole solve / whole blur in one single-CTA launch per member

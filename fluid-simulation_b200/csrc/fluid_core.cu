@@ -498,7 +498,7 @@ extern "C" int fluid_ctx_set_wavefront_tile(fluid_ctx* c, int tile)
 extern "C" int fluid_ctx_set_wavefront_persistent(fluid_ctx* c, int on)
 {
 	CHECK_CTX(c);
-	if (on < 0 || on > 2) return fail(FLUID_ERR_INVALID, "wavefront_persistent=%d must be 0 (never), 1 (automatic) or 2 (always)", on);
+	if (on < 0 || on > 3) return fail(FLUID_ERR_INVALID, "wavefront_persistent=%d must be 0 (never), 1 (automatic), 2 (tile tickets) or 3 (row pipeline)", on);
 	c->wavefront_persistent = on;
 	return FLUID_OK;
 }
@@ -615,9 +615,14 @@ extern "C" int fluid_ctx_sync(fluid_ctx* c)
 	CHECK_CTX(c);
 	CU_TRY(cudaStreamSynchronize(c->stream));
 	CU_TRY(cudaGetLastError());
-	if (c->slab_count > 1) {
+	if (c->slab_count > 1 || c->rowwave_used) {
 		int oob = 0;
 		CU_TRY(cudaMemcpy(&oob, c->d_oob, sizeof(int), cudaMemcpyDeviceToHost));
+		c->rowwave_used = false;
+		if (oob & 4) {
+			CU_TRY(cudaMemset(c->d_oob, 0, sizeof(int)));
+			return fail(FLUID_ERR_CUDA, "reference-order solve: a warp of the row pipeline waited ~3 s for a neighbour and gave up; results are invalid");
+		}
 		if (oob & 2) {
 			CU_TRY(cudaMemset(c->d_oob, 0, sizeof(int)));
 			return fail(FLUID_ERR_CUDA, "halo refresh: a neighbouring slab did not deliver its rows within ~2 s (its process ended, or the slabs "

@@ -2,7 +2,10 @@
 // fields -- which kernel family runs a solve (small-grid, streaming, tile, one colour per launch,
 // reference-order wavefront), the pass schedule, the verified division and the redo lists.
 #include "ctx.h"
+#include <vector>
+
 #include "kernels_relax.cuh"
+#include "kernels_rowwave.cuh"
 #include "kernels_rb_stream.cuh"
 #include "kernels_rb_tile.cuh"
 #include "kernels_blur_stream.cuh"
@@ -538,6 +541,58 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		// where launches dominate: measured ms/step, persistent vs per-hyperplane launches: N=1024 6.4 vs 7.0, N=2048 12.8 vs
 		// 11.4, N=8192 81 vs 47 -- a tile's waits, fences and L2-only loads cost more than the launch gaps they replace once
 		// every launch carries thousands of tiles.  Automatic choice: grids up to 1024 cells wide; mode 2 forces it.
+		// Row pipeline (kernels_rowwave.cuh): warps own 32-row bands per sweep and stream along the rows; one launch per solve.
+		// Measured ms per step, row pipeline / tile tickets / launch per hyperplane: N=256 2.22 / 2.10 / 2.05, N=512 3.75 / 4.20 /
+		// 4.66, N=1024 5.99 / 6.38 / 7.19, N=1536 7.06 / 8.68 / 9.33, N=2048 9.40 / 13.2 / 10.6, N=3072 16.5 / - / 14.6, N=4096
+		// 24.2 / - / 18.8, N=8192 59.5 / - / 47.0 (profiles/r02_wavefront_modes.jsonl): the pipeline's duration is (bands +
+		// sweeps) hand-offs of ~17 us plus one task, and a task runs at half its speed once every SM holds twelve of them.
+		// Automatic: the pipeline between those ends.
+		const bool rowwave = c->wavefront_persistent == 3 || (c->wavefront_persistent == 1 && c->g.N >= 384 && c->g.N <= 2560 && c->g.NY >= 384);
+		if (rowwave) {
+			DivC dv;
+			FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
+			const int nb = rowwave_bands(c->g.NY);
+			const long long tasks = (long long) c->batch * nb * limit;
+			if (tasks < (1LL << 28)) {
+				int*& wsync = c->d_wf_sync[c->lane ? 1 : 0];
+				long long& wcap = c->wf_sync_capacity[c->lane ? 1 : 0];
+				if (tasks + 2 > wcap) {
+					if (wsync) CU_TRY(cudaFree(wsync));
+					wsync = nullptr;
+					CU_TRY(cudaMalloc(&wsync, sizeof(int) * (size_t) (tasks + 2)));
+					wcap = tasks + 2;
+				}
+				CU_TRY(cudaMemsetAsync(wsync, 0, sizeof(int) * (size_t) (tasks + 2), c->stream));
+				int e = 0;
+				const bool pow2 = cc > 0.0f && isfinite(cc) && frexpf(cc, &e) == 0.5f && (1.0f / cc) >= 1.17549435e-38f;
+				// diagnostics: FLUID_RW_STAMPS=<file> dumps four timestamps per task of every solve (blocking; see kernels_rowwave.cuh)
+				static const char* stamp_path = getenv("FLUID_RW_STAMPS");
+				unsigned long long* stamps = nullptr;
+				if (stamp_path) {
+					CU_TRY(cudaMalloc(&stamps, sizeof(unsigned long long) * 4 * (size_t) tasks));
+					CU_TRY(cudaMemsetAsync(stamps, 0, sizeof(unsigned long long) * 4 * (size_t) tasks, c->stream));
+				}
+				const int grid = (int) std::min<long long>(tasks, (long long) c->num_sms * 12); // 12 CTAs of one warp fit an SM's shared memory
+				if (pow2) LAUNCH(k_gs_rowwave<2>, grid, 64, 0, c->stream, c->g, b, x, x0, a, dv, limit, nb, c->batch, wsync, c->d_oob, stamps);
+				else if (dv.full) LAUNCH(k_gs_rowwave<1>, grid, 64, 0, c->stream, c->g, b, x, x0, a, dv, limit, nb, c->batch, wsync, c->d_oob, stamps);
+				else LAUNCH(k_gs_rowwave<0>, grid, 64, 0, c->stream, c->g, b, x, x0, a, dv, limit, nb, c->batch, wsync, c->d_oob, stamps);
+				c->rowwave_used = true;
+				CU_TRY(cudaGetLastError());
+				if (stamps) {
+					std::vector<unsigned long long> h(4 * (size_t) tasks);
+					CU_TRY(cudaMemcpyAsync(h.data(), stamps, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost, c->stream));
+					CU_TRY(cudaStreamSynchronize(c->stream));
+					CU_TRY(cudaFree(stamps));
+					if (FILE* f = fopen(stamp_path, "a")) {
+						fprintf(f, "solve N=%d NY=%d nb=%d limit=%d batch=%d\n", c->g.N, c->g.NY, nb, limit, c->batch);
+						for (long long t = 0; t < tasks; t++)
+							fprintf(f, "%lld %llu %llu %llu %llu\n", t, h[4 * t], h[4 * t + 1], h[4 * t + 2], h[4 * t + 3]);
+						fclose(f);
+					}
+				}
+				return FLUID_OK;
+			}
+		}
 		const bool persistent = c->wavefront_persistent == 2 || (c->wavefront_persistent == 1 && c->g.N <= 1024);
 		if (persistent && tickets < (1LL << 28)) {
 			int*& wsync = c->d_wf_sync[c->lane ? 1 : 0];

@@ -407,7 +407,8 @@ class FluidSystem:
 
     def SetWavefrontTile(self, tile): check(lib().fluid_ctx_set_wavefront_tile(self.h, tile))
     def SetWavefrontPersistent(self, on):
-        """True / 2 = always one launch per solve, False / 0 = never, 1 = automatic (the default)."""
+        """0 / False = one launch per hyperplane of tiles, 1 = automatic (the default: the row pipeline), 2 / True = one launch per
+        solve with tile tickets, 3 = the row pipeline (kernels_rowwave.cuh)."""
         check(lib().fluid_ctx_set_wavefront_persistent(self.h, (2 if on else 0) if isinstance(on, bool) else int(on)))
 
     def SetSmallGridKernels(self, on): check(lib().fluid_ctx_set_small_grid_kernels(self.h, 1 if on else 0))

@@ -284,9 +284,10 @@ int fluid_ctx_get_cell_info(fluid_ctx *ctx, unsigned char *host_info);
 int fluid_ctx_set_visc_air(fluid_ctx *ctx, float visc_air);
 /* Tile edge of the reference-order (wavefront) kernel: 0 = automatic, 32 or 64.  Results identical. */
 int fluid_ctx_set_wavefront_tile(fluid_ctx *ctx, int tile);
-/* Reference-order solve as ONE launch whose CTAs take (sweep, tile column) tickets and order themselves with
- * progress counters: 0 = never (one launch per hyperplane of the (tile, sweep) schedule), 1 = automatic (grids up
- * to 1024 cells wide, where it is the faster of the two; default), 2 = always.  Results identical. */
+/* Reference-order solve as ONE launch: 0 = never (one launch per hyperplane of the (tile, sweep) schedule),
+ * 2 = CTAs take (sweep, tile column) tickets and order themselves with progress counters, 3 = the row pipeline (a
+ * warp per band of 30 rows and sweep streams along the rows; bands and sweeps hand over through counters),
+ * 1 = automatic (default): whichever measured fastest for the grid's size.  Results identical. */
 int fluid_ctx_set_wavefront_persistent(fluid_ctx *ctx, int on);
 /* Grids of N <= 128 run a whole lin_solve (all sweeps, either order) or a whole Blur
  * (all passes) as ONE single-CTA launch per ensemble member, from shared memory.  on = 0

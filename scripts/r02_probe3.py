@@ -71,3 +71,25 @@ if what in ("ensemble_modes",):
         print(json.dumps({"case": "ensemble 512x512", "stream_kernel": mode, "ms_per_step": ms, "cell_updates_per_s": M * N * N / (ms * 1e-3),
                           "classes_ms_per_step": {k: v[0] / 5 for k, v in prof.items()}, "launches": {k: v[1] // 5 for k, v in prof.items()}}), flush=True)
         fs.close()
+if what in ("wavefront_rows",):
+    # the reference-order step: row pipeline (3) against tile tickets (2) and a launch per hyperplane (0)
+    for N, steps in ((256, 20), (512, 20), (1024, 10), (1536, 6), (2048, 5), (3072, 4), (4096, 3), (8192, 2)):
+        for mode in (3, 2, 0, 1):
+            if mode == 2 and N > 2048:
+                continue
+            fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_WAVEFRONT)
+            fs.SetWavefrontPersistent(mode)
+            fs.SetSources(src_of(N))
+            fs.Update(0.1, 3)
+            fs.Sync()
+            fs.Update(0.1, steps)
+            fs.Sync()
+            ms = fs.LastStepMs() / steps
+            fs.SetProfiling(True)
+            fs.Profile(reset=True)
+            fs.Update(0.1, steps)
+            fs.Sync()
+            prof = fs.Profile(reset=True)
+            print(json.dumps({"case": "wavefront", "N": N, "mode": mode, "ms_per_step": ms, "cell_updates_per_s": N * N / (ms * 1e-3),
+                              "classes_ms_serial": {k: round(v[0] / steps, 3) for k, v in prof.items()}}), flush=True)
+            fs.close()

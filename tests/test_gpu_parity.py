@@ -661,6 +661,68 @@ def test_wavefront_persistent_many_sweeps_and_members(fl, oracle):
     fs.close()
 
 
+@pytest.mark.parametrize("fast_div", [0, 2])
+def test_row_pipeline_reference_order_bitwise(fl, oracle, fast_div):
+    """The reference-order solve as a pipeline of warps (kernels_rowwave.cuh: a warp per 32-row band and sweep, streaming
+    along the rows, ordered by progress counters), forced onto grids of every shape class: fewer rows than a band, rows
+    that are not whole float4 groups (N % 4 = 0..3), a partial top band, ensemble members,
+    one sweep and many; with IEEE division (fast_div = 0), the scaled short division proven for the divisor (2; fields
+    with subnormal patches, exact zeros and a patch beyond 2^64 that overflows it) and a power-of-two divisor.  Every
+    value against the CPU's lexicographic sweep, bit for bit."""
+    import oracle_py as op
+    rng = np.random.default_rng(31337 + fast_div)
+    cases = [(5, 1, 3), (33, 1, 7), (130, 1, 7), (257, 2, 5), (258, 1, 20), (131, 1, 1), (320, 3, 4), (1000, 1, 20)]
+    for N, B, iters in cases:
+        fs = fl.FluidSystem().Setup(N, gs_order=fl.GS_WAVEFRONT, gs_iters=iters, batch=B)
+        fs.SetSmallGridKernels(False)
+        fs.SetWavefrontPersistent(3)
+        fs.SetFastDivision(fast_div)
+        for b, a, c in ((0, np.float32(0.6), None), (1, np.float32(10.49), None), (2, np.float32(1.0), np.float32(4.0)), (3, np.float32(0.3), None)):
+            c = np.float32(1 + 4 * a) if c is None else c
+            members = []
+            for sim in range(B):
+                x, x0 = rand_field(rng, N), rand_field(rng, N)
+                for arr in (x, x0):
+                    g = arr.reshape(N + 2, N + 2)
+                    g[N // 3:N // 2, 2:N // 2] *= np.float32(1e-38)
+                    g[N // 2:N // 2 + 3, :] = 0.0
+                    if N >= 100:
+                        g[N - 20:N - 10, N - 40:N - 5] *= np.float32(1e28)
+                members.append((x, x0))
+                fs.upload(fl.U, x, sim)
+                fs.upload(fl.V, x0, sim)
+            fs.lin_solve(b, fl.U, fl.V, a, c)
+            fs.Sync()
+            for sim, (x, x0) in enumerate(members):
+                oracle.lin_solve(N, b, x, x0, a, c, iters, op.GS_LEX)
+                assert_bits(fs.download(fl.U, sim), x, "row pipeline N=%d members=%d iters=%d b=%d member %d fast_div=%d" % (N, B, iters, b, sim, fast_div))
+        fs.close()
+
+
+def test_row_pipeline_whole_frames_match_tile_wavefront(fl):
+    """Whole frames (forcing, both projections, density step) in the reference's order: the row pipeline against the
+    per-hyperplane tile kernels on a grid whose rows are slab-shaped (NY != N) and one that is square, u and v solved on
+    two streams side by side."""
+    rng = np.random.default_rng(99)
+    for N, NY in ((700, 300), (513, 513)):
+        init = [(rng.uniform(-1, 1, (NY + 2, N + 2)) * 0.3).astype(np.float32) for _ in range(3)]
+        src = [(2, N // 2, NY // 2, 0, 100.0), (0, N // 2, NY // 2, 0, 5.0), (1, N // 3, NY // 3, 0, -5.0)]
+        got = {}
+        for mode in (3, 0):
+            fs = fl.FluidSystem().Setup(N, 1e-4, 1e-4, gs_order=fl.GS_WAVEFRONT, gs_iters=10, slab=(0, 1, NY))
+            fs.SetWavefrontPersistent(mode)
+            fs.SetFastDivision(2)
+            fs.SetSources(src)
+            for k, fid in enumerate((fl.U, fl.V, fl.DENS)):
+                fs.upload(fid, init[k].ravel())
+            fs.Update(0.1, 3)
+            fs.Sync()
+            got[mode] = [fs.download(fid).copy() for fid in (fl.U, fl.V, fl.DENS)]
+            fs.close()
+        for k, name in enumerate("u v dens".split()):
+            assert_bits(got[3][k], got[0][k], "N=%d NY=%d %s" % (N, NY, name))
+
+
 @pytest.mark.parametrize("small", [True, False])
 @pytest.mark.parametrize("N", [1, 2, 9, 64, 65, 127, 128])
 def test_small_grid_kernels_match_large_grid_kernels(fl, oracle, N, small):
