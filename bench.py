@@ -68,7 +68,7 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc, self.lines, self.t0, self.t1 = index, None, [], None, None
+        self.index, self.proc, self.lines, self.t0, self.t1, self.nvml = index, None, [], None, None, None
 
     def begin(self):
         """Timed region starts (the sampler has been running since before the warm-up: nvidia-smi takes
@@ -81,6 +81,18 @@ class ClockSampler:
     def start(self):
         if os.environ.get("FLUID_BENCH_NO_SAMPLER"):  # diagnostic only: does polling nvidia-smi disturb the run?
             return
+        # NVML in-process (a sample every few milliseconds from the first moment) when the bindings are there: on an
+        # 8-GPU box nvidia-smi needs longer to print its first line than a whole default run lasts.
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml, self.handle = pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.stop_flag = threading.Event()
+            self.t = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", os.environ.get("FLUID_BENCH_SAMPLE_MS", "25")],
@@ -94,14 +106,33 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append((time.perf_counter(), line.strip()))
 
+    def _poll_nvml(self):
+        n = self.nvml
+        period = float(os.environ.get("FLUID_BENCH_SAMPLE_MS", "25")) / 5e3  # five times as often as the nvidia-smi loop
+        reasons_of = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag.is_set():
+            try:
+                sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+                r = int(reasons_of(self.handle))
+                flags = ["Active" if r & m else "Not Active" for m in (0x8, 0x40, 0x20, 0x4)]  # hw, hw thermal, sw thermal, sw power cap
+                self.lines.append((time.perf_counter(), "%d, %d, 0, %s" % (sm, mx, ", ".join(flags))))
+            except Exception:
+                pass
+            self.stop_flag.wait(period)
+
     def stop(self):
-        if not self.proc:
+        if getattr(self, "nvml", None):
+            self.stop_flag.set()
+            self.t.join(timeout=2)
+        elif not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
+        else:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         lines = self.lines
@@ -125,7 +156,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "source": "nvml" if getattr(self, "nvml", None) else "nvidia-smi"}
 
 
 def dist_setup(n_gpus):

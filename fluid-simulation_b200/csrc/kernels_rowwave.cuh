@@ -45,11 +45,17 @@ namespace fluid {
 
 constexpr int kRwRows = 30;     // rows a band computes (lanes 1..30)
 constexpr int kRwRing = 64;     // columns per ring (power of two): a ring is 256 bytes
-constexpr int kRwAhead = 16;    // a lane fetches the group that starts 16..19 columns ahead of its block (first read 15 steps later)
-constexpr int kRwPending = 2;   // cp.async groups (one per block of 4 steps) that may still be in flight
+#ifndef RW_AHEAD
+#define RW_AHEAD 16
+#endif
+#ifndef RW_PENDING
+#define RW_PENDING 2
+#endif
+constexpr int kRwAhead = RW_AHEAD;     // a lane fetches the group that starts kRwAhead .. +3 columns ahead of its block (first read kRwAhead - 4 steps later)
+constexpr int kRwPending = RW_PENDING; // cp.async groups (one per block of 4 steps) that may still be in flight: 4 * (kRwPending + 1) <= kRwAhead - 4
 constexpr int kRwSkew = 1;      // columns between neighbouring lanes
 constexpr int kRwPublish = 8;   // steps between progress updates (a multiple of 4)
-constexpr int kRwLead = 24;     // steps before lane 0 reaches the first interior column (the first groups are fetched on the way; a multiple of 4)
+constexpr int kRwLead = kRwAhead + 8;     // steps before lane 0 reaches the first interior column (the first groups are fetched on the way; a multiple of 4)
 
 // steps a task runs (a multiple of 4): lane 31 reaches the last interior column at step kRwLead + N - 1 + 31 * kRwSkew, and a
 // lane stores its last float4 group up to one block after it has computed the last column
