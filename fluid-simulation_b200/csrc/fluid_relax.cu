@@ -82,14 +82,14 @@ static void remember_division(fluid_ctx* c, uint32_t key, const DivC& dv)
 
 // DivC for divisor cc: verified window if known, else range = 0 (callers use the exact division).
 //
-// The proof costs 2^31 trial divisions for the window and 1.6e9 for the scaled sequence (about 3 ms of the whole GPU).  The reference's main loop feeds the solver
-// the measured frame time (SystemManager.cpp:49-52), so an integration may see a new c = 1 + 4*dt*coef*N*N every
-// frame: a proof per frame would cost more than it saves, and waiting for it would stall the host in the middle
-// of the enqueue loop.  Automatic mode therefore (a) proves only a divisor that has COME BACK -- seen in an
-// earlier frame or API call -- and has at least 2.5e8 cell updates behind it (about what the proof costs),
-// (b) runs the proof on a side stream and picks the result up when it has landed, without waiting: until
-// then, and for divisors that never recur, solves use the exact division (tile / pass kernels), (c) keeps both
-// tables bounded.  Mode 2 proves at once and waits (tests, one-off solves).
+// The exhaustive proof costs 2^31 trial divisions for the window and 1.6e9 for the scaled sequence (about 3 ms of the whole
+// GPU).  The reference's main loop feeds the solver the measured frame time (SystemManager.cpp:49-52), so an integration
+// may see a new c = 1 + 4*dt*coef*N*N every frame.  Automatic mode therefore uses the QUICK proof (one binade of dividends
+// instead of all of them, see grid.cuh), which is cheap enough to run for every new divisor and wait for.  Divisors the
+// quick proof does not cover (c < 1 or >= 2^15) are proven exhaustively, in the background, once they have COME BACK --
+// seen in an earlier frame or API call -- with at least 2.5e8 cell updates behind them; until that proof has landed, and for
+// such divisors that never recur, solves use the exact division (tile / pass kernels).  Both tables are bounded.
+// Mode 2 proves exhaustively at once and waits (tests, one-off solves).
 int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 {
 	out->c = cc;
@@ -125,6 +125,37 @@ int division_for(fluid_ctx* c, float cc, double cell_updates, DivC* out)
 		CU_TRY(cudaMemcpyAsync(bins, c->d_divbins, sizeof bins, cudaMemcpyDeviceToHost, c->stream));
 		CU_TRY(cudaStreamSynchronize(c->stream));
 		window_from_bins(bins, out);
+		remember_division(c, key, *out);
+		return FLUID_OK;
+	}
+	// Automatic mode: the quick proof (grid.cuh: k_verify_division_quick), on the side stream, waited for -- ~0.1 ms of GPU and
+	// one event wait per NEW divisor, so a run whose time step changes every frame (two new divisors per frame) keeps the
+	// fast kernels.  Divisors it does not cover (c < 1, c >= 2^15) go the slow way below.
+	if (cc >= 1.0f && cc < 32768.0f) {
+		if (!pd.stream) {
+			CU_TRY(cudaStreamCreateWithFlags(&pd.stream, cudaStreamNonBlocking));
+			CU_TRY(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
+			CU_TRY(cudaMallocHost(&pd.h_bins, 512 * sizeof(unsigned int)));
+		}
+		if (pd.active) { // an exhaustive proof in flight uses the same buffers
+			CU_TRY(cudaEventSynchronize(pd.done));
+			pd.active = false;
+		}
+		const int ec = ilogbf(cc);
+		const unsigned int lo_biased = (unsigned int) (27 + ec); // 2^(ec-100)
+		CU_TRY(cudaMemsetAsync(c->d_divbins, 0, 2 * sizeof(unsigned int), pd.stream));
+		LAUNCH(k_verify_division_quick, c->num_sms * 8, 256, 0, pd.stream, *out, (unsigned int) (ec + 3) << 23, lo_biased, c->d_divbins);
+		CU_TRY(cudaMemcpyAsync(pd.h_bins, c->d_divbins, 2 * sizeof(unsigned int), cudaMemcpyDeviceToHost, pd.stream));
+		CU_TRY(cudaEventRecord(pd.done, pd.stream));
+		CU_TRY(cudaEventSynchronize(pd.done));
+		if (pd.h_bins[0] == 0) {
+			out->lo = lo_biased << 23;
+			out->range = (255u - lo_biased) << 23;
+		}
+		out->full = (pd.h_bins[1] == 0) ? 1u : 0u;
+		if (getenv("FLUID_DEBUG_FEEDBACK"))
+			fprintf(stderr, "quick division proof for c = %.9g: window exponents [%u, %u), scaled sequence %s\n", cc, out->lo >> 23,
+				(out->lo + out->range) >> 23, out->full ? "proven" : "not proven");
 		remember_division(c, key, *out);
 		return FLUID_OK;
 	}

@@ -73,3 +73,22 @@ def test_scaled_short_division_is_exact_on_the_subnormal_fringe(tmp_path):
             assert int(tried) > 1_000_000
             if stride == 1:
                 assert int(adjusted) > 0, "the tie rule was never exercised: " + line
+
+
+def test_short_division_commutes_with_power_of_two_scaling(tmp_path):
+    """The quick proof (k_verify_division_quick, csrc/grid.cuh) tries ONE binade of dividends per divisor instead of all
+    of them, on the strength of this: from 2^(ec-100) up, every step of div_seq commutes with a scaling of the dividend by
+    a power of two.  Checked here for whole binades at the lower end of that range, in the middle and at the top: the
+    quotient's significand is the same in every binade, its exponent moves with the dividend's, and it is t / c."""
+    import os
+    import subprocess
+    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "helpers", "div_scaled_check.c")
+    exe = str(tmp_path / "div_scaled_check")
+    flags = ["-mfma"] if "fma" in open("/proc/cpuinfo").read() else []
+    subprocess.check_call(["gcc", "-O2", "-std=c11", "-ffp-contract=off"] + flags + ["-o", exe, src, "-lm"])
+    out = subprocess.check_output([exe, "seq", "1.0004", "3.0", "11.4857597", "42.96", "2685.3542", "1.9999999", "30000.5"], text=True)
+    lines = out.strip().splitlines()
+    assert len(lines) == 7
+    for line in lines:
+        c, ec, bad, moved = line.split()
+        assert int(bad) == 0 and int(moved) == 0, line
