@@ -573,12 +573,12 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		// 11.4, N=8192 81 vs 47 -- a tile's waits, fences and L2-only loads cost more than the launch gaps they replace once
 		// every launch carries thousands of tiles.  Automatic choice: grids up to 1024 cells wide; mode 2 forces it.
 		// Row pipeline (kernels_rowwave.cuh): warps own 32-row bands per sweep and stream along the rows; one launch per solve.
-		// Measured ms per step, row pipeline / tile tickets / launch per hyperplane: N=256 2.22 / 2.10 / 2.05, N=512 3.75 / 4.20 /
-		// 4.66, N=1024 5.99 / 6.38 / 7.19, N=1536 7.06 / 8.68 / 9.33, N=2048 9.40 / 13.2 / 10.6, N=3072 16.5 / - / 14.6, N=4096
-		// 24.2 / - / 18.8, N=8192 59.5 / - / 47.0 (profiles/r02_wavefront_modes.jsonl): the pipeline's duration is (bands +
-		// sweeps) hand-offs of ~17 us plus one task, and a task runs at half its speed once every SM holds twelve of them.
-		// Automatic: the pipeline between those ends.
-		const bool rowwave = c->wavefront_persistent == 3 || (c->wavefront_persistent == 1 && c->g.N >= 384 && c->g.N <= 2560 && c->g.NY >= 384);
+		// Measured ms per step, row pipeline / tile tickets / launch per hyperplane: N=256 2.05 / 2.09 / 2.15, N=512 2.86 / 4.19 /
+		// 4.65, N=1024 4.52 / 6.20 / 6.86, N=1536 6.52 / 8.49 / 8.77, N=2048 8.95 / 13.2 / 10.8, N=3072 16.5 / - / 14.6, N=4096
+		// 26.9 / - / 18.9, N=8192 65.6 / - / 46.7 (profiles/r02_wavefront_modes.jsonl): the pipeline's duration is (bands +
+		// sweeps) hand-offs of ~15 us plus one task, and a task runs at half its speed once every SM holds twelve of them.
+		// Automatic: the pipeline up to N = 2560.
+		const bool rowwave = c->wavefront_persistent == 3 || (c->wavefront_persistent == 1 && c->g.N >= 256 && c->g.N <= 2560 && c->g.NY >= 256);
 		if (rowwave) {
 			DivC dv;
 			FL_TRY(division_for(c, cc, (double) c->g.N * c->g.NY * c->batch * limit, &dv));
