@@ -574,8 +574,8 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		// every launch carries thousands of tiles.  Automatic choice: grids up to 1024 cells wide; mode 2 forces it.
 		// Row pipeline (kernels_rowwave.cuh): warps own 32-row bands per sweep and stream along the rows; one launch per solve.
 		// Measured ms per step, row pipeline / tile tickets / launch per hyperplane: N=256 2.05 / 2.09 / 2.15, N=512 2.86 / 4.19 /
-		// 4.65, N=1024 4.52 / 6.20 / 6.86, N=1536 6.52 / 8.49 / 8.77, N=2048 8.95 / 13.2 / 10.8, N=3072 16.5 / - / 14.6, N=4096
-		// 26.9 / - / 18.9, N=8192 65.6 / - / 46.7 (profiles/r02_wavefront_modes.jsonl): the pipeline's duration is (bands +
+		// 4.65, N=1024 4.32 / 6.20 / 6.86, N=1536 6.1 / 8.49 / 8.77, N=2048 8.05 / 13.2 / 10.8, N=3072 14.9 / - / 14.6, N=4096
+		// 23.4 / - / 19.0, N=8192 66.4 / - / 46.8 (profiles/r02_wavefront_modes.jsonl): the pipeline's duration is (bands +
 		// sweeps) hand-offs of ~15 us plus one task, and a task runs at half its speed once every SM holds twelve of them.
 		// Automatic: the pipeline up to N = 2560.
 		const bool rowwave = c->wavefront_persistent == 3 || (c->wavefront_persistent == 1 && c->g.N >= 256 && c->g.N <= 2560 && c->g.NY >= 256);
@@ -603,7 +603,13 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 					CU_TRY(cudaMalloc(&stamps, sizeof(unsigned long long) * 4 * (size_t) tasks));
 					CU_TRY(cudaMemsetAsync(stamps, 0, sizeof(unsigned long long) * 4 * (size_t) tasks, c->stream));
 				}
-				const int grid = (int) std::min<long long>(tasks, (long long) c->num_sms * 12); // 12 CTAs of one warp fit an SM's shared memory
+				static const int per_sm_env = getenv("FLUID_RW_CTAS_PER_SM") ? atoi(getenv("FLUID_RW_CTAS_PER_SM")) : 0; // (measurements only)
+				// 12 CTAs fit an SM's shared memory, but a task runs faster the fewer share its SM, and the front of tasks that can
+				// run at one time is narrow: ms per solve at 12 / 6 / 3 per SM: N=1024 1.56 / 1.55 / 1.47, N=2048 2.81 / 2.62 / 2.51,
+				// N=4096 5.69 / 5.29 / 6.38, N=8192 12.0 / 12.9 / 21.5 (and 8 per SM: 5.35, 11.5); three per SM also leave room for
+				// the u and v solves of a step to run side by side.
+				const int per_sm = per_sm_env > 0 ? per_sm_env : (c->g.N <= 2560 ? 3 : 8);
+				const int grid = (int) std::min<long long>(tasks, (long long) c->num_sms * per_sm);
 				if (pow2) LAUNCH(k_gs_rowwave<2>, grid, 64, 0, c->stream, c->g, b, x, x0, a, dv, limit, nb, c->batch, wsync, c->d_oob, stamps);
 				else if (dv.full) LAUNCH(k_gs_rowwave<1>, grid, 64, 0, c->stream, c->g, b, x, x0, a, dv, limit, nb, c->batch, wsync, c->d_oob, stamps);
 				else LAUNCH(k_gs_rowwave<0>, grid, 64, 0, c->stream, c->g, b, x, x0, a, dv, limit, nb, c->batch, wsync, c->d_oob, stamps);
