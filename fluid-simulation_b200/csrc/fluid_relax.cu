@@ -574,7 +574,7 @@ int dev_lin_solve(fluid_ctx* c, int b, float*& x, const float* x0, float a, floa
 		// every launch carries thousands of tiles.  Automatic choice: grids up to 1024 cells wide; mode 2 forces it.
 		// Row pipeline (kernels_rowwave.cuh): warps own 32-row bands per sweep and stream along the rows; one launch per solve.
 		// Measured ms per step, row pipeline / tile tickets / launch per hyperplane: N=256 2.05 / 2.09 / 2.15, N=512 2.86 / 4.19 /
-		// 4.65, N=1024 4.32 / 6.20 / 6.86, N=1536 6.1 / 8.49 / 8.77, N=2048 8.05 / 13.2 / 10.8, N=3072 14.9 / - / 14.6, N=4096
+		// 4.65, N=1024 4.32 / 6.20 / 6.86, N=1536 6.1 / 8.49 / 8.77, N=2048 8.1-8.5 / 13.2 / 10.8, N=3072 14.9 / - / 14.6, N=4096
 		// 23.4 / - / 19.0, N=8192 66.4 / - / 46.8 (profiles/r02_wavefront_modes.jsonl): the pipeline's duration is (bands +
 		// sweeps) hand-offs of ~15 us plus one task, and a task runs at half its speed once every SM holds twelve of them.
 		// Automatic: the pipeline up to N = 2560.
