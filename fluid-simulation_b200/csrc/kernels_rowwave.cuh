@@ -255,7 +255,7 @@ struct RwMail {
 };
 
 // Lane 0 of warp 1: polls the producers' counters into shared memory and publishes the worker's progress, fence included.
-// Memory order: the worker's row stores are ordered before `done` by __threadfence_block(); the helper reads `done`, fences at
+// Memory order: the worker's row stores are ordered before `done` by asm volatile("fence.acq_rel.cta;" ::: "memory"); the helper reads `done`, fences at
 // GPU scope and only then stores the counter, so whoever reads the counter (and fences) sees the rows -- fence-to-fence
 // synchronisation composes across the two scopes because both fences include both threads.
 __device__ __forceinline__ void rw_helper(RwMail& mail, volatile int* progress, volatile int* abort_flag)
@@ -266,7 +266,7 @@ __device__ __forceinline__ void rw_helper(RwMail& mail, volatile int* progress, 
 		if (mail.quit || *abort_flag) return;
 		const int gnow = mail.gen;
 		if (gnow != my_gen) {
-			__threadfence_block();
+			asm volatile("fence.acq_rel.cta;" ::: "memory");
 			my_gen = gnow;
 			published = 0;
 			i_mine = mail.idx[0];
@@ -289,17 +289,17 @@ __device__ __forceinline__ void rw_helper(RwMail& mail, volatile int* progress, 
 		if (news) {
 			// (a fence at GPU scope stalls the whole SM's memory pipeline for its duration -- with one per poll the worker
 			// ran at a tenth of its speed -- so only when there is something new to pass on)
-			__threadfence(); // the counters were read before anything the worker reads on their strength
+			asm volatile("fence.acq_rel.gpu;" ::: "memory"); // the counters were read before anything the worker reads on their strength (acq_rel, not the sequentially consistent __threadfence)
 #pragma unroll
 			for (int k = 0; k < 3; k++) mail.seen[k] = last[k] = v[k];
 		}
 		if (mail.ack != my_gen) { // first values for this task are in place: the worker may trust seen[] from now on
-			__threadfence_block();
+			asm volatile("fence.acq_rel.cta;" ::: "memory");
 			mail.ack = my_gen;
 		}
 		const int d = mail.done;
 		if (d > published && mail.gen == my_gen) {
-			__threadfence();
+			asm volatile("fence.acq_rel.gpu;" ::: "memory");
 			progress[i_mine] = d;
 			published = d;
 			mail.pub = d;
@@ -365,7 +365,7 @@ __global__ void __launch_bounds__(64) k_gs_rowwave(GridDesc g, int b, float* __r
 					break;
 				}
 			}
-			__threadfence_block();
+			asm volatile("fence.acq_rel.cta;" ::: "memory");
 		}
 		dead = __shfl_sync(0xffffffffu, dead ? 1 : 0, 0) != 0;
 	};
@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(64) k_gs_rowwave(GridDesc g, int b, float* __r
 			mail.idx[3] = has_below ? i_mine - 1 : -1;      // (band-1, k)
 			mail.done = 0;
 			mail.pub = 0;
-			__threadfence_block();
+			asm volatile("fence.acq_rel.cta;" ::: "memory");
 			mail.gen = ticket + 1; // (seen[] is the helper's: it is valid once ack == gen)
 		}
 
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(64) k_gs_rowwave(GridDesc g, int b, float* __r
 			__syncwarp();
 			if (((n + 4) % kRwPublish) == 0 || n + 4 >= nsteps) {
 				if (lane == 0) {
-					__threadfence_block(); // (after the __syncwarp: every lane's stores are ordered before the count; measured free)
+					asm volatile("fence.acq_rel.cta;" ::: "memory"); // (after the __syncwarp: every lane's stores are ordered before the count; measured free)
 					mail.done = min(n + 4, nsteps);
 				}
 			}
