@@ -293,12 +293,12 @@ int fluid_ctx_set_wavefront_persistent(fluid_ctx *ctx, int on);
  * (all passes) as ONE single-CTA launch per ensemble member, from shared memory.  on = 0
  * forces the large-grid kernels (identical results; used by the tests). */
 int fluid_ctx_set_small_grid_kernels(fluid_ctx *ctx, int on);
-/* The red-black tile kernel divides by the same c for a whole solve.  For a
- * given c the library can PROVE, by trying all 2^31 non-negative finite
- * dividends on the GPU (~1.5 ms, cached per context), over which exponent range
- * a 3-instruction multiply/fma sequence equals the IEEE quotient bit for bit, and
- * then uses it there (div.rn elsewhere).  mode 0 = never, 1 = when the solve is
- * large enough to repay the check (default), 2 = always.  Results never change. */
+/* A solve divides by the same c throughout.  For a given c the library PROVES on the GPU over which range of
+ * dividends a 3-instruction multiply/fma sequence equals the IEEE quotient bit for bit, and uses it there (exact
+ * division elsewhere).  mode 0 = never; 1 (default) = the quick proof at a divisor's first use -- the sequence
+ * commutes with power-of-two scaling of the dividend, so one binade of dividends decides it: ~0.1 ms and one event
+ * wait per new divisor, cached per context; 2 = the exhaustive proof (all 2^31 non-negative finite dividends, ~3 ms),
+ * at once and waited for (tests).  Results never change. */
 int fluid_ctx_set_fast_division(fluid_ctx *ctx, int mode);
 /* The proven window for `divisor`: dividends with 2^lo_exp <= |t| < 2^(hi_exp+1)
  * (hi_exp < lo_exp: none).  Runs the proof if it has not been run yet. */
