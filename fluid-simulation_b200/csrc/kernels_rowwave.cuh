@@ -241,6 +241,71 @@ __device__ __forceinline__ void rw_block_inner(RwLane& L, float a, const DivC& d
 	L.c = c + 4;
 }
 
+// ... and the blocks before those, while the lanes arrive at the first column one after the other -- what a hand-off to
+// the band above waits for, so they get a loop of their own (in one loop with the interior block the extra live values
+// slowed THAT block by a tenth).  Nothing is near the right end; a lane may still be left of its row or reach the first
+// column inside the block.  Left of the row a lane computes on whatever its ring holds (nobody uses it: the lane above is
+// left of its row at those columns too), except that the column of the left border cell "produces" that cell, so that the
+// first interior column finds it as its west neighbour; a group is stored once it is interior (the first interior column
+// starts a group: all or nothing), and the first column writes its border cell.
+template <int MODE>
+__device__ __forceinline__ void rw_block_ramp(const GridDesc& g, int b, float* __restrict__ x, RwLane& L, float a, const DivC& dv, int j,
+					      int c_first, int last_group, bool feeder)
+{
+	constexpr uint32_t M = 4u * kRwRing - 1u;
+	const int c = L.c;
+	const uint32_t off = 4u * (uint32_t) (c & (kRwRing - 1));
+	float e[4], nn[4], rhs[4];
+	const float here = rw_lds(L.ring_x + off);
+#pragma unroll
+	for (int u = 0; u < 4; u++) {
+		e[u] = rw_lds(L.ring_x + ((off + 4u * (u + 1)) & M));
+		nn[u] = rw_lds(L.ring_n + ((off + 4u * u) & M));
+		rhs[u] = rw_lds(L.ring_0 + ((off + 4u * u) & M));
+	}
+	{
+		const int fc = c + kRwAhead + L.cls;
+		if (L.real && fc >= (XO & ~3) && fc <= last_group) {
+			const uint32_t slot = (off + 4u * (uint32_t) (kRwAhead + L.cls)) & M;
+			rw_fetch(L.ring_x + slot, L.xrow + fc);
+			rw_fetch(L.ring_0 + slot, L.x0row + fc);
+		}
+	}
+	const int ub = c_first - 1 - c; // the step of this block whose column is the left border cell, if 0 .. 3
+	const float s0 = __shfl_up_sync(0xffffffffu, L.h1, 1);
+	float q0 = rw_quotient<MODE>(rhs[0], a * (((L.h1 + e[0]) + s0) + nn[0]), dv);
+	if (feeder || ub == 0) q0 = here;
+	const float s1 = __shfl_up_sync(0xffffffffu, q0, 1);
+	float q1 = rw_quotient<MODE>(rhs[1], a * (((q0 + e[1]) + s1) + nn[1]), dv);
+	if (feeder || ub == 1) q1 = e[0];
+	const float s2 = __shfl_up_sync(0xffffffffu, q1, 1);
+	float q2 = rw_quotient<MODE>(rhs[2], a * (((q1 + e[2]) + s2) + nn[2]), dv);
+	if (feeder || ub == 2) q2 = e[1];
+	const float s3 = __shfl_up_sync(0xffffffffu, q2, 1);
+	float q3 = rw_quotient<MODE>(rhs[3], a * (((q2 + e[3]) + s3) + nn[3]), dv);
+	if (feeder || ub == 3) q3 = e[2];
+	if (L.computes && ub <= 2) { // some column of this block is interior
+		float* px = L.xrow + c;
+		if (c - ((4 - L.cls) & 3) >= c_first) {
+			if (L.cls == 0) *reinterpret_cast<float4*>(px) = make_float4(q0, q1, q2, q3);
+			else if (L.cls == 1) *reinterpret_cast<float4*>(px - 3) = make_float4(L.h3, L.h2, L.h1, q0);
+			else if (L.cls == 2) *reinterpret_cast<float4*>(px - 2) = make_float4(L.h2, L.h1, q0, q1);
+			else *reinterpret_cast<float4*>(px - 1) = make_float4(L.h1, q0, q1, q2);
+		}
+		const float q[4] = { q0, q1, q2, q3 };
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			if (u <= ub) continue; // left of the row (or the border cell itself)
+			if (u == ub + 1) mirror_border(g, x, b, 1, j, q[u]); // the first column: its border cell, the corners
+			else if (L.mirror_row) L.mirror_row[c + u] = __uint_as_float(__float_as_uint(q[u]) ^ L.mirror_flip);
+		}
+	}
+	L.h3 = q1;
+	L.h2 = q2;
+	L.h1 = q3;
+	L.c = c + 4;
+}
+
 // What the worker warp and its helper share.  The worker never touches the global counters: a fence that makes its
 // stores visible to the GPU costs ~3000 cycles (ncu: 1.6 us per MEMBAR.SC.GPU with the row stores in flight) and a poll of
 // a counter another L2 round trip, which at one of each per 16 steps was most of a step's time.
@@ -432,7 +497,8 @@ __global__ void __launch_bounds__(64) k_gs_rowwave(GridDesc g, int b, float* __r
 			}
 		};
 		stamp(0);
-		for (int n = 0; n < nsteps; n += 4) {
+		// before a block: every kRwPublish steps, wait for the producers
+		auto before = [&](int n) {
 			if (n == kRwPublish) stamp(1);
 			if ((n % kRwPublish) == 0) {
 				// What the next kRwPublish steps will touch.  Step counts are comparable across tasks (same schedule), so:
@@ -450,10 +516,10 @@ __global__ void __launch_bounds__(64) k_gs_rowwave(GridDesc g, int b, float* __r
 				const int need_above = has_above ? min(nsteps, max(0, upto + kRwAhead + 8 - 31 * kRwSkew + 1)) : 0;
 				const int need_below = has_below ? min(nsteps, upto + kRwAhead + 8 + 30 * kRwSkew) : 0;
 				spin([&]() { return mail.ack == ticket + 1 && mail.seen[0] >= need_own && mail.seen[1] >= need_above && mail.seen[2] >= need_below; });
-				if (dead) break;
 			}
-			if (n >= inner_lo && n <= inner_hi && g.NY > 1) rw_block_inner<MODE>(L, a, dv, last_group, lane == 0); // (NY == 1: see mirror_row)
-			else rw_block<MODE>(g, b, x, L, a, dv, j, c_first, c_last, last_group);
+		};
+		// after a block
+		auto after = [&](int n) {
 			// what was fetched kRwPending + 1 blocks ago has arrived and is visible to the neighbouring lanes
 			asm volatile("cp.async.commit_group;" ::: "memory");
 			asm volatile("cp.async.wait_group %0;" ::"n"(kRwPending) : "memory");
@@ -464,6 +530,22 @@ __global__ void __launch_bounds__(64) k_gs_rowwave(GridDesc g, int b, float* __r
 					mail.done = min(n + 4, nsteps);
 				}
 			}
+		};
+		// The blocks in which the lanes arrive at their rows (what the band above waits for), then the rest.
+		const int ramp_end = (g.NY > 1 && inner_hi >= inner_lo) ? inner_lo : 0;
+		int n = 0;
+		for (; n < ramp_end; n += 4) {
+			before(n);
+			if (dead) break;
+			rw_block_ramp<MODE>(g, b, x, L, a, dv, j, c_first, last_group, lane == 0);
+			after(n);
+		}
+		for (; n < nsteps && !dead; n += 4) {
+			before(n);
+			if (dead) break;
+			if (n >= inner_lo && n <= inner_hi && g.NY > 1) rw_block_inner<MODE>(L, a, dv, last_group, lane == 0); // (NY == 1: see mirror_row)
+			else rw_block<MODE>(g, b, x, L, a, dv, j, c_first, c_last, last_group);
+			after(n);
 		}
 		if (dead) break;
 		stamp(2);
