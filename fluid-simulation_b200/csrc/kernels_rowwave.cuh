@@ -184,9 +184,7 @@ __device__ __forceinline__ void rw_block(const GridDesc& g, int b, float* __rest
 // The same four steps where no lane is near an end of its row (the caller knows from the step count): every computing lane's
 // four columns and the float4 group it completes are interior, so nothing but the feeder lane needs a select and the
 // instruction stream is the chains -- about a third fewer instructions than rw_block, whose predicates and branches a lone
-// warp cannot hide (a task is latency-bound: what it issues per step is what a step lasts).  (A third variant for the
-// blocks in which the lanes arrive at the first column, the ones a hand-off waits for, measured slower overall: 4.71
-// against 4.52 ms per step at N = 1024.)
+// warp cannot hide (a task is latency-bound: what it issues per step is what a step lasts).
 template <int MODE>
 __device__ __forceinline__ void rw_block_inner(RwLane& L, float a, const DivC& dv, int last_group, bool feeder)
 {
